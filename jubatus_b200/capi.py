@@ -1,0 +1,276 @@
+"""ctypes bindings of libjubann.so (include/jubann.h).
+
+Host-buffer entry points take numpy arrays; ``*_dev`` entry points take raw device
+pointers (ints, e.g. ``tensor.data_ptr()``) and a CUDA stream handle.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SIMILAR = 1
+
+EXPORTS = [
+    "version", "jubann_abi_version", "jubann_last_error", "jubann_create", "jubann_destroy",
+    "jubann_set_option", "jubann_clear", "jubann_size", "jubann_hash_csr", "jubann_set_rows_csr",
+    "jubann_set_rows_sig", "jubann_get_rows_sig", "jubann_move_row", "jubann_truncate",
+    "jubann_query_sig", "jubann_query_csr", "jubann_query_rows", "jubann_query_sig_dev",
+    "jubann_set_rows_sig_dev", "jubann_scan_local_dev", "jubann_merge_dev",
+    "jubann_diff_record_bytes", "jubann_diff_pack_dev", "jubann_diff_apply_dev", "jubann_stats",
+    "jubann_stats_reset",
+]
+
+
+class JubannError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("jubann error %d: %s" % (code, message))
+        self.code = code
+        self.message = message
+
+
+def lib_path():
+    return os.environ.get("JUBANN_LIBRARY") or os.path.join(_HERE, "libjubann.so")
+
+
+_lib = None
+
+_u64p = ctypes.POINTER(ctypes.c_uint64)
+_u32p = ctypes.POINTER(ctypes.c_uint32)
+_f32p = ctypes.POINTER(ctypes.c_float)
+_vp = ctypes.c_void_p
+
+
+def load_library():
+    """dlopen the CUDA library.  No fallback: a missing library is an error."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise ImportError(
+            "%s not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(jubatus_b200 has no CPU fallback)" % path)
+    lib = ctypes.CDLL(path)
+    lib.version.restype = ctypes.c_char_p
+    lib.jubann_last_error.restype = ctypes.c_char_p
+    lib.jubann_abi_version.restype = ctypes.c_int
+    H = _vp
+    sig = {
+        "jubann_create": [ctypes.c_char_p, ctypes.c_uint32, ctypes.c_int, ctypes.c_uint32, ctypes.c_uint32,
+                          ctypes.POINTER(_vp)],
+        "jubann_destroy": [H],
+        "jubann_set_option": [H, ctypes.c_char_p, ctypes.c_int64],
+        "jubann_clear": [H],
+        "jubann_size": [H, _u64p, _u64p],
+        "jubann_hash_csr": [H, ctypes.c_uint64, _vp, _vp, _vp, _vp, _vp, _vp],
+        "jubann_set_rows_csr": [H, ctypes.c_uint64, _vp, _vp, _vp, _vp, _vp],
+        "jubann_set_rows_sig": [H, ctypes.c_uint64, _vp, _vp, _vp],
+        "jubann_get_rows_sig": [H, ctypes.c_uint64, _vp, _vp, _vp],
+        "jubann_move_row": [H, ctypes.c_uint64, ctypes.c_uint64],
+        "jubann_truncate": [H, ctypes.c_uint64],
+        "jubann_query_sig": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp],
+        "jubann_query_csr": [H, ctypes.c_uint64, _vp, _vp, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp],
+        "jubann_query_rows": [H, ctypes.c_uint64, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp],
+        "jubann_query_sig_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp, _vp],
+        "jubann_set_rows_sig_dev": [H, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp],
+        "jubann_scan_local_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, _vp, _vp, _vp],
+        "jubann_merge_dev": [H, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp, ctypes.c_uint32,
+                             _vp, _vp, _vp, _vp],
+        "jubann_diff_record_bytes": [H, _u32p],
+        "jubann_diff_pack_dev": [H, ctypes.c_uint64, _vp, _vp, _vp],
+        "jubann_diff_apply_dev": [H, ctypes.c_uint64, _vp, _vp],
+        "jubann_stats": [H, _u64p, _u64p, ctypes.POINTER(ctypes.c_double)],
+        "jubann_stats_reset": [H, ctypes.c_int],
+    }
+    for name, argtypes in sig.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = ctypes.c_int
+    _lib = lib
+    return lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise JubannError(rc, load_library().jubann_last_error().decode("utf-8", "replace"))
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(_vp)
+
+
+def _arr(a, dtype):
+    if a is None:
+        return None
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+class Engine(object):
+    """One device-resident table + engine (jubann_t).
+
+    method: "lsh" | "euclid_lsh" | "minhash"; hash_num as in the JSON config
+    (config/nearest_neighbor/*.json `parameter.hash_num`).
+    """
+
+    def __init__(self, method, hash_num, device=0, shard_rank=0, shard_count=1, **options):
+        self._lib = load_library()
+        self._h = _vp()
+        _check(self._lib.jubann_create(method.encode(), int(hash_num), int(device), int(shard_rank),
+                                       int(shard_count), ctypes.byref(self._h)))
+        self.method = method
+        self.hash_num = int(hash_num)
+        self.w64 = (self.hash_num + 63) // 64
+        self.device = int(device)
+        self.shard_rank = int(shard_rank)
+        self.shard_count = int(shard_count)
+        for k, v in options.items():
+            self.set_option(k, v)
+
+    # -- lifetime ----------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.jubann_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- table -------------------------------------------------------------
+    def set_option(self, name, value):
+        _check(self._lib.jubann_set_option(self._h, name.encode(), int(value)))
+
+    def clear(self):
+        _check(self._lib.jubann_clear(self._h))
+
+    def size(self):
+        g, l = ctypes.c_uint64(), ctypes.c_uint64()
+        _check(self._lib.jubann_size(self._h, ctypes.byref(g), ctypes.byref(l)))
+        return g.value, l.value
+
+    def _csr(self, indptr, seed32, keyhash64, vals):
+        indptr = _arr(indptr, np.uint64)
+        return indptr, _arr(seed32, np.uint32), _arr(keyhash64, np.uint64), _arr(vals, np.float32)
+
+    def hash_csr(self, indptr, seed32, keyhash64, vals):
+        indptr, seed32, keyhash64, vals = self._csr(indptr, seed32, keyhash64, vals)
+        n = len(indptr) - 1
+        sigs = np.zeros((n, self.w64), dtype=np.uint64)
+        norms = np.zeros(n, dtype=np.float32)
+        _check(self._lib.jubann_hash_csr(self._h, n, _ptr(indptr), _ptr(seed32), _ptr(keyhash64), _ptr(vals),
+                                         _ptr(sigs), _ptr(norms)))
+        return sigs, norms
+
+    def set_rows_csr(self, row_index, indptr, seed32, keyhash64, vals):
+        indptr, seed32, keyhash64, vals = self._csr(indptr, seed32, keyhash64, vals)
+        row_index = _arr(row_index, np.uint64)
+        _check(self._lib.jubann_set_rows_csr(self._h, len(row_index), _ptr(row_index), _ptr(indptr), _ptr(seed32),
+                                             _ptr(keyhash64), _ptr(vals)))
+
+    def set_rows_sig(self, row_index, sigs, norms=None):
+        row_index = _arr(row_index, np.uint64)
+        sigs = _arr(sigs, np.uint64)
+        norms = _arr(norms, np.float32)
+        _check(self._lib.jubann_set_rows_sig(self._h, len(row_index), _ptr(row_index), _ptr(sigs), _ptr(norms)))
+
+    def get_rows_sig(self, row_index):
+        row_index = _arr(row_index, np.uint64)
+        n = len(row_index)
+        sigs = np.zeros((n, self.w64), dtype=np.uint64)
+        norms = np.zeros(n, dtype=np.float32)
+        _check(self._lib.jubann_get_rows_sig(self._h, n, _ptr(row_index), _ptr(sigs), _ptr(norms)))
+        return sigs, norms
+
+    def move_row(self, src, dst):
+        _check(self._lib.jubann_move_row(self._h, int(src), int(dst)))
+
+    def truncate(self, new_global_rows):
+        _check(self._lib.jubann_truncate(self._h, int(new_global_rows)))
+
+    # -- queries -----------------------------------------------------------
+    @staticmethod
+    def _outs(nq, k):
+        return (np.zeros((nq, k), dtype=np.uint64), np.zeros((nq, k), dtype=np.float32),
+                np.zeros(nq, dtype=np.uint32))
+
+    def query_sig(self, qsigs, qnorms, k, flags=0):
+        qsigs = _arr(qsigs, np.uint64).reshape(-1, self.w64)
+        qnorms = _arr(qnorms, np.float32)
+        nq = qsigs.shape[0]
+        idx, score, count = self._outs(nq, k)
+        _check(self._lib.jubann_query_sig(self._h, nq, _ptr(qsigs), _ptr(qnorms), int(k), int(flags), _ptr(idx),
+                                          _ptr(score), _ptr(count)))
+        return idx, score, count
+
+    def query_csr(self, indptr, seed32, keyhash64, vals, k, flags=0):
+        indptr, seed32, keyhash64, vals = self._csr(indptr, seed32, keyhash64, vals)
+        nq = len(indptr) - 1
+        idx, score, count = self._outs(nq, k)
+        _check(self._lib.jubann_query_csr(self._h, nq, _ptr(indptr), _ptr(seed32), _ptr(keyhash64), _ptr(vals),
+                                          int(k), int(flags), _ptr(idx), _ptr(score), _ptr(count)))
+        return idx, score, count
+
+    def query_rows(self, row_index, k, flags=0):
+        row_index = _arr(row_index, np.uint64)
+        nq = len(row_index)
+        idx, score, count = self._outs(nq, k)
+        _check(self._lib.jubann_query_rows(self._h, nq, _ptr(row_index), int(k), int(flags), _ptr(idx), _ptr(score),
+                                           _ptr(count)))
+        return idx, score, count
+
+    # -- raw host-pointer variant (pinned buffers, end-to-end timing) --------
+    def query_sig_ptr(self, nq, qsigs_ptr, qnorms_ptr, k, flags, out_idx_ptr, out_score_ptr, out_count_ptr):
+        _check(self._lib.jubann_query_sig(self._h, int(nq), _vp(qsigs_ptr), _vp(qnorms_ptr) if qnorms_ptr else None,
+                                          int(k), int(flags), _vp(out_idx_ptr), _vp(out_score_ptr),
+                                          _vp(out_count_ptr)))
+
+    # -- device-pointer entry points -----------------------------------------
+    def query_sig_dev(self, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count, stream=0):
+        _check(self._lib.jubann_query_sig_dev(self._h, int(nq), _vp(d_qsigs), _vp(d_qnorms) if d_qnorms else None,
+                                              int(k), int(flags), _vp(d_out_index), _vp(d_out_score),
+                                              _vp(d_out_count), _vp(stream) if stream else None))
+
+    def set_rows_sig_dev(self, n, first_row_index, d_sigs, d_norms=0, stream=0):
+        _check(self._lib.jubann_set_rows_sig_dev(self._h, int(n), int(first_row_index), _vp(d_sigs),
+                                                 _vp(d_norms) if d_norms else None, _vp(stream) if stream else None))
+
+    def scan_local_dev(self, nq, d_qsigs, d_qnorms, k, d_cand_key, d_cand_index, stream=0):
+        _check(self._lib.jubann_scan_local_dev(self._h, int(nq), _vp(d_qsigs), _vp(d_qnorms) if d_qnorms else None,
+                                               int(k), _vp(d_cand_key), _vp(d_cand_index),
+                                               _vp(stream) if stream else None))
+
+    def merge_dev(self, nq, k, parts, d_cand_key, d_cand_index, d_qnorms, flags, d_out_index, d_out_score,
+                  d_out_count, stream=0):
+        _check(self._lib.jubann_merge_dev(self._h, int(nq), int(k), int(parts), _vp(d_cand_key), _vp(d_cand_index),
+                                          _vp(d_qnorms) if d_qnorms else None, int(flags), _vp(d_out_index),
+                                          _vp(d_out_score), _vp(d_out_count), _vp(stream) if stream else None))
+
+    def diff_record_bytes(self):
+        b = ctypes.c_uint32()
+        _check(self._lib.jubann_diff_record_bytes(self._h, ctypes.byref(b)))
+        return b.value
+
+    def diff_pack_dev(self, n, d_row_index, d_records, stream=0):
+        _check(self._lib.jubann_diff_pack_dev(self._h, int(n), _vp(d_row_index), _vp(d_records),
+                                              _vp(stream) if stream else None))
+
+    def diff_apply_dev(self, n, d_records, stream=0):
+        _check(self._lib.jubann_diff_apply_dev(self._h, int(n), _vp(d_records), _vp(stream) if stream else None))
+
+    # -- stats ---------------------------------------------------------------
+    def stats(self):
+        a, b, c = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_double()
+        _check(self._lib.jubann_stats(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
+        return {"kernel_launches": a.value, "scan_launches": b.value, "scan_ms": c.value}
+
+    def stats_reset(self, time_scan_kernels=False):
+        _check(self._lib.jubann_stats_reset(self._h, 1 if time_scan_kernels else 0))

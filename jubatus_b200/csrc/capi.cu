@@ -1,0 +1,849 @@
+// extern "C" surface of libjubann.so (declared in include/jubann.h): handle, device
+// memory, batching and error plumbing around the kernels in scan.cu / signature.cu /
+// table.cu.  No CPU fallback: every entry point needs a CUDA device.
+#include "../../include/jubann.h"
+#include "internal.h"
+
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+
+using namespace jbn;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  return code;
+}
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = std::max(bytes, (size_t)4096);
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <typename T> T* as() { return static_cast<T*>(p); }
+};
+
+}  // namespace
+
+struct jubann {
+  std::mutex mu;
+  int device = 0;
+  Method method = LSH;
+  uint32_t hash_num = 0, w64 = 0, w32 = 0;
+  uint32_t shard_rank = 0, shard_count = 1;
+  int num_sms = 148;
+  cudaStream_t stream = nullptr;
+  // table
+  void* slab = nullptr;
+  float* norms = nullptr;
+  uint64_t cap_rows = 0;     // local capacity (multiple of 32)
+  uint64_t local_rows = 0;
+  uint64_t global_rows = 0;
+  // projection cache
+  ProjCache cache{};
+  bool cache_ready = false;
+  uint32_t cache_slots_opt = 1u << 20;
+  double* d_coslut = nullptr;
+  uint32_t* h_counters = nullptr;  // pinned
+  // options
+  uint32_t qp_opt = 0;
+  int variant_opt = 0;
+  int popc_variant_opt = 2;
+  // staging (grow-only)
+  DevBuf b_indptr, b_seed, b_keyhash, b_vals, b_rowidx, b_sigs, b_norms;
+  DevBuf b_qsigs, b_qnorms, b_out_idx, b_out_score, b_out_count, b_cand, b_floor;
+  // stats
+  uint64_t kernel_launches = 0, scan_launches = 0;
+  bool time_scan = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t> > scan_events;
+  double scan_ms = 0.0;
+  // sticky error
+  bool cuda_failed = false;
+  std::string sticky;
+};
+
+namespace {
+
+int cuda_fail(jubann_t* h, cudaError_t e, const char* what) {
+  h->cuda_failed = true;
+  h->sticky = std::string(what) + ": " + cudaGetErrorString(e);
+  return fail(JUBANN_E_CUDA, "%s", h->sticky.c_str());
+}
+
+#define CK(call)                                                    \
+  do {                                                              \
+    cudaError_t e_ = (call);                                        \
+    if (e_ != cudaSuccess) return cuda_fail(h, e_, #call);          \
+  } while (0)
+
+struct Guard {
+  jubann_t* h;
+  std::unique_lock<std::mutex> lk;
+  int prev_dev = -1;
+  explicit Guard(jubann_t* hh) : h(hh), lk(hh->mu) {
+    cudaGetDevice(&prev_dev);
+    if (prev_dev != h->device) cudaSetDevice(h->device);
+  }
+  ~Guard() {
+    if (prev_dev >= 0 && prev_dev != h->device) cudaSetDevice(prev_dev);
+  }
+};
+
+int check_handle(jubann_t* h) {
+  if (!h) return fail(JUBANN_E_INVALID, "null handle");
+  if (h->cuda_failed) return fail(JUBANN_E_CUDA, "handle is in a failed state: %s", h->sticky.c_str());
+  return 0;
+}
+
+TableView view(jubann_t* h) {
+  TableView t;
+  t.slab = h->slab; t.norms = h->norms; t.local_rows = h->local_rows;
+  t.w32 = h->w32; t.w64 = h->w64; t.hash_num = h->hash_num;
+  return t;
+}
+
+uint64_t local_count(uint64_t global_rows, uint32_t rank, uint32_t G) {
+  return global_rows > rank ? (global_rows - rank + G - 1) / G : 0;
+}
+
+// grow the slab (and norm column) to hold `rows` local rows; contents are preserved
+int ensure_rows(jubann_t* h, uint64_t rows) {
+  if (rows <= h->cap_rows) return 0;
+  uint64_t cap = std::max<uint64_t>(h->cap_rows * 2, 1024);
+  while (cap < rows) cap *= 2;
+  cap = (cap + 31) / 32 * 32;
+  void* nslab = nullptr;
+  float* nnorms = nullptr;
+  cudaError_t e = cudaMalloc(&nslab, slab_bytes(h->w32, cap));
+  if (e != cudaSuccess) {
+    // fall back to the exact size before giving up
+    cap = (rows + 31) / 32 * 32;
+    cudaGetLastError();
+    e = cudaMalloc(&nslab, slab_bytes(h->w32, cap));
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(JUBANN_E_NOMEM, "cudaMalloc(%llu bytes) for the signature slab failed", (unsigned long long)slab_bytes(h->w32, cap)); }
+  }
+  CK(cudaMemsetAsync(nslab, 0, slab_bytes(h->w32, cap), h->stream));
+  if (h->slab) CK(cudaMemcpyAsync(nslab, h->slab, slab_bytes(h->w32, h->cap_rows), cudaMemcpyDeviceToDevice, h->stream));
+  if (h->method == EUCLID_LSH) {
+    e = cudaMalloc(reinterpret_cast<void**>(&nnorms), cap * sizeof(float));
+    if (e != cudaSuccess) { cudaGetLastError(); cudaFree(nslab); return fail(JUBANN_E_NOMEM, "cudaMalloc for the norm column failed"); }
+    CK(cudaMemsetAsync(nnorms, 0, cap * sizeof(float), h->stream));
+    if (h->norms) CK(cudaMemcpyAsync(nnorms, h->norms, h->cap_rows * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
+  }
+  CK(cudaStreamSynchronize(h->stream));
+  if (h->slab) cudaFree(h->slab);
+  if (h->norms) cudaFree(h->norms);
+  h->slab = nslab; h->norms = nnorms; h->cap_rows = cap;
+  return 0;
+}
+
+int ensure_cache(jubann_t* h) {
+  if (h->cache_ready || h->method == MINHASH) return 0;
+  ProjCache& c = h->cache;
+  c.slots = h->cache_slots_opt;
+  c.hash_num = h->hash_num;
+  uint32_t ts = 1024;
+  while (ts < 2ull * c.slots) ts <<= 1;
+  c.table_size = ts;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&c.table), (size_t)c.slots * c.hash_num * sizeof(float));
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(JUBANN_E_NOMEM, "cudaMalloc for the projection cache (%u slots x %u floats) failed", c.slots, c.hash_num); }
+  CK(cudaMalloc(reinterpret_cast<void**>(&c.keys), (size_t)ts * 8));
+  CK(cudaMalloc(reinterpret_cast<void**>(&c.slot_of), (size_t)ts * 4));
+  CK(cudaMalloc(reinterpret_cast<void**>(&c.counters), 16));
+  CK(cudaMalloc(reinterpret_cast<void**>(&c.fill_list), (size_t)c.slots * sizeof(uint2)));
+  CK(cudaMemsetAsync(c.keys, 0, (size_t)ts * 8, h->stream));
+  CK(cudaMemsetAsync(c.slot_of, 0, (size_t)ts * 4, h->stream));
+  CK(cudaMemsetAsync(c.counters, 0, 16, h->stream));
+  h->cache_ready = true;
+  return 0;
+}
+
+void free_cache(jubann_t* h) {
+  ProjCache& c = h->cache;
+  if (c.table) cudaFree(c.table);
+  if (c.keys) cudaFree(c.keys);
+  if (c.slot_of) cudaFree(c.slot_of);
+  if (c.counters) cudaFree(c.counters);
+  if (c.fill_list) cudaFree(c.fill_list);
+  c = ProjCache{};
+  h->cache_ready = false;
+}
+
+// CSR already on the device -> signatures (+norms) on the device
+int hash_device(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d_indptr, const uint32_t* d_seed,
+                const uint64_t* d_keyhash, const float* d_vals, uint64_t* d_sigs, float* d_norms) {
+  int launches = 0;
+  if (h->method == MINHASH) {
+    CK(launch_signature_minhash(h->hash_num, n, d_indptr, d_keyhash, d_vals, d_sigs, d_norms, h->w64, h->stream));
+    ++launches;
+  } else {
+    int rc = ensure_cache(h);
+    if (rc) return rc;
+    CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, h->stream, &launches));
+    CK(cudaMemcpyAsync(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->h_counters[2]) {
+      return fail(JUBANN_E_CACHE_FULL,
+                  "projection cache full: more than %u distinct features (raise option cache_slots, then clear)",
+                  h->cache.slots);
+    }
+    const uint32_t nfill = h->h_counters[1];
+    if (nfill) {
+      CK(launch_cache_fill(h->cache, nfill, h->num_sms, h->stream, &launches));
+      CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, h->stream));
+    }
+    CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, n, d_indptr, d_seed, d_vals, d_sigs, d_norms,
+                            h->w64, h->stream));
+    ++launches;
+  }
+  h->kernel_launches += launches;
+  return 0;
+}
+
+struct CsrDev {
+  uint64_t nnz;
+  const uint64_t* indptr; const uint32_t* seed; const uint64_t* keyhash; const float* vals;
+};
+
+// stage rows [r0, r1) of a host CSR batch on the device (indptr rebased to 0)
+int stage_csr(jubann_t* h, uint64_t r0, uint64_t r1, const uint64_t* indptr, const uint32_t* seed32,
+              const uint64_t* keyhash64, const float* vals, CsrDev* out) {
+  const uint64_t n = r1 - r0, base = indptr[r0], nnz = indptr[r1] - base;
+  if (h->method == MINHASH) { if (!keyhash64 && nnz) return fail(JUBANN_E_INVALID, "minhash needs keyhash64"); }
+  else if (!seed32 && nnz) return fail(JUBANN_E_INVALID, "lsh/euclid_lsh need seed32");
+  if (!vals && nnz) return fail(JUBANN_E_INVALID, "vals is null");
+  std::vector<uint64_t> rebased(n + 1);
+  for (uint64_t i = 0; i <= n; ++i) {
+    if (indptr[r0 + i] < base || (i && indptr[r0 + i] < indptr[r0 + i - 1])) return fail(JUBANN_E_INVALID, "indptr is not non-decreasing");
+    rebased[i] = indptr[r0 + i] - base;
+  }
+  CK(h->b_indptr.ensure((n + 1) * 8));
+  CK(cudaMemcpyAsync(h->b_indptr.p, rebased.data(), (n + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));  // `rebased` is a temporary
+  CK(h->b_vals.ensure(std::max<uint64_t>(nnz, 1) * 4));
+  if (nnz) CK(cudaMemcpyAsync(h->b_vals.p, vals + base, nnz * 4, cudaMemcpyHostToDevice, h->stream));
+  if (h->method == MINHASH) {
+    CK(h->b_keyhash.ensure(std::max<uint64_t>(nnz, 1) * 8));
+    if (nnz) CK(cudaMemcpyAsync(h->b_keyhash.p, keyhash64 + base, nnz * 8, cudaMemcpyHostToDevice, h->stream));
+  } else {
+    CK(h->b_seed.ensure(std::max<uint64_t>(nnz, 1) * 4));
+    if (nnz) CK(cudaMemcpyAsync(h->b_seed.p, seed32 + base, nnz * 4, cudaMemcpyHostToDevice, h->stream));
+  }
+  out->nnz = nnz;
+  out->indptr = h->b_indptr.as<uint64_t>();
+  out->seed = h->b_seed.as<uint32_t>();
+  out->keyhash = h->b_keyhash.as<uint64_t>();
+  out->vals = h->b_vals.as<float>();
+  return 0;
+}
+
+const uint64_t CSR_CHUNK_ROWS = 1u << 18;
+
+// validates row indices (append or overwrite, no holes) and returns the new global size
+int check_row_indices(jubann_t* h, uint64_t n, const uint64_t* row_index, uint64_t* new_global) {
+  uint64_t g = h->global_rows;
+  for (uint64_t r = 0; r < n; ++r) {
+    if (row_index[r] > g) return fail(JUBANN_E_RANGE, "row index %llu skips past the table end %llu", (unsigned long long)row_index[r], (unsigned long long)g);
+    if (row_index[r] == g) ++g;
+  }
+  *new_global = g;
+  return 0;
+}
+
+int grow_to(jubann_t* h, uint64_t new_global) {
+  const uint64_t nl = local_count(new_global, h->shard_rank, h->shard_count);
+  if (nl > 0xFFFFFFF0ull) return fail(JUBANN_E_RANGE, "more than 2^32-16 rows per shard are not supported");
+  int rc = ensure_rows(h, nl);
+  if (rc) return rc;
+  h->global_rows = new_global;
+  h->local_rows = nl;
+  return 0;
+}
+
+void record_scan_begin(jubann_t* h, cudaStream_t s, cudaEvent_t* a, cudaEvent_t* b) {
+  *a = *b = nullptr;
+  if (!h->time_scan) return;
+  if (cudaEventCreate(a) != cudaSuccess || cudaEventCreate(b) != cudaSuccess) { *a = *b = nullptr; return; }
+  cudaEventRecord(*a, s);
+}
+void record_scan_end(jubann_t* h, cudaStream_t s, cudaEvent_t a, cudaEvent_t b) {
+  if (!a) return;
+  cudaEventRecord(b, s);
+  h->scan_events.push_back(std::make_pair(a, b));
+}
+
+// The query path.  All pointers are device pointers; work is enqueued on `s`.
+// Exactly one of (final outputs) / (raw candidate outputs) is given.
+int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const float* d_qnorms, uint32_t k,
+                 uint32_t flags, uint64_t* d_out_index, float* d_out_score, uint32_t* d_out_count,
+                 uint32_t* d_cand_key, uint64_t* d_cand_index, cudaStream_t s) {
+  if (nq64 == 0) return 0;
+  if (nq64 > 0x7FFFFFFFull) return fail(JUBANN_E_INVALID, "too many queries in one call");
+  const uint32_t nq = (uint32_t)nq64;
+  const bool euclid = (h->method == EUCLID_LSH);
+  if (euclid && !d_qnorms) return fail(JUBANN_E_INVALID, "euclid_lsh queries need norms");
+  if (d_cand_key) {
+    if (k) {
+      CK(cudaMemsetAsync(d_cand_key, 0xFF, (size_t)nq * k * 4, s));
+      CK(cudaMemsetAsync(d_cand_index, 0xFF, (size_t)nq * k * 8, s));
+    }
+  } else {
+    CK(cudaMemsetAsync(d_out_count, 0, (size_t)nq * 4, s));
+  }
+  const uint64_t keff64 = std::min<uint64_t>(k, h->local_rows);
+  if (keff64 == 0) return 0;
+  const uint32_t keff = (uint32_t)keff64;
+  const TableView t = view(h);
+  const uint32_t kpage = std::min(keff, max_k_per_pass());
+  const uint32_t pages = (keff + kpage - 1) / kpage;
+  ScanConfig cfg;
+  if (!plan_scan(t, euclid, nq, kpage, h->variant_opt, h->popc_variant_opt, h->qp_opt, h->num_sms, &cfg))
+    return fail(JUBANN_E_INVALID, "cannot plan a scan for k=%u", kpage);
+  // queries per launch bounded by candidate scratch (<= 256 MiB)
+  const size_t per_query = (size_t)cfg.nchunks * kpage * 8;
+  uint32_t nq_launch = (uint32_t)std::max<size_t>(cfg.qp, ((size_t)256 << 20) / per_query);
+  nq_launch = std::max(cfg.qp, nq_launch / cfg.qp * cfg.qp);
+  nq_launch = std::min(nq_launch, (nq + cfg.qp - 1) / cfg.qp * cfg.qp);
+  if (nq_launch / cfg.qp > 65535u) nq_launch = 65535u * cfg.qp;
+  CK(h->b_cand.ensure((size_t)nq_launch * per_query));
+  if (pages > 1) CK(h->b_floor.ensure((size_t)nq * 8));
+  for (uint32_t q0 = 0; q0 < nq; q0 += nq_launch) {
+    const uint32_t nql = std::min(nq_launch, nq - q0);
+    for (uint32_t p = 0; p < pages; ++p) {
+      const uint32_t kthis = std::min(kpage, keff - p * kpage);
+      const uint64_t* floor = (p == 0) ? nullptr : h->b_floor.as<uint64_t>() + q0;
+      cudaEvent_t ea, eb;
+      record_scan_begin(h, s, &ea, &eb);
+      CK(launch_scan(t, euclid, cfg, d_qsigs + (size_t)q0 * h->w64, d_qnorms ? d_qnorms + q0 : nullptr,
+                     h->d_coslut, nql, kthis, floor, h->b_cand.as<uint64_t>(), s));
+      record_scan_end(h, s, ea, eb);
+      MergeOut o{};
+      o.kout = k; o.col0 = p * kpage;
+      o.shard_rank = h->shard_rank; o.shard_count = h->shard_count;
+      o.hash_num = h->hash_num; o.euclid = euclid ? 1 : 0; o.flags = flags;
+      o.qnorms = d_qnorms ? d_qnorms + q0 : nullptr;
+      o.count_accumulate = (p > 0);
+      o.last_key = (pages > 1) ? h->b_floor.as<uint64_t>() + q0 : nullptr;
+      if (d_cand_key) {
+        o.cand_key = d_cand_key + (size_t)q0 * k;
+        o.cand_index = d_cand_index + (size_t)q0 * k;
+      } else {
+        o.out_index = d_out_index + (size_t)q0 * k;
+        o.out_score = d_out_score + (size_t)q0 * k;
+        o.out_count = d_out_count + q0;
+      }
+      CK(launch_merge_local(h->b_cand.as<uint64_t>(), nql, cfg.nchunks, kthis, o, s));
+      h->kernel_launches += 2;
+      h->scan_launches += 1;
+    }
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* version(void) { return "jubann-b200 0.1.0 (jubatus 0.9.2 nearest_neighbor backend, sm_100a)"; }
+int jubann_abi_version(void) { return JUBANN_ABI_VERSION; }
+const char* jubann_last_error(void) { return g_last_error.c_str(); }
+
+int jubann_create(const char* method, uint32_t hash_num, int device, uint32_t shard_rank,
+                  uint32_t shard_count, jubann_t** out) {
+  if (!out) return fail(JUBANN_E_INVALID, "out is null");
+  *out = nullptr;
+  if (!method) return fail(JUBANN_E_INVALID, "method is null");
+  Method m;
+  if (!strcmp(method, "lsh")) m = LSH;
+  else if (!strcmp(method, "euclid_lsh")) m = EUCLID_LSH;
+  else if (!strcmp(method, "minhash")) m = MINHASH;
+  else return fail(JUBANN_E_INVALID, "unsupported_method: %s", method);
+  if (hash_num < 1) return fail(JUBANN_E_INVALID, "invalid_parameter: hash_num should be >= 1");
+  if (hash_num > 1024) return fail(JUBANN_E_INVALID, "invalid_parameter: hash_num > 1024 is not supported by this build");
+  if (shard_count < 1 || shard_rank >= shard_count) return fail(JUBANN_E_INVALID, "invalid shard %u of %u", shard_rank, shard_count);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return fail(JUBANN_E_CUDA, "no CUDA device: %s (this library has no CPU path)", e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  }
+  if (device < 0 || device >= ndev) return fail(JUBANN_E_INVALID, "device %d out of range (%d devices)", device, ndev);
+  jubann_t* h = new jubann;
+  h->device = device; h->method = m; h->hash_num = hash_num;
+  h->w64 = (hash_num + 63) / 64; h->w32 = padded_w32(hash_num);
+  h->shard_rank = shard_rank; h->shard_count = shard_count;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  bool ok = true;
+  ok = ok && cudaSetDevice(device) == cudaSuccess;
+  cudaDeviceProp prop;
+  ok = ok && cudaGetDeviceProperties(&prop, device) == cudaSuccess;
+  if (ok) h->num_sms = prop.multiProcessorCount;
+  ok = ok && cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 16) == cudaSuccess;
+  if (ok && m == EUCLID_LSH) {
+    // cos(theta_h), theta_h = (float)(h * M_PI / (float)hash_num), evaluated in double by the host
+    // libm so that the table holds the very values the CPU engine computes per row
+    std::vector<double> lut(hash_num + 1);
+    const float denom = static_cast<float>(hash_num);
+    for (uint32_t i = 0; i <= hash_num; ++i) {
+      const float theta = static_cast<float>(static_cast<uint64_t>(i) * M_PI / denom);
+      lut[i] = cos(static_cast<double>(theta));
+    }
+    ok = ok && cudaMalloc(reinterpret_cast<void**>(&h->d_coslut), lut.size() * 8) == cudaSuccess;
+    ok = ok && cudaMemcpy(h->d_coslut, lut.data(), lut.size() * 8, cudaMemcpyHostToDevice) == cudaSuccess;
+  }
+  if (!ok) {
+    cudaError_t le = cudaGetLastError();
+    fail(JUBANN_E_CUDA, "CUDA initialisation failed on device %d: %s", device, cudaGetErrorString(le));
+    cudaSetDevice(prev);
+    delete h;
+    return JUBANN_E_CUDA;
+  }
+  cudaSetDevice(prev);
+  *out = h;
+  return 0;
+}
+
+int jubann_destroy(jubann_t* h) {
+  if (!h) return 0;
+  {
+    Guard g(h);
+    cudaStreamSynchronize(h->stream);
+    if (h->slab) cudaFree(h->slab);
+    if (h->norms) cudaFree(h->norms);
+    free_cache(h);
+    if (h->d_coslut) cudaFree(h->d_coslut);
+    if (h->h_counters) cudaFreeHost(h->h_counters);
+    DevBuf* bufs[] = {&h->b_indptr, &h->b_seed, &h->b_keyhash, &h->b_vals, &h->b_rowidx, &h->b_sigs, &h->b_norms,
+                      &h->b_qsigs, &h->b_qnorms, &h->b_out_idx, &h->b_out_score, &h->b_out_count, &h->b_cand, &h->b_floor};
+    for (DevBuf* b : bufs) b->release();
+    for (auto& ev : h->scan_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
+    if (h->stream) cudaStreamDestroy(h->stream);
+  }
+  delete h;
+  return 0;
+}
+
+int jubann_set_option(jubann_t* h, const char* name, int64_t value) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (!name) return fail(JUBANN_E_INVALID, "option name is null");
+  Guard g(h);
+  if (!strcmp(name, "cache_slots")) {
+    if (value < 1 || value > (1ll << 28)) return fail(JUBANN_E_INVALID, "cache_slots out of range");
+    if (h->cache_ready) return fail(JUBANN_E_INVALID, "cache_slots must be set before the first row or query (or after clear)");
+    h->cache_slots_opt = (uint32_t)value;
+  } else if (!strcmp(name, "queries_per_pass")) {
+    if (value < 0 || value > 64) return fail(JUBANN_E_INVALID, "queries_per_pass out of range (0..64)");
+    h->qp_opt = (uint32_t)value;
+  } else if (!strcmp(name, "scan_variant")) {
+    if (value < 0 || value > 2) return fail(JUBANN_E_INVALID, "scan_variant out of range (0..2)");
+    h->variant_opt = (int)value;
+  } else if (!strcmp(name, "popc_variant")) {
+    if (value < 0 || value > 2) return fail(JUBANN_E_INVALID, "popc_variant out of range (0..2)");
+    h->popc_variant_opt = (int)value;
+  } else {
+    return fail(JUBANN_E_INVALID, "unknown option: %s", name);
+  }
+  return 0;
+}
+
+int jubann_clear(jubann_t* h) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  Guard g(h);
+  CK(cudaStreamSynchronize(h->stream));
+  if (h->slab) CK(cudaMemsetAsync(h->slab, 0, slab_bytes(h->w32, h->cap_rows), h->stream));
+  if (h->norms) CK(cudaMemsetAsync(h->norms, 0, h->cap_rows * sizeof(float), h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->local_rows = 0;
+  h->global_rows = 0;
+  if (h->cache_ready && h->h_counters[2]) free_cache(h);  // a cache that overflowed is rebuilt
+  return 0;
+}
+
+int jubann_size(jubann_t* h, uint64_t* global_rows, uint64_t* local_rows) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  Guard g(h);
+  if (global_rows) *global_rows = h->global_rows;
+  if (local_rows) *local_rows = h->local_rows;
+  return 0;
+}
+
+int jubann_hash_csr(jubann_t* h, uint64_t n, const uint64_t* indptr, const uint32_t* seed32,
+                    const uint64_t* keyhash64, const float* vals, uint64_t* out_sigs, float* out_norms) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!indptr || !out_sigs) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  for (uint64_t r0 = 0; r0 < n; r0 += CSR_CHUNK_ROWS) {
+    const uint64_t r1 = std::min(n, r0 + CSR_CHUNK_ROWS), m = r1 - r0;
+    CsrDev d;
+    rc = stage_csr(h, r0, r1, indptr, seed32, keyhash64, vals, &d);
+    if (rc) return rc;
+    CK(h->b_sigs.ensure(m * h->w64 * 8));
+    CK(h->b_norms.ensure(m * 4));
+    rc = hash_device(h, m, d.nnz, d.indptr, d.seed, d.keyhash, d.vals, h->b_sigs.as<uint64_t>(), h->b_norms.as<float>());
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(out_sigs + r0 * h->w64, h->b_sigs.p, m * h->w64 * 8, cudaMemcpyDeviceToHost, h->stream));
+    if (out_norms) CK(cudaMemcpyAsync(out_norms + r0, h->b_norms.p, m * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  return 0;
+}
+
+int jubann_set_rows_csr(jubann_t* h, uint64_t n, const uint64_t* row_index, const uint64_t* indptr,
+                        const uint32_t* seed32, const uint64_t* keyhash64, const float* vals) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!row_index || !indptr) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  uint64_t new_global;
+  rc = check_row_indices(h, n, row_index, &new_global);
+  if (rc) return rc;
+  rc = grow_to(h, new_global);
+  if (rc) return rc;
+  for (uint64_t r0 = 0; r0 < n; r0 += CSR_CHUNK_ROWS) {
+    const uint64_t r1 = std::min(n, r0 + CSR_CHUNK_ROWS), m = r1 - r0;
+    CsrDev d;
+    rc = stage_csr(h, r0, r1, indptr, seed32, keyhash64, vals, &d);
+    if (rc) return rc;
+    CK(h->b_sigs.ensure(m * h->w64 * 8));
+    CK(h->b_norms.ensure(m * 4));
+    CK(h->b_rowidx.ensure(m * 8));
+    CK(cudaMemcpyAsync(h->b_rowidx.p, row_index + r0, m * 8, cudaMemcpyHostToDevice, h->stream));
+    rc = hash_device(h, m, d.nnz, d.indptr, d.seed, d.keyhash, d.vals, h->b_sigs.as<uint64_t>(), h->b_norms.as<float>());
+    if (rc) return rc;
+    CK(launch_scatter_rows(view(h), m, h->b_rowidx.as<uint64_t>(), 0, h->b_sigs.as<uint64_t>(),
+                           h->b_norms.as<float>(), h->shard_rank, h->shard_count, h->stream));
+    h->kernel_launches += 1;
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  return 0;
+}
+
+int jubann_set_rows_sig(jubann_t* h, uint64_t n, const uint64_t* row_index, const uint64_t* sigs,
+                        const float* norms) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!row_index || !sigs) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  uint64_t new_global;
+  rc = check_row_indices(h, n, row_index, &new_global);
+  if (rc) return rc;
+  rc = grow_to(h, new_global);
+  if (rc) return rc;
+  CK(h->b_sigs.ensure(n * h->w64 * 8));
+  CK(h->b_rowidx.ensure(n * 8));
+  CK(cudaMemcpyAsync(h->b_sigs.p, sigs, n * h->w64 * 8, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(h->b_rowidx.p, row_index, n * 8, cudaMemcpyHostToDevice, h->stream));
+  const float* dn = nullptr;
+  if (norms && h->method == EUCLID_LSH) {
+    CK(h->b_norms.ensure(n * 4));
+    CK(cudaMemcpyAsync(h->b_norms.p, norms, n * 4, cudaMemcpyHostToDevice, h->stream));
+    dn = h->b_norms.as<float>();
+  }
+  CK(launch_scatter_rows(view(h), n, h->b_rowidx.as<uint64_t>(), 0, h->b_sigs.as<uint64_t>(), dn,
+                         h->shard_rank, h->shard_count, h->stream));
+  h->kernel_launches += 1;
+  CK(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int jubann_set_rows_sig_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, const uint64_t* d_sigs,
+                            const float* d_norms, void* stream) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!d_sigs) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  if (first_row_index > h->global_rows) return fail(JUBANN_E_RANGE, "row index skips past the table end");
+  rc = grow_to(h, std::max(h->global_rows, first_row_index + n));
+  if (rc) return rc;
+  CK(launch_scatter_rows(view(h), n, nullptr, first_row_index, d_sigs, h->method == EUCLID_LSH ? d_norms : nullptr,
+                         h->shard_rank, h->shard_count, static_cast<cudaStream_t>(stream)));
+  h->kernel_launches += 1;
+  return 0;
+}
+
+int jubann_get_rows_sig(jubann_t* h, uint64_t n, const uint64_t* row_index, uint64_t* out_sigs,
+                        float* out_norms) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!row_index || !out_sigs) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  for (uint64_t r = 0; r < n; ++r)
+    if (row_index[r] >= h->global_rows) return fail(JUBANN_E_RANGE, "row index %llu out of range", (unsigned long long)row_index[r]);
+  CK(h->b_sigs.ensure(n * h->w64 * 8));
+  CK(h->b_norms.ensure(n * 4));
+  CK(h->b_rowidx.ensure(n * 8));
+  CK(cudaMemcpyAsync(h->b_rowidx.p, row_index, n * 8, cudaMemcpyHostToDevice, h->stream));
+  CK(launch_gather_rows(view(h), n, h->b_rowidx.as<uint64_t>(), h->b_sigs.as<uint64_t>(), h->b_norms.as<float>(),
+                        h->shard_rank, h->shard_count, h->stream));
+  h->kernel_launches += 1;
+  CK(cudaMemcpyAsync(out_sigs, h->b_sigs.p, n * h->w64 * 8, cudaMemcpyDeviceToHost, h->stream));
+  if (out_norms) CK(cudaMemcpyAsync(out_norms, h->b_norms.p, n * 4, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int jubann_move_row(jubann_t* h, uint64_t src_index, uint64_t dst_index) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  Guard g(h);
+  if (src_index >= h->global_rows || dst_index >= h->global_rows) return fail(JUBANN_E_RANGE, "row index out of range");
+  if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "move_row is the single-shard fast path; sharded hosts use get_rows_sig + set_rows_sig");
+  if (src_index == dst_index) return 0;
+  CK(h->b_sigs.ensure(h->w64 * 8));
+  CK(h->b_norms.ensure(4));
+  CK(h->b_rowidx.ensure(16));
+  const uint64_t idx[2] = {src_index, dst_index};
+  CK(cudaMemcpyAsync(h->b_rowidx.p, idx, 16, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  CK(launch_gather_rows(view(h), 1, h->b_rowidx.as<uint64_t>(), h->b_sigs.as<uint64_t>(), h->b_norms.as<float>(), 0, 1, h->stream));
+  CK(launch_scatter_rows(view(h), 1, h->b_rowidx.as<uint64_t>() + 1, 0, h->b_sigs.as<uint64_t>(),
+                         h->method == EUCLID_LSH ? h->b_norms.as<float>() : nullptr, 0, 1, h->stream));
+  h->kernel_launches += 2;
+  CK(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int jubann_truncate(jubann_t* h, uint64_t new_global_rows) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  Guard g(h);
+  if (new_global_rows > h->global_rows) return fail(JUBANN_E_RANGE, "truncate cannot grow the table");
+  h->global_rows = new_global_rows;
+  h->local_rows = local_count(new_global_rows, h->shard_rank, h->shard_count);
+  return 0;
+}
+
+static int query_host_outputs(jubann_t* h, uint64_t nq, uint32_t k, uint64_t* out_index, float* out_score,
+                              uint32_t* out_count) {
+  if (k) {
+    CK(cudaMemcpyAsync(out_index, h->b_out_idx.p, nq * k * 8, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(out_score, h->b_out_score.p, nq * k * 4, cudaMemcpyDeviceToHost, h->stream));
+  }
+  CK(cudaMemcpyAsync(out_count, h->b_out_count.p, nq * 4, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+static int ensure_query_outputs(jubann_t* h, uint64_t nq, uint32_t k) {
+  CK(h->b_out_idx.ensure(std::max<uint64_t>(nq * k, 1) * 8));
+  CK(h->b_out_score.ensure(std::max<uint64_t>(nq * k, 1) * 4));
+  CK(h->b_out_count.ensure(nq * 4));
+  return 0;
+}
+
+int jubann_query_sig(jubann_t* h, uint64_t nq, const uint64_t* qsigs, const float* qnorms, uint32_t k,
+                     uint32_t flags, uint64_t* out_index, float* out_score, uint32_t* out_count) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (nq == 0) return 0;
+  if (!qsigs || !out_count || (k && (!out_index || !out_score))) return fail(JUBANN_E_INVALID, "null argument");
+  if (h->method == EUCLID_LSH && !qnorms) return fail(JUBANN_E_INVALID, "euclid_lsh queries need norms");
+  Guard g(h);
+  if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
+  CK(h->b_qsigs.ensure(nq * h->w64 * 8));
+  CK(cudaMemcpyAsync(h->b_qsigs.p, qsigs, nq * h->w64 * 8, cudaMemcpyHostToDevice, h->stream));
+  const float* dqn = nullptr;
+  if (h->method == EUCLID_LSH) {
+    CK(h->b_qnorms.ensure(nq * 4));
+    CK(cudaMemcpyAsync(h->b_qnorms.p, qnorms, nq * 4, cudaMemcpyHostToDevice, h->stream));
+    dqn = h->b_qnorms.as<float>();
+  }
+  rc = ensure_query_outputs(h, nq, k);
+  if (rc) return rc;
+  rc = query_device(h, nq, h->b_qsigs.as<uint64_t>(), dqn, k, flags, h->b_out_idx.as<uint64_t>(),
+                    h->b_out_score.as<float>(), h->b_out_count.as<uint32_t>(), nullptr, nullptr, h->stream);
+  if (rc) return rc;
+  return query_host_outputs(h, nq, k, out_index, out_score, out_count);
+}
+
+int jubann_query_csr(jubann_t* h, uint64_t nq, const uint64_t* indptr, const uint32_t* seed32,
+                     const uint64_t* keyhash64, const float* vals, uint32_t k, uint32_t flags,
+                     uint64_t* out_index, float* out_score, uint32_t* out_count) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (nq == 0) return 0;
+  if (!indptr || !out_count || (k && (!out_index || !out_score))) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
+  for (uint64_t r0 = 0; r0 < nq; r0 += CSR_CHUNK_ROWS) {
+    const uint64_t r1 = std::min(nq, r0 + CSR_CHUNK_ROWS), m = r1 - r0;
+    CsrDev d;
+    rc = stage_csr(h, r0, r1, indptr, seed32, keyhash64, vals, &d);
+    if (rc) return rc;
+    CK(h->b_qsigs.ensure(m * h->w64 * 8));
+    CK(h->b_qnorms.ensure(m * 4));
+    rc = hash_device(h, m, d.nnz, d.indptr, d.seed, d.keyhash, d.vals, h->b_qsigs.as<uint64_t>(), h->b_qnorms.as<float>());
+    if (rc) return rc;
+    rc = ensure_query_outputs(h, m, k);
+    if (rc) return rc;
+    rc = query_device(h, m, h->b_qsigs.as<uint64_t>(), h->b_qnorms.as<float>(), k, flags, h->b_out_idx.as<uint64_t>(),
+                      h->b_out_score.as<float>(), h->b_out_count.as<uint32_t>(), nullptr, nullptr, h->stream);
+    if (rc) return rc;
+    rc = query_host_outputs(h, m, k, out_index + r0 * k, out_score + r0 * k, out_count + r0);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+int jubann_query_rows(jubann_t* h, uint64_t nq, const uint64_t* row_index, uint32_t k, uint32_t flags,
+                      uint64_t* out_index, float* out_score, uint32_t* out_count) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (nq == 0) return 0;
+  if (!row_index || !out_count || (k && (!out_index || !out_score))) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "query_rows needs a single-shard handle");
+  for (uint64_t r = 0; r < nq; ++r)
+    if (row_index[r] >= h->global_rows) return fail(JUBANN_E_RANGE, "row index %llu out of range", (unsigned long long)row_index[r]);
+  CK(h->b_rowidx.ensure(nq * 8));
+  CK(h->b_qsigs.ensure(nq * h->w64 * 8));
+  CK(h->b_qnorms.ensure(nq * 4));
+  CK(cudaMemcpyAsync(h->b_rowidx.p, row_index, nq * 8, cudaMemcpyHostToDevice, h->stream));
+  CK(launch_gather_rows(view(h), nq, h->b_rowidx.as<uint64_t>(), h->b_qsigs.as<uint64_t>(), h->b_qnorms.as<float>(), 0, 1, h->stream));
+  h->kernel_launches += 1;
+  rc = ensure_query_outputs(h, nq, k);
+  if (rc) return rc;
+  rc = query_device(h, nq, h->b_qsigs.as<uint64_t>(), h->b_qnorms.as<float>(), k, flags, h->b_out_idx.as<uint64_t>(),
+                    h->b_out_score.as<float>(), h->b_out_count.as<uint32_t>(), nullptr, nullptr, h->stream);
+  if (rc) return rc;
+  return query_host_outputs(h, nq, k, out_index, out_score, out_count);
+}
+
+int jubann_query_sig_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms, uint32_t k,
+                         uint32_t flags, uint64_t* d_out_index, float* d_out_score, uint32_t* d_out_count,
+                         void* stream) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (nq == 0) return 0;
+  if (!d_qsigs || !d_out_count || (k && (!d_out_index || !d_out_score))) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
+  return query_device(h, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count, nullptr, nullptr,
+                      static_cast<cudaStream_t>(stream));
+}
+
+int jubann_scan_local_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms, uint32_t k,
+                          uint32_t* d_cand_key, uint64_t* d_cand_index, void* stream) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (nq == 0 || k == 0) return 0;
+  if (!d_qsigs || !d_cand_key || !d_cand_index) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  return query_device(h, nq, d_qsigs, d_qnorms, k, 0, nullptr, nullptr, nullptr, d_cand_key, d_cand_index,
+                      static_cast<cudaStream_t>(stream));
+}
+
+int jubann_merge_dev(jubann_t* h, uint64_t nq, uint32_t k, uint32_t parts, const uint32_t* d_cand_key,
+                     const uint64_t* d_cand_index, const float* d_qnorms, uint32_t flags, uint64_t* d_out_index,
+                     float* d_out_score, uint32_t* d_out_count, void* stream) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (nq == 0) return 0;
+  if (!d_out_count) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (k == 0 || parts == 0) { CK(cudaMemsetAsync(d_out_count, 0, nq * 4, s)); return 0; }
+  if (!d_cand_key || !d_cand_index || !d_out_index || !d_out_score) return fail(JUBANN_E_INVALID, "null argument");
+  if (h->method == EUCLID_LSH && !d_qnorms) return fail(JUBANN_E_INVALID, "euclid_lsh queries need norms");
+  MergeOut o{};
+  o.out_index = d_out_index; o.out_score = d_out_score; o.out_count = d_out_count;
+  o.kout = k; o.col0 = 0;
+  o.hash_num = h->hash_num; o.euclid = (h->method == EUCLID_LSH) ? 1 : 0; o.flags = flags; o.qnorms = d_qnorms;
+  CK(launch_merge_parts(d_cand_key, d_cand_index, (uint32_t)nq, k, parts, o, s));
+  h->kernel_launches += 1;
+  return 0;
+}
+
+int jubann_diff_record_bytes(jubann_t* h, uint32_t* bytes) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (!bytes) return fail(JUBANN_E_INVALID, "null argument");
+  *bytes = 8 + 8 * h->w64 + 8;
+  return 0;
+}
+
+int jubann_diff_pack_dev(jubann_t* h, uint64_t n, const uint64_t* d_row_index, void* d_records, void* stream) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!d_row_index || !d_records) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  CK(launch_diff_pack(view(h), n, d_row_index, d_records, 8 + 8 * h->w64 + 8, h->shard_rank, h->shard_count,
+                      static_cast<cudaStream_t>(stream)));
+  h->kernel_launches += 1;
+  return 0;
+}
+
+int jubann_diff_apply_dev(jubann_t* h, uint64_t n, const void* d_records, void* stream) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!d_records) return fail(JUBANN_E_INVALID, "null argument");
+  Guard g(h);
+  CK(launch_diff_apply(view(h), n, d_records, 8 + 8 * h->w64 + 8, h->shard_rank, h->shard_count,
+                       static_cast<cudaStream_t>(stream)));
+  h->kernel_launches += 1;
+  return 0;
+}
+
+int jubann_stats(jubann_t* h, uint64_t* kernel_launches, uint64_t* scan_launches, double* scan_ms) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  Guard g(h);
+  for (auto& ev : h->scan_events) {
+    float ms = 0.0f;
+    cudaEventSynchronize(ev.second);
+    if (cudaEventElapsedTime(&ms, ev.first, ev.second) == cudaSuccess) h->scan_ms += ms;
+    cudaEventDestroy(ev.first);
+    cudaEventDestroy(ev.second);
+  }
+  h->scan_events.clear();
+  if (kernel_launches) *kernel_launches = h->kernel_launches;
+  if (scan_launches) *scan_launches = h->scan_launches;
+  if (scan_ms) *scan_ms = h->scan_ms;
+  return 0;
+}
+
+int jubann_stats_reset(jubann_t* h, int time_scan_kernels) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  Guard g(h);
+  for (auto& ev : h->scan_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
+  h->scan_events.clear();
+  h->kernel_launches = 0; h->scan_launches = 0; h->scan_ms = 0.0;
+  h->time_scan = time_scan_kernels != 0;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,626 @@
+// Batched Hamming / euclid_lsh scan with exact top-k  (sm_100a).
+//
+// Replaces, for a batch of queries,
+//   [core] nearest_neighbor/bit_vector_ranking.cpp  ranking_hamming_bit_vectors
+//   [core] nearest_neighbor/euclid_lsh.cpp          neighbor_row_from_hash
+//   [core] storage/fixed_size_heap.hpp
+// (jubatus_core 0.3.2, reached from jubatus/server/server/nearest_neighbor_serv.cpp:144,153,
+//  162,171).  Result order is the reference's: ascending (distance, row index).
+//
+// One CTA streams a contiguous range of 32-row tiles once and ranks `qp` queries against
+// it.  Lane = row in tile; the row's words sit in registers, query words are broadcast
+// from shared memory, XOR + popcount (optionally through a carry-save adder tree that
+// trades POPC-pipe work for LOP3s).  Each (CTA, query) owns a candidate list in shared
+// memory guarded by a threshold: a row is appended only if its key
+// ((distance << 32) | row) is below the k-th smallest key seen so far by the CTA, so after
+// a short warm-up almost every row costs one compare.  A full list is compacted (bitonic
+// sort by the appending warp, keep k, tighten the threshold) under a per-query spin lock.
+// The CTA's k best are written to scratch; merge_local_kernel reduces the per-CTA lists.
+#include "internal.h"
+
+#include <string.h>
+
+namespace jbn {
+
+#define FULL_MASK 0xffffffffu
+static const int SCAN_THREADS = 512;
+static const int SCAN_WARPS = SCAN_THREADS / 32;
+static const int MERGE_THREADS = 256;
+static const uint32_t MAX_CAP = 4096;  // => at most 2048 results per pass
+
+struct ScanArgs {
+  const unsigned char* slab;
+  const float* norms;
+  uint64_t local_rows;
+  uint64_t ntiles;
+  const uint64_t* qsigs;
+  const float* qnorms;
+  const double* coslut;
+  const uint64_t* floor_keys;
+  uint64_t* cand;
+  uint32_t nq, k, cap, qp, w64, hash_num, tiles_per_chunk, nchunks;
+};
+
+// ---------------------------------------------------------------------------
+// streaming loads: read-once data, keep it out of L1
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint2 ld_stream_v2(const void* p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float ld_stream_f32(const float* p) {
+  float r;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+
+template <int W32>
+__device__ __forceinline__ void load_row(const unsigned char* slab, uint64_t tile, int lane,
+                                         uint32_t (&r)[W32]) {
+  if (W32 == 2) {
+    uint2 v = ld_stream_v2(slab + (tile * 32 + lane) * 8ull);
+    r[0] = v.x; r[1] = v.y;
+  } else {
+    constexpr int C = W32 / 4;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      uint4 v = ld_stream_v4(slab + ((tile * C + c) * 32 + lane) * 16ull);
+      r[4 * c + 0] = v.x; r[4 * c + 1] = v.y; r[4 * c + 2] = v.z; r[4 * c + 3] = v.w;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Hamming distance of the register row against a query in shared memory.
+// PV 0: one POPC per word.  PV 1/2: carry-save adders (3 words -> sum + carry, two LOP3)
+// so fewer words reach the quarter-rate POPC pipe.
+// ---------------------------------------------------------------------------
+#define CSA(h, l, a, b, c)                         \
+  {                                                \
+    uint32_t a_ = (a), b_ = (b), c_ = (c);         \
+    l = a_ ^ b_ ^ c_;                              \
+    h = (a_ & b_) | (a_ & c_) | (b_ & c_);         \
+  }
+
+template <int PV>
+__device__ __forceinline__ uint32_t popc16(const uint32_t (&x)[16]) {
+  if (PV == 0) {
+    uint32_t d = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) d += __popc(x[i]);
+    return d;
+  } else if (PV == 1) {
+    uint32_t o[5], t[5];
+#pragma unroll
+    for (int g = 0; g < 5; ++g) CSA(t[g], o[g], x[3 * g], x[3 * g + 1], x[3 * g + 2]);
+    uint32_t ones = __popc(o[0]) + __popc(o[1]) + __popc(o[2]) + __popc(o[3]) + __popc(o[4]) + __popc(x[15]);
+    uint32_t twos = __popc(t[0]) + __popc(t[1]) + __popc(t[2]) + __popc(t[3]) + __popc(t[4]);
+    return ones + 2 * twos;
+  } else {
+    uint32_t o[7], t[10], f[4], e0;
+#pragma unroll
+    for (int g = 0; g < 5; ++g) CSA(t[g], o[g], x[3 * g], x[3 * g + 1], x[3 * g + 2]);
+    CSA(t[5], o[5], o[0], o[1], o[2]);
+    CSA(t[6], o[6], o[3], o[4], x[15]);
+    CSA(f[0], t[7], t[0], t[1], t[2]);
+    CSA(f[1], t[8], t[3], t[4], t[5]);
+    CSA(f[2], t[9], t[6], t[7], t[8]);
+    CSA(e0, f[3], f[0], f[1], f[2]);
+    return __popc(o[5]) + __popc(o[6]) + 2 * __popc(t[9]) + 4 * __popc(f[3]) + 8 * __popc(e0);
+  }
+}
+
+template <int PV>
+__device__ __forceinline__ uint32_t popc8(const uint32_t (&x)[8]) {
+  if (PV == 0) {
+    uint32_t d = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) d += __popc(x[i]);
+    return d;
+  } else {
+    uint32_t o0, o1, o2, t0, t1, t2, t3, f0;
+    CSA(t0, o0, x[0], x[1], x[2]);
+    CSA(t1, o1, x[3], x[4], x[5]);
+    CSA(t2, o2, o0, o1, x[6]);
+    CSA(f0, t3, t0, t1, t2);
+    return __popc(o2) + __popc(x[7]) + 2 * __popc(t3) + 4 * __popc(f0);
+  }
+}
+
+template <int W32, int PV>
+__device__ __forceinline__ uint32_t hamming(const uint32_t (&r)[W32], const uint32_t* sq) {
+  uint32_t x[W32];
+  if (W32 == 2) {
+    uint2 v = *reinterpret_cast<const uint2*>(sq);
+    x[0] = r[0] ^ v.x; x[1] = r[1] ^ v.y;
+  } else {
+#pragma unroll
+    for (int c = 0; c < W32 / 4; ++c) {
+      uint4 v = reinterpret_cast<const uint4*>(sq)[c];
+      x[4 * c + 0] = r[4 * c + 0] ^ v.x; x[4 * c + 1] = r[4 * c + 1] ^ v.y;
+      x[4 * c + 2] = r[4 * c + 2] ^ v.z; x[4 * c + 3] = r[4 * c + 3] ^ v.w;
+    }
+  }
+  if (W32 == 2) {
+    return __popc(x[0]) + __popc(x[1]);
+  } else if (W32 == 4) {
+    if (PV == 0) return __popc(x[0]) + __popc(x[1]) + __popc(x[2]) + __popc(x[3]);
+    uint32_t o, t;
+    CSA(t, o, x[0], x[1], x[2]);
+    return __popc(o) + __popc(x[3]) + 2 * __popc(t);
+  } else if (W32 == 8) {
+    uint32_t y[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) y[i] = x[i];
+    return popc8<PV>(y);
+  } else {
+    uint32_t d = 0;
+#pragma unroll
+    for (int b = 0; b < W32 / 16; ++b) {
+      uint32_t y[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) y[i] = x[16 * b + i];
+      d += popc16<PV>(y);
+    }
+    return d;
+  }
+}
+
+// order-preserving image of a float (no NaN expected); -0 is folded into +0 first so that
+// equal scores tie exactly like operator< on float does in the reference heap
+__device__ __forceinline__ uint32_t float_key(float f) {
+  f = __fadd_rn(f, 0.0f);
+  uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float key_float(uint32_t k) {
+  uint32_t b = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  float f; memcpy(&f, &b, 4); return f;
+#endif
+}
+
+// ---------------------------------------------------------------------------
+// per-(CTA, query) candidate list
+// ---------------------------------------------------------------------------
+struct ListCtl {
+  unsigned long long* list;  // [qp][cap]
+  unsigned long long* tau;   // [qp] exclusive upper bound on admissible keys
+  unsigned long long* floor; // [qp] exclusive lower bound (pagination) when has_floor
+  uint32_t* cnt;             // [qp]
+  uint32_t* lock;            // [qp]
+  uint32_t* tau_hi;          // [qp] fast reject: key_hi > tau_hi cannot be admissible
+  uint32_t cap, k;
+  bool has_floor;
+};
+
+__device__ __forceinline__ void warp_bitonic_sort(unsigned long long* a, uint32_t n, int lane) {
+  for (uint32_t size = 2; size <= n; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t i = lane; i < (n >> 1); i += 32) {
+        uint32_t lo = ((i & ~(stride - 1)) << 1) | (i & (stride - 1));
+        uint32_t hi = lo | stride;
+        bool asc = ((lo & size) == 0);
+        unsigned long long x = a[lo], y = a[hi];
+        if ((x > y) == asc && x != y) { a[lo] = y; a[hi] = x; }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// Sort list q, keep the k smallest, tighten the threshold.  Called by one full warp that
+// holds lock q (or after the CTA-wide barrier at the end).  Returns the new count.
+__device__ __noinline__ uint32_t list_compact(const ListCtl& L, uint32_t q, uint32_t cnt, int lane) {
+  unsigned long long* a = L.list + (size_t)q * L.cap;
+  for (uint32_t i = cnt + lane; i < L.cap; i += 32) a[i] = KEY_SENTINEL;
+  __syncwarp();
+  warp_bitonic_sort(a, L.cap, lane);
+  uint32_t n = cnt < L.k ? cnt : L.k;
+  if (n == L.k && lane == 0) {
+    unsigned long long t = a[L.k - 1];
+    *reinterpret_cast<volatile unsigned long long*>(L.tau + q) = t;
+    *reinterpret_cast<volatile uint32_t*>(L.tau_hi + q) = (uint32_t)(t >> 32);
+  }
+  __syncwarp();
+  return n;
+}
+
+// Warp-uniform slow path: lanes with cand != 0 offer (key_hi, row).
+__device__ __noinline__ void list_offer(const ListCtl& L, uint32_t q, uint32_t key_hi, uint32_t row,
+                                        bool cand, int lane) {
+  const unsigned long long key = ((unsigned long long)key_hi << 32) | row;
+  volatile unsigned long long* tau_p = L.tau + q;
+  bool pass = cand && key < *tau_p;
+  if (L.has_floor) pass = pass && key > L.floor[q];
+  if (!__any_sync(FULL_MASK, pass)) return;
+  if (lane == 0) {
+    while (atomicCAS(L.lock + q, 0u, 1u) != 0u) __nanosleep(40);
+  }
+  __syncwarp();
+  __threadfence_block();
+  pass = pass && key < *tau_p;  // threshold may have tightened while we waited
+  const unsigned m = __ballot_sync(FULL_MASK, pass);
+  if (m) {
+    uint32_t cnt = *reinterpret_cast<volatile uint32_t*>(L.cnt + q);
+    if (pass) {
+      uint32_t pos = cnt + __popc(m & ((1u << lane) - 1u));
+      L.list[(size_t)q * L.cap + pos] = key;
+    }
+    cnt += __popc(m);
+    __syncwarp();
+    if (cnt > L.cap - 32) cnt = list_compact(L, q, cnt, lane);
+    if (lane == 0) *reinterpret_cast<volatile uint32_t*>(L.cnt + q) = cnt;
+  }
+  __syncwarp();
+  __threadfence_block();
+  if (lane == 0) atomicExch(L.lock + q, 0u);
+}
+
+__host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+
+struct SmemPlan {
+  size_t q_off, lut_off, list_off, tau_off, floor_off, cnt_off, lock_off, tauhi_off, total;
+};
+__host__ __device__ inline SmemPlan plan_smem(uint32_t qp, uint32_t w32, uint32_t cap, bool euclid,
+                                              uint32_t hash_num, size_t base) {
+  SmemPlan p;
+  size_t o = base;
+  p.q_off = o; o = align16(o + (size_t)qp * w32 * 4);
+  p.lut_off = o; if (euclid) o = align16(o + (size_t)qp * (hash_num + 1) * 8);
+  p.list_off = o; o = align16(o + (size_t)qp * cap * 8);
+  p.tau_off = o; o = align16(o + (size_t)qp * 8);
+  p.floor_off = o; o = align16(o + (size_t)qp * 8);
+  p.cnt_off = o; o = align16(o + (size_t)qp * 4);
+  p.lock_off = o; o = align16(o + (size_t)qp * 4);
+  p.tauhi_off = o; o = align16(o + (size_t)qp * 4);
+  p.total = o;
+  return p;
+}
+
+// ---------------------------------------------------------------------------
+// variant 1: rows streamed with coalesced 128-bit LDG, one tile prefetched per warp
+// ---------------------------------------------------------------------------
+template <int W32, bool EUCLID, int PV>
+__global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0);
+  uint32_t* s_q = reinterpret_cast<uint32_t*>(smem + sp.q_off);
+  double* s_lut = reinterpret_cast<double*>(smem + sp.lut_off);
+  ListCtl L;
+  L.list = reinterpret_cast<unsigned long long*>(smem + sp.list_off);
+  L.tau = reinterpret_cast<unsigned long long*>(smem + sp.tau_off);
+  L.floor = reinterpret_cast<unsigned long long*>(smem + sp.floor_off);
+  L.cnt = reinterpret_cast<uint32_t*>(smem + sp.cnt_off);
+  L.lock = reinterpret_cast<uint32_t*>(smem + sp.lock_off);
+  L.tau_hi = reinterpret_cast<uint32_t*>(smem + sp.tauhi_off);
+  L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t q0 = blockIdx.y * a.qp;
+  const uint32_t nqp = min(a.qp, a.nq - q0);
+
+  for (uint32_t i = tid; i < nqp * W32; i += SCAN_THREADS) {
+    uint32_t q = i / W32, w = i % W32;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)(q0 + q) * a.w64);
+    s_q[i] = (w < 2 * a.w64) ? src[w] : 0u;
+  }
+  if (EUCLID) {
+    const uint32_t hn = a.hash_num + 1;
+    for (uint32_t i = tid; i < nqp * hn; i += SCAN_THREADS) {
+      uint32_t q = i / hn, h = i % hn;
+      float two_nq = 2.0f * a.qnorms[q0 + q];
+      s_lut[i] = __dmul_rn((double)two_nq, a.coslut[h]);
+    }
+  }
+  if (tid < nqp) {
+    L.cnt[tid] = 0; L.lock[tid] = 0; L.tau_hi[tid] = 0xFFFFFFFFu; L.tau[tid] = KEY_SENTINEL;
+    L.floor[tid] = a.floor_keys ? a.floor_keys[q0 + tid] : 0ull;
+  }
+  __syncthreads();
+
+  const uint64_t t_begin = (uint64_t)blockIdx.x * a.tiles_per_chunk;
+  const uint64_t t_end = min(a.ntiles, t_begin + (uint64_t)a.tiles_per_chunk);
+  uint32_t cur[W32], nxt[W32];
+  float ncur = 0.0f, nnxt = 0.0f;
+  uint64_t t = t_begin + warp;
+  if (t < t_end) {
+    load_row<W32>(a.slab, t, lane, cur);
+    if (EUCLID) ncur = ld_stream_f32(a.norms + t * 32 + lane);
+  }
+  const volatile uint32_t* v_tau_hi = L.tau_hi;
+  for (; t < t_end; t += SCAN_WARPS) {
+    const uint64_t tn = t + SCAN_WARPS;
+    if (tn < t_end) {
+      load_row<W32>(a.slab, tn, lane, nxt);
+      if (EUCLID) nnxt = ld_stream_f32(a.norms + tn * 32 + lane);
+    }
+    const uint64_t row = t * 32 + lane;
+    const bool valid = row < a.local_rows;
+    const double ni = (double)ncur;
+#pragma unroll 2
+    for (uint32_t q = 0; q < nqp; ++q) {
+      const uint32_t d = hamming<W32, PV>(cur, s_q + q * W32);
+      uint32_t key_hi = d;
+      if (EUCLID) {
+        // score = norm_i * (norm_i - 2*norm_q*cos(theta)), evaluated in double with one
+        // rounding per operation, then narrowed to float: same values as the CPU engine
+        const double l2 = s_lut[q * (a.hash_num + 1) + d];
+        const double s = __dmul_rn(ni, __dsub_rn(ni, l2));
+        key_hi = float_key(__double2float_rn(s));
+      }
+      const bool cand = valid && key_hi <= v_tau_hi[q];
+      if (__any_sync(FULL_MASK, cand)) list_offer(L, q, key_hi, (uint32_t)row, cand, lane);
+    }
+#pragma unroll
+    for (int w = 0; w < W32; ++w) cur[w] = nxt[w];
+    ncur = nnxt;
+  }
+  __syncthreads();
+  for (uint32_t q = warp; q < nqp; q += SCAN_WARPS) {
+    uint32_t n = list_compact(L, q, L.cnt[q], lane);
+    const unsigned long long* src = L.list + (size_t)q * a.cap;
+    unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
+                              ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
+    for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n) ? src[j] : KEY_SENTINEL;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// merge of the per-CTA lists of one query: k smallest of nlists*k keys
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void block_bitonic_sort(unsigned long long* a, uint32_t n, int tid, int nthreads) {
+  for (uint32_t size = 2; size <= n; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t i = tid; i < (n >> 1); i += nthreads) {
+        uint32_t lo = ((i & ~(stride - 1)) << 1) | (i & (stride - 1));
+        uint32_t hi = lo | stride;
+        bool asc = ((lo & size) == 0);
+        unsigned long long x = a[lo], y = a[hi];
+        if ((x > y) == asc && x != y) { a[lo] = y; a[hi] = x; }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+__device__ __forceinline__ float final_score(uint32_t key_hi, const MergeOut& o, uint32_t q) {
+  float s;
+  if (o.euclid) {
+    // sqrt(norm_q^2 + score): float mul, float add, correctly rounded sqrt
+    const float nq = o.qnorms[q];
+    s = __fsqrt_rn(__fadd_rn(__fmul_rn(nq, nq), key_float(key_hi)));
+    if (o.flags & 1u) s = -s;
+  } else {
+    s = __fdiv_rn((float)key_hi, (float)o.hash_num);
+    if (o.flags & 1u) s = __fsub_rn(1.0f, s);
+  }
+  return s;
+}
+
+// half: elements kept between sorts (>= k, >= MERGE_THREADS*2, power of two); smem holds 2*half keys
+__global__ void __launch_bounds__(MERGE_THREADS) merge_local_kernel(const unsigned long long* cand,
+                                                                    uint32_t nlists, uint32_t k,
+                                                                    uint32_t half, MergeOut o) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  unsigned long long* buf = reinterpret_cast<unsigned long long*>(smem);
+  __shared__ uint32_t s_n;
+  const int tid = threadIdx.x;
+  const uint32_t q = blockIdx.x;
+  const unsigned long long* src = cand + (size_t)q * nlists * k;
+  const size_t total = (size_t)nlists * k;
+  for (uint32_t i = tid; i < 2 * half; i += MERGE_THREADS) buf[i] = KEY_SENTINEL;
+  if (tid == 0) s_n = 0;
+  __syncthreads();
+  unsigned long long tau = KEY_SENTINEL;  // k-th smallest key so far (uniform across the CTA)
+  uint32_t pending = 0;                   // keys waiting in buf[half..), uniform
+  for (size_t base = 0; base < total; base += MERGE_THREADS) {
+    const size_t i = base + tid;
+    bool take = false;
+    if (i < total) {
+      unsigned long long key = src[i];
+      take = key < tau;
+      if (take) {
+        uint32_t pos = atomicAdd(&s_n, 1u);
+        buf[half + pos] = key;
+      }
+    }
+    pending += __syncthreads_count(take);
+    const bool last = (base + MERGE_THREADS >= total);
+    if (pending + MERGE_THREADS > half || last) {
+      for (uint32_t j = half + pending + tid; j < 2 * half; j += MERGE_THREADS) buf[j] = KEY_SENTINEL;
+      __syncthreads();
+      block_bitonic_sort(buf, 2 * half, tid, MERGE_THREADS);
+      tau = buf[k - 1];
+      pending = 0;
+      if (tid == 0) s_n = 0;
+      __syncthreads();
+    }
+  }
+  // buf[0..k) ascending
+  uint32_t count = 0;
+  for (uint32_t j = tid; j < k; j += MERGE_THREADS) {
+    const unsigned long long key = buf[j];
+    const bool ok = key != KEY_SENTINEL;
+    const uint32_t key_hi = (uint32_t)(key >> 32);
+    const uint64_t gidx = ok ? (uint64_t)(uint32_t)key * o.shard_count + o.shard_rank : IDX_SENTINEL;
+    if (o.cand_key && ok) {  // unused slots were pre-filled with sentinels by the host
+      o.cand_key[(size_t)q * o.kout + o.col0 + j] = key_hi;
+      o.cand_index[(size_t)q * o.kout + o.col0 + j] = gidx;
+    }
+    if (o.out_index && ok) {
+      o.out_index[(size_t)q * o.kout + o.col0 + j] = gidx;
+      o.out_score[(size_t)q * o.kout + o.col0 + j] = final_score(key_hi, o, q);
+    }
+    count += ok ? 1u : 0u;
+  }
+  // count valid entries
+  __shared__ uint32_t s_count;
+  if (tid == 0) s_count = 0;
+  __syncthreads();
+  if (count) atomicAdd(&s_count, count);
+  __syncthreads();
+  if (tid == 0) {
+    if (o.out_count) o.out_count[q] = (o.count_accumulate ? o.out_count[q] : 0u) + s_count;
+    if (o.last_key) o.last_key[q] = s_count ? buf[s_count - 1] : KEY_SENTINEL;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// merge of `parts` shard-local candidate lists ([parts][nq][k], each ascending by
+// (key, global index), sentinel padded): rank of an element = its position in its own list
+// + number of smaller elements in every other list (binary search); rank < k -> output.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ bool cand_less(uint32_t ka, uint64_t ia, uint32_t kb, uint64_t ib) {
+  return ka < kb || (ka == kb && ia < ib);
+}
+
+__global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32_t* ckey, const uint64_t* cidx,
+                                                                    uint32_t nq, uint32_t k, uint32_t parts,
+                                                                    MergeOut o) {
+  const uint32_t q = blockIdx.x;
+  __shared__ uint32_t s_count;
+  if (threadIdx.x == 0) s_count = 0;
+  __syncthreads();
+  uint32_t mine = 0;
+  for (uint32_t e = threadIdx.x; e < parts * k; e += MERGE_THREADS) {
+    const uint32_t p = e / k, j = e % k;
+    const size_t at = ((size_t)p * nq + q) * k + j;
+    const uint32_t key = ckey[at];
+    const uint64_t idx = cidx[at];
+    if (idx == IDX_SENTINEL) continue;
+    uint32_t rank = j;
+    for (uint32_t p2 = 0; p2 < parts && rank < k; ++p2) {
+      if (p2 == p) continue;
+      const size_t b = ((size_t)p2 * nq + q) * k;
+      uint32_t lo = 0, hi = k;  // first element of list p2 that is not less than (key, idx)
+      while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (cand_less(ckey[b + mid], cidx[b + mid], key, idx)) lo = mid + 1; else hi = mid;
+      }
+      rank += lo;
+    }
+    if (rank < k) {
+      o.out_index[(size_t)q * o.kout + o.col0 + rank] = idx;
+      o.out_score[(size_t)q * o.kout + o.col0 + rank] = final_score(key, o, q);
+      ++mine;
+    }
+  }
+  if (mine) atomicAdd(&s_count, mine);
+  __syncthreads();
+  if (threadIdx.x == 0 && o.out_count) o.out_count[q] = s_count;
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+uint32_t max_k_per_pass() { return MAX_CAP / 2; }
+
+static uint32_t list_cap_for(uint32_t k) {
+  uint32_t need = k < 32 ? 64 : 2 * k;
+  uint32_t cap = 64;
+  while (cap < need) cap <<= 1;
+  return cap;
+}
+
+bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int variant, int popc_variant,
+               uint32_t qp_opt, int num_sms, ScanConfig* cfg) {
+  if (k == 0 || k > max_k_per_pass()) return false;
+  cfg->variant = variant <= 0 ? 1 : variant;
+  cfg->popc_variant = popc_variant < 0 ? 0 : popc_variant;
+  cfg->cap = list_cap_for(k);
+  // queries per pass: bounded by shared memory (two CTAs per SM => ~100 KB each)
+  const size_t budget = 100 * 1024;
+  uint32_t qp = qp_opt ? qp_opt : 8;
+  if (qp > nq) qp = nq;
+  if (qp < 1) qp = 1;
+  while (qp > 1 && plan_smem(qp, t.w32, cfg->cap, euclid, t.hash_num, 0).total > budget) --qp;
+  cfg->qp = qp;
+  cfg->smem_bytes = plan_smem(qp, t.w32, cfg->cap, euclid, t.hash_num, 0).total;
+  const uint64_t ntiles = (t.local_rows + 31) / 32;
+  // at least 64 tiles per CTA; at most two resident CTAs per SM worth of chunks
+  uint64_t nchunks = (ntiles + 63) / 64;
+  const uint64_t max_chunks = (uint64_t)num_sms * 2;
+  if (nchunks > max_chunks) nchunks = max_chunks;
+  if (nchunks < 1) nchunks = 1;
+  cfg->nchunks = (uint32_t)nchunks;
+  cfg->tiles_per_chunk = (uint32_t)((ntiles + nchunks - 1) / nchunks);
+  if (cfg->tiles_per_chunk == 0) cfg->tiles_per_chunk = 1;
+  return true;
+}
+
+template <int W32, bool EUCLID, int PV>
+static cudaError_t launch_scan_t(const ScanArgs& a, const ScanConfig& cfg, dim3 grid, cudaStream_t s) {
+  auto kern = scan_ldg_kernel<W32, EUCLID, PV>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem_bytes);
+  if (e != cudaSuccess) return e;
+  kern<<<grid, SCAN_THREADS, cfg.smem_bytes, s>>>(a);
+  return cudaGetLastError();
+}
+
+template <int W32, bool EUCLID>
+static cudaError_t launch_scan_pv(const ScanArgs& a, const ScanConfig& cfg, dim3 grid, cudaStream_t s) {
+  switch (cfg.popc_variant) {
+    case 0: return launch_scan_t<W32, EUCLID, 0>(a, cfg, grid, s);
+    case 1: return launch_scan_t<W32, EUCLID, 1>(a, cfg, grid, s);
+    default: return launch_scan_t<W32, EUCLID, 2>(a, cfg, grid, s);
+  }
+}
+
+template <bool EUCLID>
+static cudaError_t launch_scan_w(uint32_t w32, const ScanArgs& a, const ScanConfig& cfg, dim3 grid,
+                                 cudaStream_t s) {
+  switch (w32) {
+    case 2: return launch_scan_t<2, EUCLID, 0>(a, cfg, grid, s);
+    case 4: return launch_scan_pv<4, EUCLID>(a, cfg, grid, s);
+    case 8: return launch_scan_pv<8, EUCLID>(a, cfg, grid, s);
+    case 16: return launch_scan_pv<16, EUCLID>(a, cfg, grid, s);
+    case 32: return launch_scan_pv<32, EUCLID>(a, cfg, grid, s);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, const uint64_t* d_qsigs,
+                        const float* d_qnorms, const double* d_coslut, uint32_t nq, uint32_t k,
+                        const uint64_t* d_floor_keys, uint64_t* d_cand, cudaStream_t s) {
+  ScanArgs a;
+  a.slab = static_cast<const unsigned char*>(t.slab);
+  a.norms = t.norms;
+  a.local_rows = t.local_rows;
+  a.ntiles = (t.local_rows + 31) / 32;
+  a.qsigs = d_qsigs; a.qnorms = d_qnorms; a.coslut = d_coslut; a.floor_keys = d_floor_keys;
+  a.cand = d_cand;
+  a.nq = nq; a.k = k; a.cap = cfg.cap; a.qp = cfg.qp; a.w64 = t.w64; a.hash_num = t.hash_num;
+  a.tiles_per_chunk = cfg.tiles_per_chunk; a.nchunks = cfg.nchunks;
+  dim3 grid(cfg.nchunks, (nq + cfg.qp - 1) / cfg.qp, 1);
+  return euclid ? launch_scan_w<true>(t.w32, a, cfg, grid, s) : launch_scan_w<false>(t.w32, a, cfg, grid, s);
+}
+
+cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nlists, uint32_t k,
+                               const MergeOut& out, cudaStream_t s) {
+  uint32_t half = 2 * MERGE_THREADS;
+  while (half < k) half <<= 1;
+  const size_t smem = (size_t)2 * half * 8;
+  cudaError_t e = cudaFuncSetAttribute(merge_local_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  merge_local_kernel<<<nq, MERGE_THREADS, smem, s>>>(reinterpret_cast<const unsigned long long*>(d_cand),
+                                                     nlists, k, half, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_merge_parts(const uint32_t* d_cand_key, const uint64_t* d_cand_index, uint32_t nq,
+                               uint32_t k, uint32_t parts, const MergeOut& out, cudaStream_t s) {
+  merge_parts_kernel<<<nq, MERGE_THREADS, 0, s>>>(d_cand_key, d_cand_index, nq, k, parts, out);
+  return cudaGetLastError();
+}
+
+}  // namespace jbn
