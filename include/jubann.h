@@ -78,7 +78,9 @@ int jubann_destroy(jubann_t* h);
 /* Tunables, to be set before the first row or query.  Names: "cache_slots" (distinct
  * feature seeds held by the projection cache, default 2^20), "queries_per_pass" (how many
  * queries share one streaming pass over the table; 0 = automatic), "scan_variant"
- * (0 = automatic, 1 = LDG streaming, 2 = TMA bulk-copy pipeline). */
+ * (0 = automatic, 1 = LDG streaming, 2 = TMA bulk-copy pipeline), "popc_variant" (0 = one
+ * POPC per word, 1/2 = carry-save adder trees), "reserve_rows" (allocate the slab for this
+ * many global rows up front; may be set at any time). */
 int jubann_set_option(jubann_t* h, const char* name, int64_t value);
 
 /* nearest_neighbor_base::clear() -> column_table::clear()  (nearest_neighbor_serv.cpp:125) */

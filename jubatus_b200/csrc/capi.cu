@@ -454,6 +454,28 @@ int jubann_set_option(jubann_t* h, const char* name, int64_t value) {
     if (value < 1 || value > (1ll << 28)) return fail(JUBANN_E_INVALID, "cache_slots out of range");
     if (h->cache_ready) return fail(JUBANN_E_INVALID, "cache_slots must be set before the first row or query (or after clear)");
     h->cache_slots_opt = (uint32_t)value;
+  } else if (!strcmp(name, "reserve_rows")) {
+    if (value < 0) return fail(JUBANN_E_INVALID, "reserve_rows out of range");
+    const uint64_t nl = local_count((uint64_t)value, h->shard_rank, h->shard_count);
+    if (nl > h->cap_rows) {
+      // exact-size allocation: no doubling for a table whose final size is known
+      const uint64_t keep = h->cap_rows;
+      h->cap_rows = keep;
+      uint64_t want = (nl + 31) / 32 * 32;
+      void* nslab = nullptr; float* nnorms = nullptr;
+      if (cudaMalloc(&nslab, slab_bytes(h->w32, want)) != cudaSuccess) { cudaGetLastError(); return fail(JUBANN_E_NOMEM, "cudaMalloc for %llu reserved rows failed", (unsigned long long)want); }
+      CK(cudaMemsetAsync(nslab, 0, slab_bytes(h->w32, want), h->stream));
+      if (h->slab) CK(cudaMemcpyAsync(nslab, h->slab, slab_bytes(h->w32, keep), cudaMemcpyDeviceToDevice, h->stream));
+      if (h->method == EUCLID_LSH) {
+        if (cudaMalloc(reinterpret_cast<void**>(&nnorms), want * sizeof(float)) != cudaSuccess) { cudaGetLastError(); cudaFree(nslab); return fail(JUBANN_E_NOMEM, "cudaMalloc for the norm column failed"); }
+        CK(cudaMemsetAsync(nnorms, 0, want * sizeof(float), h->stream));
+        if (h->norms) CK(cudaMemcpyAsync(nnorms, h->norms, keep * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
+      }
+      CK(cudaStreamSynchronize(h->stream));
+      if (h->slab) cudaFree(h->slab);
+      if (h->norms) cudaFree(h->norms);
+      h->slab = nslab; h->norms = nnorms; h->cap_rows = want;
+    }
   } else if (!strcmp(name, "queries_per_pass")) {
     if (value < 0 || value > 64) return fail(JUBANN_E_INVALID, "queries_per_pass out of range (0..64)");
     h->qp_opt = (uint32_t)value;

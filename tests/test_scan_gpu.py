@@ -1,0 +1,203 @@
+"""Parity of the CUDA scan + top-k (through the C-ABI) with the oracle: bit-exact ids, order
+and scores, including ties (smaller row index first), k > N, k = 0, empty and ragged tables."""
+import numpy as np
+import pytest
+
+from gpu_util import assert_same_ranking, random_rows
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(method, hash_num, **opt):
+    from jubatus_b200 import Engine
+    return Engine(method, hash_num, **opt)
+
+
+@pytest.mark.parametrize("hash_num", [64, 100, 128, 192, 256, 512, 1024, 1])
+@pytest.mark.parametrize("popc_variant", [0, 1, 2])
+def test_hamming_topk_random(oracle, hash_num, popc_variant):
+    rng = np.random.RandomState(hash_num + popc_variant)
+    n, nq, k = 5000, 9, 10
+    rows = random_rows(rng, n, hash_num)
+    q = random_rows(rng, nq, hash_num)
+    q[0] = rows[17]
+    with _engine("lsh", hash_num, popc_variant=popc_variant) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        got = e.query_sig(q, None, k)
+    want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3]
+    assert_same_ranking(got, want, nq, k)
+
+
+@pytest.mark.parametrize("n,k", [(0, 5), (1, 5), (31, 40), (32, 32), (33, 1), (1000, 0), (1000, 100), (4097, 257),
+                                 (70000, 100), (300, 299)])
+def test_hamming_sizes_and_k(oracle, n, k):
+    rng = np.random.RandomState(n * 7 + k)
+    hash_num, nq = 256, 5
+    rows = random_rows(rng, n, hash_num)
+    q = random_rows(rng, nq, hash_num)
+    with _engine("lsh", hash_num) as e:
+        if n:
+            e.set_rows_sig(np.arange(n), rows)
+        got = e.query_sig(q, None, k)
+        assert e.size() == (n, n)
+    want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3]
+    assert_same_ranking(got, want, nq, k)
+
+
+@pytest.mark.parametrize("qp", [1, 2, 3, 8])
+def test_adversarial_ties(oracle, qp):
+    # few distinct signatures -> huge tie groups; order must be by row index
+    rng = np.random.RandomState(11)
+    hash_num, n, nq, k = 128, 20000, 7, 100
+    base = random_rows(rng, 4, hash_num)
+    rows = base[rng.randint(0, 4, size=n)]
+    q = np.concatenate([base, random_rows(rng, nq - 4, hash_num)])
+    with _engine("lsh", hash_num, queries_per_pass=qp) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        got = e.query_sig(q, None, k)
+    want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3]
+    assert_same_ranking(got, want, nq, k)
+
+
+def test_all_identical_rows(oracle):
+    hash_num, n, k = 512, 50000, 100
+    rows = np.tile(random_rows(np.random.RandomState(1), 1, hash_num), (n, 1))
+    q = rows[:2].copy()
+    q[1, 0] ^= np.uint64(0xFF)
+    with _engine("lsh", hash_num) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        idx, score, count = e.query_sig(q, None, k)
+    assert list(idx[0]) == list(range(k)) and list(idx[1]) == list(range(k))
+    assert (score[0] == 0).all() and (score[1] == np.float32(8) / np.float32(512)).all()
+
+
+def test_descending_distances_worst_case(oracle):
+    # every later row is closer than all earlier ones: the threshold path is exercised at every row
+    hash_num, n, k = 512, 512, 20
+    rows = np.zeros((n, 8), dtype=np.uint64)
+    for i in range(n):
+        nbits = n - i  # distance to the all-zero query
+        for b in range(nbits):
+            rows[i, b // 64] |= np.uint64(1) << np.uint64(b % 64)
+    q = np.zeros((1, 8), dtype=np.uint64)
+    with _engine("lsh", hash_num) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        got = e.query_sig(q, None, k)
+    want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3]
+    assert_same_ranking(got, want, 1, k)
+
+
+def test_large_k_pagination(oracle):
+    rng = np.random.RandomState(3)
+    hash_num, n, nq, k = 64, 9000, 3, 5000   # > 2048 results per pass -> several pages
+    rows = random_rows(rng, n, hash_num)
+    q = random_rows(rng, nq, hash_num)
+    with _engine("lsh", hash_num) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        got = e.query_sig(q, None, k)
+    want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3]
+    assert_same_ranking(got, want, nq, k)
+
+
+def test_similar_flag_and_minhash_method(oracle):
+    from jubatus_b200 import SIMILAR
+    rng = np.random.RandomState(8)
+    hash_num, n, nq, k = 128, 3000, 4, 50
+    rows = random_rows(rng, n, hash_num)
+    q = random_rows(rng, nq, hash_num)
+    for method in ("lsh", "minhash"):
+        with _engine(method, hash_num) as e:
+            e.set_rows_sig(np.arange(n), rows)
+            got = e.query_sig(q, None, k, SIMILAR)
+        want = oracle.scan_batch(method, q, None, rows, None, hash_num, k, similar=True)[:3]
+        assert_same_ranking(got, want, nq, k)
+
+
+@pytest.mark.parametrize("hash_num", [64, 256, 100])
+def test_euclid_scores(oracle, hash_num):
+    from jubatus_b200 import SIMILAR
+    rng = np.random.RandomState(hash_num)
+    n, nq, k = 6000, 6, 100
+    rows = random_rows(rng, n, hash_num)
+    norms = (rng.rand(n) * 10).astype(np.float32)
+    norms[5] = 0.0
+    norms[6] = 0.0
+    q = random_rows(rng, nq, hash_num)
+    qn = (rng.rand(nq) * 10).astype(np.float32)
+    q[1] = rows[100]
+    qn[1] = norms[100]
+    qn[2] = 0.0
+    with _engine("euclid_lsh", hash_num) as e:
+        e.set_rows_sig(np.arange(n), rows, norms)
+        got = e.query_sig(q, qn, k)
+        got_sim = e.query_sig(q, qn, k, SIMILAR)
+    want = oracle.scan_batch("euclid_lsh", q, qn, rows, norms, hash_num, k)[:3]
+    want_sim = oracle.scan_batch("euclid_lsh", q, qn, rows, norms, hash_num, k, similar=True)[:3]
+    # ids/order bit-exact; scores: same float operations -> bit-exact as well (NaN-safe compare)
+    for g, w_ in ((got, want), (got_sim, want_sim)):
+        for qi in range(nq):
+            c = int(w_[2][qi])
+            assert int(g[2][qi]) == c
+            assert np.array_equal(g[0][qi, :c], w_[0][qi, :c])
+            assert np.array_equal(g[1][qi, :c].view(np.uint32), w_[1][qi, :c].view(np.uint32))
+
+
+def test_query_rows_uses_stored_signature(oracle):
+    rng = np.random.RandomState(21)
+    hash_num, n, k = 256, 4000, 10
+    rows = random_rows(rng, n, hash_num)
+    rows[2000] = rows[3]
+    with _engine("lsh", hash_num) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        got = e.query_rows([3, 2000, 77], k)
+    want = oracle.scan_batch("lsh", rows[[3, 2000, 77]], None, rows, None, hash_num, k)[:3]
+    assert_same_ranking(got, want, 3, k)
+    assert list(got[0][0][:2]) == [3, 2000] and list(got[0][1][:2]) == [3, 2000]   # itself is not excluded
+
+
+def test_many_queries_batch(oracle):
+    rng = np.random.RandomState(4)
+    hash_num, n, nq, k = 512, 20000, 300, 10
+    rows = random_rows(rng, n, hash_num)
+    q = random_rows(rng, nq, hash_num)
+    q[:50] = rows[rng.randint(0, n, size=50)]
+    with _engine("lsh", hash_num) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        got = e.query_sig(q, None, k)
+        st = e.stats()
+    assert st["kernel_launches"] > 0 and st["scan_launches"] > 0
+    want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k, threads=4)[:3]
+    assert_same_ranking(got, want, nq, k)
+
+
+def test_table_mutation_matches_column_table(oracle):
+    # update in place, delete = move last row into the hole, then re-query
+    rng = np.random.RandomState(6)
+    hash_num, n, k = 128, 1000, 30
+    rows = random_rows(rng, n, hash_num)
+    with _engine("lsh", hash_num) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        rows[10] = rows[500]
+        e.set_rows_sig([10], rows[10:11])                 # update in place
+        e.move_row(n - 1, 20); e.truncate(n - 1)          # delete_row(key of row 20)
+        rows[20] = rows[n - 1]; rows = rows[: n - 1]
+        got = e.query_sig(rows[500:502], None, k)
+        back, _ = e.get_rows_sig([10, 20, 998])
+    assert np.array_equal(back, rows[[10, 20, 998]])
+    want = oracle.scan_batch("lsh", rows[500:502], None, rows, None, hash_num, k)[:3]
+    assert_same_ranking(got, want, 2, k)
+
+
+def test_errors(oracle):
+    from jubatus_b200 import JubannError
+    with _engine("lsh", 64) as e:
+        with pytest.raises(JubannError):
+            e.set_rows_sig([5], np.zeros((1, 1), dtype=np.uint64))   # skips past the end
+        with pytest.raises(JubannError):
+            e.query_rows([0], 1)                                       # unknown row
+        with pytest.raises(JubannError):
+            e.set_option("nope", 1)
+    with _engine("euclid_lsh", 64) as e:
+        e.set_rows_sig([0], np.zeros((1, 1), dtype=np.uint64), np.ones(1, dtype=np.float32))
+        with pytest.raises(JubannError):
+            e.query_sig(np.zeros((1, 1), dtype=np.uint64), None, 1)   # norms required
