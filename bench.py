@@ -354,6 +354,8 @@ def run_b200(a):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    passes_per_launch = st["scan_passes"] / float(max(1, st["scan_launches"]))
+    bytes_per_launch = bytes_per_launch * passes_per_launch   # a launch streams the shard once per pass
     avg_ms = st["scan_ms"] / max(1, st["scan_launches"])
     achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9
     traffic = None
@@ -367,13 +369,13 @@ def run_b200(a):
         micro = json.load(open(os.path.join(ROOT, "profiles", "microbench.json")))
     except Exception:
         pass
-    qp_eff = (a.nq * a.steps) / max(1, st["scan_launches"])
+    qp_eff = (a.nq * a.steps) / float(max(1, st["scan_passes"]))
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                 "kernel": "scan_*_kernel", "bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_ms,
-                "launches": st["scan_launches"], "queries_per_pass": qp_eff,
+                "launches": st["scan_launches"], "passes_per_launch": passes_per_launch, "queries_per_pass": qp_eff,
                 "scan_share_of_step": st["scan_ms"] / ms_total}
-    popc32 = local_rows * qp_eff * (a.hash_num / 32.0) / (avg_ms * 1e-3)
+    popc32 = local_rows * qp_eff * passes_per_launch * (a.hash_num / 32.0) / (avg_ms * 1e-3)
     roofline["int_popc32_per_s"] = popc32
     if micro.get("popc_only_per_s"):
         roofline["int_frac_of_measured_popc_peak"] = popc32 / micro["popc_only_per_s"]
@@ -422,7 +424,7 @@ def run_b200(a):
         "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u32", "data": "synthetic (uniform random signature words, scan-only fill; queries random + planted exact copies)",
         "config": {"workload": workload_name(a), "parallelism": "rows sharded round-robin over %d GPU(s)" % G,
-                   "cache": "table %.1f GB per GPU >> 126 MB L2, streamed once per pass (inputs larger than L2)" % (bytes_per_launch / 1e9),
+                   "cache": "table %.1f GB per GPU >> 126 MB L2, streamed once per pass (inputs larger than L2)" % (local_rows * row_bytes / 1e9),
                    "queries_per_pass": qp_eff},
         "roofline": roofline, "e2e": e2e, "gpu_launches": st["kernel_launches"], "clocks": clocks,
     }

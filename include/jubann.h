@@ -79,7 +79,9 @@ int jubann_destroy(jubann_t* h);
  * feature seeds held by the projection cache, default 2^20), "queries_per_pass" (how many
  * queries share one streaming pass over the table; 0 = automatic), "scan_variant"
  * (0 = automatic, 1 = LDG streaming, 2 = TMA bulk-copy pipeline), "popc_variant" (0 = one
- * POPC per word, 1/2 = carry-save adder trees), "reserve_rows" (allocate the slab for this
+ * POPC per word, 1..4 = carry-save adder trees), "scan_order" (1 = CTAs take turns over
+ * consecutive tile groups so the whole GPU sweeps one front, 0 = one contiguous range per CTA),
+ * "reserve_rows" (allocate the slab for this
  * many global rows up front; may be set at any time). */
 int jubann_set_option(jubann_t* h, const char* name, int64_t value);
 
@@ -174,10 +176,13 @@ int jubann_diff_pack_dev(jubann_t* h, uint64_t n, const uint64_t* d_row_index, v
                          void* stream);
 int jubann_diff_apply_dev(jubann_t* h, uint64_t n, const void* d_records, void* stream);
 
-/* Introspection for bench.py / tests: kernels launched by this handle since creation,
- * duration (ms, CUDA events on the launching stream) and launch count of scan kernels
- * accumulated since the last reset when profiling is switched on. */
-int jubann_stats(jubann_t* h, uint64_t* kernel_launches, uint64_t* scan_launches, double* scan_ms);
+/* Introspection for bench.py / tests: kernels launched by this handle since the last reset;
+ * scan-kernel launches; streaming passes over the table (a launch covers several passes
+ * when the batch holds more queries than share one pass); and, when switched on with
+ * jubann_stats_reset(h, 1), the summed duration of the scan kernels in ms (CUDA events
+ * on the launching stream). */
+int jubann_stats(jubann_t* h, uint64_t* kernel_launches, uint64_t* scan_launches, uint64_t* scan_passes,
+                 double* scan_ms);
 int jubann_stats_reset(jubann_t* h, int time_scan_kernels);
 
 #ifdef __cplusplus

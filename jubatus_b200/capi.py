@@ -80,7 +80,7 @@ def load_library():
         "jubann_diff_record_bytes": [H, _u32p],
         "jubann_diff_pack_dev": [H, ctypes.c_uint64, _vp, _vp, _vp],
         "jubann_diff_apply_dev": [H, ctypes.c_uint64, _vp, _vp],
-        "jubann_stats": [H, _u64p, _u64p, ctypes.POINTER(ctypes.c_double)],
+        "jubann_stats": [H, _u64p, _u64p, _u64p, ctypes.POINTER(ctypes.c_double)],
         "jubann_stats_reset": [H, ctypes.c_int],
     }
     for name, argtypes in sig.items():
@@ -268,9 +268,9 @@ class Engine(object):
 
     # -- stats ---------------------------------------------------------------
     def stats(self):
-        a, b, c = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_double()
-        _check(self._lib.jubann_stats(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
-        return {"kernel_launches": a.value, "scan_launches": b.value, "scan_ms": c.value}
+        a, b, p, c = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_double()
+        _check(self._lib.jubann_stats(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(p), ctypes.byref(c)))
+        return {"kernel_launches": a.value, "scan_launches": b.value, "scan_passes": p.value, "scan_ms": c.value}
 
     def stats_reset(self, time_scan_kernels=False):
         _check(self._lib.jubann_stats_reset(self._h, 1 if time_scan_kernels else 0))

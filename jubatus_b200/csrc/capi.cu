@@ -69,11 +69,12 @@ struct jubann {
   uint32_t qp_opt = 0;
   int variant_opt = 0;
   int popc_variant_opt = 2;
+  int interleave_opt = 1;
   // staging (grow-only)
   DevBuf b_indptr, b_seed, b_keyhash, b_vals, b_rowidx, b_sigs, b_norms;
   DevBuf b_qsigs, b_qnorms, b_out_idx, b_out_score, b_out_count, b_cand, b_floor;
   // stats
-  uint64_t kernel_launches = 0, scan_launches = 0;
+  uint64_t kernel_launches = 0, scan_launches = 0, scan_passes = 0;
   bool time_scan = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t> > scan_events;
   double scan_ms = 0.0;
@@ -317,7 +318,7 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
   const uint32_t kpage = std::min(keff, max_k_per_pass());
   const uint32_t pages = (keff + kpage - 1) / kpage;
   ScanConfig cfg;
-  if (!plan_scan(t, euclid, nq, kpage, h->variant_opt, h->popc_variant_opt, h->qp_opt, h->num_sms, &cfg))
+  if (!plan_scan(t, euclid, nq, kpage, h->variant_opt, h->popc_variant_opt, h->qp_opt, h->interleave_opt, h->num_sms, &cfg))
     return fail(JUBANN_E_INVALID, "cannot plan a scan for k=%u", kpage);
   // queries per launch bounded by candidate scratch (<= 256 MiB)
   const size_t per_query = (size_t)cfg.nchunks * kpage * 8;
@@ -355,6 +356,7 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
       CK(launch_merge_local(h->b_cand.as<uint64_t>(), nql, cfg.nchunks, kthis, o, s));
       h->kernel_launches += 2;
       h->scan_launches += 1;
+      h->scan_passes += (nql + cfg.qp - 1) / cfg.qp;
     }
   }
   return 0;
@@ -482,8 +484,11 @@ int jubann_set_option(jubann_t* h, const char* name, int64_t value) {
   } else if (!strcmp(name, "scan_variant")) {
     if (value < 0 || value > 2) return fail(JUBANN_E_INVALID, "scan_variant out of range (0..2)");
     h->variant_opt = (int)value;
+  } else if (!strcmp(name, "scan_order")) {
+    if (value < 0 || value > 1) return fail(JUBANN_E_INVALID, "scan_order out of range (0..1)");
+    h->interleave_opt = (int)value;
   } else if (!strcmp(name, "popc_variant")) {
-    if (value < 0 || value > 2) return fail(JUBANN_E_INVALID, "popc_variant out of range (0..2)");
+    if (value < 0 || value > 4) return fail(JUBANN_E_INVALID, "popc_variant out of range (0..4)");
     h->popc_variant_opt = (int)value;
   } else {
     return fail(JUBANN_E_INVALID, "unknown option: %s", name);
@@ -839,7 +844,8 @@ int jubann_diff_apply_dev(jubann_t* h, uint64_t n, const void* d_records, void* 
   return 0;
 }
 
-int jubann_stats(jubann_t* h, uint64_t* kernel_launches, uint64_t* scan_launches, double* scan_ms) {
+int jubann_stats(jubann_t* h, uint64_t* kernel_launches, uint64_t* scan_launches, uint64_t* scan_passes,
+                 double* scan_ms) {
   int rc = check_handle(h);
   if (rc) return rc;
   Guard g(h);
@@ -853,6 +859,7 @@ int jubann_stats(jubann_t* h, uint64_t* kernel_launches, uint64_t* scan_launches
   h->scan_events.clear();
   if (kernel_launches) *kernel_launches = h->kernel_launches;
   if (scan_launches) *scan_launches = h->scan_launches;
+  if (scan_passes) *scan_passes = h->scan_passes;
   if (scan_ms) *scan_ms = h->scan_ms;
   return 0;
 }
@@ -863,7 +870,7 @@ int jubann_stats_reset(jubann_t* h, int time_scan_kernels) {
   Guard g(h);
   for (auto& ev : h->scan_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
   h->scan_events.clear();
-  h->kernel_launches = 0; h->scan_launches = 0; h->scan_ms = 0.0;
+  h->kernel_launches = 0; h->scan_launches = 0; h->scan_passes = 0; h->scan_ms = 0.0;
   h->time_scan = time_scan_kernels != 0;
   return 0;
 }

@@ -58,12 +58,14 @@ struct ScanConfig {
   uint32_t nchunks;   // grid.x
   uint32_t tiles_per_chunk;
   uint32_t cap;       // candidate list capacity per (CTA, query), power of two
+  uint32_t stages, tiles_per_warp;  // TMA ring geometry (variant 2)
+  uint32_t interleave;
   size_t smem_bytes;
 };
 
 // Chooses grid/smem for (table, nq, k).  Returns false if k does not fit one pass.
 bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int variant, int popc_variant,
-               uint32_t qp_opt, int num_sms, ScanConfig* cfg);
+               uint32_t qp_opt, int interleave, int num_sms, ScanConfig* cfg);
 uint32_t max_k_per_pass();
 
 // cand: [nq][nchunks][k] keys ((key_hi << 32) | local row), ascending, KEY_SENTINEL padded.

@@ -39,6 +39,7 @@ struct ScanArgs {
   const uint64_t* floor_keys;
   uint64_t* cand;
   uint32_t nq, k, cap, qp, w64, hash_num, tiles_per_chunk, nchunks;
+  uint32_t interleave;  // 1: CTAs take turns tile-group by tile-group (one sweep front); 0: one contiguous range per CTA
 };
 
 // ---------------------------------------------------------------------------
@@ -103,7 +104,31 @@ __device__ __forceinline__ uint32_t popc16(const uint32_t (&x)[16]) {
     uint32_t ones = __popc(o[0]) + __popc(o[1]) + __popc(o[2]) + __popc(o[3]) + __popc(o[4]) + __popc(x[15]);
     uint32_t twos = __popc(t[0]) + __popc(t[1]) + __popc(t[2]) + __popc(t[3]) + __popc(t[4]);
     return ones + 2 * twos;
+  } else if (PV == 3) {
+    // 7 adders: 9 POPC
+    uint32_t o[7], t[7];
+#pragma unroll
+    for (int g = 0; g < 5; ++g) CSA(t[g], o[g], x[3 * g], x[3 * g + 1], x[3 * g + 2]);
+    CSA(t[5], o[5], o[0], o[1], o[2]);
+    CSA(t[6], o[6], o[3], o[4], x[15]);
+    uint32_t ones = __popc(o[5]) + __popc(o[6]);
+    uint32_t twos = __popc(t[0]) + __popc(t[1]) + __popc(t[2]) + __popc(t[3]) + __popc(t[4]) + __popc(t[5]) + __popc(t[6]);
+    return ones + 2 * twos;
+  } else if (PV == 4) {
+    // 9 adders: 7 POPC
+    uint32_t o[7], t[9], f[2];
+#pragma unroll
+    for (int g = 0; g < 5; ++g) CSA(t[g], o[g], x[3 * g], x[3 * g + 1], x[3 * g + 2]);
+    CSA(t[5], o[5], o[0], o[1], o[2]);
+    CSA(t[6], o[6], o[3], o[4], x[15]);
+    CSA(f[0], t[7], t[0], t[1], t[2]);
+    CSA(f[1], t[8], t[3], t[4], t[5]);
+    uint32_t ones = __popc(o[5]) + __popc(o[6]);
+    uint32_t twos = __popc(t[6]) + __popc(t[7]) + __popc(t[8]);
+    uint32_t fours = __popc(f[0]) + __popc(f[1]);
+    return ones + 2 * twos + 4 * fours;
   } else {
+    // 11 adders: 5 POPC
     uint32_t o[7], t[10], f[4], e0;
 #pragma unroll
     for (int g = 0; g < 5; ++g) CSA(t[g], o[g], x[3 * g], x[3 * g + 1], x[3 * g + 2]);
@@ -198,7 +223,9 @@ struct ListCtl {
   unsigned long long* floor; // [qp] exclusive lower bound (pagination) when has_floor
   uint32_t* cnt;             // [qp]
   uint32_t* lock;            // [qp]
-  uint32_t* tau_hi;          // [qp] fast reject: key_hi > tau_hi cannot be admissible
+  uint32_t* tau_hi;          // word 0 of query 0's threshold; query q at tau_hi[q * tau_stride]
+  uint32_t tau_stride;
+  uint32_t local_rows;
   uint32_t cap, k;
   bool has_floor;
 };
@@ -229,7 +256,7 @@ __device__ __noinline__ uint32_t list_compact(const ListCtl& L, uint32_t q, uint
   if (n == L.k && lane == 0) {
     unsigned long long t = a[L.k - 1];
     *reinterpret_cast<volatile unsigned long long*>(L.tau + q) = t;
-    *reinterpret_cast<volatile uint32_t*>(L.tau_hi + q) = (uint32_t)(t >> 32);
+    *reinterpret_cast<volatile uint32_t*>(L.tau_hi + (size_t)q * L.tau_stride) = (uint32_t)(t >> 32);
   }
   __syncwarp();
   return n;
@@ -240,7 +267,7 @@ __device__ __noinline__ void list_offer(const ListCtl& L, uint32_t q, uint32_t k
                                         bool cand, int lane) {
   const unsigned long long key = ((unsigned long long)key_hi << 32) | row;
   volatile unsigned long long* tau_p = L.tau + q;
-  bool pass = cand && key < *tau_p;
+  bool pass = cand && row < L.local_rows && key < *tau_p;  // rows of the padded last tile are not rows
   if (L.has_floor) pass = pass && key > L.floor[q];
   if (!__any_sync(FULL_MASK, pass)) return;
   if (lane == 0) {
@@ -267,6 +294,9 @@ __device__ __noinline__ void list_offer(const ListCtl& L, uint32_t q, uint32_t k
 }
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+// a query's shared-memory block: W32 signature words, then the fast-reject threshold word
+// (tau_hi), padded to 16 bytes -- one base address serves the whole inner loop
+__host__ __device__ inline uint32_t q_stride(uint32_t w32) { return w32 + 4; }
 
 struct SmemPlan {
   size_t q_off, lut_off, list_off, tau_off, floor_off, cnt_off, lock_off, tauhi_off, total;
@@ -275,16 +305,95 @@ __host__ __device__ inline SmemPlan plan_smem(uint32_t qp, uint32_t w32, uint32_
                                               uint32_t hash_num, size_t base) {
   SmemPlan p;
   size_t o = base;
-  p.q_off = o; o = align16(o + (size_t)qp * w32 * 4);
+  p.q_off = o; o = align16(o + (size_t)qp * q_stride(w32) * 4);
   p.lut_off = o; if (euclid) o = align16(o + (size_t)qp * (hash_num + 1) * 8);
   p.list_off = o; o = align16(o + (size_t)qp * cap * 8);
   p.tau_off = o; o = align16(o + (size_t)qp * 8);
   p.floor_off = o; o = align16(o + (size_t)qp * 8);
   p.cnt_off = o; o = align16(o + (size_t)qp * 4);
   p.lock_off = o; o = align16(o + (size_t)qp * 4);
-  p.tauhi_off = o; o = align16(o + (size_t)qp * 4);
+  p.tauhi_off = o;  // (tau_hi lives inside the query blocks)
   p.total = o;
   return p;
+}
+
+// ---------------------------------------------------------------------------
+// one tile (lane = row) against the CTA's queries
+// ---------------------------------------------------------------------------
+template <int W32, bool EUCLID, int PV>
+__device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t row, double ni, uint32_t nqp,
+                                          const uint32_t* s_q, const double* s_lut, uint32_t hash_num,
+                                          const ListCtl& L, int lane) {
+  constexpr uint32_t QS = W32 + 4;
+  uint32_t q = 0;
+  for (; q + 2 <= nqp; q += 2) {  // two independent distance chains in flight
+    const uint32_t* b0 = s_q + q * QS;
+    const uint32_t* b1 = b0 + QS;
+    const uint32_t d0 = hamming<W32, PV>(cur, b0);
+    const uint32_t d1 = hamming<W32, PV>(cur, b1);
+    uint32_t k0 = d0, k1 = d1;
+    if (EUCLID) {
+      // score = norm_i * (norm_i - 2*norm_q*cos(theta)), evaluated in double with one rounding
+      // per operation, then narrowed to float: the same values as the CPU engine
+      const double l0 = s_lut[q * (hash_num + 1) + d0];
+      const double l1 = s_lut[(q + 1) * (hash_num + 1) + d1];
+      k0 = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l0))));
+      k1 = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l1))));
+    }
+    const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
+    const bool c1 = k1 <= *reinterpret_cast<const volatile uint32_t*>(b1 + W32);
+    if (__any_sync(FULL_MASK, c0 || c1)) {
+      if (__any_sync(FULL_MASK, c0)) list_offer(L, q, k0, row, c0, lane);
+      if (__any_sync(FULL_MASK, c1)) list_offer(L, q + 1, k1, row, c1, lane);
+    }
+  }
+  if (q < nqp) {
+    const uint32_t* b0 = s_q + q * QS;
+    const uint32_t d0 = hamming<W32, PV>(cur, b0);
+    uint32_t k0 = d0;
+    if (EUCLID) {
+      const double l0 = s_lut[q * (hash_num + 1) + d0];
+      k0 = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l0))));
+    }
+    const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
+    if (__any_sync(FULL_MASK, c0)) list_offer(L, q, k0, row, c0, lane);
+  }
+}
+
+// shared prologue: query blocks, euclid LUT, list control
+template <int W32, bool EUCLID>
+__device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* smem, const SmemPlan& sp, ListCtl& L,
+                                              uint32_t*& s_q, double*& s_lut, uint32_t q0, uint32_t nqp, int tid,
+                                              int nthreads) {
+  constexpr uint32_t QS = W32 + 4;
+  s_q = reinterpret_cast<uint32_t*>(smem + sp.q_off);
+  s_lut = reinterpret_cast<double*>(smem + sp.lut_off);
+  L.list = reinterpret_cast<unsigned long long*>(smem + sp.list_off);
+  L.tau = reinterpret_cast<unsigned long long*>(smem + sp.tau_off);
+  L.floor = reinterpret_cast<unsigned long long*>(smem + sp.floor_off);
+  L.cnt = reinterpret_cast<uint32_t*>(smem + sp.cnt_off);
+  L.lock = reinterpret_cast<uint32_t*>(smem + sp.lock_off);
+  L.tau_hi = s_q + W32;
+  L.tau_stride = QS;
+  L.local_rows = (uint32_t)a.local_rows;
+  L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr);
+  for (uint32_t i = tid; i < nqp * QS; i += nthreads) {
+    uint32_t q = i / QS, w = i % QS;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)(q0 + q) * a.w64);
+    s_q[i] = (w < W32) ? ((w < 2 * a.w64) ? src[w] : 0u) : 0xFFFFFFFFu;
+  }
+  if (EUCLID) {
+    const uint32_t hn = a.hash_num + 1;
+    for (uint32_t i = tid; i < nqp * hn; i += nthreads) {
+      uint32_t q = i / hn, h = i % hn;
+      float two_nq = 2.0f * a.qnorms[q0 + q];
+      s_lut[i] = __dmul_rn((double)two_nq, a.coslut[h]);
+    }
+  }
+  if ((uint32_t)tid < nqp) {
+    L.cnt[tid] = 0; L.lock[tid] = 0; L.tau[tid] = KEY_SENTINEL;
+    L.floor[tid] = a.floor_keys ? a.floor_keys[q0 + tid] : 0ull;
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -294,79 +403,211 @@ template <int W32, bool EUCLID, int PV>
 __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0);
-  uint32_t* s_q = reinterpret_cast<uint32_t*>(smem + sp.q_off);
-  double* s_lut = reinterpret_cast<double*>(smem + sp.lut_off);
-  ListCtl L;
-  L.list = reinterpret_cast<unsigned long long*>(smem + sp.list_off);
-  L.tau = reinterpret_cast<unsigned long long*>(smem + sp.tau_off);
-  L.floor = reinterpret_cast<unsigned long long*>(smem + sp.floor_off);
-  L.cnt = reinterpret_cast<uint32_t*>(smem + sp.cnt_off);
-  L.lock = reinterpret_cast<uint32_t*>(smem + sp.lock_off);
-  L.tau_hi = reinterpret_cast<uint32_t*>(smem + sp.tauhi_off);
-  L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr);
-
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t q0 = blockIdx.y * a.qp;
   const uint32_t nqp = min(a.qp, a.nq - q0);
-
-  for (uint32_t i = tid; i < nqp * W32; i += SCAN_THREADS) {
-    uint32_t q = i / W32, w = i % W32;
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)(q0 + q) * a.w64);
-    s_q[i] = (w < 2 * a.w64) ? src[w] : 0u;
-  }
-  if (EUCLID) {
-    const uint32_t hn = a.hash_num + 1;
-    for (uint32_t i = tid; i < nqp * hn; i += SCAN_THREADS) {
-      uint32_t q = i / hn, h = i % hn;
-      float two_nq = 2.0f * a.qnorms[q0 + q];
-      s_lut[i] = __dmul_rn((double)two_nq, a.coslut[h]);
-    }
-  }
-  if (tid < nqp) {
-    L.cnt[tid] = 0; L.lock[tid] = 0; L.tau_hi[tid] = 0xFFFFFFFFu; L.tau[tid] = KEY_SENTINEL;
-    L.floor[tid] = a.floor_keys ? a.floor_keys[q0 + tid] : 0ull;
-  }
+  ListCtl L;
+  uint32_t* s_q;
+  double* s_lut;
+  scan_prologue<W32, EUCLID>(a, smem, sp, L, s_q, s_lut, q0, nqp, tid, SCAN_THREADS);
   __syncthreads();
 
-  const uint64_t t_begin = (uint64_t)blockIdx.x * a.tiles_per_chunk;
-  const uint64_t t_end = min(a.ntiles, t_begin + (uint64_t)a.tiles_per_chunk);
+  uint64_t t, t_end, t_step;
+  if (a.interleave) {
+    t = (uint64_t)blockIdx.x * SCAN_WARPS + warp;
+    t_end = a.ntiles;
+    t_step = (uint64_t)gridDim.x * SCAN_WARPS;
+  } else {
+    const uint64_t t_begin = (uint64_t)blockIdx.x * a.tiles_per_chunk;
+    t = t_begin + warp;
+    t_end = min(a.ntiles, t_begin + (uint64_t)a.tiles_per_chunk);
+    t_step = SCAN_WARPS;
+  }
   uint32_t cur[W32], nxt[W32];
   float ncur = 0.0f, nnxt = 0.0f;
-  uint64_t t = t_begin + warp;
   if (t < t_end) {
     load_row<W32>(a.slab, t, lane, cur);
     if (EUCLID) ncur = ld_stream_f32(a.norms + t * 32 + lane);
   }
-  const volatile uint32_t* v_tau_hi = L.tau_hi;
-  for (; t < t_end; t += SCAN_WARPS) {
-    const uint64_t tn = t + SCAN_WARPS;
+  for (; t < t_end; t += t_step) {
+    const uint64_t tn = t + t_step;
     if (tn < t_end) {
       load_row<W32>(a.slab, tn, lane, nxt);
       if (EUCLID) nnxt = ld_stream_f32(a.norms + tn * 32 + lane);
     }
-    const uint64_t row = t * 32 + lane;
-    const bool valid = row < a.local_rows;
-    const double ni = (double)ncur;
-#pragma unroll 2
-    for (uint32_t q = 0; q < nqp; ++q) {
-      const uint32_t d = hamming<W32, PV>(cur, s_q + q * W32);
-      uint32_t key_hi = d;
-      if (EUCLID) {
-        // score = norm_i * (norm_i - 2*norm_q*cos(theta)), evaluated in double with one
-        // rounding per operation, then narrowed to float: same values as the CPU engine
-        const double l2 = s_lut[q * (a.hash_num + 1) + d];
-        const double s = __dmul_rn(ni, __dsub_rn(ni, l2));
-        key_hi = float_key(__double2float_rn(s));
-      }
-      const bool cand = valid && key_hi <= v_tau_hi[q];
-      if (__any_sync(FULL_MASK, cand)) list_offer(L, q, key_hi, (uint32_t)row, cand, lane);
-    }
+    rank_tile<W32, EUCLID, PV>(cur, (uint32_t)(t * 32 + lane), (double)ncur, nqp, s_q, s_lut, a.hash_num, L, lane);
 #pragma unroll
     for (int w = 0; w < W32; ++w) cur[w] = nxt[w];
     ncur = nnxt;
   }
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += SCAN_WARPS) {
+    uint32_t n = list_compact(L, q, L.cnt[q], lane);
+    const unsigned long long* src = L.list + (size_t)q * a.cap;
+    unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
+                              ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
+    for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n) ? src[j] : KEY_SENTINEL;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// variant 2: rows staged through shared memory by the TMA engine.  One producer thread
+// issues 1-D bulk copies (cp.async.bulk -> UBLKCP) of whole runs of tiles into a ring of
+// stages, completion is tracked by mbarrier transaction counts; 16 consumer warps read their
+// tile from shared memory with conflict-free 128-bit loads (the slab's tile-transposed
+// layout is kept as is) and release the stage through a second mbarrier.  No row data
+// passes through registers before it is needed, so the kernel is spill-free at 1 CTA / SM
+// and the memory pipeline runs ahead of the popcount work by several stages.
+// ---------------------------------------------------------------------------
+static const int TMA_CONSUMER_WARPS = 16;
+static const int TMA_THREADS = (TMA_CONSUMER_WARPS + 1) * 32;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+struct TmaPlan {
+  uint32_t stages, tiles_per_warp;   // a stage holds TMA_CONSUMER_WARPS * tiles_per_warp tiles
+  size_t ring_off, norm_off, bar_off, total;
+};
+__host__ __device__ inline TmaPlan plan_tma(uint32_t qp, uint32_t w32, uint32_t cap, bool euclid, uint32_t hash_num,
+                                            uint32_t stages, uint32_t tiles_per_warp) {
+  TmaPlan t;
+  t.stages = stages; t.tiles_per_warp = tiles_per_warp;
+  const size_t stage_tiles = (size_t)TMA_CONSUMER_WARPS * tiles_per_warp;
+  size_t o = (plan_smem(qp, w32, cap, euclid, hash_num, 0).total + 127) & ~(size_t)127;
+  t.ring_off = o; o += stages * stage_tiles * w32 * 128;
+  t.norm_off = o; if (euclid) o += stages * stage_tiles * 128;
+  t.bar_off = o; o += (size_t)stages * 16;
+  t.total = o;
+  return t;
+}
+
+template <int W32>
+__device__ __forceinline__ void load_row_smem(const unsigned char* stage, uint32_t tile_in_stage, int lane,
+                                              uint32_t (&r)[W32]) {
+  if (W32 == 2) {
+    uint2 v = *reinterpret_cast<const uint2*>(stage + ((size_t)tile_in_stage * 32 + lane) * 8);
+    r[0] = v.x; r[1] = v.y;
+  } else {
+    constexpr int C = W32 / 4;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      uint4 v = *reinterpret_cast<const uint4*>(stage + (((size_t)tile_in_stage * C + c) * 32 + lane) * 16);
+      r[4 * c + 0] = v.x; r[4 * c + 1] = v.y; r[4 * c + 2] = v.z; r[4 * c + 3] = v.w;
+    }
+  }
+}
+
+template <int W32, bool EUCLID, int PV>
+__global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, uint32_t stages, uint32_t tiles_per_warp) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0);
+  const TmaPlan tp = plan_tma(a.qp, W32, a.cap, EUCLID, a.hash_num, stages, tiles_per_warp);
+  unsigned char* ring = smem + tp.ring_off;
+  float* nring = reinterpret_cast<float*>(smem + tp.norm_off);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + tp.bar_off);
+  uint64_t* empty_bar = full_bar + stages;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t q0 = blockIdx.y * a.qp;
+  const uint32_t nqp = min(a.qp, a.nq - q0);
+  const uint32_t stage_tiles = TMA_CONSUMER_WARPS * tiles_per_warp;
+  const size_t tile_bytes = (size_t)W32 * 128;
+  const size_t stage_bytes = stage_tiles * tile_bytes;
+  ListCtl L;
+  uint32_t* s_q;
+  double* s_lut;
+  scan_prologue<W32, EUCLID>(a, smem, sp, L, s_q, s_lut, q0, nqp, tid, TMA_THREADS);
+  if (tid == 0) {
+    for (uint32_t s = 0; s < stages; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, TMA_CONSUMER_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+
+  // stage `it` of this CTA starts at tile stage_t0(it)
+  uint64_t t_first, t_stride, t_end;
+  uint32_t iters;
+  if (a.interleave) {
+    const uint64_t nstage = (a.ntiles + stage_tiles - 1) / stage_tiles;
+    t_first = (uint64_t)blockIdx.x * stage_tiles;
+    t_stride = (uint64_t)gridDim.x * stage_tiles;
+    t_end = a.ntiles;
+    iters = nstage > blockIdx.x ? (uint32_t)((nstage - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0u;
+  } else {
+    t_first = (uint64_t)blockIdx.x * a.tiles_per_chunk;
+    t_stride = stage_tiles;
+    t_end = min(a.ntiles, t_first + (uint64_t)a.tiles_per_chunk);
+    const uint64_t my_tiles = t_end > t_first ? t_end - t_first : 0;
+    iters = (uint32_t)((my_tiles + stage_tiles - 1) / stage_tiles);
+  }
+
+  if (warp == TMA_CONSUMER_WARPS) {
+    // ---- producer: one elected thread feeds the ring ----
+    if (lane == 0) {
+      for (uint32_t it = 0; it < iters; ++it) {
+        const uint32_t s = it % stages, ph = (it / stages) & 1u;
+        if (it >= stages) mbar_wait(empty_bar + s, ph ^ 1u);
+        const uint64_t t0 = t_first + (uint64_t)it * t_stride;
+        const uint32_t ntile = (uint32_t)min((uint64_t)stage_tiles, t_end - t0);
+        const uint32_t bytes = ntile * (uint32_t)tile_bytes;
+        mbar_expect_tx(full_bar + s, bytes + (EUCLID ? ntile * 128u : 0u));
+        bulk_g2s(ring + s * stage_bytes, a.slab + t0 * tile_bytes, bytes, full_bar + s);
+        if (EUCLID) bulk_g2s(nring + (size_t)s * stage_tiles * 32, a.norms + t0 * 32, ntile * 128u, full_bar + s);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---- consumers ----
+    for (uint32_t it = 0; it < iters; ++it) {
+      const uint32_t s = it % stages, ph = (it / stages) & 1u;
+      mbar_wait(full_bar + s, ph);
+      const unsigned char* stage = ring + s * stage_bytes;
+      const uint64_t t0 = t_first + (uint64_t)it * t_stride;
+      for (uint32_t j = 0; j < tiles_per_warp; ++j) {
+        const uint32_t tis = j * TMA_CONSUMER_WARPS + warp;
+        const uint64_t t = t0 + tis;
+        if (t >= t_end) break;
+        uint32_t cur[W32];
+        load_row_smem<W32>(stage, tis, lane, cur);
+        double ni = 0.0;
+        if (EUCLID) ni = (double)nring[((size_t)s * stage_tiles + tis) * 32 + lane];
+        rank_tile<W32, EUCLID, PV>(cur, (uint32_t)(t * 32 + lane), ni, nqp, s_q, s_lut, a.hash_num, L, lane);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_bar + s);
+    }
+  }
+  __syncthreads();
+  for (uint32_t q = warp; q < nqp; q += TMA_CONSUMER_WARPS + 1) {
     uint32_t n = list_compact(L, q, L.cnt[q], lane);
     const unsigned long long* src = L.list + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
@@ -533,23 +774,41 @@ static uint32_t list_cap_for(uint32_t k) {
 }
 
 bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int variant, int popc_variant,
-               uint32_t qp_opt, int num_sms, ScanConfig* cfg) {
+               uint32_t qp_opt, int interleave, int num_sms, ScanConfig* cfg) {
   if (k == 0 || k > max_k_per_pass()) return false;
   cfg->variant = variant <= 0 ? 1 : variant;
   cfg->popc_variant = popc_variant < 0 ? 0 : popc_variant;
   cfg->cap = list_cap_for(k);
-  // queries per pass: bounded by shared memory (two CTAs per SM => ~100 KB each)
-  const size_t budget = 100 * 1024;
+  const uint64_t ntiles = (t.local_rows + 31) / 32;
   uint32_t qp = qp_opt ? qp_opt : 8;
   if (qp > nq) qp = nq;
   if (qp < 1) qp = 1;
-  while (qp > 1 && plan_smem(qp, t.w32, cfg->cap, euclid, t.hash_num, 0).total > budget) --qp;
+  cfg->stages = 0; cfg->tiles_per_warp = 0;
+  cfg->interleave = interleave ? 1u : 0u;
+  uint64_t max_chunks;
+  if (cfg->variant == 2) {
+    // one CTA per SM; ring of >= 2 stages of ~32 KB; the rest of shared memory for the lists
+    const size_t budget = 226 * 1024;
+    uint32_t tpw = 1;
+    while ((size_t)TMA_CONSUMER_WARPS * tpw * t.w32 * 128 < 32 * 1024) tpw <<= 1;
+    while (qp > 1 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) --qp;
+    while (tpw > 1 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) tpw >>= 1;
+    if (plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) return false;
+    uint32_t stages = 2;
+    while (stages < 6 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, stages + 1, tpw).total <= budget) ++stages;
+    cfg->stages = stages; cfg->tiles_per_warp = tpw;
+    cfg->smem_bytes = plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, stages, tpw).total;
+    max_chunks = (uint64_t)num_sms;
+  } else {
+    // two CTAs per SM => ~100 KB of shared memory each
+    const size_t budget = 100 * 1024;
+    while (qp > 1 && plan_smem(qp, t.w32, cfg->cap, euclid, t.hash_num, 0).total > budget) --qp;
+    cfg->smem_bytes = plan_smem(qp, t.w32, cfg->cap, euclid, t.hash_num, 0).total;
+    max_chunks = (uint64_t)num_sms * 2;
+  }
   cfg->qp = qp;
-  cfg->smem_bytes = plan_smem(qp, t.w32, cfg->cap, euclid, t.hash_num, 0).total;
-  const uint64_t ntiles = (t.local_rows + 31) / 32;
-  // at least 64 tiles per CTA; at most two resident CTAs per SM worth of chunks
+  // at least 64 tiles per CTA
   uint64_t nchunks = (ntiles + 63) / 64;
-  const uint64_t max_chunks = (uint64_t)num_sms * 2;
   if (nchunks > max_chunks) nchunks = max_chunks;
   if (nchunks < 1) nchunks = 1;
   cfg->nchunks = (uint32_t)nchunks;
@@ -560,6 +819,13 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
 
 template <int W32, bool EUCLID, int PV>
 static cudaError_t launch_scan_t(const ScanArgs& a, const ScanConfig& cfg, dim3 grid, cudaStream_t s) {
+  if (cfg.variant == 2) {
+    auto kern = scan_tma_kernel<W32, EUCLID, PV>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem_bytes);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, TMA_THREADS, cfg.smem_bytes, s>>>(a, cfg.stages, cfg.tiles_per_warp);
+    return cudaGetLastError();
+  }
   auto kern = scan_ldg_kernel<W32, EUCLID, PV>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem_bytes);
   if (e != cudaSuccess) return e;
@@ -572,7 +838,9 @@ static cudaError_t launch_scan_pv(const ScanArgs& a, const ScanConfig& cfg, dim3
   switch (cfg.popc_variant) {
     case 0: return launch_scan_t<W32, EUCLID, 0>(a, cfg, grid, s);
     case 1: return launch_scan_t<W32, EUCLID, 1>(a, cfg, grid, s);
-    default: return launch_scan_t<W32, EUCLID, 2>(a, cfg, grid, s);
+    case 2: return launch_scan_t<W32, EUCLID, 2>(a, cfg, grid, s);
+    case 3: return launch_scan_t<W32, EUCLID, 3>(a, cfg, grid, s);
+    default: return launch_scan_t<W32, EUCLID, 4>(a, cfg, grid, s);
   }
 }
 
@@ -601,6 +869,7 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   a.cand = d_cand;
   a.nq = nq; a.k = k; a.cap = cfg.cap; a.qp = cfg.qp; a.w64 = t.w64; a.hash_num = t.hash_num;
   a.tiles_per_chunk = cfg.tiles_per_chunk; a.nchunks = cfg.nchunks;
+  a.interleave = cfg.interleave;
   dim3 grid(cfg.nchunks, (nq + cfg.qp - 1) / cfg.qp, 1);
   return euclid ? launch_scan_w<true>(t.w32, a, cfg, grid, s) : launch_scan_w<false>(t.w32, a, cfg, grid, s);
 }

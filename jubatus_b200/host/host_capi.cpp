@@ -1,0 +1,262 @@
+// Flat C entry points over jubann_host.hpp so the host layer (string ids, datums, JSON
+// configs, MIX, recommender, light_lof) can be driven from Python tests through ctypes.
+// This is a test/bindings convenience; a C++ server links jubann_host.hpp directly
+// (INTEGRATION.md).  Results with string ids come back '\n'-joined.
+#include "jubann_host.hpp"
+
+#include <string.h>
+
+using namespace jubatus_b200;
+
+namespace {
+thread_local std::string g_err;
+
+struct host_box {
+  std::shared_ptr<jubann_api> api;
+  std::unique_ptr<nearest_neighbor_serv> serv;             // jubanearest_neighbor
+  std::shared_ptr<gpu_nearest_neighbor> engine;            // nested engines
+  std::shared_ptr<datum_to_fv_converter> converter;
+  std::unique_ptr<nearest_neighbor_recommender> recommender;
+  std::unique_ptr<light_lof> lof;
+  gpu_nearest_neighbor* nn() { return serv ? serv->get_driver()->engine() : engine.get(); }
+  const datum_to_fv_converter& conv() { return serv ? serv->get_driver()->converter() : *converter; }
+};
+
+datum make_datum(const char* const* skeys, const char* const* svals, uint64_t ns, const char* const* nkeys,
+                 const double* nvals, uint64_t nn) {
+  datum d;
+  for (uint64_t i = 0; i < ns; ++i) d.add_string(skeys[i], svals[i]);
+  for (uint64_t i = 0; i < nn; ++i) d.add_number(nkeys[i], nvals[i]);
+  return d;
+}
+
+int emit(const neighbor_result& r, char* ids_buf, uint64_t ids_cap, float* scores, uint64_t scores_cap, uint64_t* count) {
+  std::string joined;
+  if (r.size() > scores_cap) { g_err = "scores buffer too small"; return -1; }
+  for (size_t i = 0; i < r.size(); ++i) { joined += r[i].first; joined += '\n'; scores[i] = r[i].second; }
+  if (joined.size() + 1 > ids_cap) { g_err = "ids buffer too small"; return -1; }
+  memcpy(ids_buf, joined.c_str(), joined.size() + 1);
+  *count = r.size();
+  return 0;
+}
+
+template <typename F>
+int guarded(F f) {
+  try { return f(); }
+  catch (const std::exception& e) { g_err = e.what(); return -1; }
+}
+}  // namespace
+
+extern "C" {
+
+const char* jubahost_last_error() { return g_err.c_str(); }
+
+// kind: "nearest_neighbor" | "recommender" | "anomaly"; config = the server's JSON config
+void* jubahost_create(const char* kind, const char* config_json, const char* lib_path, const char* my_id, int device) {
+  host_box* b = new host_box;
+  int rc = guarded([&]() {
+    b->api = jubann_api::load(lib_path ? lib_path : "libjubann.so");
+    const std::string k(kind);
+    if (k == "nearest_neighbor") {
+      b->serv.reset(new nearest_neighbor_serv(b->api, my_id ? my_id : "", device));
+      b->serv->set_config(config_json);
+      return 0;
+    }
+    json::ptr root;
+    try { root = json::parse(config_json); } catch (const json::parse_error& e) { throw config_exception(e.what()); }
+    json::ptr m = root->find("method"), p = root->find("parameter"), c = root->find("converter");
+    if (!m || m->kind != json::value::STR) throw config_exception("\"method\" is required");
+    if (!c) throw config_exception("\"converter\" is required");
+    b->converter = datum_to_fv_converter::from_config(c);
+    if (!p || p->kind != json::value::OBJ) throw config_exception("\"parameter\" is required");
+    json::ptr im = p->find("method");
+    if (!im || im->kind != json::value::STR) throw config_exception("nested \"method\" is required");
+    if (k == "recommender") {
+      // recommender_serv.cpp:93-119 -> recommender_factory; only the nearest_neighbor_recommender family is on this path
+      if (m->str != "nearest_neighbor_recommender") throw unsupported_method(m->str);
+      for (size_t i = 0; i < p->obj.size(); ++i) {
+        const std::string& key = p->obj[i].first;
+        if (key != "method" && key != "parameter" && key != "unlearner" && key != "unlearner_parameter")
+          throw config_exception("unknown parameter key: " + key);
+      }
+      if (p->find("unlearner")) throw config_exception("unlearner is not supported by this build");
+      b->engine = create_nearest_neighbor(im->str, p->find("parameter"), b->api, my_id ? my_id : "", device);
+      b->recommender.reset(new nearest_neighbor_recommender(b->engine));
+    } else if (k == "anomaly") {
+      // anomaly_serv.cpp:112-142 -> anomaly_factory; light_lof only
+      if (m->str != "light_lof") throw unsupported_method(m->str);
+      int nn_num = 10, rnn_num = 30;
+      for (size_t i = 0; i < p->obj.size(); ++i) {
+        const std::string& key = p->obj[i].first;
+        const json::ptr& v = p->obj[i].second;
+        if (key == "nearest_neighbor_num" || key == "reverse_nearest_neighbor_num") {
+          if (v->kind != json::value::NUM || !v->is_integer) throw config_exception("\"" + key + "\" must be an integer");
+          (key == "nearest_neighbor_num" ? nn_num : rnn_num) = static_cast<int>(v->num);
+        } else if (key == "unlearner" || key == "unlearner_parameter") {
+          throw config_exception("unlearner is not supported by this build");
+        } else if (key != "method" && key != "parameter") {
+          throw config_exception("unknown parameter key: " + key);
+        }
+      }
+      b->engine = create_nearest_neighbor(im->str, p->find("parameter"), b->api, my_id ? my_id : "", device);
+      b->lof.reset(new light_lof(b->engine, nn_num, rnn_num));
+    } else {
+      throw jubatus_exception("unknown server kind: " + k);
+    }
+    return 0;
+  });
+  if (rc) { delete b; return 0; }
+  return b;
+}
+void jubahost_destroy(void* h) { delete static_cast<host_box*>(h); }
+
+// datum -> sfv only (no device): keys come back '\n'-joined
+int jubahost_convert(const char* converter_json, const char* const* skeys, const char* const* svals, uint64_t ns,
+                     const char* const* nkeys, const double* nvals, uint64_t nn, char* keys_buf, uint64_t keys_cap,
+                     float* vals, uint64_t vals_cap, uint64_t* count) {
+  return guarded([&]() {
+    json::ptr c;
+    try { c = json::parse(converter_json); } catch (const json::parse_error& e) { throw config_exception(e.what()); }
+    std::shared_ptr<datum_to_fv_converter> conv = datum_to_fv_converter::from_config(c);
+    sfv_t sfv;
+    conv->convert(make_datum(skeys, svals, ns, nkeys, nvals, nn), sfv);
+    return emit(sfv, keys_buf, keys_cap, vals, vals_cap, count);
+  });
+}
+
+int jubahost_clear(void* h) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (b->serv) b->serv->clear(); else if (b->recommender) b->recommender->clear(); else b->lof->clear();
+    return 0;
+  });
+}
+uint64_t jubahost_size(void* h) { return static_cast<host_box*>(h)->nn()->get_table()->size(); }
+
+// set_row (nearest_neighbor) / update_row (recommender) / add-with-id (anomaly: light_lof::set_row)
+int jubahost_set_row(void* h, const char* id, const char* const* skeys, const char* const* svals, uint64_t ns,
+                     const char* const* nkeys, const double* nvals, uint64_t nn) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    datum d = make_datum(skeys, svals, ns, nkeys, nvals, nn);
+    if (b->serv) { b->serv->set_row(id, d); return 0; }
+    sfv_t v;
+    b->conv().convert(d, v);
+    if (b->recommender) b->recommender->update_row(id, v); else b->lof->set_row(id, v);
+    return 0;
+  });
+}
+// batched set_row over n datums that carry only number values: nkeys/nvals are flattened, offs[n+1]
+int jubahost_set_rows(void* h, uint64_t n, const char* const* ids, const uint64_t* offs, const char* const* nkeys,
+                      const double* nvals) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->serv) throw jubatus_exception("set_rows: nearest_neighbor server only");
+    std::vector<std::string> vid(n);
+    std::vector<datum> ds(n);
+    for (uint64_t i = 0; i < n; ++i) {
+      vid[i] = ids[i];
+      for (uint64_t j = offs[i]; j < offs[i + 1]; ++j) ds[i].add_number(nkeys[j], nvals[j]);
+    }
+    b->serv->get_driver()->set_rows(vid, ds);
+    return 0;
+  });
+}
+int jubahost_delete_row(void* h, const char* id) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (b->recommender) { b->recommender->clear_row(id); return 0; }
+    return b->nn()->delete_row(id) ? 0 : 1;
+  });
+}
+int jubahost_query_datum(void* h, const char* const* skeys, const char* const* svals, uint64_t ns,
+                         const char* const* nkeys, const double* nvals, uint64_t nn, uint64_t k, int similar,
+                         char* ids_buf, uint64_t ids_cap, float* scores, uint64_t scores_cap, uint64_t* count) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    datum d = make_datum(skeys, svals, ns, nkeys, nvals, nn);
+    neighbor_result r;
+    if (b->serv) {
+      r = similar ? b->serv->similar_row_from_datum(d, k) : b->serv->neighbor_row_from_datum(d, k);
+    } else {
+      sfv_t v;
+      b->conv().convert(d, v);
+      if (b->recommender) { if (similar) b->recommender->similar_row(v, r, k); else b->recommender->neighbor_row(v, r, k); }
+      else { if (similar) b->nn()->similar_row(v, r, k); else b->nn()->neighbor_row(v, r, k); }
+    }
+    return emit(r, ids_buf, ids_cap, scores, scores_cap, count);
+  });
+}
+int jubahost_query_id(void* h, const char* id, uint64_t k, int similar, char* ids_buf, uint64_t ids_cap, float* scores,
+                      uint64_t scores_cap, uint64_t* count) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    neighbor_result r;
+    if (b->serv) r = similar ? b->serv->similar_row_from_id(id, k) : b->serv->neighbor_row_from_id(id, k);
+    else if (b->recommender) { if (similar) b->recommender->similar_row(std::string(id), r, k); else b->recommender->neighbor_row(std::string(id), r, k); }
+    else { if (similar) b->nn()->similar_row(std::string(id), r, k); else b->nn()->neighbor_row(std::string(id), r, k); }
+    return emit(r, ids_buf, ids_cap, scores, scores_cap, count);
+  });
+}
+int jubahost_get_all_rows(void* h, char* ids_buf, uint64_t ids_cap, uint64_t* count) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    std::vector<std::string> ids;
+    b->nn()->get_all_row_ids(ids);
+    neighbor_result r;
+    for (size_t i = 0; i < ids.size(); ++i) r.push_back(std::make_pair(ids[i], 0.0f));
+    std::vector<float> dummy(ids.size() + 1);
+    return emit(r, ids_buf, ids_cap, dummy.data(), dummy.size(), count);
+  });
+}
+int jubahost_get_signature(void* h, const char* id, uint64_t* sig, float* norm) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    std::pair<bool, uint64_t> hit = b->nn()->get_table()->exact_match(id);
+    if (!hit.first) return 1;
+    packed_row r = b->nn()->get_table()->get_row(hit.second);
+    memcpy(sig, r.sig.data(), r.sig.size() * 8);
+    if (norm) *norm = r.norm;
+    return 0;
+  });
+}
+// push_mixer order (framework/mixer/push_mixer.cpp:335-408) between two in-process engines
+int jubahost_mix_pair(void* ha, void* hb) {
+  host_box* a = static_cast<host_box*>(ha);
+  host_box* b = static_cast<host_box*>(hb);
+  return guarded([&]() {
+    mixable_versioned_table* ma = a->nn()->get_mixable();
+    mixable_versioned_table* mb = b->nn()->get_mixable();
+    version_clock arg_a = ma->get_argument(), arg_b = mb->get_argument();
+    std::vector<packed_row> from_b, from_a;
+    mb->pull(arg_a, from_b);
+    ma->pull(arg_b, from_a);
+    mb->push(from_a);
+    ma->push(from_b);
+    return 0;
+  });
+}
+int jubahost_calc_score_datum(void* h, const char* const* nkeys, const double* nvals, uint64_t nn, float* score) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->lof) throw jubatus_exception("calc_score: anomaly server only");
+    sfv_t v;
+    b->conv().convert(make_datum(0, 0, 0, nkeys, nvals, nn), v);
+    *score = b->lof->calc_anomaly_score(v);
+    return 0;
+  });
+}
+int jubahost_calc_score_id(void* h, const char* id, float* score) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->lof) throw jubatus_exception("calc_score: anomaly server only");
+    *score = b->lof->calc_anomaly_score(std::string(id));
+    return 0;
+  });
+}
+int jubahost_lof_params(void* h, const char* id, float* kdist, float* lrd) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() { return b->lof && b->lof->get_row_parameter(id, kdist, lrd) ? 0 : 1; });
+}
+
+}  // extern "C"

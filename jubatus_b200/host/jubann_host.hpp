@@ -1,0 +1,825 @@
+// Host side of the drop-in: the reference's C++ interfaces for the nearest-neighbor path,
+// re-stated over the C-ABI of libjubann.so (include/jubann.h).
+//
+// What mirrors what (jubatus_core 0.3.2 is un-vendored; cited by the reference call site):
+//   jubatus_b200::nearest_neighbor_base / gpu_nearest_neighbor / create_nearest_neighbor
+//       <- core::nearest_neighbor::nearest_neighbor_base, {lsh,euclid_lsh,minhash},
+//          create_nearest_neighbor   (jubatus/server/server/nearest_neighbor_serv.cpp:106-108)
+//   jubatus_b200::device_table       <- core::storage::column_table (keys, versions, index on
+//          the host; columns on the device)          (nearest_neighbor_serv.cpp:99-100)
+//   jubatus_b200::mixable_versioned_table <- core::framework::mixable_versioned_table
+//          (driven by framework/mixer/push_mixer.cpp:410-472, linear_mixer.cpp:547-561,613-628)
+//   jubatus_b200::driver::nearest_neighbor <- core::driver::nearest_neighbor
+//          (nearest_neighbor_serv.cpp:125,134,144,153,162,171,177)
+//   jubatus_b200::nearest_neighbor_recommender <- core::recommender::nearest_neighbor_recommender
+//          (recommender_serv.cpp:111-116,136-144,170-200)
+//   jubatus_b200::light_lof          <- core::anomaly::light_lof
+//          (anomaly_serv.cpp:134-138,169,216,224,238)
+//   jubatus_b200::datum_to_fv_converter <- core::fv_converter (num / str rules of the shipped
+//          configs only, config/nearest_neighbor/lsh.json:2-15)
+//   jubatus_b200::nearest_neighbor_serv <- jubatus::server::nearest_neighbor_serv (RPC surface of
+//          nearest_neighbor.idl:6-27, config schema of nearest_neighbor_serv.cpp:45-54)
+// Errors are exceptions, as in the reference (JUBATUS_EXCEPTION); the RPC dispatcher turns them
+// into error strings (common/mprpc/rpc_server.cpp:41-53).
+#ifndef JUBANN_HOST_HPP_
+#define JUBANN_HOST_HPP_
+
+#include <dlfcn.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+
+#include <algorithm>
+#include <limits>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+#include <unordered_set>
+#include <utility>
+#include <vector>
+
+#include "jubann.h"
+#include "json_lite.hpp"
+
+namespace jubatus_b200 {
+
+// ---------------------------------------------------------------------------------------
+// exceptions (names follow jubatus::core::common::exception)
+// ---------------------------------------------------------------------------------------
+class jubatus_exception : public std::runtime_error {
+ public:
+  explicit jubatus_exception(const std::string& m) : std::runtime_error(m) {}
+};
+class config_exception : public jubatus_exception {
+ public:
+  explicit config_exception(const std::string& m) : jubatus_exception("config_exception: " + m) {}
+};
+class invalid_parameter : public jubatus_exception {
+ public:
+  explicit invalid_parameter(const std::string& m) : jubatus_exception("invalid_parameter: " + m) {}
+};
+class unsupported_method : public jubatus_exception {
+ public:
+  explicit unsupported_method(const std::string& m) : jubatus_exception("unsupported_method: " + m) {}
+};
+class converter_exception : public jubatus_exception {
+ public:
+  explicit converter_exception(const std::string& m) : jubatus_exception("converter_exception: " + m) {}
+};
+
+typedef std::vector<std::pair<std::string, float> > sfv_t;  // core::common::sfv_t
+
+// jubatus::client::common::datum wire struct (jubatus/client/common/datum.hpp:29-47)
+struct datum {
+  std::vector<std::pair<std::string, std::string> > string_values;
+  std::vector<std::pair<std::string, double> > num_values;
+  std::vector<std::pair<std::string, std::string> > binary_values;
+  datum& add_string(const std::string& k, const std::string& v) { string_values.push_back(std::make_pair(k, v)); return *this; }
+  datum& add_number(const std::string& k, double v) { num_values.push_back(std::make_pair(k, v)); return *this; }
+};
+
+// common::hash_util::calc_string_hash: 64-bit FNV-1, `char` sign-extends
+inline uint64_t calc_string_hash(const std::string& s) {
+  uint64_t h = 14695981039346656037ULL;
+  for (size_t i = 0; i < s.size(); ++i) {
+    h *= 1099511628211ULL;
+    h ^= static_cast<uint64_t>(static_cast<int64_t>(static_cast<signed char>(s[i])));
+  }
+  return h;
+}
+
+// ---------------------------------------------------------------------------------------
+// libjubann.so, loaded like an fv_converter plugin
+// (jubatus/server/fv_converter/dynamic_loader.cpp:44-94: absolute/relative path as given,
+//  else $JUBATUS_PLUGIN_PATH/<name>, else the configured plugin dir)
+// ---------------------------------------------------------------------------------------
+struct jubann_api {
+  void* dl;
+  const char* (*version)(void);
+  const char* (*last_error)(void);
+  int (*create)(const char*, uint32_t, int, uint32_t, uint32_t, jubann_t**);
+  int (*destroy)(jubann_t*);
+  int (*set_option)(jubann_t*, const char*, int64_t);
+  int (*clear)(jubann_t*);
+  int (*size)(jubann_t*, uint64_t*, uint64_t*);
+  int (*hash_csr)(jubann_t*, uint64_t, const uint64_t*, const uint32_t*, const uint64_t*, const float*, uint64_t*, float*);
+  int (*set_rows_csr)(jubann_t*, uint64_t, const uint64_t*, const uint64_t*, const uint32_t*, const uint64_t*, const float*);
+  int (*set_rows_sig)(jubann_t*, uint64_t, const uint64_t*, const uint64_t*, const float*);
+  int (*get_rows_sig)(jubann_t*, uint64_t, const uint64_t*, uint64_t*, float*);
+  int (*move_row)(jubann_t*, uint64_t, uint64_t);
+  int (*truncate)(jubann_t*, uint64_t);
+  int (*query_sig)(jubann_t*, uint64_t, const uint64_t*, const float*, uint32_t, uint32_t, uint64_t*, float*, uint32_t*);
+  int (*query_csr)(jubann_t*, uint64_t, const uint64_t*, const uint32_t*, const uint64_t*, const float*, uint32_t, uint32_t, uint64_t*, float*, uint32_t*);
+  int (*query_rows)(jubann_t*, uint64_t, const uint64_t*, uint32_t, uint32_t, uint64_t*, float*, uint32_t*);
+
+  static std::shared_ptr<jubann_api> load(const std::string& path_or_name = "libjubann.so") {
+    void* dl = 0;
+    std::string tried;
+    if (path_or_name.find('/') != std::string::npos) {
+      dl = ::dlopen(path_or_name.c_str(), RTLD_LAZY);
+      tried = path_or_name;
+    } else {
+      const char* dir = ::getenv("JUBATUS_PLUGIN_PATH");
+      if (dir) { tried = std::string(dir) + "/" + path_or_name; dl = ::dlopen(tried.c_str(), RTLD_LAZY); }
+      if (!dl) { tried = path_or_name; dl = ::dlopen(path_or_name.c_str(), RTLD_LAZY); }
+    }
+    if (!dl) {
+      const char* e = ::dlerror();
+      throw jubatus_exception("cannot load dynamic library: " + tried + ": " + (e ? e : "?"));
+    }
+    std::shared_ptr<jubann_api> a(new jubann_api);
+    a->dl = dl;
+#define JUBANN_SYM(field, name)                                                     \
+  *reinterpret_cast<void**>(&a->field) = ::dlsym(dl, name);                          \
+  if (!a->field) throw jubatus_exception(std::string("symbol not found: ") + name)
+    JUBANN_SYM(version, "version");
+    JUBANN_SYM(last_error, "jubann_last_error");
+    JUBANN_SYM(create, "jubann_create");
+    JUBANN_SYM(destroy, "jubann_destroy");
+    JUBANN_SYM(set_option, "jubann_set_option");
+    JUBANN_SYM(clear, "jubann_clear");
+    JUBANN_SYM(size, "jubann_size");
+    JUBANN_SYM(hash_csr, "jubann_hash_csr");
+    JUBANN_SYM(set_rows_csr, "jubann_set_rows_csr");
+    JUBANN_SYM(set_rows_sig, "jubann_set_rows_sig");
+    JUBANN_SYM(get_rows_sig, "jubann_get_rows_sig");
+    JUBANN_SYM(move_row, "jubann_move_row");
+    JUBANN_SYM(truncate, "jubann_truncate");
+    JUBANN_SYM(query_sig, "jubann_query_sig");
+    JUBANN_SYM(query_csr, "jubann_query_csr");
+    JUBANN_SYM(query_rows, "jubann_query_rows");
+#undef JUBANN_SYM
+    return a;
+  }
+  void check(int rc) const {
+    if (rc == 0) return;
+    const std::string msg = last_error();
+    if (rc == JUBANN_E_INVALID) {
+      if (msg.compare(0, 18, "unsupported_method") == 0) throw unsupported_method(msg.substr(20));
+      throw invalid_parameter(msg);
+    }
+    throw jubatus_exception(msg);
+  }
+};
+
+// ---------------------------------------------------------------------------------------
+// datum -> sfv (the `num` and `str` rules the shipped configs use)
+// ---------------------------------------------------------------------------------------
+class datum_to_fv_converter {
+ public:
+  struct rule { std::string key, type, sample_weight, global_weight; };
+  datum_to_fv_converter() : hash_max_size_(0) {}
+
+  static std::shared_ptr<datum_to_fv_converter> from_config(const json::ptr& conv) {
+    std::shared_ptr<datum_to_fv_converter> c(new datum_to_fv_converter);
+    if (!conv || conv->kind != json::value::OBJ) throw config_exception("converter must be an object");
+    static const char* const known[] = {"string_filter_types", "string_filter_rules", "num_filter_types",
+                                        "num_filter_rules", "string_types", "string_rules", "num_types", "num_rules",
+                                        "binary_types", "binary_rules", "combination_types", "combination_rules",
+                                        "hash_max_size"};
+    for (size_t i = 0; i < conv->obj.size(); ++i) {
+      bool ok = false;
+      for (size_t j = 0; j < sizeof(known) / sizeof(known[0]); ++j) ok = ok || conv->obj[i].first == known[j];
+      if (!ok) throw config_exception("unknown converter key: " + conv->obj[i].first);
+    }
+    json::ptr nr = conv->find("num_rules");
+    if (nr) for (size_t i = 0; i < nr->arr.size(); ++i) {
+      rule r; r.key = str(nr->arr[i], "key"); r.type = str(nr->arr[i], "type");
+      if (r.type != "num" && r.type != "log" && r.type != "str") throw converter_exception("unknown num feature type: " + r.type);
+      c->num_rules_.push_back(r);
+    }
+    json::ptr sr = conv->find("string_rules");
+    if (sr) for (size_t i = 0; i < sr->arr.size(); ++i) {
+      rule r; r.key = str(sr->arr[i], "key"); r.type = str(sr->arr[i], "type");
+      r.sample_weight = str(sr->arr[i], "sample_weight"); r.global_weight = str(sr->arr[i], "global_weight");
+      if (r.type != "str") throw converter_exception("string feature type not supported by this build: " + r.type);
+      if (r.sample_weight != "bin" && r.sample_weight != "tf") throw converter_exception("unknown sample_weight: " + r.sample_weight);
+      if (r.global_weight != "bin") throw converter_exception("global_weight not supported by this build: " + r.global_weight);
+      c->string_rules_.push_back(r);
+    }
+    json::ptr hm = conv->find("hash_max_size");
+    if (hm && hm->kind == json::value::NUM) c->hash_max_size_ = static_cast<uint64_t>(hm->num);
+    return c;
+  }
+
+  // strings first, then numbers, each in datum order and rule order (datum_to_fv_converter::convert)
+  void convert(const datum& d, sfv_t& out) const {
+    out.clear();
+    for (size_t r = 0; r < string_rules_.size(); ++r) {
+      std::map<std::string, float> tf;
+      std::vector<std::string> order;
+      for (size_t i = 0; i < d.string_values.size(); ++i) {
+        if (!match(string_rules_[r].key, d.string_values[i].first)) continue;
+        std::string f = d.string_values[i].first + "$" + d.string_values[i].second + "@" + string_rules_[r].type + "#" +
+                        string_rules_[r].sample_weight + "/" + string_rules_[r].global_weight;
+        if (tf.find(f) == tf.end()) order.push_back(f);
+        tf[f] += 1.0f;
+      }
+      for (size_t i = 0; i < order.size(); ++i)
+        out.push_back(std::make_pair(order[i], string_rules_[r].sample_weight == "bin" ? 1.0f : tf[order[i]]));
+    }
+    for (size_t r = 0; r < num_rules_.size(); ++r) {
+      for (size_t i = 0; i < d.num_values.size(); ++i) {
+        if (!match(num_rules_[r].key, d.num_values[i].first)) continue;
+        const std::string& t = num_rules_[r].type;
+        if (t == "num") out.push_back(std::make_pair(d.num_values[i].first + "@num", static_cast<float>(d.num_values[i].second)));
+        else if (t == "log") out.push_back(std::make_pair(d.num_values[i].first + "@log", static_cast<float>(log(std::max(1.0, d.num_values[i].second)))));
+        else {
+          char buf[64]; snprintf(buf, sizeof(buf), "%g", d.num_values[i].second);
+          out.push_back(std::make_pair(d.num_values[i].first + "$" + buf + "@str", 1.0f));
+        }
+      }
+    }
+    if (hash_max_size_) {
+      for (size_t i = 0; i < out.size(); ++i) out[i].first = std::to_string(calc_string_hash(out[i].first) % hash_max_size_);
+    }
+  }
+
+ private:
+  static std::string str(const json::ptr& o, const char* k) {
+    json::ptr v = o ? o->find(k) : json::ptr();
+    if (!v || v->kind != json::value::STR) throw config_exception(std::string("rule needs a string \"") + k + "\"");
+    return v->str;
+  }
+  static bool match(const std::string& pat, const std::string& key) {
+    if (pat == "*" || pat.empty()) return true;
+    if (pat[0] == '*') { std::string suf = pat.substr(1); return key.size() >= suf.size() && key.compare(key.size() - suf.size(), suf.size(), suf) == 0; }
+    if (pat[pat.size() - 1] == '*') return key.compare(0, pat.size() - 1, pat, 0, pat.size() - 1) == 0;
+    return pat == key;
+  }
+  std::vector<rule> num_rules_, string_rules_;
+  uint64_t hash_max_size_;
+};
+
+// ---------------------------------------------------------------------------------------
+// device_table: column_table with the columns on the GPU
+// ---------------------------------------------------------------------------------------
+typedef std::pair<std::string, uint64_t> version_t;       // (owner, clock)
+typedef std::map<std::string, uint64_t> version_clock;     // owner -> newest clock seen
+
+struct packed_row {                                        // what column_table::get_row serialises
+  std::string key;
+  version_t version;
+  std::vector<uint64_t> sig;
+  float norm;
+};
+
+class device_table {
+ public:
+  device_table(const std::shared_ptr<jubann_api>& api, const std::string& method, uint32_t hash_num, int device)
+      : api_(api), h_(0), hash_num_(hash_num), w64_((hash_num + 63) / 64), clock_(0) {
+    api_->check(api_->create(method.c_str(), hash_num, device, 0, 1, &h_));
+  }
+  ~device_table() { if (h_) api_->destroy(h_); }
+  device_table(const device_table&) = delete;
+  device_table& operator=(const device_table&) = delete;
+
+  jubann_t* handle() const { return h_; }
+  const jubann_api& api() const { return *api_; }
+  uint64_t size() const { return keys_.size(); }
+  uint32_t words() const { return w64_; }
+  void clear() {
+    api_->check(api_->clear(h_));
+    keys_.clear(); versions_.clear(); index_.clear(); clock_ = 0;
+  }
+  std::pair<bool, uint64_t> exact_match(const std::string& key) const {
+    std::unordered_map<std::string, uint64_t>::const_iterator it = index_.find(key);
+    if (it == index_.end()) return std::make_pair(false, 0);
+    return std::make_pair(true, it->second);
+  }
+  const std::string& get_key(uint64_t idx) const { return keys_.at(idx); }
+  const version_t& get_version(uint64_t idx) const { return versions_.at(idx); }
+  std::vector<std::string> get_all_row_ids() const { return keys_; }
+
+  // column_table::add for a batch: assigns row indices (append or in-place), stamps
+  // (owner, clock++) per row, returns the indices.
+  std::vector<uint64_t> assign(const std::vector<std::string>& keys, const std::string& owner) {
+    std::vector<uint64_t> idx(keys.size());
+    for (size_t i = 0; i < keys.size(); ++i) {
+      std::unordered_map<std::string, uint64_t>::iterator it = index_.find(keys[i]);
+      if (it == index_.end()) {
+        idx[i] = keys_.size();
+        keys_.push_back(keys[i]);
+        versions_.push_back(version_t(owner, clock_));
+        index_[keys[i]] = idx[i];
+      } else {
+        idx[i] = it->second;
+        versions_[idx[i]] = version_t(owner, clock_);
+      }
+      ++clock_;
+    }
+    return idx;
+  }
+  // column_table::delete_row: the last row moves into the hole
+  bool delete_row(const std::string& key) {
+    std::unordered_map<std::string, uint64_t>::iterator it = index_.find(key);
+    if (it == index_.end()) return false;
+    const uint64_t idx = it->second, last = keys_.size() - 1;
+    if (idx != last) {
+      api_->check(api_->move_row(h_, last, idx));
+      keys_[idx] = keys_[last];
+      versions_[idx] = versions_[last];
+      index_[keys_[idx]] = idx;
+    }
+    api_->check(api_->truncate(h_, last));
+    index_.erase(key);
+    keys_.pop_back(); versions_.pop_back();
+    return true;
+  }
+  packed_row get_row(uint64_t idx) const {
+    packed_row r;
+    r.key = keys_.at(idx); r.version = versions_[idx]; r.sig.resize(w64_); r.norm = 0;
+    api_->check(api_->get_rows_sig(h_, 1, &idx, r.sig.data(), &r.norm));
+    return r;
+  }
+  void get_rows(const std::vector<uint64_t>& idx, std::vector<packed_row>& out) const {
+    out.resize(idx.size());
+    if (idx.empty()) return;
+    std::vector<uint64_t> sigs(idx.size() * w64_);
+    std::vector<float> norms(idx.size());
+    api_->check(api_->get_rows_sig(h_, idx.size(), idx.data(), sigs.data(), norms.data()));
+    for (size_t i = 0; i < idx.size(); ++i) {
+      out[i].key = keys_.at(idx[i]); out[i].version = versions_[idx[i]];
+      out[i].sig.assign(sigs.begin() + i * w64_, sigs.begin() + (i + 1) * w64_);
+      out[i].norm = norms[i];
+    }
+  }
+  // column_table::set_row(packed) for a batch: upsert by key; an existing row is overwritten
+  // only if its clock <= the incoming clock; the local clock moves past every incoming clock.
+  void set_rows(const std::vector<packed_row>& rows, std::vector<version_t>* applied_versions) {
+    std::vector<uint64_t> idx, sigs;
+    std::vector<float> norms;
+    for (size_t i = 0; i < rows.size(); ++i) {
+      const packed_row& r = rows[i];
+      std::unordered_map<std::string, uint64_t>::iterator it = index_.find(r.key);
+      bool store = true;
+      uint64_t at;
+      if (it == index_.end()) {
+        at = keys_.size();
+        keys_.push_back(r.key); versions_.push_back(r.version); index_[r.key] = at;
+      } else {
+        at = it->second;
+        if (versions_[at].second <= r.version.second) versions_[at] = r.version; else store = false;
+      }
+      if (clock_ <= r.version.second) clock_ = r.version.second + 1;
+      if (applied_versions) applied_versions->push_back(r.version);
+      if (store) {
+        idx.push_back(at);
+        sigs.insert(sigs.end(), r.sig.begin(), r.sig.end());
+        norms.push_back(r.norm);
+      }
+    }
+    // rows are appended in increasing index order and an index may repeat (later wins), which
+    // is what one ordered batch gives
+    if (!idx.empty()) api_->check(api_->set_rows_sig(h_, idx.size(), idx.data(), sigs.data(), norms.data()));
+  }
+  uint64_t clock() const { return clock_; }
+
+ private:
+  std::shared_ptr<jubann_api> api_;
+  jubann_t* h_;
+  uint32_t hash_num_, w64_;
+  uint64_t clock_;
+  std::vector<std::string> keys_;
+  std::vector<version_t> versions_;
+  std::unordered_map<std::string, uint64_t> index_;
+};
+
+// ---------------------------------------------------------------------------------------
+// mixable_versioned_table
+// ---------------------------------------------------------------------------------------
+class mixable_versioned_table {
+ public:
+  explicit mixable_versioned_table(device_table* t) : table_(t) {}
+  void update_version(const version_t& v) {
+    version_clock::iterator it = vc_.find(v.first);
+    if (it == vc_.end()) vc_[v.first] = v.second;
+    else if (it->second < v.second) it->second = v.second;
+  }
+  version_clock get_argument() {
+    for (uint64_t i = 0; i < table_->size(); ++i) update_version(table_->get_version(i));
+    return vc_;
+  }
+  void pull(const version_clock& arg, std::vector<packed_row>& diff) const {
+    std::vector<uint64_t> idx;
+    for (uint64_t i = 0; i < table_->size(); ++i) {
+      const version_t& v = table_->get_version(i);
+      version_clock::const_iterator it = arg.find(v.first);
+      if (it == arg.end() || it->second < v.second) idx.push_back(i);
+    }
+    table_->get_rows(idx, diff);
+  }
+  void push(const std::vector<packed_row>& diff) {
+    std::vector<version_t> applied;
+    table_->set_rows(diff, &applied);
+    for (size_t i = 0; i < applied.size(); ++i) update_version(applied[i]);
+  }
+  // linear_mixable call shape
+  void get_diff(std::vector<packed_row>& diff) const { pull(vc_, diff); }
+  static void mix(const std::vector<packed_row>& lhs, std::vector<packed_row>& acc) { acc.insert(acc.end(), lhs.begin(), lhs.end()); }
+  bool put_diff(const std::vector<packed_row>& diff) { push(diff); return true; }
+
+ private:
+  device_table* table_;
+  version_clock vc_;
+};
+
+// ---------------------------------------------------------------------------------------
+// nearest_neighbor_base and the GPU engine
+// ---------------------------------------------------------------------------------------
+typedef std::vector<std::pair<std::string, float> > neighbor_result;
+
+class nearest_neighbor_base {
+ public:
+  virtual ~nearest_neighbor_base() {}
+  virtual std::string type() const = 0;
+  virtual void clear() = 0;
+  virtual void set_row(const std::string& id, const sfv_t& sfv) = 0;
+  virtual void neighbor_row(const sfv_t& query, neighbor_result& ids, uint64_t ret_num) const = 0;
+  virtual void neighbor_row(const std::string& query_id, neighbor_result& ids, uint64_t ret_num) const = 0;
+  virtual float calc_similarity(float distance) const { return 1 - distance; }
+  void similar_row(const sfv_t& query, neighbor_result& ids, uint64_t ret_num) const {
+    neighbor_row(query, ids, ret_num);
+    for (size_t i = 0; i < ids.size(); ++i) ids[i].second = calc_similarity(ids[i].second);
+  }
+  void similar_row(const std::string& query_id, neighbor_result& ids, uint64_t ret_num) const {
+    neighbor_row(query_id, ids, ret_num);
+    for (size_t i = 0; i < ids.size(); ++i) ids[i].second = calc_similarity(ids[i].second);
+  }
+  virtual void get_all_row_ids(std::vector<std::string>& ids) const = 0;
+};
+
+struct csr_batch {
+  std::vector<uint64_t> indptr;
+  std::vector<uint32_t> seed32;
+  std::vector<uint64_t> keyhash64;
+  std::vector<float> vals;
+  csr_batch() : indptr(1, 0) {}
+  void add(const sfv_t& sfv) {
+    for (size_t i = 0; i < sfv.size(); ++i) {
+      const uint64_t k = calc_string_hash(sfv[i].first);
+      keyhash64.push_back(k);
+      seed32.push_back(static_cast<uint32_t>(k));
+      vals.push_back(sfv[i].second);
+    }
+    indptr.push_back(vals.size());
+  }
+  uint64_t rows() const { return indptr.size() - 1; }
+};
+
+class gpu_nearest_neighbor : public nearest_neighbor_base {
+ public:
+  gpu_nearest_neighbor(const std::string& method, uint32_t hash_num, const std::shared_ptr<device_table>& table,
+                       const std::string& my_id)
+      : method_(method), hash_num_(hash_num), table_(table), my_id_(my_id), mixable_(table.get()) {}
+
+  std::string type() const { return method_; }
+  void clear() { table_->clear(); }
+  std::shared_ptr<device_table> get_table() { return table_; }
+  std::shared_ptr<const device_table> get_const_table() const { return table_; }
+  mixable_versioned_table* get_mixable() { return &mixable_; }
+  float calc_similarity(float d) const { return method_ == "euclid_lsh" ? -d : 1 - d; }
+
+  void set_row(const std::string& id, const sfv_t& sfv) {
+    std::vector<std::string> ids(1, id);
+    std::vector<sfv_t> rows(1, sfv);
+    set_rows(ids, rows);
+  }
+  // batched set_row: one device call for the whole batch (same result as calling set_row in order)
+  void set_rows(const std::vector<std::string>& ids, const std::vector<sfv_t>& sfvs) {
+    if (ids.empty()) return;
+    csr_batch b;
+    for (size_t i = 0; i < sfvs.size(); ++i) b.add(sfvs[i]);
+    std::vector<uint64_t> idx = table_->assign(ids, my_id_);
+    const jubann_api& a = table_->api();
+    a.check(a.set_rows_csr(table_->handle(), idx.size(), idx.data(), b.indptr.data(), b.seed32.data(),
+                           b.keyhash64.data(), b.vals.data()));
+  }
+  void neighbor_row(const sfv_t& query, neighbor_result& ids, uint64_t ret_num) const {
+    std::vector<sfv_t> q(1, query);
+    std::vector<neighbor_result> out;
+    neighbor_rows(q, out, ret_num, false);
+    ids.swap(out[0]);
+  }
+  void neighbor_row(const std::string& query_id, neighbor_result& ids, uint64_t ret_num) const {
+    std::vector<std::string> q(1, query_id);
+    std::vector<neighbor_result> out;
+    neighbor_rows_from_ids(q, out, ret_num, false);
+    ids.swap(out[0]);
+  }
+  // batched queries (what the server-side micro-batcher would call)
+  void neighbor_rows(const std::vector<sfv_t>& queries, std::vector<neighbor_result>& out, uint64_t ret_num,
+                     bool similar) const {
+    csr_batch b;
+    for (size_t i = 0; i < queries.size(); ++i) b.add(queries[i]);
+    const uint32_t k = clamp_k(ret_num);
+    std::vector<uint64_t> oi(queries.size() * std::max<uint32_t>(k, 1));
+    std::vector<float> os(oi.size());
+    std::vector<uint32_t> oc(queries.size());
+    const jubann_api& a = table_->api();
+    a.check(a.query_csr(table_->handle(), queries.size(), b.indptr.data(), b.seed32.data(), b.keyhash64.data(),
+                        b.vals.data(), k, similar ? JUBANN_SIMILAR : 0, oi.data(), os.data(), oc.data()));
+    emit(queries.size(), k, oi, os, oc, std::vector<bool>(), out);
+  }
+  // unknown ids give an empty result, not an error
+  void neighbor_rows_from_ids(const std::vector<std::string>& query_ids, std::vector<neighbor_result>& out,
+                              uint64_t ret_num, bool similar) const {
+    std::vector<uint64_t> rows;
+    std::vector<bool> known(query_ids.size());
+    for (size_t i = 0; i < query_ids.size(); ++i) {
+      std::pair<bool, uint64_t> hit = table_->exact_match(query_ids[i]);
+      known[i] = hit.first;
+      if (hit.first) rows.push_back(hit.second);
+    }
+    const uint32_t k = clamp_k(ret_num);
+    std::vector<uint64_t> oi(rows.size() * std::max<uint32_t>(k, 1));
+    std::vector<float> os(oi.size());
+    std::vector<uint32_t> oc(rows.size());
+    if (!rows.empty()) {
+      const jubann_api& a = table_->api();
+      a.check(a.query_rows(table_->handle(), rows.size(), rows.data(), k, similar ? JUBANN_SIMILAR : 0, oi.data(),
+                           os.data(), oc.data()));
+    }
+    emit(query_ids.size(), k, oi, os, oc, known, out);
+  }
+  void get_all_row_ids(std::vector<std::string>& ids) const { ids = table_->get_all_row_ids(); }
+  bool delete_row(const std::string& id) { return table_->delete_row(id); }
+
+ private:
+  uint32_t clamp_k(uint64_t ret_num) const {
+    // ret_num > rows returns all rows; no result list is longer than the table
+    return static_cast<uint32_t>(std::min<uint64_t>(ret_num, std::max<uint64_t>(table_->size(), 1)));
+  }
+  void emit(size_t nq, uint32_t k, const std::vector<uint64_t>& oi, const std::vector<float>& os,
+            const std::vector<uint32_t>& oc, const std::vector<bool>& known, std::vector<neighbor_result>& out) const {
+    out.assign(nq, neighbor_result());
+    size_t r = 0;
+    for (size_t q = 0; q < nq; ++q) {
+      if (!known.empty() && !known[q]) continue;
+      for (uint32_t j = 0; j < oc[r]; ++j)
+        out[q].push_back(std::make_pair(table_->get_key(oi[r * std::max<uint32_t>(k, 1) + j]), os[r * std::max<uint32_t>(k, 1) + j]));
+      ++r;
+    }
+  }
+  std::string method_;
+  uint32_t hash_num_;
+  std::shared_ptr<device_table> table_;
+  std::string my_id_;
+  mixable_versioned_table mixable_;
+};
+
+// {"hash_num": int [, "threads": int]}; unknown keys are rejected (config_cast_check)
+struct nn_parameter {
+  int32_t hash_num;
+  int32_t threads;
+  nn_parameter() : hash_num(64), threads(1) {}
+  static nn_parameter from_json(const json::ptr& p) {
+    nn_parameter c;
+    if (!p) return c;
+    if (p->kind != json::value::OBJ) throw config_exception("parameter must be an object");
+    for (size_t i = 0; i < p->obj.size(); ++i) {
+      const std::string& k = p->obj[i].first;
+      const json::ptr& v = p->obj[i].second;
+      if (k == "hash_num" || k == "threads") {
+        if (v->kind != json::value::NUM || !v->is_integer) throw config_exception("\"" + k + "\" must be an integer");
+        (k == "hash_num" ? c.hash_num : c.threads) = static_cast<int32_t>(v->num);
+      } else {
+        throw config_exception("unknown parameter key: " + k);
+      }
+    }
+    return c;
+  }
+};
+
+// core::nearest_neighbor::create_nearest_neighbor(method, param, table, my_id).  The device table
+// is created here because its geometry depends on (method, hash_num); `threads` is accepted and
+// has no effect (the GPU scan is always parallel).
+inline std::shared_ptr<gpu_nearest_neighbor> create_nearest_neighbor(const std::string& method, const json::ptr& param,
+                                                                     const std::shared_ptr<jubann_api>& api,
+                                                                     const std::string& my_id, int device = 0) {
+  if (method != "lsh" && method != "euclid_lsh" && method != "minhash") throw unsupported_method(method);
+  nn_parameter p = nn_parameter::from_json(param);
+  if (p.hash_num < 1) throw invalid_parameter("hash_num should be >= 1");
+  std::shared_ptr<device_table> table(new device_table(api, method, static_cast<uint32_t>(p.hash_num), device));
+  return std::shared_ptr<gpu_nearest_neighbor>(new gpu_nearest_neighbor(method, p.hash_num, table, my_id));
+}
+
+// ---------------------------------------------------------------------------------------
+// driver::nearest_neighbor and the server facade
+// ---------------------------------------------------------------------------------------
+namespace driver {
+class nearest_neighbor {
+ public:
+  nearest_neighbor(const std::shared_ptr<gpu_nearest_neighbor>& nn, const std::shared_ptr<datum_to_fv_converter>& conv)
+      : nn_(nn), converter_(conv) {}
+  std::shared_ptr<device_table> get_table() { return nn_->get_table(); }
+  gpu_nearest_neighbor* engine() { return nn_.get(); }
+  void set_row(const std::string& id, const datum& d) { sfv_t v; converter_->convert(d, v); nn_->set_row(id, v); }
+  void set_rows(const std::vector<std::string>& ids, const std::vector<datum>& ds) {
+    std::vector<sfv_t> v(ds.size());
+    for (size_t i = 0; i < ds.size(); ++i) converter_->convert(ds[i], v[i]);
+    nn_->set_rows(ids, v);
+  }
+  neighbor_result neighbor_row_from_id(const std::string& id, size_t size) { neighbor_result r; nn_->neighbor_row(id, r, size); return r; }
+  neighbor_result neighbor_row_from_datum(const datum& d, size_t size) { sfv_t v; converter_->convert(d, v); neighbor_result r; nn_->neighbor_row(v, r, size); return r; }
+  neighbor_result similar_row(const std::string& id, size_t n) { neighbor_result r; nn_->similar_row(id, r, n); return r; }
+  neighbor_result similar_row(const datum& d, size_t n) { sfv_t v; converter_->convert(d, v); neighbor_result r; nn_->similar_row(v, r, n); return r; }
+  std::vector<neighbor_result> neighbor_rows_from_datums(const std::vector<datum>& ds, size_t size, bool similar) {
+    std::vector<sfv_t> v(ds.size());
+    for (size_t i = 0; i < ds.size(); ++i) converter_->convert(ds[i], v[i]);
+    std::vector<neighbor_result> out;
+    nn_->neighbor_rows(v, out, size, similar);
+    return out;
+  }
+  std::vector<std::string> get_all_rows() { std::vector<std::string> r; nn_->get_all_row_ids(r); return r; }
+  void clear() { nn_->clear(); }
+  mixable_versioned_table* get_mixable() { return nn_->get_mixable(); }
+  const datum_to_fv_converter& converter() const { return *converter_; }
+ private:
+  std::shared_ptr<gpu_nearest_neighbor> nn_;
+  std::shared_ptr<datum_to_fv_converter> converter_;
+};
+}  // namespace driver
+
+// jubatus::server::nearest_neighbor_serv: config -> engine, RPC-named pass-throughs
+class nearest_neighbor_serv {
+ public:
+  explicit nearest_neighbor_serv(const std::shared_ptr<jubann_api>& api, const std::string& my_id = "", int device = 0)
+      : api_(api), my_id_(my_id), device_(device), update_row_cnt_(0) {}
+  void set_config(const std::string& config) {
+    json::ptr root;
+    try { root = json::parse(config); } catch (const json::parse_error& e) { throw config_exception(e.what()); }
+    if (root->kind != json::value::OBJ) throw config_exception("config must be an object");
+    for (size_t i = 0; i < root->obj.size(); ++i) {
+      const std::string& k = root->obj[i].first;
+      if (k != "method" && k != "parameter" && k != "converter") throw config_exception("unknown config key: " + k);
+    }
+    json::ptr m = root->find("method");
+    if (!m || m->kind != json::value::STR) throw config_exception("\"method\" is required");
+    json::ptr conv = root->find("converter");
+    if (!conv) throw config_exception("\"converter\" is required");
+    std::shared_ptr<datum_to_fv_converter> c = datum_to_fv_converter::from_config(conv);
+    std::shared_ptr<gpu_nearest_neighbor> nn = create_nearest_neighbor(m->str, root->find("parameter"), api_, my_id_, device_);
+    nearest_neighbor_.reset(new driver::nearest_neighbor(nn, c));
+    config_ = config;
+  }
+  std::string get_config() const { check_set_config(); return config_; }
+  bool clear() { check_set_config(); update_row_cnt_ = 0; nearest_neighbor_->clear(); return true; }
+  bool set_row(const std::string& id, const datum& d) { check_set_config(); ++update_row_cnt_; nearest_neighbor_->set_row(id, d); return true; }
+  neighbor_result neighbor_row_from_id(const std::string& id, size_t size) { check_set_config(); return nearest_neighbor_->neighbor_row_from_id(id, size); }
+  neighbor_result neighbor_row_from_datum(const datum& d, size_t size) { check_set_config(); return nearest_neighbor_->neighbor_row_from_datum(d, size); }
+  neighbor_result similar_row_from_id(const std::string& id, size_t n) { check_set_config(); return nearest_neighbor_->similar_row(id, n); }
+  neighbor_result similar_row_from_datum(const datum& d, size_t n) { check_set_config(); return nearest_neighbor_->similar_row(d, n); }
+  std::vector<std::string> get_all_rows() const { check_set_config(); return nearest_neighbor_->get_all_rows(); }
+  uint64_t update_row_cnt() const { return update_row_cnt_; }
+  driver::nearest_neighbor* get_driver() { check_set_config(); return nearest_neighbor_.get(); }
+ private:
+  void check_set_config() const { if (!nearest_neighbor_) throw config_exception("config is not set"); }
+  std::shared_ptr<jubann_api> api_;
+  std::string my_id_;
+  int device_;
+  std::string config_;
+  uint64_t update_row_cnt_;
+  std::shared_ptr<driver::nearest_neighbor> nearest_neighbor_;
+};
+
+// ---------------------------------------------------------------------------------------
+// recommender::nearest_neighbor_recommender
+// ---------------------------------------------------------------------------------------
+class nearest_neighbor_recommender {
+ public:
+  explicit nearest_neighbor_recommender(const std::shared_ptr<gpu_nearest_neighbor>& nn) : nn_(nn) {}
+  void clear() { orig_.clear(); nn_->clear(); }
+  // update_row merges the diff into the stored original row, then re-hashes the FULL row
+  void update_row(const std::string& id, const sfv_t& diff) {
+    std::vector<std::pair<std::string, float> >& row = orig_[id];
+    for (size_t i = 0; i < diff.size(); ++i) {
+      bool found = false;
+      for (size_t j = 0; j < row.size(); ++j) if (row[j].first == diff[i].first) { row[j].second = diff[i].second; found = true; break; }
+      if (!found) row.push_back(diff[i]);
+    }
+    nn_->set_row(id, row);
+  }
+  void clear_row(const std::string& id) { orig_.erase(id); nn_->delete_row(id); }
+  void similar_row(const sfv_t& q, neighbor_result& ids, size_t n) const { nn_->similar_row(q, ids, n); }
+  void neighbor_row(const sfv_t& q, neighbor_result& ids, size_t n) const { nn_->neighbor_row(q, ids, n); }
+  // *_from_id re-hashes the stored original row (not the stored signature); unknown id -> empty
+  void similar_row(const std::string& id, neighbor_result& ids, size_t n) const {
+    std::unordered_map<std::string, sfv_t>::const_iterator it = orig_.find(id);
+    if (it == orig_.end()) { ids.clear(); return; }
+    nn_->similar_row(it->second, ids, n);
+  }
+  void neighbor_row(const std::string& id, neighbor_result& ids, size_t n) const {
+    std::unordered_map<std::string, sfv_t>::const_iterator it = orig_.find(id);
+    if (it == orig_.end()) { ids.clear(); return; }
+    nn_->neighbor_row(it->second, ids, n);
+  }
+  void decode_row(const std::string& id, sfv_t& out) const {
+    std::unordered_map<std::string, sfv_t>::const_iterator it = orig_.find(id);
+    if (it == orig_.end()) out.clear(); else out = it->second;
+  }
+  void get_all_row_ids(std::vector<std::string>& ids) const { nn_->get_all_row_ids(ids); }
+  std::string type() const { return "nearest_neighbor_recommender:" + nn_->type(); }
+ private:
+  std::shared_ptr<gpu_nearest_neighbor> nn_;
+  std::unordered_map<std::string, sfv_t> orig_;
+};
+
+// ---------------------------------------------------------------------------------------
+// anomaly::light_lof -- the 1 + reverse_nearest_neighbor_num re-queries of one add() go to the
+// device as ONE batched call (they share the streaming passes)
+// ---------------------------------------------------------------------------------------
+class light_lof {
+ public:
+  light_lof(const std::shared_ptr<gpu_nearest_neighbor>& nn, int nearest_neighbor_num, int reverse_nearest_neighbor_num)
+      : nn_(nn), nn_num_(nearest_neighbor_num), rnn_num_(reverse_nearest_neighbor_num) {
+    if (nn_num_ < 2) throw invalid_parameter("nearest_neighbor_num should be >= 2");
+    if (rnn_num_ < nn_num_) throw invalid_parameter("reverse_nearest_neighbor_num should be >= nearest_neighbor_num");
+  }
+  void clear() { nn_->clear(); kdist_.clear(); lrd_.clear(); }
+  static float calculate_lof(float lrd, const std::vector<float>& neighbor_lrds) {
+    if (neighbor_lrds.empty()) return lrd == 0 ? 1.0f : std::numeric_limits<float>::infinity();
+    float sum = 0.0f;
+    for (size_t i = 0; i < neighbor_lrds.size(); ++i) sum += neighbor_lrds[i];
+    if (std::isinf(sum) && std::isinf(lrd)) return 1.0f;
+    return sum / (neighbor_lrds.size() * lrd);
+  }
+  float calc_anomaly_score(const sfv_t& query) const {
+    neighbor_result nb;
+    nn_->neighbor_row(query, nb, nn_num_);
+    return score_from_neighbors(nb);
+  }
+  float calc_anomaly_score(const std::string& id) const {
+    neighbor_result nb;
+    nn_->neighbor_row(id, nb, nn_num_);
+    return score_from_neighbors(nb);
+  }
+  bool set_row(const std::string& id, const sfv_t& sfv) {
+    std::vector<std::string> order;
+    std::unordered_set<std::string> seen;
+    if (nn_->get_table()->exact_match(id).first) collect_neighbors(id, order, seen);
+    nn_->set_row(id, sfv);
+    collect_neighbors(id, order, seen);
+    kdist_[id] = -1.0f; lrd_[id] = -1.0f;
+    if (seen.insert(id).second) order.push_back(id);
+    update_entries(order);
+    return true;
+  }
+  void update_entries(const std::vector<std::string>& ids) {
+    std::vector<neighbor_result> nn;
+    nn_->neighbor_rows_from_ids(ids, nn, nn_num_, false);   // one device call for every id
+    for (size_t i = 0; i < ids.size(); ++i) {
+      if (kdist_.find(ids[i]) == kdist_.end()) throw jubatus_exception("row not found in lof table: " + ids[i]);
+      kdist_[ids[i]] = nn[i].empty() ? 0.0f : nn[i].back().second;
+    }
+    for (size_t i = 0; i < ids.size(); ++i) {
+      const size_t length = std::min<size_t>(nn[i].size(), nn_num_);
+      float sum_reach = 0.0f;
+      for (size_t j = 0; j < length; ++j) {
+        std::unordered_map<std::string, float>::const_iterator it = kdist_.find(nn[i][j].first);
+        sum_reach += std::max(nn[i][j].second, it == kdist_.end() ? 0.0f : it->second);
+      }
+      lrd_[ids[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
+    }
+  }
+  bool get_row_parameter(const std::string& id, float* kdist, float* lrd) const {
+    std::unordered_map<std::string, float>::const_iterator a = kdist_.find(id), b = lrd_.find(id);
+    if (a == kdist_.end() || b == lrd_.end()) return false;
+    *kdist = a->second; *lrd = b->second;
+    return true;
+  }
+  gpu_nearest_neighbor* engine() { return nn_.get(); }
+ private:
+  void collect_neighbors(const std::string& id, std::vector<std::string>& order, std::unordered_set<std::string>& seen) const {
+    neighbor_result nb;
+    nn_->neighbor_row(id, nb, rnn_num_);
+    for (size_t i = 0; i < nb.size(); ++i) if (seen.insert(nb[i].first).second) order.push_back(nb[i].first);
+  }
+  float score_from_neighbors(const neighbor_result& nb) const {
+    std::vector<float> lrds;
+    float lrd;
+    if (nb.empty()) {
+      lrd = std::numeric_limits<float>::infinity();
+    } else {
+      lrds.resize(nb.size());
+      float sum_reach = 0.0f;
+      for (size_t i = 0; i < nb.size(); ++i) {
+        std::unordered_map<std::string, float>::const_iterator a = kdist_.find(nb[i].first), b = lrd_.find(nb[i].first);
+        if (a == kdist_.end() || b == lrd_.end()) throw jubatus_exception("row not found in lof table: " + nb[i].first);
+        lrds[i] = b->second;
+        sum_reach += std::max(nb[i].second, a->second);
+      }
+      lrd = sum_reach == 0 ? std::numeric_limits<float>::infinity() : nb.size() / sum_reach;
+    }
+    return calculate_lof(lrd, lrds);
+  }
+  std::shared_ptr<gpu_nearest_neighbor> nn_;
+  int nn_num_, rnn_num_;
+  std::unordered_map<std::string, float> kdist_, lrd_;
+};
+
+}  // namespace jubatus_b200
+#endif  // JUBANN_HOST_HPP_

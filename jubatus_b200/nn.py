@@ -1,0 +1,306 @@
+"""Reference-shaped host API over the C++ adapter (jubatus_b200/host/, libjubann_host.so).
+
+Class and method names follow the RPC surface of the three servers that reach the
+nearest-neighbor engines:
+
+* :class:`NearestNeighbor` -- jubanearest_neighbor (jubatus/server/server/nearest_neighbor.idl:6-27)
+* :class:`Recommender`     -- jubarecommender with method nearest_neighbor_recommender
+  (recommender.idl:22-57; only the calls that reach the engine)
+* :class:`Anomaly`         -- jubaanomaly with method light_lof (anomaly.idl:22-51)
+
+Each takes the server's JSON config string (config/*/*.json).  All arithmetic happens in
+libjubann.so on the GPU; this module only marshals strings.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import capi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_vp = ctypes.c_void_p
+_lib = None
+
+
+class JubatusError(RuntimeError):
+    """A jubatus_exception from the host layer (config_exception, invalid_parameter, ...)."""
+
+
+def host_lib_path():
+    return os.path.join(_HERE, "libjubann_host.so")
+
+
+def _load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = host_lib_path()
+    if not os.path.exists(path):
+        raise ImportError("%s not found: run __graft_entry__.build()" % path)
+    lib = ctypes.CDLL(path)
+    lib.jubahost_last_error.restype = ctypes.c_char_p
+    lib.jubahost_create.restype = _vp
+    lib.jubahost_create.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int]
+    lib.jubahost_destroy.argtypes = [_vp]
+    lib.jubahost_convert.argtypes = [ctypes.c_char_p, _vp, _vp, ctypes.c_uint64, _vp, _vp, ctypes.c_uint64, _vp,
+                                     ctypes.c_uint64, _vp, ctypes.c_uint64, _vp]
+    lib.jubahost_clear.argtypes = [_vp]
+    lib.jubahost_size.restype = ctypes.c_uint64
+    lib.jubahost_size.argtypes = [_vp]
+    lib.jubahost_set_row.argtypes = [_vp, ctypes.c_char_p, _vp, _vp, ctypes.c_uint64, _vp, _vp, ctypes.c_uint64]
+    lib.jubahost_set_rows.argtypes = [_vp, ctypes.c_uint64, _vp, _vp, _vp, _vp]
+    lib.jubahost_delete_row.argtypes = [_vp, ctypes.c_char_p]
+    lib.jubahost_query_datum.argtypes = [_vp, _vp, _vp, ctypes.c_uint64, _vp, _vp, ctypes.c_uint64, ctypes.c_uint64,
+                                         ctypes.c_int, _vp, ctypes.c_uint64, _vp, ctypes.c_uint64, _vp]
+    lib.jubahost_query_id.argtypes = [_vp, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int, _vp, ctypes.c_uint64, _vp,
+                                      ctypes.c_uint64, _vp]
+    lib.jubahost_get_all_rows.argtypes = [_vp, _vp, ctypes.c_uint64, _vp]
+    lib.jubahost_get_signature.argtypes = [_vp, ctypes.c_char_p, _vp, _vp]
+    lib.jubahost_mix_pair.argtypes = [_vp, _vp]
+    lib.jubahost_calc_score_datum.argtypes = [_vp, _vp, _vp, ctypes.c_uint64, _vp]
+    lib.jubahost_calc_score_id.argtypes = [_vp, ctypes.c_char_p, _vp]
+    lib.jubahost_lof_params.argtypes = [_vp, ctypes.c_char_p, _vp, _vp]
+    _lib = lib
+    return lib
+
+
+def _raise():
+    raise JubatusError(_load().jubahost_last_error().decode("utf-8", "replace"))
+
+
+class Datum(object):
+    """jubatus::client::common::datum (jubatus/client/common/datum.hpp:29-47)."""
+
+    def __init__(self, values=None):
+        self.string_values = []
+        self.num_values = []
+        if values:
+            for k, v in (values.items() if isinstance(values, dict) else values):
+                if isinstance(v, str):
+                    self.add_string(k, v)
+                else:
+                    self.add_number(k, v)
+
+    def add_string(self, key, value):
+        self.string_values.append((key, value))
+        return self
+
+    def add_number(self, key, value):
+        self.num_values.append((key, float(value)))
+        return self
+
+
+def _cstrs(items):
+    arr = (ctypes.c_char_p * max(len(items), 1))()
+    for i, s in enumerate(items):
+        arr[i] = s.encode("utf-8") if isinstance(s, str) else s
+    return arr
+
+
+def _datum_args(d):
+    sk = _cstrs([k for k, _ in d.string_values])
+    sv = _cstrs([v for _, v in d.string_values])
+    nk = _cstrs([k for k, _ in d.num_values])
+    nv = np.array([v for _, v in d.num_values] or [0.0], dtype=np.float64)
+    return sk, sv, len(d.string_values), nk, nv, len(d.num_values)
+
+
+def convert(converter_json, d):
+    """datum -> sfv with the converter section of a config (no device needed)."""
+    lib = _load()
+    sk, sv, ns, nk, nv, nn = _datum_args(d)
+    cap = 1 << 16
+    buf = ctypes.create_string_buffer(cap)
+    vals = np.zeros(4096, dtype=np.float32)
+    count = ctypes.c_uint64()
+    rc = lib.jubahost_convert(converter_json.encode(), sk, sv, ns, nk, nv.ctypes.data_as(_vp), nn, buf, cap,
+                              vals.ctypes.data_as(_vp), len(vals), ctypes.byref(count))
+    if rc:
+        _raise()
+    keys = buf.value.decode().split("\n")[:count.value]
+    return [(keys[i], float(vals[i])) for i in range(count.value)]
+
+
+class _HostHandle(object):
+    kind = None
+
+    def __init__(self, config, my_id="", device=0):
+        self._lib = _load()
+        capi.load_library()   # fail loudly when the CUDA library is missing
+        self._h = self._lib.jubahost_create(self.kind.encode(), config.encode(), capi.lib_path().encode(),
+                                            my_id.encode(), int(device))
+        if not self._h:
+            _raise()
+        self._config = config
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.jubahost_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def get_config(self):
+        return self._config
+
+    def clear(self):
+        if self._lib.jubahost_clear(self._h):
+            _raise()
+        return True
+
+    def size(self):
+        return int(self._lib.jubahost_size(self._h))
+
+    def get_all_rows(self):
+        cap = 64 * (self.size() + 1) + 64
+        buf = ctypes.create_string_buffer(cap)
+        count = ctypes.c_uint64()
+        if self._lib.jubahost_get_all_rows(self._h, buf, cap, ctypes.byref(count)):
+            _raise()
+        return buf.value.decode().split("\n")[:count.value]
+
+    def _set_row(self, row_id, d):
+        sk, sv, ns, nk, nv, nn = _datum_args(d)
+        if self._lib.jubahost_set_row(self._h, row_id.encode(), sk, sv, ns, nk, nv.ctypes.data_as(_vp), nn):
+            _raise()
+        return True
+
+    def _query_datum(self, d, k, similar):
+        sk, sv, ns, nk, nv, nn = _datum_args(d)
+        cap = 64 * (k + 1) + 64
+        buf = ctypes.create_string_buffer(cap)
+        scores = np.zeros(max(k, 1), dtype=np.float32)
+        count = ctypes.c_uint64()
+        rc = self._lib.jubahost_query_datum(self._h, sk, sv, ns, nk, nv.ctypes.data_as(_vp), nn, k, similar, buf, cap,
+                                            scores.ctypes.data_as(_vp), len(scores), ctypes.byref(count))
+        if rc:
+            _raise()
+        ids = buf.value.decode().split("\n")[:count.value]
+        return [(ids[i], float(scores[i])) for i in range(count.value)]
+
+    def _query_id(self, row_id, k, similar):
+        cap = 64 * (k + 1) + 64
+        buf = ctypes.create_string_buffer(cap)
+        scores = np.zeros(max(k, 1), dtype=np.float32)
+        count = ctypes.c_uint64()
+        rc = self._lib.jubahost_query_id(self._h, row_id.encode(), k, similar, buf, cap, scores.ctypes.data_as(_vp),
+                                         len(scores), ctypes.byref(count))
+        if rc:
+            _raise()
+        ids = buf.value.decode().split("\n")[:count.value]
+        return [(ids[i], float(scores[i])) for i in range(count.value)]
+
+    def get_signature(self, row_id, hash_num):
+        sig = np.zeros((hash_num + 63) // 64, dtype=np.uint64)
+        norm = ctypes.c_float()
+        rc = self._lib.jubahost_get_signature(self._h, row_id.encode(), sig.ctypes.data_as(_vp), ctypes.byref(norm))
+        if rc < 0:
+            _raise()
+        return None if rc else (sig, norm.value)
+
+    def mix_with(self, other):
+        """One push_mixer round between two in-process servers (push_mixer.cpp:335-408)."""
+        if self._lib.jubahost_mix_pair(self._h, other._h):
+            _raise()
+
+
+class NearestNeighbor(_HostHandle):
+    kind = "nearest_neighbor"
+
+    def set_row(self, row_id, d):
+        return self._set_row(row_id, d)
+
+    def set_rows(self, ids, datums):
+        """Batched set_row (number-valued datums): one device call."""
+        offs = np.zeros(len(ids) + 1, dtype=np.uint64)
+        keys, vals = [], []
+        for i, d in enumerate(datums):
+            assert not d.string_values
+            keys.extend(k for k, _ in d.num_values)
+            vals.extend(v for _, v in d.num_values)
+            offs[i + 1] = len(keys)
+        vals = np.array(vals or [0.0], dtype=np.float64)
+        rc = self._lib.jubahost_set_rows(self._h, len(ids), _cstrs(ids), offs.ctypes.data_as(_vp), _cstrs(keys),
+                                         vals.ctypes.data_as(_vp))
+        if rc:
+            _raise()
+        return True
+
+    def neighbor_row_from_id(self, row_id, size):
+        return self._query_id(row_id, size, 0)
+
+    def neighbor_row_from_datum(self, d, size):
+        return self._query_datum(d, size, 0)
+
+    def similar_row_from_id(self, row_id, ret_num):
+        return self._query_id(row_id, ret_num, 1)
+
+    def similar_row_from_datum(self, d, ret_num):
+        return self._query_datum(d, ret_num, 1)
+
+    def delete_row(self, row_id):
+        """column_table::delete_row (what an unlearner calls)."""
+        rc = self._lib.jubahost_delete_row(self._h, row_id.encode())
+        if rc < 0:
+            _raise()
+        return rc == 0
+
+
+class Recommender(_HostHandle):
+    kind = "recommender"
+
+    def update_row(self, row_id, d):
+        return self._set_row(row_id, d)
+
+    def clear_row(self, row_id):
+        if self._lib.jubahost_delete_row(self._h, row_id.encode()) < 0:
+            _raise()
+        return True
+
+    def similar_row_from_id(self, row_id, size):
+        return self._query_id(row_id, size, 1)
+
+    def similar_row_from_datum(self, d, size):
+        return self._query_datum(d, size, 1)
+
+
+class Anomaly(_HostHandle):
+    kind = "anomaly"
+
+    def __init__(self, config, my_id="", device=0):
+        super().__init__(config, my_id, device)
+        self._next_id = 0   # global_id_generator_standalone starts at 0 (common/global_id_generator_standalone.cpp:53-57)
+
+    def add(self, d):
+        row_id = str(self._next_id)
+        self._next_id += 1
+        self._set_row(row_id, d)
+        return row_id, self.calc_score_id(row_id)
+
+    def update(self, row_id, d):
+        self._set_row(row_id, d)
+        return self.calc_score_id(row_id)
+
+    def calc_score(self, d):
+        _, _, _, nk, nv, nn = _datum_args(d)
+        s = ctypes.c_float()
+        if self._lib.jubahost_calc_score_datum(self._h, nk, nv.ctypes.data_as(_vp), nn, ctypes.byref(s)):
+            _raise()
+        return s.value
+
+    def calc_score_id(self, row_id):
+        s = ctypes.c_float()
+        if self._lib.jubahost_calc_score_id(self._h, row_id.encode(), ctypes.byref(s)):
+            _raise()
+        return s.value
+
+    def lof_params(self, row_id):
+        kd, lrd = ctypes.c_float(), ctypes.c_float()
+        if self._lib.jubahost_lof_params(self._h, row_id.encode(), ctypes.byref(kd), ctypes.byref(lrd)):
+            return None
+        return kd.value, lrd.value

@@ -1,0 +1,44 @@
+"""Host-layer logic that needs no GPU: datum -> sfv conversion and config validation."""
+import json
+
+import pytest
+
+from jubatus_b200 import nn
+
+CONVERTER = {
+    "string_filter_types": {}, "string_filter_rules": [], "num_filter_types": {}, "num_filter_rules": [],
+    "string_types": {}, "string_rules": [{"key": "*", "type": "str", "sample_weight": "bin", "global_weight": "bin"}],
+    "num_types": {}, "num_rules": [{"key": "*", "type": "num"}],
+}
+
+
+def test_num_and_str_rules():
+    d = nn.Datum().add_number("age", 31).add_string("name", "juba").add_number("w", -0.5)
+    sfv = nn.convert(json.dumps(CONVERTER), d)
+    # strings first, then numbers, in datum order (datum_to_fv_converter::convert)
+    assert sfv == [("name$juba@str#bin/bin", 1.0), ("age@num", 31.0), ("w@num", -0.5)]
+
+
+def test_key_matchers_and_log():
+    conv = dict(CONVERTER, num_rules=[{"key": "a*", "type": "num"}, {"key": "*z", "type": "log"}], string_rules=[])
+    d = nn.Datum().add_number("ab", 2).add_number("xz", 100).add_number("q", 1)
+    sfv = nn.convert(json.dumps(conv), d)
+    assert sfv[0] == ("ab@num", 2.0)
+    assert sfv[1][0] == "xz@log" and abs(sfv[1][1] - 4.60517) < 1e-5
+    assert len(sfv) == 2
+
+
+def test_converter_errors():
+    with pytest.raises(nn.JubatusError):
+        nn.convert("{not json", nn.Datum())
+    with pytest.raises(nn.JubatusError):
+        nn.convert(json.dumps(dict(CONVERTER, bogus=1)), nn.Datum())
+    with pytest.raises(nn.JubatusError):
+        nn.convert(json.dumps(dict(CONVERTER, num_rules=[{"key": "*", "type": "nope"}])), nn.Datum())
+
+
+def test_shipped_config_schema_is_accepted_by_the_parser():
+    # the reference's example configs (config/nearest_neighbor/*.json) share this shape
+    cfg = {"method": "lsh", "parameter": {"hash_num": 64}, "converter": CONVERTER}
+    sfv = nn.convert(json.dumps(cfg["converter"]), nn.Datum().add_number("key", 1.0))
+    assert sfv == [("key@num", 1.0)]

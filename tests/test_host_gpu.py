@@ -1,0 +1,168 @@
+"""The reference-shaped host API (config JSON, string ids, datums) on the GPU against the
+oracle engine: these read like client_test/nearest_neighbor_test.cpp, plus the numeric
+assertions the reference's own tests lack."""
+import json
+
+import numpy as np
+import pytest
+
+from jubatus_b200 import nn, workload as w
+
+pytestmark = pytest.mark.gpu
+
+CONVERTER = {
+    "string_filter_types": {}, "string_filter_rules": [], "num_filter_types": {}, "num_filter_rules": [],
+    "string_types": {}, "string_rules": [{"key": "*", "type": "str", "sample_weight": "bin", "global_weight": "bin"}],
+    "num_types": {}, "num_rules": [{"key": "*", "type": "num"}],
+}
+
+
+def config(method, hash_num, **extra):
+    c = {"method": method, "parameter": dict({"hash_num": hash_num}, **extra), "converter": CONVERTER}
+    return json.dumps(c)
+
+
+def datum_of(ids, vals):
+    d = nn.Datum()
+    for f, v in zip(ids, vals):
+        d.add_number(str(int(f)), float(v))
+    return d
+
+
+def sfv_of(ids, vals):
+    return [("%d@num" % int(f), float(v)) for f, v in zip(ids, vals)]
+
+
+def same(got, want, rel=0.0):
+    assert [g[0] for g in got] == [x[0] for x in want]
+    for g, x in zip(got, want):
+        assert g[1] == x[1] or abs(g[1] - x[1]) <= rel * abs(x[1]), (g, x)
+
+
+@pytest.mark.parametrize("method,hash_num", [("lsh", 64), ("euclid_lsh", 64), ("minhash", 64), ("lsh", 512)])
+def test_rpc_surface_matches_oracle(oracle, method, hash_num):
+    n, k = 300, 10
+    ids, vals = w.synth_rows(w.MASTER_SEED, 0, n, nnz=20, nfeat_log2=10)
+    cli = nn.NearestNeighbor(config(method, hash_num))
+    ora = oracle.OracleNN(method, hash_num)
+    for r in range(n):
+        assert cli.set_row("row%d" % r, datum_of(ids[r], vals[r]))
+        ora.set_row("row%d" % r, sfv_of(ids[r], vals[r]))
+    assert cli.size() == n and cli.get_all_rows() == ora.get_all_rows()
+    # stored signatures: bit agreement (minhash: logf ulp differences may flip a near-tie)
+    diff = sum(bin(int(a ^ b)).count("1") for r in range(0, n, 7)
+               for a, b in zip(cli.get_signature("row%d" % r, hash_num)[0], ora.get_signature("row%d" % r)[0]))
+    assert diff <= 1
+    if diff == 0:
+        for r in (0, 17, 299):
+            same(cli.neighbor_row_from_id("row%d" % r, k), ora.neighbor_row_from_id("row%d" % r, k), 1e-5)
+            same(cli.similar_row_from_id("row%d" % r, k), ora.similar_row_from_id("row%d" % r, k), 1e-5)
+            q = datum_of(ids[r][:15], vals[r][:15])
+            qs = sfv_of(ids[r][:15], vals[r][:15])
+            same(cli.neighbor_row_from_datum(q, k), ora.neighbor_row_from_datum(qs, k), 1e-5)
+            same(cli.similar_row_from_datum(q, k), ora.similar_row_from_datum(qs, k), 1e-5)
+    assert cli.neighbor_row_from_id("no such id", 3) == []
+    assert cli.clear() and cli.size() == 0 and cli.get_all_rows() == []
+
+
+def test_client_test_sequence():
+    # client_test/nearest_neighbor_test.cpp:57-98, with results checked
+    cli = nn.NearestNeighbor(config("lsh", 64))
+    d = nn.Datum().add_number("key", 1.0)
+    assert cli.set_row("id", d)
+    assert cli.set_row("neighbor_row_from_id", d)
+    assert cli.neighbor_row_from_id("neighbor_row_from_id", 1) == [("id", 0.0)]
+    assert cli.neighbor_row_from_datum(d, 5) == [("id", 0.0), ("neighbor_row_from_id", 0.0)]
+    assert cli.similar_row_from_id("id", 1) == [("id", 1.0)]
+    assert cli.similar_row_from_datum(d, 1) == [("id", 1.0)]
+    assert json.loads(cli.get_config())["method"] == "lsh"
+    assert cli.clear()
+
+
+def test_update_delete_and_batched_set_rows(oracle):
+    hash_num, n, k = 128, 200, 20
+    ids, vals = w.synth_rows(w.MASTER_SEED, 500, n, nnz=10, nfeat_log2=8)
+    cli = nn.NearestNeighbor(config("lsh", hash_num))
+    ora = oracle.OracleNN("lsh", hash_num)
+    cli.set_rows(["r%d" % r for r in range(n)], [datum_of(ids[r], vals[r]) for r in range(n)])
+    for r in range(n):
+        ora.set_row("r%d" % r, sfv_of(ids[r], vals[r]))
+    cli.set_row("r5", datum_of(ids[77], vals[77])); ora.set_row("r5", sfv_of(ids[77], vals[77]))   # update in place
+    for victim in ("r10", "r199", "r0"):
+        assert cli.delete_row(victim) and ora.delete_row(victim)                                       # swap-delete
+    assert not cli.delete_row("r10")
+    assert cli.get_all_rows() == ora.get_all_rows()
+    for r in ("r5", "r77", "r198"):
+        same(cli.neighbor_row_from_id(r, k), ora.neighbor_row_from_id(r, k))
+
+
+def test_config_errors():
+    with pytest.raises(nn.JubatusError, match="unsupported_method"):
+        nn.NearestNeighbor(config("nope", 64))
+    with pytest.raises(nn.JubatusError, match="hash_num"):
+        nn.NearestNeighbor(config("lsh", 0))
+    with pytest.raises(nn.JubatusError, match="unknown parameter key"):
+        nn.NearestNeighbor(config("lsh", 64, bogus=1))
+    with pytest.raises(nn.JubatusError):
+        nn.NearestNeighbor("{")
+    nn.NearestNeighbor(config("lsh", 64, threads=2)).close()       # lsh_multithread.json is accepted
+
+
+def test_mix_between_replicas(oracle):
+    hash_num = 64
+    ids, vals = w.synth_rows(w.MASTER_SEED, 900, 40, nnz=10, nfeat_log2=8)
+    a, b = nn.NearestNeighbor(config("lsh", hash_num), my_id="A"), nn.NearestNeighbor(config("lsh", hash_num), my_id="B")
+    oa, ob = oracle.OracleNN("lsh", hash_num, my_id="A"), oracle.OracleNN("lsh", hash_num, my_id="B")
+    for r in range(40):
+        tgt, otgt = (a, oa) if r % 2 == 0 else (b, ob)
+        tgt.set_row("r%d" % r, datum_of(ids[r], vals[r])); otgt.set_row("r%d" % r, sfv_of(ids[r], vals[r]))
+    a.mix_with(b); oa.mix_with(ob)
+    assert a.get_all_rows() == oa.get_all_rows() and b.get_all_rows() == ob.get_all_rows()
+    b.set_row("r0", datum_of(ids[1], vals[1])); ob.set_row("r0", sfv_of(ids[1], vals[1]))   # newer version on B
+    a.mix_with(b); oa.mix_with(ob)
+    for r in ("r0", "r1", "r39"):
+        assert np.array_equal(a.get_signature(r, hash_num)[0], oa.get_signature(r)[0])
+        same(a.neighbor_row_from_id(r, 10), oa.neighbor_row_from_id(r, 10))
+        same(b.neighbor_row_from_id(r, 10), ob.neighbor_row_from_id(r, 10))
+
+
+def test_recommender_nearest_neighbor_recommender(oracle):
+    cfg = json.dumps({"method": "nearest_neighbor_recommender", "converter": CONVERTER,
+                      "parameter": {"method": "minhash", "parameter": {"hash_num": 128}}})
+    rec = nn.Recommender(cfg)
+    ora = oracle.OracleNN("minhash", 128)
+    ids, vals = w.synth_rows(w.MASTER_SEED, 40, 60, nnz=12, nfeat_log2=8)
+    for r in range(60):
+        rec.update_row("u%d" % r, datum_of(ids[r], vals[r])); ora.set_row("u%d" % r, sfv_of(ids[r], vals[r]))
+    q = datum_of(ids[3], vals[3])
+    got, want = rec.similar_row_from_datum(q, 10), ora.similar_row_from_datum(sfv_of(ids[3], vals[3]), 10)
+    assert got[0] == ("u3", 1.0)
+    assert [g[0] for g in got][:3] == [x[0] for x in want][:3]
+    assert rec.similar_row_from_id("u3", 1) == [("u3", 1.0)]
+    assert rec.similar_row_from_id("nobody", 3) == []
+    rec.clear_row("u3")
+    assert "u3" not in rec.get_all_rows()
+    with pytest.raises(nn.JubatusError):
+        nn.Recommender(json.dumps({"method": "lsh", "converter": CONVERTER, "parameter": {"method": "lsh", "parameter": {}}}))
+
+
+def test_anomaly_light_lof(oracle):
+    cfg = json.dumps({"method": "light_lof", "converter": CONVERTER,
+                      "parameter": {"nearest_neighbor_num": 3, "reverse_nearest_neighbor_num": 6, "method": "lsh",
+                                    "parameter": {"hash_num": 256}}})
+    an = nn.Anomaly(cfg)
+    ora = oracle.OracleNN("lsh", 256, lof=(3, 6))
+    ids, vals = w.synth_rows(w.MASTER_SEED, 70, 40, nnz=8, nfeat_log2=6)
+    for r in range(40):
+        rid, score = an.add(datum_of(ids[r], vals[r]))
+        ora.set_row(str(r), sfv_of(ids[r], vals[r]))
+        want = ora.calc_score_id(str(r))
+        assert rid == str(r)
+        assert score == want or abs(score - want) <= 1e-5 * abs(want) or (np.isinf(score) and np.isinf(want)), (r, score, want)
+    for r in (0, 7, 39):
+        got, want = an.lof_params(str(r)), ora.lof_params(str(r))
+        assert np.allclose(got, want, rtol=1e-5)
+    q = datum_of(ids[5][:6], vals[5][:6])
+    assert abs(an.calc_score(q) - ora.calc_score(sfv_of(ids[5][:6], vals[5][:6]))) <= 1e-5
+    with pytest.raises(nn.JubatusError):
+        nn.Anomaly(json.dumps({"method": "lof", "converter": CONVERTER, "parameter": {"method": "lsh", "parameter": {}}}))

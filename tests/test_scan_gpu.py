@@ -14,28 +14,29 @@ def _engine(method, hash_num, **opt):
 
 
 @pytest.mark.parametrize("hash_num", [64, 100, 128, 192, 256, 512, 1024, 1])
-@pytest.mark.parametrize("popc_variant", [0, 1, 2])
-def test_hamming_topk_random(oracle, hash_num, popc_variant):
+@pytest.mark.parametrize("popc_variant,scan_variant", [(0, 1), (1, 1), (2, 1), (3, 1), (4, 1), (0, 2), (2, 2), (3, 2)])
+def test_hamming_topk_random(oracle, hash_num, popc_variant, scan_variant):
     rng = np.random.RandomState(hash_num + popc_variant)
     n, nq, k = 5000, 9, 10
     rows = random_rows(rng, n, hash_num)
     q = random_rows(rng, nq, hash_num)
     q[0] = rows[17]
-    with _engine("lsh", hash_num, popc_variant=popc_variant) as e:
+    with _engine("lsh", hash_num, popc_variant=popc_variant, scan_variant=scan_variant) as e:
         e.set_rows_sig(np.arange(n), rows)
         got = e.query_sig(q, None, k)
     want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3]
     assert_same_ranking(got, want, nq, k)
 
 
+@pytest.mark.parametrize("scan_variant", [1, 2])
 @pytest.mark.parametrize("n,k", [(0, 5), (1, 5), (31, 40), (32, 32), (33, 1), (1000, 0), (1000, 100), (4097, 257),
                                  (70000, 100), (300, 299)])
-def test_hamming_sizes_and_k(oracle, n, k):
+def test_hamming_sizes_and_k(oracle, n, k, scan_variant):
     rng = np.random.RandomState(n * 7 + k)
     hash_num, nq = 256, 5
     rows = random_rows(rng, n, hash_num)
     q = random_rows(rng, nq, hash_num)
-    with _engine("lsh", hash_num) as e:
+    with _engine("lsh", hash_num, scan_variant=scan_variant) as e:
         if n:
             e.set_rows_sig(np.arange(n), rows)
         got = e.query_sig(q, None, k)
@@ -44,15 +45,16 @@ def test_hamming_sizes_and_k(oracle, n, k):
     assert_same_ranking(got, want, nq, k)
 
 
+@pytest.mark.parametrize("scan_variant", [1, 2])
 @pytest.mark.parametrize("qp", [1, 2, 3, 8])
-def test_adversarial_ties(oracle, qp):
+def test_adversarial_ties(oracle, qp, scan_variant):
     # few distinct signatures -> huge tie groups; order must be by row index
     rng = np.random.RandomState(11)
     hash_num, n, nq, k = 128, 20000, 7, 100
     base = random_rows(rng, 4, hash_num)
     rows = base[rng.randint(0, 4, size=n)]
     q = np.concatenate([base, random_rows(rng, nq - 4, hash_num)])
-    with _engine("lsh", hash_num, queries_per_pass=qp) as e:
+    with _engine("lsh", hash_num, queries_per_pass=qp, scan_variant=scan_variant) as e:
         e.set_rows_sig(np.arange(n), rows)
         got = e.query_sig(q, None, k)
     want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3]
@@ -87,12 +89,13 @@ def test_descending_distances_worst_case(oracle):
     assert_same_ranking(got, want, 1, k)
 
 
-def test_large_k_pagination(oracle):
+@pytest.mark.parametrize("scan_variant", [1, 2])
+def test_large_k_pagination(oracle, scan_variant):
     rng = np.random.RandomState(3)
     hash_num, n, nq, k = 64, 9000, 3, 5000   # > 2048 results per pass -> several pages
     rows = random_rows(rng, n, hash_num)
     q = random_rows(rng, nq, hash_num)
-    with _engine("lsh", hash_num) as e:
+    with _engine("lsh", hash_num, scan_variant=scan_variant) as e:
         e.set_rows_sig(np.arange(n), rows)
         got = e.query_sig(q, None, k)
     want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3]
@@ -113,8 +116,9 @@ def test_similar_flag_and_minhash_method(oracle):
         assert_same_ranking(got, want, nq, k)
 
 
+@pytest.mark.parametrize("scan_variant", [1, 2])
 @pytest.mark.parametrize("hash_num", [64, 256, 100])
-def test_euclid_scores(oracle, hash_num):
+def test_euclid_scores(oracle, hash_num, scan_variant):
     from jubatus_b200 import SIMILAR
     rng = np.random.RandomState(hash_num)
     n, nq, k = 6000, 6, 100
@@ -127,7 +131,7 @@ def test_euclid_scores(oracle, hash_num):
     q[1] = rows[100]
     qn[1] = norms[100]
     qn[2] = 0.0
-    with _engine("euclid_lsh", hash_num) as e:
+    with _engine("euclid_lsh", hash_num, scan_variant=scan_variant) as e:
         e.set_rows_sig(np.arange(n), rows, norms)
         got = e.query_sig(q, qn, k)
         got_sim = e.query_sig(q, qn, k, SIMILAR)
@@ -201,3 +205,18 @@ def test_errors(oracle):
         e.set_rows_sig([0], np.zeros((1, 1), dtype=np.uint64), np.ones(1, dtype=np.float32))
         with pytest.raises(JubannError):
             e.query_sig(np.zeros((1, 1), dtype=np.uint64), None, 1)   # norms required
+
+
+@pytest.mark.parametrize("scan_variant", [1, 2])
+@pytest.mark.parametrize("scan_order", [0, 1])
+def test_scan_order_option(oracle, scan_variant, scan_order):
+    rng = np.random.RandomState(scan_order)
+    hash_num, n, nq, k = 512, 150001, 5, 100
+    rows = random_rows(rng, n, hash_num)
+    q = random_rows(rng, nq, hash_num)
+    q[0] = rows[n - 1]
+    with _engine("lsh", hash_num, scan_variant=scan_variant, scan_order=scan_order) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        got = e.query_sig(q, None, k)
+    want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k, threads=4)[:3]
+    assert_same_ranking(got, want, nq, k)

@@ -1,0 +1,45 @@
+"""Condense an .ncu-rep into the handful of metrics DESIGN.md / bench.py quote (run here, no GPU)."""
+import csv
+import io
+import json
+import subprocess
+import sys
+
+WANT = [
+    "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
+    "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic",
+    "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+    "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum", "sm__cycles_elapsed.avg",
+    "sm__cycles_elapsed.avg.per_second", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smsp__warps_eligible.avg.per_cycle_active",
+    "lts__t_sector_hit_rate.pct", "lts__t_bytes.sum",
+]
+
+
+def main():
+    rep = sys.argv[1]
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=subprocess.PIPE, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units = rows[0], rows[1]
+    res = []
+    for vals in rows[2:]:
+        d = {}
+        for i, h in enumerate(hdr):
+            if h in ("Kernel Name", "ID") or h in WANT or ("issue_stalled" in h and h.endswith("per_issue_active.ratio")):
+                v = vals[i]
+                try:
+                    v = float(v)
+                except ValueError:
+                    pass
+                if "issue_stalled" in h and isinstance(v, float) and v < 0.3:
+                    continue
+                d[h + (" [%s]" % units[i] if units[i] else "")] = v
+        res.append(d)
+    print(json.dumps(res, indent=1))
+
+
+if __name__ == "__main__":
+    main()

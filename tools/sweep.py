@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--pvs", default="0,1,2")
     ap.add_argument("--variants", default="1")
     ap.add_argument("--passes", type=int, default=6)
+    ap.add_argument("--orders", default="1")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     euclid = a.method == "euclid_lsh"
@@ -39,8 +40,9 @@ def main():
         eng.set_rows_sig_dev(n, r0, sig.data_ptr(), nrm.data_ptr() if euclid else 0, stream)
         torch.cuda.synchronize()
     row_bytes = w64 * 8 + (4 if euclid else 0)
-    for variant in [int(x) for x in a.variants.split(",")]:
+    for order, variant in [(int(o), int(x)) for o in a.orders.split(",") for x in a.variants.split(",")]:
         eng.set_option("scan_variant", variant)
+        eng.set_option("scan_order", order)
         for pv in [int(x) for x in a.pvs.split(",")]:
             eng.set_option("popc_variant", pv)
             for qp in [int(x) for x in a.qps.split(",")]:
@@ -61,9 +63,9 @@ def main():
                     torch.cuda.synchronize()
                 st = eng.stats()
                 ms = e0.elapsed_time(e1)
-                avg = st["scan_ms"] / max(1, st["scan_launches"])
-                print(json.dumps({"variant": variant, "pv": pv, "qp": qp, "nq": nq, "total_ms": round(ms, 3),
-                                  "scan_launches": st["scan_launches"], "avg_scan_ms": round(avg, 4),
+                avg = st["scan_ms"] / max(1, st["scan_passes"])
+                print(json.dumps({"order": order, "variant": variant, "pv": pv, "qp": qp, "nq": nq, "total_ms": round(ms, 3),
+                                  "scan_passes": st["scan_passes"], "ms_per_pass": round(avg, 4),
                                   "scan_GBps": round(a.rows * row_bytes / (avg * 1e-3) / 1e9, 1),
                                   "qps": round(nq / (ms * 1e-3), 1),
                                   "pairs_per_s": float("%.4g" % (a.rows * qp / (avg * 1e-3)))}), flush=True)
