@@ -159,20 +159,25 @@ __device__ __forceinline__ uint32_t popc8(const uint32_t (&x)[8]) {
   }
 }
 
-template <int W32, int PV>
-__device__ __forceinline__ uint32_t hamming(const uint32_t (&r)[W32], const uint32_t* sq) {
-  uint32_t x[W32];
+template <int W32>
+__device__ __forceinline__ void load_query(const uint32_t* sq, uint32_t (&q)[W32]) {
   if (W32 == 2) {
     uint2 v = *reinterpret_cast<const uint2*>(sq);
-    x[0] = r[0] ^ v.x; x[1] = r[1] ^ v.y;
+    q[0] = v.x; q[1] = v.y;
   } else {
 #pragma unroll
     for (int c = 0; c < W32 / 4; ++c) {
       uint4 v = reinterpret_cast<const uint4*>(sq)[c];
-      x[4 * c + 0] = r[4 * c + 0] ^ v.x; x[4 * c + 1] = r[4 * c + 1] ^ v.y;
-      x[4 * c + 2] = r[4 * c + 2] ^ v.z; x[4 * c + 3] = r[4 * c + 3] ^ v.w;
+      q[4 * c + 0] = v.x; q[4 * c + 1] = v.y; q[4 * c + 2] = v.z; q[4 * c + 3] = v.w;
     }
   }
+}
+
+template <int W32, int PV>
+__device__ __forceinline__ uint32_t hamming_rq(const uint32_t (&r)[W32], const uint32_t (&q)[W32]) {
+  uint32_t x[W32];
+#pragma unroll
+  for (int i = 0; i < W32; ++i) x[i] = r[i] ^ q[i];
   if (W32 == 2) {
     return __popc(x[0]) + __popc(x[1]);
   } else if (W32 == 4) {
@@ -196,6 +201,13 @@ __device__ __forceinline__ uint32_t hamming(const uint32_t (&r)[W32], const uint
     }
     return d;
   }
+}
+
+template <int W32, int PV>
+__device__ __forceinline__ uint32_t hamming(const uint32_t (&r)[W32], const uint32_t* sq) {
+  uint32_t q[W32];
+  load_query<W32>(sq, q);
+  return hamming_rq<W32, PV>(r, q);
 }
 
 // order-preserving image of a float (no NaN expected); -0 is folded into +0 first so that
@@ -357,6 +369,36 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
     }
     const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
     if (__any_sync(FULL_MASK, c0)) list_offer(L, q, k0, row, c0, lane);
+  }
+}
+
+// two tiles at once (lane holds row A and row B): every query word fetched from shared memory
+// serves two rows, and the two distance chains are independent
+template <int W32, bool EUCLID, int PV>
+__device__ __forceinline__ void rank_tile2(const uint32_t (&ra)[W32], const uint32_t (&rb)[W32], uint32_t rowa,
+                                           uint32_t rowb, double nia, double nib, uint32_t nqp, const uint32_t* s_q,
+                                           const double* s_lut, uint32_t hash_num, const ListCtl& L, int lane) {
+  constexpr uint32_t QS = W32 + 4;
+  const uint32_t* b0 = s_q;
+#pragma unroll 2
+  for (uint32_t q = 0; q < nqp; ++q, b0 += QS) {
+    uint32_t qw[W32];
+    load_query<W32>(b0, qw);
+    const uint32_t da = hamming_rq<W32, PV>(ra, qw);
+    const uint32_t db = hamming_rq<W32, PV>(rb, qw);
+    uint32_t ka = da, kb = db;
+    if (EUCLID) {
+      const double la = s_lut[q * (hash_num + 1) + da];
+      const double lb = s_lut[q * (hash_num + 1) + db];
+      ka = float_key(__double2float_rn(__dmul_rn(nia, __dsub_rn(nia, la))));
+      kb = float_key(__double2float_rn(__dmul_rn(nib, __dsub_rn(nib, lb))));
+    }
+    const uint32_t tau = *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
+    const bool ca = ka <= tau, cb = kb <= tau;
+    if (__any_sync(FULL_MASK, ca || cb)) {
+      if (__any_sync(FULL_MASK, ca)) list_offer(L, q, ka, rowa, ca, lane);
+      if (__any_sync(FULL_MASK, cb)) list_offer(L, q, kb, rowb, cb, lane);
+    }
   }
 }
 
@@ -573,37 +615,49 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
   if (warp == TMA_CONSUMER_WARPS) {
     // ---- producer: one elected thread feeds the ring ----
     if (lane == 0) {
-      for (uint32_t it = 0; it < iters; ++it) {
-        const uint32_t s = it % stages, ph = (it / stages) & 1u;
+      uint32_t s = 0, ph = 0;
+      uint64_t t0 = t_first;
+      for (uint32_t it = 0; it < iters; ++it, t0 += t_stride) {
         if (it >= stages) mbar_wait(empty_bar + s, ph ^ 1u);
-        const uint64_t t0 = t_first + (uint64_t)it * t_stride;
         const uint32_t ntile = (uint32_t)min((uint64_t)stage_tiles, t_end - t0);
         const uint32_t bytes = ntile * (uint32_t)tile_bytes;
         mbar_expect_tx(full_bar + s, bytes + (EUCLID ? ntile * 128u : 0u));
         bulk_g2s(ring + s * stage_bytes, a.slab + t0 * tile_bytes, bytes, full_bar + s);
         if (EUCLID) bulk_g2s(nring + (size_t)s * stage_tiles * 32, a.norms + t0 * 32, ntile * 128u, full_bar + s);
+        if (++s == stages) { s = 0; ph ^= 1u; }
       }
     }
     __syncwarp();
   } else {
-    // ---- consumers ----
-    for (uint32_t it = 0; it < iters; ++it) {
-      const uint32_t s = it % stages, ph = (it / stages) & 1u;
+    // ---- consumers: warp w owns tiles 2w, 2w+1 (+ 2*16 per further pair) of every stage ----
+    uint32_t s = 0, ph = 0;
+    uint64_t t0 = t_first;
+    for (uint32_t it = 0; it < iters; ++it, t0 += t_stride) {
       mbar_wait(full_bar + s, ph);
       const unsigned char* stage = ring + s * stage_bytes;
-      const uint64_t t0 = t_first + (uint64_t)it * t_stride;
-      for (uint32_t j = 0; j < tiles_per_warp; ++j) {
-        const uint32_t tis = j * TMA_CONSUMER_WARPS + warp;
+      const float* nstage = nring + (size_t)s * stage_tiles * 32;
+      for (uint32_t j = 0; j < tiles_per_warp; j += 2) {
+        const uint32_t tis = (j * TMA_CONSUMER_WARPS) + 2 * warp;
         const uint64_t t = t0 + tis;
         if (t >= t_end) break;
-        uint32_t cur[W32];
-        load_row_smem<W32>(stage, tis, lane, cur);
-        double ni = 0.0;
-        if (EUCLID) ni = (double)nring[((size_t)s * stage_tiles + tis) * 32 + lane];
-        rank_tile<W32, EUCLID, PV>(cur, (uint32_t)(t * 32 + lane), ni, nqp, s_q, s_lut, a.hash_num, L, lane);
+        uint32_t ra[W32];
+        load_row_smem<W32>(stage, tis, lane, ra);
+        double nia = 0.0;
+        if (EUCLID) nia = (double)nstage[tis * 32 + lane];
+        const uint32_t rowa = (uint32_t)(t * 32 + lane);
+        if (t + 1 < t_end) {
+          uint32_t rb[W32];
+          load_row_smem<W32>(stage, tis + 1, lane, rb);
+          double nib = 0.0;
+          if (EUCLID) nib = (double)nstage[(tis + 1) * 32 + lane];
+          rank_tile2<W32, EUCLID, PV>(ra, rb, rowa, rowa + 32, nia, nib, nqp, s_q, s_lut, a.hash_num, L, lane);
+        } else {
+          rank_tile<W32, EUCLID, PV>(ra, rowa, nia, nqp, s_q, s_lut, a.hash_num, L, lane);
+        }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_bar + s);
+      if (++s == stages) { s = 0; ph ^= 1u; }
     }
   }
   __syncthreads();
@@ -789,11 +843,14 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
   if (cfg->variant == 2) {
     // one CTA per SM; ring of >= 2 stages of ~32 KB; the rest of shared memory for the lists
     const size_t budget = 226 * 1024;
-    uint32_t tpw = 1;
-    while ((size_t)TMA_CONSUMER_WARPS * tpw * t.w32 * 128 < 32 * 1024) tpw <<= 1;
+    uint32_t tpw = 2;  // consumer warps take tiles in pairs
+    while ((size_t)TMA_CONSUMER_WARPS * tpw * t.w32 * 128 < 64 * 1024) tpw <<= 1;
     while (qp > 1 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) --qp;
-    while (tpw > 1 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) tpw >>= 1;
-    if (plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) return false;
+    while (tpw > 2 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) tpw >>= 1;
+    if (plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) {
+      // the ring does not fit beside the lists (very wide rows / very large k): stream with LDG instead
+      return plan_scan(t, euclid, nq, k, 1, popc_variant, qp_opt, interleave, num_sms, cfg);
+    }
     uint32_t stages = 2;
     while (stages < 6 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, stages + 1, tpw).total <= budget) ++stages;
     cfg->stages = stages; cfg->tiles_per_warp = tpw;
