@@ -154,6 +154,25 @@ int jubann_query_sig_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, cons
 int jubann_set_rows_sig_dev(jubann_t* h, uint64_t n, uint64_t first_row_index,
                             const uint64_t* d_sigs, const float* d_norms, void* stream);
 
+/* No counterpart in the reference.  Same inputs, outputs and results as
+ * jubann_query_sig_dev, for callers that may not allocate device memory once they are
+ * running: a server whose GPU memory is parcelled out at start-up by its own pool, RPC
+ * threads with a latency budget (cudaMalloc/cudaFree stall the whole device), a process in
+ * which another thread may be recording work on a stream.  The kernels' scratch (per-CTA
+ * candidate lists) is a fixed array of JUBANN_NOALLOC_SCRATCH_BYTES inside the library image
+ * instead of a buffer grown with cudaMalloc; every GPU that loads the library holds it until
+ * exit.  This call allocates and frees nothing.  It needs nq * chunks * min(k, rows) * 8
+ * bytes (chunks <= 2 per SM); a larger request, or k above 2048, returns JUBANN_E_INVALID
+ * with a message.  The first call on a device looks up the array's address
+ * (cudaGetSymbolAddress): make it at start-up, before any stream capture.  Calls share the
+ * array and it keeps the previous call's contents; nothing in it needs to start at zero, and
+ * calls whose GPU work overlaps race on it -- keep them on one stream.  Single-shard
+ * handles only. */
+#define JUBANN_NOALLOC_SCRATCH_BYTES (32u << 20)
+int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms,
+                                 uint32_t k, uint32_t flags, uint64_t* d_out_index, float* d_out_score,
+                                 uint32_t* d_out_count, void* stream);
+
 /* Sharded query, stage 1: shard-local top-k as raw candidates, [nq][k] each:
  * d_cand_key = ordering key (Hamming distance, or the order-preserving image of the
  * pre-sqrt euclid score), d_cand_index = GLOBAL row index; unused slots hold

@@ -18,7 +18,7 @@ EXPORTS = [
     "jubann_query_sig", "jubann_query_csr", "jubann_query_rows", "jubann_query_sig_dev",
     "jubann_set_rows_sig_dev", "jubann_scan_local_dev", "jubann_merge_dev",
     "jubann_diff_record_bytes", "jubann_diff_pack_dev", "jubann_diff_apply_dev", "jubann_stats",
-    "jubann_stats_reset",
+    "jubann_stats_reset", "jubann_query_sig_noalloc_dev",
 ]
 
 
@@ -73,6 +73,8 @@ def load_library():
         "jubann_query_csr": [H, ctypes.c_uint64, _vp, _vp, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp],
         "jubann_query_rows": [H, ctypes.c_uint64, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp],
         "jubann_query_sig_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp, _vp],
+        "jubann_query_sig_noalloc_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp,
+                                         _vp],
         "jubann_set_rows_sig_dev": [H, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp],
         "jubann_scan_local_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, _vp, _vp, _vp],
         "jubann_merge_dev": [H, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp, ctypes.c_uint32,
@@ -238,6 +240,15 @@ class Engine(object):
         _check(self._lib.jubann_query_sig_dev(self._h, int(nq), _vp(d_qsigs), _vp(d_qnorms) if d_qnorms else None,
                                               int(k), int(flags), _vp(d_out_index), _vp(d_out_score),
                                               _vp(d_out_count), _vp(stream) if stream else None))
+
+    def query_sig_noalloc_dev(self, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count, stream=0):
+        """Like query_sig_dev, for callers that may not allocate: the kernels' scratch is the
+        fixed 32 MiB array inside the library, so this call never reaches cudaMalloc.  Requests
+        that do not fit are refused (JubannError).  Calls share that array: keep them on one stream."""
+        _check(self._lib.jubann_query_sig_noalloc_dev(self._h, int(nq), _vp(d_qsigs),
+                                                      _vp(d_qnorms) if d_qnorms else None, int(k), int(flags),
+                                                      _vp(d_out_index), _vp(d_out_score), _vp(d_out_count),
+                                                      _vp(stream) if stream else None))
 
     def set_rows_sig_dev(self, n, first_row_index, d_sigs, d_norms=0, stream=0):
         _check(self._lib.jubann_set_rows_sig_dev(self._h, int(n), int(first_row_index), _vp(d_sigs),

@@ -364,6 +364,24 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
 
 }  // namespace
 
+namespace jbn {
+int set_error(int code, const char* message) { return fail(code, "%s", message); }
+int handle_info(jubann* h, HandleInfo* out) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  out->table = view(h);
+  out->device = h->device;
+  out->euclid = (h->method == EUCLID_LSH);
+  out->shard_rank = h->shard_rank; out->shard_count = h->shard_count;
+  out->variant = h->variant_opt; out->popc_variant = h->popc_variant_opt; out->interleave = h->interleave_opt;
+  out->qp = h->qp_opt; out->num_sms = h->num_sms; out->coslut = h->d_coslut; out->mu = &h->mu;
+  return 0;
+}
+void handle_add_launches(jubann* h, uint64_t kernels, uint64_t scans, uint64_t passes) {
+  h->kernel_launches += kernels; h->scan_launches += scans; h->scan_passes += passes;
+}
+}  // namespace jbn
+
 extern "C" {
 
 const char* version(void) { return "jubann-b200 0.1.0 (jubatus 0.9.2 nearest_neighbor backend, sm_100a)"; }

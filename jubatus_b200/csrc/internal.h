@@ -127,5 +127,25 @@ cudaError_t launch_signature_minhash(uint32_t hash_num, uint64_t n, const uint64
                                      const uint64_t* d_keyhash64, const float* d_vals, uint64_t* d_sigs,
                                      float* d_norms, uint32_t w64, cudaStream_t s);
 
+
+// ---- read-only view of a handle for translation units other than capi.cu ------------
+struct HandleInfo {
+  TableView table;
+  int device;
+  bool euclid;
+  uint32_t shard_rank, shard_count;
+  int variant, popc_variant, interleave;
+  uint32_t qp;
+  int num_sms;
+  const double* coslut;
+  std::mutex* mu;
+};
+}  // namespace jbn
+struct jubann;
+namespace jbn {
+// fills `out`; returns 0, or a negative JUBANN_E_* code with the message set
+int handle_info(jubann* h, HandleInfo* out);
+void handle_add_launches(jubann* h, uint64_t kernels, uint64_t scans, uint64_t passes);
+int set_error(int code, const char* message);
 }  // namespace jbn
 #endif
