@@ -502,6 +502,8 @@ int jubann_set_option(jubann_t* h, const char* name, int64_t value) {
   } else if (!strcmp(name, "scan_variant")) {
     if (value < 0 || value > 2) return fail(JUBANN_E_INVALID, "scan_variant out of range (0..2)");
     h->variant_opt = (int)value;
+  } else if (!strcmp(name, "tma_geometry")) {   // tuning: (tiles_per_warp << 8) | stages, 0 = automatic
+    set_tma_geometry_override((uint32_t)(value >> 8), (uint32_t)(value & 0xff));
   } else if (!strcmp(name, "scan_order")) {
     if (value < 0 || value > 1) return fail(JUBANN_E_INVALID, "scan_order out of range (0..1)");
     h->interleave_opt = (int)value;

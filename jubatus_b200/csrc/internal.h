@@ -67,6 +67,7 @@ struct ScanConfig {
 bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int variant, int popc_variant,
                uint32_t qp_opt, int interleave, int num_sms, ScanConfig* cfg);
 uint32_t max_k_per_pass();
+void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages);  // tuning experiments; 0 = automatic
 
 // cand: [nq][nchunks][k] keys ((key_hi << 32) | local row), ascending, KEY_SENTINEL padded.
 // floor_keys (nullable): per query exclusive lower bound (pagination when k > max_k_per_pass).

@@ -259,7 +259,12 @@ __device__ __forceinline__ void warp_bitonic_sort(unsigned long long* a, uint32_
 
 // Sort list q, keep the k smallest, tighten the threshold.  Called by one full warp that
 // holds lock q (or after the CTA-wide barrier at the end).  Returns the new count.
-__device__ __noinline__ uint32_t list_compact(const ListCtl& L, uint32_t q, uint32_t cnt, int lane) {
+// The control block lives in shared memory (written once by the prologue): the rare-path
+// functions read it from there, so the hot loop keeps nothing address-taken in local memory.
+__shared__ ListCtl s_L;
+
+__device__ __noinline__ uint32_t list_compact(uint32_t q, uint32_t cnt, int lane) {
+  const ListCtl& L = s_L;
   unsigned long long* a = L.list + (size_t)q * L.cap;
   for (uint32_t i = cnt + lane; i < L.cap; i += 32) a[i] = KEY_SENTINEL;
   __syncwarp();
@@ -275,8 +280,8 @@ __device__ __noinline__ uint32_t list_compact(const ListCtl& L, uint32_t q, uint
 }
 
 // Warp-uniform slow path: lanes with cand != 0 offer (key_hi, row).
-__device__ __noinline__ void list_offer(const ListCtl& L, uint32_t q, uint32_t key_hi, uint32_t row,
-                                        bool cand, int lane) {
+__device__ __noinline__ void list_offer(uint32_t q, uint32_t key_hi, uint32_t row, bool cand, int lane) {
+  const ListCtl& L = s_L;
   const unsigned long long key = ((unsigned long long)key_hi << 32) | row;
   volatile unsigned long long* tau_p = L.tau + q;
   bool pass = cand && row < L.local_rows && key < *tau_p;  // rows of the padded last tile are not rows
@@ -297,7 +302,7 @@ __device__ __noinline__ void list_offer(const ListCtl& L, uint32_t q, uint32_t k
     }
     cnt += __popc(m);
     __syncwarp();
-    if (cnt > L.cap - 32) cnt = list_compact(L, q, cnt, lane);
+    if (cnt > L.cap - 32) cnt = list_compact(q, cnt, lane);
     if (lane == 0) *reinterpret_cast<volatile uint32_t*>(L.cnt + q) = cnt;
   }
   __syncwarp();
@@ -355,8 +360,8 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
     const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
     const bool c1 = k1 <= *reinterpret_cast<const volatile uint32_t*>(b1 + W32);
     if (__any_sync(FULL_MASK, c0 || c1)) {
-      if (__any_sync(FULL_MASK, c0)) list_offer(L, q, k0, row, c0, lane);
-      if (__any_sync(FULL_MASK, c1)) list_offer(L, q + 1, k1, row, c1, lane);
+      if (__any_sync(FULL_MASK, c0)) list_offer(q, k0, row, c0, lane);
+      if (__any_sync(FULL_MASK, c1)) list_offer(q + 1, k1, row, c1, lane);
     }
   }
   if (q < nqp) {
@@ -368,7 +373,7 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
       k0 = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l0))));
     }
     const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
-    if (__any_sync(FULL_MASK, c0)) list_offer(L, q, k0, row, c0, lane);
+    if (__any_sync(FULL_MASK, c0)) list_offer(q, k0, row, c0, lane);
   }
 }
 
@@ -396,8 +401,8 @@ __device__ __forceinline__ void rank_tile2(const uint32_t (&ra)[W32], const uint
     const uint32_t tau = *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
     const bool ca = ka <= tau, cb = kb <= tau;
     if (__any_sync(FULL_MASK, ca || cb)) {
-      if (__any_sync(FULL_MASK, ca)) list_offer(L, q, ka, rowa, ca, lane);
-      if (__any_sync(FULL_MASK, cb)) list_offer(L, q, kb, rowb, cb, lane);
+      if (__any_sync(FULL_MASK, ca)) list_offer(q, ka, rowa, ca, lane);
+      if (__any_sync(FULL_MASK, cb)) list_offer(q, kb, rowb, cb, lane);
     }
   }
 }
@@ -419,6 +424,7 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
   L.tau_stride = QS;
   L.local_rows = (uint32_t)a.local_rows;
   L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr);
+  if (tid == 0) s_L = L;
   for (uint32_t i = tid; i < nqp * QS; i += nthreads) {
     uint32_t q = i / QS, w = i % QS;
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)(q0 + q) * a.w64);
@@ -484,7 +490,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
   }
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += SCAN_WARPS) {
-    uint32_t n = list_compact(L, q, L.cnt[q], lane);
+    uint32_t n = list_compact(q, L.cnt[q], lane);
     const unsigned long long* src = L.list + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
                               ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
@@ -662,7 +668,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
   }
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += TMA_CONSUMER_WARPS + 1) {
-    uint32_t n = list_compact(L, q, L.cnt[q], lane);
+    uint32_t n = list_compact(q, L.cnt[q], lane);
     const unsigned long long* src = L.list + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
                               ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
@@ -820,6 +826,11 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32
 // ---------------------------------------------------------------------------
 uint32_t max_k_per_pass() { return MAX_CAP / 2; }
 
+static uint32_t g_tma_tpw_override = 0, g_tma_stages_override = 0;
+void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages) {
+  g_tma_tpw_override = tiles_per_warp; g_tma_stages_override = stages;
+}
+
 static uint32_t list_cap_for(uint32_t k) {
   uint32_t need = k < 32 ? 64 : 2 * k;
   uint32_t cap = 64;
@@ -851,8 +862,11 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
       // the ring does not fit beside the lists (very wide rows / very large k): stream with LDG instead
       return plan_scan(t, euclid, nq, k, 1, popc_variant, qp_opt, interleave, num_sms, cfg);
     }
+    if (g_tma_tpw_override >= 2 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, g_tma_tpw_override & ~1u).total <= budget)
+      tpw = g_tma_tpw_override & ~1u;
     uint32_t stages = 2;
-    while (stages < 6 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, stages + 1, tpw).total <= budget) ++stages;
+    const uint32_t max_stages = g_tma_stages_override >= 2 ? g_tma_stages_override : 6;
+    while (stages < max_stages && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, stages + 1, tpw).total <= budget) ++stages;
     cfg->stages = stages; cfg->tiles_per_warp = tpw;
     cfg->smem_bytes = plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, stages, tpw).total;
     max_chunks = (uint64_t)num_sms;

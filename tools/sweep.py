@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--variants", default="1")
     ap.add_argument("--passes", type=int, default=6)
     ap.add_argument("--orders", default="1")
+    ap.add_argument("--geoms", default="0", help="tma geometry overrides tpw:stages,...")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     euclid = a.method == "euclid_lsh"
@@ -40,7 +41,9 @@ def main():
         eng.set_rows_sig_dev(n, r0, sig.data_ptr(), nrm.data_ptr() if euclid else 0, stream)
         torch.cuda.synchronize()
     row_bytes = w64 * 8 + (4 if euclid else 0)
-    for order, variant in [(int(o), int(x)) for o in a.orders.split(",") for x in a.variants.split(",")]:
+    geoms = [(0, 0)] if a.geoms == "0" else [tuple(int(y) for y in g.split(":")) for g in a.geoms.split(",")]
+    for order, variant, geom in [(int(o), int(x), g) for o in a.orders.split(",") for x in a.variants.split(",") for g in geoms]:
+        eng.set_option("tma_geometry", (geom[0] << 8) | geom[1])
         eng.set_option("scan_variant", variant)
         eng.set_option("scan_order", order)
         for pv in [int(x) for x in a.pvs.split(",")]:
@@ -64,7 +67,7 @@ def main():
                 st = eng.stats()
                 ms = e0.elapsed_time(e1)
                 avg = st["scan_ms"] / max(1, st["scan_passes"])
-                print(json.dumps({"order": order, "variant": variant, "pv": pv, "qp": qp, "nq": nq, "total_ms": round(ms, 3),
+                print(json.dumps({"geom": "%d:%d" % geom, "order": order, "variant": variant, "pv": pv, "qp": qp, "nq": nq, "total_ms": round(ms, 3),
                                   "scan_passes": st["scan_passes"], "ms_per_pass": round(avg, 4),
                                   "scan_GBps": round(a.rows * row_bytes / (avg * 1e-3) / 1e9, 1),
                                   "qps": round(nq / (ms * 1e-3), 1),
