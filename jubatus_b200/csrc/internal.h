@@ -71,9 +71,10 @@ void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages);  // tu
 
 // cand: [nq][nchunks][k] keys ((key_hi << 32) | local row), ascending, KEY_SENTINEL padded.
 // floor_keys (nullable): per query exclusive lower bound (pagination when k > max_k_per_pass).
+// d_tau_scratch (nullable): nq u64 of scratch for the sample pre-pass that seeds the thresholds.
 cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, const uint64_t* d_qsigs,
                         const float* d_qnorms, const double* d_coslut, uint32_t nq, uint32_t k,
-                        const uint64_t* d_floor_keys, uint64_t* d_cand, cudaStream_t s);
+                        const uint64_t* d_floor_keys, uint64_t* d_tau_scratch, uint64_t* d_cand, cudaStream_t s);
 
 // Per query: k smallest keys among nlists*k candidates.  If d_out_index != nullptr writes the
 // final (index, score, count) outputs at column offset `col0` of rows of width `kout`;

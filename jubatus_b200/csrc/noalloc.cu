@@ -16,7 +16,7 @@
 //  * The array is part of the library image: every GPU that loads libjubann.so holds
 //    JUBANN_NOALLOC_SCRATCH_BYTES (32 MiB) of device memory until the process exits,
 //    whether or not this entry point is ever called.
-//  * A call needs  nq * chunks * min(k, rows) * 8  bytes of it (chunks = CTAs along the
+//  * A call needs  nq * (chunks * min(k, rows) + 1) * 8  bytes of it (chunks = CTAs along the
 //    table, at most 2 per SM).  A request that does not fit, or k above the single-pass
 //    limit of 2048, is refused with JUBANN_E_INVALID and a message; nothing is launched.
 //  * The first call on a device looks up the array's device address
@@ -118,7 +118,7 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   if (keff) {
     if (!plan_scan(hi.table, hi.euclid, nq, keff, hi.variant, hi.popc_variant, hi.qp, hi.interleave, hi.num_sms, &cfg))
       return set_error(JUBANN_E_INVALID, "no-alloc query: cannot plan a scan for this k");
-    const uint64_t need = (uint64_t)nq * cfg.nchunks * keff * 8ull;
+    const uint64_t need = (uint64_t)nq * cfg.nchunks * keff * 8ull + (uint64_t)nq * 8ull;  // lists + one threshold per query
     if (need > (uint64_t)JUBANN_NOALLOC_SCRATCH_BYTES) {
       snprintf(msg, sizeof(msg),
                "no-alloc query: %u queries x %u table chunks x k=%u need %llu bytes of scratch, the fixed array holds %llu; "
@@ -135,7 +135,8 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   cudaError_t e = cudaMemsetAsync(d_out_count, 0, (size_t)nq * 4, s);
   if (e != cudaSuccess) return cuda_error("cudaMemsetAsync(out_count)", e);
   if (keff == 0) return 0;
-  e = launch_scan(hi.table, hi.euclid, cfg, d_qsigs, d_qnorms, hi.coslut, nq, keff, nullptr,
+  uint64_t* tau_scratch = static_cast<uint64_t*>(scratch) + (size_t)nq * cfg.nchunks * keff;
+  e = launch_scan(hi.table, hi.euclid, cfg, d_qsigs, d_qnorms, hi.coslut, nq, keff, nullptr, tau_scratch,
                   static_cast<uint64_t*>(scratch), s);
   if (e != cudaSuccess) return cuda_error("scan launch (no-alloc)", e);
   MergeOut o{};
@@ -146,6 +147,6 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   o.out_index = d_out_index; o.out_score = d_out_score; o.out_count = d_out_count;
   e = launch_merge_local(static_cast<const uint64_t*>(scratch), nq, cfg.nchunks, keff, o, s);
   if (e != cudaSuccess) return cuda_error("merge launch (no-alloc)", e);
-  handle_add_launches(h, 2, 1, (nq + cfg.qp - 1) / cfg.qp);
+  handle_add_launches(h, 3, 1, (nq + cfg.qp - 1) / cfg.qp);
   return 0;
 }

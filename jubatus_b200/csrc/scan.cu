@@ -20,6 +20,8 @@
 
 #include <string.h>
 
+#include <algorithm>
+
 namespace jbn {
 
 #define FULL_MASK 0xffffffffu
@@ -37,8 +39,10 @@ struct ScanArgs {
   const float* qnorms;
   const double* coslut;
   const uint64_t* floor_keys;
+  const uint64_t* tau_init;   // per query: exclusive upper bound of admissible keys from the sample pre-pass (nullable)
   uint64_t* cand;
   uint32_t nq, k, cap, qp, w64, hash_num, tiles_per_chunk, nchunks;
+  uint32_t w32;
   uint32_t interleave;  // 1: CTAs take turns tile-group by tile-group (one sweep front); 0: one contiguous range per CTA
 };
 
@@ -226,6 +230,11 @@ __host__ __device__ __forceinline__ float key_float(uint32_t k) {
 #endif
 }
 
+// largest key_hi that can still be below the exclusive bound `tau`
+__host__ __device__ __forceinline__ uint32_t tau_hi_of(unsigned long long tau) {
+  return tau ? (uint32_t)((tau - 1ull) >> 32) : 0u;
+}
+
 // ---------------------------------------------------------------------------
 // per-(CTA, query) candidate list
 // ---------------------------------------------------------------------------
@@ -273,7 +282,7 @@ __device__ __noinline__ uint32_t list_compact(uint32_t q, uint32_t cnt, int lane
   if (n == L.k && lane == 0) {
     unsigned long long t = a[L.k - 1];
     *reinterpret_cast<volatile unsigned long long*>(L.tau + q) = t;
-    *reinterpret_cast<volatile uint32_t*>(L.tau_hi + (size_t)q * L.tau_stride) = (uint32_t)(t >> 32);
+    *reinterpret_cast<volatile uint32_t*>(L.tau_hi + (size_t)q * L.tau_stride) = tau_hi_of(t);
   }
   __syncwarp();
   return n;
@@ -428,7 +437,7 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
   for (uint32_t i = tid; i < nqp * QS; i += nthreads) {
     uint32_t q = i / QS, w = i % QS;
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)(q0 + q) * a.w64);
-    s_q[i] = (w < W32) ? ((w < 2 * a.w64) ? src[w] : 0u) : 0xFFFFFFFFu;
+    s_q[i] = (w < W32) ? ((w < 2 * a.w64) ? src[w] : 0u) : tau_hi_of(a.tau_init ? a.tau_init[q0 + q] : KEY_SENTINEL);
   }
   if (EUCLID) {
     const uint32_t hn = a.hash_num + 1;
@@ -439,7 +448,7 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
     }
   }
   if ((uint32_t)tid < nqp) {
-    L.cnt[tid] = 0; L.lock[tid] = 0; L.tau[tid] = KEY_SENTINEL;
+    L.cnt[tid] = 0; L.lock[tid] = 0; L.tau[tid] = a.tau_init ? a.tau_init[q0 + tid] : KEY_SENTINEL;
     L.floor[tid] = a.floor_keys ? a.floor_keys[q0 + tid] : 0ull;
   }
 }
@@ -822,6 +831,56 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32
 }
 
 // ---------------------------------------------------------------------------
+// sample pre-pass: an admissible-key bound per query before the scan starts.
+// One CTA per query ranks the first S rows and takes the k-th smallest ordering key t;
+// at least k rows have key_hi <= t, so every top-k key is below (t + 1) << 32.  Starting the
+// scan with this bound removes the warm-up in which every row of a CTA's first tiles is a
+// candidate and all warps queue on the list lock.
+// ---------------------------------------------------------------------------
+static const int TAU_THREADS = 256;
+
+template <bool EUCLID>
+__global__ void __launch_bounds__(TAU_THREADS) tau_init_kernel(ScanArgs a, uint32_t S, uint32_t SP,
+                                                               unsigned long long* tau_out) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint32_t* keys = reinterpret_cast<uint32_t*>(smem);
+  const uint32_t q = blockIdx.x;
+  const uint32_t* qw = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)q * a.w64);
+  for (uint32_t i = threadIdx.x; i < SP; i += TAU_THREADS) {
+    uint32_t key = 0xFFFFFFFFu;
+    if (i < S) {
+      uint32_t d = 0;
+      for (uint32_t w = 0; w < 2 * a.w64; ++w)
+        d += __popc(*reinterpret_cast<const uint32_t*>(a.slab + word_offset(a.w32, i, w)) ^ qw[w]);
+      key = d;
+      if (EUCLID) {
+        const double ni = (double)a.norms[i];
+        const double l2 = __dmul_rn((double)(2.0f * a.qnorms[q]), a.coslut[d]);
+        key = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l2))));
+      }
+    }
+    keys[i] = key;
+  }
+  __syncthreads();
+  for (uint32_t size = 2; size <= SP; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t i = threadIdx.x; i < (SP >> 1); i += TAU_THREADS) {
+        uint32_t lo = ((i & ~(stride - 1)) << 1) | (i & (stride - 1));
+        uint32_t hi = lo | stride;
+        bool asc = ((lo & size) == 0);
+        uint32_t x = keys[lo], y = keys[hi];
+        if ((x > y) == asc && x != y) { keys[lo] = y; keys[hi] = x; }
+      }
+      __syncthreads();
+    }
+  }
+  if (threadIdx.x == 0) {
+    const uint32_t t = (a.k <= S) ? keys[a.k - 1] : 0xFFFFFFFFu;
+    tau_out[q] = (t == 0xFFFFFFFFu) ? KEY_SENTINEL : (((unsigned long long)t + 1ull) << 32);
+  }
+}
+
+// ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
 uint32_t max_k_per_pass() { return MAX_CAP / 2; }
@@ -930,17 +989,34 @@ static cudaError_t launch_scan_w(uint32_t w32, const ScanArgs& a, const ScanConf
 
 cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, const uint64_t* d_qsigs,
                         const float* d_qnorms, const double* d_coslut, uint32_t nq, uint32_t k,
-                        const uint64_t* d_floor_keys, uint64_t* d_cand, cudaStream_t s) {
+                        const uint64_t* d_floor_keys, uint64_t* d_tau_scratch, uint64_t* d_cand, cudaStream_t s) {
   ScanArgs a;
   a.slab = static_cast<const unsigned char*>(t.slab);
   a.norms = t.norms;
   a.local_rows = t.local_rows;
   a.ntiles = (t.local_rows + 31) / 32;
   a.qsigs = d_qsigs; a.qnorms = d_qnorms; a.coslut = d_coslut; a.floor_keys = d_floor_keys;
+  a.tau_init = nullptr;
   a.cand = d_cand;
   a.nq = nq; a.k = k; a.cap = cfg.cap; a.qp = cfg.qp; a.w64 = t.w64; a.hash_num = t.hash_num;
   a.tiles_per_chunk = cfg.tiles_per_chunk; a.nchunks = cfg.nchunks;
+  a.w32 = t.w32;
   a.interleave = cfg.interleave;
+  // sample pre-pass (not with a pagination floor: the bound would not hold for keys above it),
+  // worthwhile only when the table is much larger than the sample
+  if (d_tau_scratch && !d_floor_keys) {
+    uint64_t S = std::max<uint64_t>(2048, 4ull * k);
+    if (S > 8192) S = 8192;
+    if (t.local_rows >= 16 * S && k <= S) {
+      uint32_t SP = 1;
+      while (SP < S) SP <<= 1;
+      if (euclid) tau_init_kernel<true><<<nq, TAU_THREADS, SP * 4, s>>>(a, (uint32_t)S, SP, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+      else tau_init_kernel<false><<<nq, TAU_THREADS, SP * 4, s>>>(a, (uint32_t)S, SP, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+      cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) return e;
+      a.tau_init = d_tau_scratch;
+    }
+  }
   dim3 grid(cfg.nchunks, (nq + cfg.qp - 1) / cfg.qp, 1);
   return euclid ? launch_scan_w<true>(t.w32, a, cfg, grid, s) : launch_scan_w<false>(t.w32, a, cfg, grid, s);
 }

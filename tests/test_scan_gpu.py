@@ -220,3 +220,24 @@ def test_scan_order_option(oracle, scan_variant, scan_order):
         got = e.query_sig(q, None, k)
     want = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k, threads=4)[:3]
     assert_same_ranking(got, want, nq, k)
+
+
+@pytest.mark.parametrize("scan_variant", [1, 2])
+@pytest.mark.parametrize("method,hash_num,n,k", [("euclid_lsh", 256, 40000, 100), ("lsh", 64, 100000, 600),
+                                                 ("lsh", 512, 70001, 1), ("euclid_lsh", 64, 140000, 2048)])
+def test_sample_prepass_bound_is_safe(oracle, method, hash_num, n, k, scan_variant):
+    # tables large enough for the sample pre-pass that seeds the thresholds; heavy ties in the sample
+    rng = np.random.RandomState(n + k)
+    nq = 6
+    rows = random_rows(rng, n, hash_num)
+    rows[:3000] = rows[0]                      # the sampled prefix is one repeated row
+    q = random_rows(rng, nq, hash_num)
+    q[0] = rows[0]
+    q[1] = rows[n - 5]
+    norms = (rng.rand(n) * 3).astype(np.float32) if method == "euclid_lsh" else None
+    qn = (rng.rand(nq) * 3).astype(np.float32) if method == "euclid_lsh" else None
+    with _engine(method, hash_num, scan_variant=scan_variant) as e:
+        e.set_rows_sig(np.arange(n), rows, norms)
+        got = e.query_sig(q, qn, k)
+    want = oracle.scan_batch(method, q, qn, rows, norms, hash_num, k, threads=4)[:3]
+    assert_same_ranking(got, want, nq, k)
