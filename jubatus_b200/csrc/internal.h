@@ -69,7 +69,7 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
 uint32_t max_k_per_pass();
 void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages);  // tuning experiments; 0 = automatic
 
-// cand: [nq][nchunks][k] keys ((key_hi << 32) | local row), ascending, KEY_SENTINEL padded.
+// cand: [nq][nchunks][k] keys ((key_hi << 32) | local row) in no particular order, KEY_SENTINEL padded.
 // floor_keys (nullable): per query exclusive lower bound (pagination when k > max_k_per_pass).
 // d_tau_scratch (nullable): nq u64 of scratch for the sample pre-pass that seeds the thresholds.
 cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, const uint64_t* d_qsigs,

@@ -238,94 +238,174 @@ __host__ __device__ __forceinline__ uint32_t tau_hi_of(unsigned long long tau) {
 // ---------------------------------------------------------------------------
 // per-(CTA, query) candidate list
 // ---------------------------------------------------------------------------
+// All list state lives in the kernel's dynamic shared memory.  The control block holds byte
+// offsets from its base (not generic pointers), so every access below is an LDS/STS/ATOMS.
+extern __shared__ __align__(128) unsigned char g_smem[];
+
 struct ListCtl {
-  unsigned long long* list;  // [qp][cap]
-  unsigned long long* tau;   // [qp] exclusive upper bound on admissible keys
-  unsigned long long* floor; // [qp] exclusive lower bound (pagination) when has_floor
-  uint32_t* cnt;             // [qp]
-  uint32_t* lock;            // [qp]
-  uint32_t* tau_hi;          // word 0 of query 0's threshold; query q at tau_hi[q * tau_stride]
+  uint32_t list_off;   // u64 [qp][cap]
+  uint32_t tau_off;    // u64 [qp] exclusive upper bound on admissible keys
+  uint32_t floor_off;  // u64 [qp] exclusive lower bound (pagination) when has_floor
+  uint32_t cnt_off;    // u32 [qp]
+  uint32_t lock_off;   // u32 [qp]
+  uint32_t tauhi_off;  // u32: fast-reject word of query 0; query q at + q * tau_stride words
+  uint32_t stash_off;  // per warp: u64 key[STASH] | u32 query[STASH] | u32 count | pad
   uint32_t tau_stride;
   uint32_t local_rows;
   uint32_t cap, k;
-  bool has_floor;
+  uint32_t has_floor;
 };
+__shared__ ListCtl s_L;   // written once by the prologue, read by the rare-path functions
 
-__device__ __forceinline__ void warp_bitonic_sort(unsigned long long* a, uint32_t n, int lane) {
-  for (uint32_t size = 2; size <= n; size <<= 1) {
-    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
-      for (uint32_t i = lane; i < (n >> 1); i += 32) {
-        uint32_t lo = ((i & ~(stride - 1)) << 1) | (i & (stride - 1));
-        uint32_t hi = lo | stride;
-        bool asc = ((lo & size) == 0);
-        unsigned long long x = a[lo], y = a[hi];
-        if ((x > y) == asc && x != y) { a[lo] = y; a[hi] = x; }
-      }
-      __syncwarp();
-    }
-  }
-}
+__device__ __forceinline__ unsigned long long* sm_u64(uint32_t off) { return reinterpret_cast<unsigned long long*>(g_smem + off); }
+__device__ __forceinline__ uint32_t* sm_u32(uint32_t off) { return reinterpret_cast<uint32_t*>(g_smem + off); }
 
-// Sort list q, keep the k smallest, tighten the threshold.  Called by one full warp that
-// holds lock q (or after the CTA-wide barrier at the end).  Returns the new count.
-// The control block lives in shared memory (written once by the prologue): the rare-path
-// functions read it from there, so the hot loop keeps nothing address-taken in local memory.
-__shared__ ListCtl s_L;
-
+// Keep the k smallest of the cnt (distinct) keys of list q and tighten the threshold to the
+// k-th smallest.  No sort: the k-th smallest key is found by a most-significant-bit-first search
+// (count keys below a trial value, one warp reduction per bit), then the survivors are packed to
+// the front in place.  Called by one full warp that holds lock q (or after the CTA-wide barrier
+// at the end).  Returns the new count; the survivors are NOT ordered.
 __device__ __noinline__ uint32_t list_compact(uint32_t q, uint32_t cnt, int lane) {
-  const ListCtl& L = s_L;
-  unsigned long long* a = L.list + (size_t)q * L.cap;
-  for (uint32_t i = cnt + lane; i < L.cap; i += 32) a[i] = KEY_SENTINEL;
-  __syncwarp();
-  warp_bitonic_sort(a, L.cap, lane);
-  uint32_t n = cnt < L.k ? cnt : L.k;
-  if (n == L.k && lane == 0) {
-    unsigned long long t = a[L.k - 1];
-    *reinterpret_cast<volatile unsigned long long*>(L.tau + q) = t;
-    *reinterpret_cast<volatile uint32_t*>(L.tau_hi + (size_t)q * L.tau_stride) = tau_hi_of(t);
+  const uint32_t cap = s_L.cap, k = s_L.k;
+  unsigned long long* a = sm_u64(s_L.list_off) + (size_t)q * cap;
+  if (cnt <= k) return cnt;
+  unsigned long long mx = 0;
+  for (uint32_t i = lane; i < cnt; i += 32) mx = max(mx, a[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(FULL_MASK, mx, o));
+  unsigned long long prefix = 0;
+  for (int bit = 63 - __clzll((long long)(mx | 1ull)); bit >= 0; --bit) {
+    const unsigned long long trial = prefix | (1ull << bit);
+    uint32_t c = 0;
+    for (uint32_t i = lane; i < cnt; i += 32) c += (a[i] < trial) ? 1u : 0u;
+    c = __reduce_add_sync(FULL_MASK, c);
+    if (c < k) prefix = trial;   // fewer than k keys below trial: the k-th smallest is >= trial
+  }
+  // prefix is now the k-th smallest key; exactly k keys are <= prefix
+  uint32_t w = 0;
+  for (uint32_t base = 0; base < cnt; base += 32) {
+    const uint32_t i = base + lane;
+    const unsigned long long v = (i < cnt) ? a[i] : KEY_SENTINEL;
+    const bool keep = v <= prefix;
+    const unsigned m = __ballot_sync(FULL_MASK, keep);
+    __syncwarp();
+    if (keep) a[w + __popc(m & ((1u << lane) - 1u))] = v;
+    w += __popc(m);
+    __syncwarp();
+  }
+  if (lane == 0) {
+    *reinterpret_cast<volatile unsigned long long*>(sm_u64(s_L.tau_off) + q) = prefix;
+    *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride) = tau_hi_of(prefix);
   }
   __syncwarp();
-  return n;
+  return w;
 }
 
 // Warp-uniform slow path: lanes with cand != 0 offer (key_hi, row).
 __device__ __noinline__ void list_offer(uint32_t q, uint32_t key_hi, uint32_t row, bool cand, int lane) {
-  const ListCtl& L = s_L;
   const unsigned long long key = ((unsigned long long)key_hi << 32) | row;
-  volatile unsigned long long* tau_p = L.tau + q;
-  bool pass = cand && row < L.local_rows && key < *tau_p;  // rows of the padded last tile are not rows
-  if (L.has_floor) pass = pass && key > L.floor[q];
+  volatile unsigned long long* tau_p = sm_u64(s_L.tau_off) + q;
+  bool pass = cand && row < s_L.local_rows && key < *tau_p;  // rows of the padded last tile are not rows
+  if (s_L.has_floor) pass = pass && key > sm_u64(s_L.floor_off)[q];
   if (!__any_sync(FULL_MASK, pass)) return;
+  // per-query spin lock with acquire / release semantics on the atomics themselves (no
+  // stand-alone fences: the critical section is a handful of shared-memory accesses)
+  const uint32_t lock = (uint32_t)__cvta_generic_to_shared(sm_u32(s_L.lock_off) + q);
   if (lane == 0) {
-    while (atomicCAS(L.lock + q, 0u, 1u) != 0u) __nanosleep(40);
+    uint32_t old;
+    do {
+      asm volatile("atom.acquire.cta.shared.cas.b32 %0, [%1], 0, 1;" : "=r"(old) : "r"(lock) : "memory");
+    } while (old != 0u);
   }
   __syncwarp();
-  __threadfence_block();
   pass = pass && key < *tau_p;  // threshold may have tightened while we waited
   const unsigned m = __ballot_sync(FULL_MASK, pass);
   if (m) {
-    uint32_t cnt = *reinterpret_cast<volatile uint32_t*>(L.cnt + q);
+    volatile uint32_t* cnt_p = sm_u32(s_L.cnt_off) + q;
+    uint32_t cnt = *cnt_p;
     if (pass) {
       uint32_t pos = cnt + __popc(m & ((1u << lane) - 1u));
-      L.list[(size_t)q * L.cap + pos] = key;
+      sm_u64(s_L.list_off)[(size_t)q * s_L.cap + pos] = key;
     }
     cnt += __popc(m);
     __syncwarp();
-    if (cnt > L.cap - 32) cnt = list_compact(q, cnt, lane);
-    if (lane == 0) *reinterpret_cast<volatile uint32_t*>(L.cnt + q) = cnt;
+    if (cnt > s_L.cap - 32) cnt = list_compact(q, cnt, lane);
+    if (lane == 0) *cnt_p = cnt;
   }
   __syncwarp();
-  __threadfence_block();
-  if (lane == 0) atomicExch(L.lock + q, 0u);
+  if (lane == 0) {
+    uint32_t old;
+    asm volatile("atom.release.cta.shared.exch.b32 %0, [%1], 0;" : "=r"(old) : "r"(lock) : "memory");
+  }
 }
+
+// Insert everything this warp has stashed (grouped by query, one list_offer per distinct query).
+__device__ __noinline__ void stash_flush(int warp, int lane) {
+  unsigned char* base = g_smem + s_L.stash_off + (size_t)warp * (32 * 8 + 32 * 4 + 16);
+  unsigned long long* skey = reinterpret_cast<unsigned long long*>(base);
+  uint32_t* sq = reinterpret_cast<uint32_t*>(base + 32 * 8);
+  volatile uint32_t* scnt = reinterpret_cast<uint32_t*>(base + 32 * 8 + 32 * 4);
+  const uint32_t n = *scnt;
+  __syncwarp();
+  const bool have = (uint32_t)lane < n;
+  const unsigned long long key = have ? skey[lane] : 0ull;
+  const uint32_t q = have ? sq[lane] : 0xFFFFFFFFu;
+  __syncwarp();
+  if (lane == 0) *scnt = 0;
+  unsigned todo = __ballot_sync(FULL_MASK, have);
+  while (todo) {
+    const uint32_t qcur = __shfl_sync(FULL_MASK, q, __ffs(todo) - 1);
+    const bool sel = have && q == qcur;
+    list_offer(qcur, (uint32_t)(key >> 32), (uint32_t)key, sel, lane);
+    todo &= ~__ballot_sync(FULL_MASK, sel);
+  }
+}
+
+// Warp-uniform: lanes with cand offer (key_hi, row) for query q; admissible ones are stashed.
+__device__ __noinline__ void stash_push(uint32_t q, uint32_t key_hi, uint32_t row, bool cand, int warp, int lane) {
+  const unsigned long long key = ((unsigned long long)key_hi << 32) | row;
+  bool pass = cand && row < s_L.local_rows &&
+              key < *reinterpret_cast<volatile unsigned long long*>(sm_u64(s_L.tau_off) + q);
+  if (s_L.has_floor) pass = pass && key > sm_u64(s_L.floor_off)[q];
+  const unsigned m = __ballot_sync(FULL_MASK, pass);
+  if (!m) return;
+  unsigned char* base = g_smem + s_L.stash_off + (size_t)warp * (32 * 8 + 32 * 4 + 16);
+  volatile uint32_t* scnt = reinterpret_cast<uint32_t*>(base + 32 * 8 + 32 * 4);
+  uint32_t n = *scnt;
+  if (n + __popc(m) > 32) {   // no room: insert what is stashed now
+    stash_flush(warp, lane);
+    n = 0;
+  }
+  if (pass) {
+    const uint32_t pos = n + __popc(m & ((1u << lane) - 1u));
+    reinterpret_cast<unsigned long long*>(base)[pos] = key;
+    reinterpret_cast<uint32_t*>(base + 32 * 8)[pos] = q;
+  }
+  __syncwarp();
+  if (lane == 0) *scnt = n + __popc(m);
+  __syncwarp();
+}
+
+__device__ __forceinline__ uint32_t stash_count(const ListCtl& L, int warp) {
+  return *reinterpret_cast<const volatile uint32_t*>(g_smem + L.stash_off + (size_t)warp * (32 * 8 + 32 * 4 + 16) + 32 * 8 + 32 * 4);
+}
+// Insertions are batched: one lock acquisition moves up to 32 candidates, which matters while a
+// CTA's threshold is still loose and every tile yields some.
+static const uint32_t STASH_FLUSH_AT = 16;
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 // a query's shared-memory block: W32 signature words, then the fast-reject threshold word
 // (tau_hi), padded to 16 bytes -- one base address serves the whole inner loop
 __host__ __device__ inline uint32_t q_stride(uint32_t w32) { return w32 + 4; }
 
+// per-warp stash of candidates whose list insertion is deferred until the warp has released
+// the stage it was reading (so a slow insertion never holds up the memory pipeline)
+static const uint32_t STASH = 32;                       // entries per warp
+static const uint32_t STASH_BYTES = STASH * 8 + STASH * 4 + 16;
+static const uint32_t STASH_WARPS = 17;
+
 struct SmemPlan {
-  size_t q_off, lut_off, list_off, tau_off, floor_off, cnt_off, lock_off, tauhi_off, total;
+  size_t q_off, lut_off, list_off, tau_off, floor_off, cnt_off, lock_off, tauhi_off, stash_off, total;
 };
 __host__ __device__ inline SmemPlan plan_smem(uint32_t qp, uint32_t w32, uint32_t cap, bool euclid,
                                               uint32_t hash_num, size_t base) {
@@ -339,6 +419,7 @@ __host__ __device__ inline SmemPlan plan_smem(uint32_t qp, uint32_t w32, uint32_
   p.cnt_off = o; o = align16(o + (size_t)qp * 4);
   p.lock_off = o; o = align16(o + (size_t)qp * 4);
   p.tauhi_off = o;  // (tau_hi lives inside the query blocks)
+  p.stash_off = o; o = align16(o + (size_t)STASH_WARPS * STASH_BYTES);
   p.total = o;
   return p;
 }
@@ -369,8 +450,8 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
     const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
     const bool c1 = k1 <= *reinterpret_cast<const volatile uint32_t*>(b1 + W32);
     if (__any_sync(FULL_MASK, c0 || c1)) {
-      if (__any_sync(FULL_MASK, c0)) list_offer(q, k0, row, c0, lane);
-      if (__any_sync(FULL_MASK, c1)) list_offer(q + 1, k1, row, c1, lane);
+      stash_push(q, k0, row, c0, threadIdx.x >> 5, lane);
+      stash_push(q + 1, k1, row, c1, threadIdx.x >> 5, lane);
     }
   }
   if (q < nqp) {
@@ -382,7 +463,7 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
       k0 = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l0))));
     }
     const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
-    if (__any_sync(FULL_MASK, c0)) list_offer(q, k0, row, c0, lane);
+    if (__any_sync(FULL_MASK, c0)) stash_push(q, k0, row, c0, threadIdx.x >> 5, lane);
   }
 }
 
@@ -410,8 +491,8 @@ __device__ __forceinline__ void rank_tile2(const uint32_t (&ra)[W32], const uint
     const uint32_t tau = *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
     const bool ca = ka <= tau, cb = kb <= tau;
     if (__any_sync(FULL_MASK, ca || cb)) {
-      if (__any_sync(FULL_MASK, ca)) list_offer(q, ka, rowa, ca, lane);
-      if (__any_sync(FULL_MASK, cb)) list_offer(q, kb, rowb, cb, lane);
+      stash_push(q, ka, rowa, ca, threadIdx.x >> 5, lane);
+      stash_push(q, kb, rowb, cb, threadIdx.x >> 5, lane);
     }
   }
 }
@@ -424,16 +505,15 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
   constexpr uint32_t QS = W32 + 4;
   s_q = reinterpret_cast<uint32_t*>(smem + sp.q_off);
   s_lut = reinterpret_cast<double*>(smem + sp.lut_off);
-  L.list = reinterpret_cast<unsigned long long*>(smem + sp.list_off);
-  L.tau = reinterpret_cast<unsigned long long*>(smem + sp.tau_off);
-  L.floor = reinterpret_cast<unsigned long long*>(smem + sp.floor_off);
-  L.cnt = reinterpret_cast<uint32_t*>(smem + sp.cnt_off);
-  L.lock = reinterpret_cast<uint32_t*>(smem + sp.lock_off);
-  L.tau_hi = s_q + W32;
+  L.list_off = (uint32_t)sp.list_off; L.tau_off = (uint32_t)sp.tau_off; L.floor_off = (uint32_t)sp.floor_off;
+  L.cnt_off = (uint32_t)sp.cnt_off; L.lock_off = (uint32_t)sp.lock_off;
+  L.tauhi_off = (uint32_t)(sp.q_off + W32 * 4);
+  L.stash_off = (uint32_t)sp.stash_off;
   L.tau_stride = QS;
   L.local_rows = (uint32_t)a.local_rows;
-  L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr);
+  L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr) ? 1u : 0u;
   if (tid == 0) s_L = L;
+  if ((uint32_t)tid < STASH_WARPS) *reinterpret_cast<uint32_t*>(smem + sp.stash_off + (size_t)tid * STASH_BYTES + STASH * 12) = 0u;
   for (uint32_t i = tid; i < nqp * QS; i += nthreads) {
     uint32_t q = i / QS, w = i % QS;
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)(q0 + q) * a.w64);
@@ -448,8 +528,9 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
     }
   }
   if ((uint32_t)tid < nqp) {
-    L.cnt[tid] = 0; L.lock[tid] = 0; L.tau[tid] = a.tau_init ? a.tau_init[q0 + tid] : KEY_SENTINEL;
-    L.floor[tid] = a.floor_keys ? a.floor_keys[q0 + tid] : 0ull;
+    sm_u32(L.cnt_off)[tid] = 0; sm_u32(L.lock_off)[tid] = 0;
+    sm_u64(L.tau_off)[tid] = a.tau_init ? a.tau_init[q0 + tid] : KEY_SENTINEL;
+    sm_u64(L.floor_off)[tid] = a.floor_keys ? a.floor_keys[q0 + tid] : 0ull;
   }
 }
 
@@ -458,7 +539,7 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
 // ---------------------------------------------------------------------------
 template <int W32, bool EUCLID, int PV>
 __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  unsigned char* smem = g_smem;
   const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t q0 = blockIdx.y * a.qp;
@@ -493,14 +574,16 @@ __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
       if (EUCLID) nnxt = ld_stream_f32(a.norms + tn * 32 + lane);
     }
     rank_tile<W32, EUCLID, PV>(cur, (uint32_t)(t * 32 + lane), (double)ncur, nqp, s_q, s_lut, a.hash_num, L, lane);
+    if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush(warp, lane);   // the next tile's loads are already in flight
 #pragma unroll
     for (int w = 0; w < W32; ++w) cur[w] = nxt[w];
     ncur = nnxt;
   }
+  if (stash_count(L, warp)) stash_flush(warp, lane);
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += SCAN_WARPS) {
-    uint32_t n = list_compact(q, L.cnt[q], lane);
-    const unsigned long long* src = L.list + (size_t)q * a.cap;
+    uint32_t n = list_compact(q, sm_u32(L.cnt_off)[q], lane);
+    const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
                               ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
     for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n) ? src[j] : KEY_SENTINEL;
@@ -582,7 +665,7 @@ __device__ __forceinline__ void load_row_smem(const unsigned char* stage, uint32
 
 template <int W32, bool EUCLID, int PV>
 __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, uint32_t stages, uint32_t tiles_per_warp) {
-  extern __shared__ __align__(128) unsigned char smem[];
+  unsigned char* smem = g_smem;
   const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0);
   const TmaPlan tp = plan_tma(a.qp, W32, a.cap, EUCLID, a.hash_num, stages, tiles_per_warp);
   unsigned char* ring = smem + tp.ring_off;
@@ -671,14 +754,16 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
         }
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(empty_bar + s);
+      if (lane == 0) mbar_arrive(empty_bar + s);   // release the stage first ...
+      if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush(warp, lane);   // ... then do the slow insertions
       if (++s == stages) { s = 0; ph ^= 1u; }
     }
+    if (stash_count(L, warp)) stash_flush(warp, lane);
   }
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += TMA_CONSUMER_WARPS + 1) {
-    uint32_t n = list_compact(q, L.cnt[q], lane);
-    const unsigned long long* src = L.list + (size_t)q * a.cap;
+    uint32_t n = list_compact(q, sm_u32(L.cnt_off)[q], lane);
+    const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
                               ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
     for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n) ? src[j] : KEY_SENTINEL;
