@@ -162,11 +162,13 @@ int jubann_set_rows_sig_dev(jubann_t* h, uint64_t n, uint64_t first_row_index,
  * candidate lists) is a fixed array of JUBANN_NOALLOC_SCRATCH_BYTES inside the library image
  * instead of a buffer grown with cudaMalloc; every GPU that loads the library holds it until
  * exit.  This call allocates and frees nothing.  It needs nq * (chunks * min(k, rows) + 1) * 8
- * bytes (chunks <= 2 per SM); a larger request, or k above 2048, returns JUBANN_E_INVALID
+ * + nq * (hash_num + 33) * 4 bytes (chunks <= 2 per SM); a larger request, or k above 2048,
+ * returns JUBANN_E_INVALID
  * with a message.  The first call on a device looks up the array's address
  * (cudaGetSymbolAddress): make it at start-up, before any stream capture.  Calls share the
- * array and it keeps the previous call's contents; nothing in it needs to start at zero, and
- * calls whose GPU work overlaps race on it -- keep them on one stream.  Single-shard
+ * array and it keeps the previous call's contents (the part that must start at zero, a small
+ * histogram, is cleared on the stream by each call); calls whose GPU work overlaps race on it --
+ * keep them on one stream.  Single-shard
  * handles only. */
 #define JUBANN_NOALLOC_SCRATCH_BYTES (32u << 20)
 int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms,

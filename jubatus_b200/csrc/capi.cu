@@ -72,7 +72,7 @@ struct jubann {
   int interleave_opt = 1;
   // staging (grow-only)
   DevBuf b_indptr, b_seed, b_keyhash, b_vals, b_rowidx, b_sigs, b_norms;
-  DevBuf b_qsigs, b_qnorms, b_out_idx, b_out_score, b_out_count, b_cand, b_floor, b_tau;
+  DevBuf b_qsigs, b_qnorms, b_out_idx, b_out_score, b_out_count, b_cand, b_floor, b_tau, b_hist;
   // stats
   uint64_t kernel_launches = 0, scan_launches = 0, scan_passes = 0;
   bool time_scan = false;
@@ -329,6 +329,7 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
   CK(h->b_cand.ensure((size_t)nq_launch * per_query));
   if (pages > 1) CK(h->b_floor.ensure((size_t)nq * 8));
   CK(h->b_tau.ensure((size_t)nq_launch * 8));
+  CK(h->b_hist.ensure(hist_scratch_bytes(nq_launch, h->hash_num)));
   for (uint32_t q0 = 0; q0 < nq; q0 += nq_launch) {
     const uint32_t nql = std::min(nq_launch, nq - q0);
     for (uint32_t p = 0; p < pages; ++p) {
@@ -337,7 +338,7 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
       cudaEvent_t ea, eb;
       record_scan_begin(h, s, &ea, &eb);
       CK(launch_scan(t, euclid, cfg, d_qsigs + (size_t)q0 * h->w64, d_qnorms ? d_qnorms + q0 : nullptr,
-                     h->d_coslut, nql, kthis, floor, h->b_tau.as<uint64_t>(), h->b_cand.as<uint64_t>(), s));
+                     h->d_coslut, nql, kthis, floor, h->b_tau.as<uint64_t>(), h->b_hist.as<uint32_t>(), h->b_cand.as<uint64_t>(), s));
       record_scan_end(h, s, ea, eb);
       MergeOut o{};
       o.kout = k; o.col0 = p * kpage;
@@ -457,7 +458,7 @@ int jubann_destroy(jubann_t* h) {
     if (h->d_coslut) cudaFree(h->d_coslut);
     if (h->h_counters) cudaFreeHost(h->h_counters);
     DevBuf* bufs[] = {&h->b_indptr, &h->b_seed, &h->b_keyhash, &h->b_vals, &h->b_rowidx, &h->b_sigs, &h->b_norms,
-                      &h->b_qsigs, &h->b_qnorms, &h->b_out_idx, &h->b_out_score, &h->b_out_count, &h->b_cand, &h->b_floor, &h->b_tau};
+                      &h->b_qsigs, &h->b_qnorms, &h->b_out_idx, &h->b_out_score, &h->b_out_count, &h->b_cand, &h->b_floor, &h->b_tau, &h->b_hist};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : h->scan_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
     if (h->stream) cudaStreamDestroy(h->stream);

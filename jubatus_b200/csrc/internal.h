@@ -67,6 +67,10 @@ struct ScanConfig {
 bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int variant, int popc_variant,
                uint32_t qp_opt, int interleave, int num_sms, ScanConfig* cfg);
 uint32_t max_k_per_pass();
+// d_hist_scratch (nullable, hamming engines): hist_scratch_bytes(nq, hash_num) of scratch for the
+// distance histogram all CTAs share to derive a GPU-wide bound
+uint32_t hist_stride_for(uint32_t hash_num);
+size_t hist_scratch_bytes(uint32_t nq, uint32_t hash_num);
 void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages);  // tuning experiments; 0 = automatic
 
 // cand: [nq][nchunks][k] keys ((key_hi << 32) | local row) in no particular order, KEY_SENTINEL padded.
@@ -74,7 +78,8 @@ void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages);  // tu
 // d_tau_scratch (nullable): nq u64 of scratch for the sample pre-pass that seeds the thresholds.
 cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, const uint64_t* d_qsigs,
                         const float* d_qnorms, const double* d_coslut, uint32_t nq, uint32_t k,
-                        const uint64_t* d_floor_keys, uint64_t* d_tau_scratch, uint64_t* d_cand, cudaStream_t s);
+                        const uint64_t* d_floor_keys, uint64_t* d_tau_scratch, uint32_t* d_hist_scratch,
+                        uint64_t* d_cand, cudaStream_t s);
 
 // Per query: k smallest keys among nlists*k candidates.  If d_out_index != nullptr writes the
 // final (index, score, count) outputs at column offset `col0` of rows of width `kout`;

@@ -16,15 +16,17 @@
 //  * The array is part of the library image: every GPU that loads libjubann.so holds
 //    JUBANN_NOALLOC_SCRATCH_BYTES (32 MiB) of device memory until the process exits,
 //    whether or not this entry point is ever called.
-//  * A call needs  nq * (chunks * min(k, rows) + 1) * 8  bytes of it (chunks = CTAs along the
+//  * A call needs  nq * (chunks * min(k, rows) + 1) * 8 + nq * (hash_num + 33) * 4  bytes of it (chunks = CTAs along the
 //    table, at most 2 per SM).  A request that does not fit, or k above the single-pass
 //    limit of 2048, is refused with JUBANN_E_INVALID and a message; nothing is launched.
 //  * The first call on a device looks up the array's device address
 //    (cudaGetSymbolAddress).  Make that first call during start-up, before any stream
 //    capture is begun.
 //  * All calls on a device share the one array, and it keeps whatever the last call left in
-//    it.  Nothing in it has to start at zero: every slot the merge kernel reads is written by
-//    the scan kernel of the same call, so no clearing is done.  Two calls whose GPU work
+//    it.  The candidate slots need no clearing (every slot the merge kernel reads is written
+//    by the scan kernel of the same call); the part that must start from a known state -- the
+//    distance histogram and bound words the CTAs share -- is reset on the stream
+//    (cudaMemsetAsync) at the start of every call.  Two calls whose GPU work
 //    overlaps (different streams, different handles or threads) would overwrite each other's
 //    candidates -- run them on one stream or order them yourself.
 //  * Inputs and outputs are the caller's device buffers, exactly as for
@@ -118,7 +120,8 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   if (keff) {
     if (!plan_scan(hi.table, hi.euclid, nq, keff, hi.variant, hi.popc_variant, hi.qp, hi.interleave, hi.num_sms, &cfg))
       return set_error(JUBANN_E_INVALID, "no-alloc query: cannot plan a scan for this k");
-    const uint64_t need = (uint64_t)nq * cfg.nchunks * keff * 8ull + (uint64_t)nq * 8ull;  // lists + one threshold per query
+    const uint64_t need = (uint64_t)nq * cfg.nchunks * keff * 8ull + (uint64_t)nq * 8ull +   // lists + one threshold per query
+                          hist_scratch_bytes(nq, hi.table.hash_num);                          // + shared distance histogram
     if (need > (uint64_t)JUBANN_NOALLOC_SCRATCH_BYTES) {
       snprintf(msg, sizeof(msg),
                "no-alloc query: %u queries x %u table chunks x k=%u need %llu bytes of scratch, the fixed array holds %llu; "
@@ -136,7 +139,8 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   if (e != cudaSuccess) return cuda_error("cudaMemsetAsync(out_count)", e);
   if (keff == 0) return 0;
   uint64_t* tau_scratch = static_cast<uint64_t*>(scratch) + (size_t)nq * cfg.nchunks * keff;
-  e = launch_scan(hi.table, hi.euclid, cfg, d_qsigs, d_qnorms, hi.coslut, nq, keff, nullptr, tau_scratch,
+  uint32_t* hist_scratch = reinterpret_cast<uint32_t*>(tau_scratch + nq);
+  e = launch_scan(hi.table, hi.euclid, cfg, d_qsigs, d_qnorms, hi.coslut, nq, keff, nullptr, tau_scratch, hist_scratch,
                   static_cast<uint64_t*>(scratch), s);
   if (e != cudaSuccess) return cuda_error("scan launch (no-alloc)", e);
   MergeOut o{};

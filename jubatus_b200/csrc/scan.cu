@@ -39,6 +39,8 @@ struct ScanArgs {
   const float* qnorms;
   const double* coslut;
   const uint64_t* floor_keys;
+  uint32_t* ghist;            // hamming only: [nq] shared bound words, then [nq][hist_stride] distance counts (nullable)
+  uint32_t hist_stride;
   const uint64_t* tau_init;   // per query: exclusive upper bound of admissible keys from the sample pre-pass (nullable)
   uint64_t* cand;
   uint32_t nq, k, cap, qp, w64, hash_num, tiles_per_chunk, nchunks;
@@ -254,6 +256,8 @@ struct ListCtl {
   uint32_t local_rows;
   uint32_t cap, k;
   uint32_t has_floor;
+  uint32_t nq, q0, hist_stride;
+  uint32_t* ghist;     // global: [nq] bound words | [nq][hist_stride] counts; nullptr when unused
 };
 __shared__ ListCtl s_L;   // written once by the prologue, read by the rare-path functions
 
@@ -293,9 +297,9 @@ __device__ __noinline__ uint32_t list_compact(uint32_t q, uint32_t cnt, int lane
     w += __popc(m);
     __syncwarp();
   }
-  if (lane == 0) {
-    *reinterpret_cast<volatile unsigned long long*>(sm_u64(s_L.tau_off) + q) = prefix;
-    *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride) = tau_hi_of(prefix);
+  if (lane == 0) {   // atomicMin: a tighter bound may have arrived from the shared histogram meanwhile
+    atomicMin(sm_u64(s_L.tau_off) + q, prefix);
+    atomicMin(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride, tau_hi_of(prefix));
   }
   __syncwarp();
   return w;
@@ -339,6 +343,43 @@ __device__ __noinline__ void list_offer(uint32_t q, uint32_t key_hi, uint32_t ro
   }
 }
 
+// Hamming only.  Every inserted candidate is also counted in a histogram of distances shared
+// by all CTAs (global memory).  If the counts of distances <= D add up to k, k rows with
+// distance <= D exist, so no key with distance > D can be in the top k: (D + 1) << 32 is a valid
+// bound for every CTA.  Unlike a CTA's own k-th best it reflects what the whole GPU has seen.
+__device__ __forceinline__ void apply_shared_bound(uint32_t q, uint32_t D) {
+  atomicMin(sm_u64(s_L.tau_off) + q, ((unsigned long long)D + 1ull) << 32);
+  atomicMin(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride, D);
+}
+
+__device__ __noinline__ void hist_refresh(uint32_t q, int lane) {
+  const uint32_t gq = s_L.q0 + q;
+  const volatile uint32_t* h = s_L.ghist + s_L.nq + (size_t)gq * s_L.hist_stride;
+  const uint32_t cur = *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride);
+  const uint32_t limit = min(cur, s_L.hist_stride - 1);   // only a bound below the current one is of interest
+  uint32_t run = 0;
+  for (uint32_t base = 0; base <= limit; base += 32) {
+    const uint32_t d = base + lane;
+    uint32_t v = (d <= limit) ? h[d] : 0u;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t n = __shfl_up_sync(FULL_MASK, v, o);
+      if (lane >= o) v += n;
+    }
+    const unsigned hit = __ballot_sync(FULL_MASK, run + v >= s_L.k);
+    if (hit) {
+      const uint32_t D = base + (__ffs(hit) - 1);
+      if (lane == 0 && D < cur) {
+        apply_shared_bound(q, D);
+        atomicMin(s_L.ghist + gq, D);   // publish for CTAs that insert rarely
+      }
+      break;
+    }
+    run += __shfl_sync(FULL_MASK, v, 31);
+  }
+  __syncwarp();
+}
+
 // Insert everything this warp has stashed (grouped by query, one list_offer per distinct query).
 __device__ __noinline__ void stash_flush(int warp, int lane) {
   unsigned char* base = g_smem + s_L.stash_off + (size_t)warp * (32 * 8 + 32 * 4 + 16);
@@ -352,12 +393,26 @@ __device__ __noinline__ void stash_flush(int warp, int lane) {
   const uint32_t q = have ? sq[lane] : 0xFFFFFFFFu;
   __syncwarp();
   if (lane == 0) *scnt = 0;
+  if (s_L.ghist && have) atomicAdd(s_L.ghist + s_L.nq + (size_t)(s_L.q0 + q) * s_L.hist_stride + (uint32_t)(key >> 32), 1u);
   unsigned todo = __ballot_sync(FULL_MASK, have);
   while (todo) {
     const uint32_t qcur = __shfl_sync(FULL_MASK, q, __ffs(todo) - 1);
     const bool sel = have && q == qcur;
     list_offer(qcur, (uint32_t)(key >> 32), (uint32_t)key, sel, lane);
+    if (s_L.ghist) hist_refresh(qcur, lane);
     todo &= ~__ballot_sync(FULL_MASK, sel);
+  }
+}
+
+// One warp per CTA polls the bounds other CTAs have published (a coalesced read of nqp words).
+__device__ __forceinline__ void poll_shared_bounds(const ListCtl& L, uint32_t nqp, int lane) {
+  if (L.ghist == nullptr) return;
+  for (uint32_t q = lane; q < nqp; q += 32) {
+    const uint32_t D = *reinterpret_cast<const volatile uint32_t*>(L.ghist + L.q0 + q);
+    if (D < *reinterpret_cast<const volatile uint32_t*>(sm_u32(L.tauhi_off) + (size_t)q * L.tau_stride)) {
+      atomicMin(sm_u64(L.tau_off) + q, ((unsigned long long)D + 1ull) << 32);
+      atomicMin(sm_u32(L.tauhi_off) + (size_t)q * L.tau_stride, D);
+    }
   }
 }
 
@@ -512,6 +567,7 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
   L.tau_stride = QS;
   L.local_rows = (uint32_t)a.local_rows;
   L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr) ? 1u : 0u;
+  L.nq = a.nq; L.q0 = q0; L.hist_stride = a.hist_stride; L.ghist = EUCLID ? nullptr : a.ghist;
   if (tid == 0) s_L = L;
   if ((uint32_t)tid < STASH_WARPS) *reinterpret_cast<uint32_t*>(smem + sp.stash_off + (size_t)tid * STASH_BYTES + STASH * 12) = 0u;
   for (uint32_t i = tid; i < nqp * QS; i += nthreads) {
@@ -563,6 +619,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
   }
   uint32_t cur[W32], nxt[W32];
   float ncur = 0.0f, nnxt = 0.0f;
+  uint32_t poll_tick = 0;
   if (t < t_end) {
     load_row<W32>(a.slab, t, lane, cur);
     if (EUCLID) ncur = ld_stream_f32(a.norms + t * 32 + lane);
@@ -575,6 +632,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
     }
     rank_tile<W32, EUCLID, PV>(cur, (uint32_t)(t * 32 + lane), (double)ncur, nqp, s_q, s_lut, a.hash_num, L, lane);
     if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush(warp, lane);   // the next tile's loads are already in flight
+    if (warp == 0 && ((++poll_tick) & 7u) == 0u) poll_shared_bounds(L, nqp, lane);
 #pragma unroll
     for (int w = 0; w < W32; ++w) cur[w] = nxt[w];
     ncur = nnxt;
@@ -756,6 +814,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_bar + s);   // release the stage first ...
       if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush(warp, lane);   // ... then do the slow insertions
+      if (warp == 0) poll_shared_bounds(L, nqp, lane);
       if (++s == stages) { s = 0; ph ^= 1u; }
     }
     if (stash_count(L, warp)) stash_flush(warp, lane);
@@ -969,6 +1028,8 @@ __global__ void __launch_bounds__(TAU_THREADS) tau_init_kernel(ScanArgs a, uint3
 // host side
 // ---------------------------------------------------------------------------
 uint32_t max_k_per_pass() { return MAX_CAP / 2; }
+uint32_t hist_stride_for(uint32_t hash_num) { return (hash_num + 1 + 31) / 32 * 32; }
+size_t hist_scratch_bytes(uint32_t nq, uint32_t hash_num) { return ((size_t)nq + (size_t)nq * hist_stride_for(hash_num)) * 4; }
 
 static uint32_t g_tma_tpw_override = 0, g_tma_stages_override = 0;
 void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages) {
@@ -1074,7 +1135,8 @@ static cudaError_t launch_scan_w(uint32_t w32, const ScanArgs& a, const ScanConf
 
 cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, const uint64_t* d_qsigs,
                         const float* d_qnorms, const double* d_coslut, uint32_t nq, uint32_t k,
-                        const uint64_t* d_floor_keys, uint64_t* d_tau_scratch, uint64_t* d_cand, cudaStream_t s) {
+                        const uint64_t* d_floor_keys, uint64_t* d_tau_scratch, uint32_t* d_hist_scratch,
+                        uint64_t* d_cand, cudaStream_t s) {
   ScanArgs a;
   a.slab = static_cast<const unsigned char*>(t.slab);
   a.norms = t.norms;
@@ -1082,6 +1144,7 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   a.ntiles = (t.local_rows + 31) / 32;
   a.qsigs = d_qsigs; a.qnorms = d_qnorms; a.coslut = d_coslut; a.floor_keys = d_floor_keys;
   a.tau_init = nullptr;
+  a.ghist = nullptr; a.hist_stride = hist_stride_for(t.hash_num);
   a.cand = d_cand;
   a.nq = nq; a.k = k; a.cap = cfg.cap; a.qp = cfg.qp; a.w64 = t.w64; a.hash_num = t.hash_num;
   a.tiles_per_chunk = cfg.tiles_per_chunk; a.nchunks = cfg.nchunks;
@@ -1101,6 +1164,12 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
       if (e != cudaSuccess) return e;
       a.tau_init = d_tau_scratch;
     }
+  }
+  if (d_hist_scratch && !euclid && t.local_rows >= (1u << 16)) {
+    cudaError_t e = cudaMemsetAsync(d_hist_scratch, 0xFF, (size_t)nq * 4, s);   // published bounds: none yet
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_hist_scratch + nq, 0, (size_t)nq * a.hist_stride * 4, s);
+    if (e != cudaSuccess) return e;
+    a.ghist = d_hist_scratch;
   }
   dim3 grid(cfg.nchunks, (nq + cfg.qp - 1) / cfg.qp, 1);
   return euclid ? launch_scan_w<true>(t.w32, a, cfg, grid, s) : launch_scan_w<false>(t.w32, a, cfg, grid, s);
