@@ -457,7 +457,7 @@ __host__ __device__ inline uint32_t q_stride(uint32_t w32) { return w32 + 4; }
 // the stage it was reading (so a slow insertion never holds up the memory pipeline)
 static const uint32_t STASH = 32;                       // entries per warp
 static const uint32_t STASH_BYTES = STASH * 8 + STASH * 4 + 16;
-static const uint32_t STASH_WARPS = 17;
+static const uint32_t STASH_WARPS = 33;
 
 struct SmemPlan {
   size_t q_off, lut_off, list_off, tau_off, floor_off, cnt_off, lock_off, tauhi_off, stash_off, total;
@@ -657,7 +657,10 @@ __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
 // passes through registers before it is needed, so the kernel is spill-free at 1 CTA / SM
 // and the memory pipeline runs ahead of the popcount work by several stages.
 // ---------------------------------------------------------------------------
-static const int TMA_CONSUMER_WARPS = 16;
+#ifndef JBN_TMA_CW
+#define JBN_TMA_CW 16
+#endif
+static const int TMA_CONSUMER_WARPS = JBN_TMA_CW;
 static const int TMA_THREADS = (TMA_CONSUMER_WARPS + 1) * 32;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -1046,13 +1049,17 @@ static uint32_t list_cap_for(uint32_t k) {
 bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int variant, int popc_variant,
                uint32_t qp_opt, int interleave, int num_sms, ScanConfig* cfg) {
   if (k == 0 || k > max_k_per_pass()) return false;
-  cfg->variant = variant <= 0 ? 1 : variant;
   cfg->popc_variant = popc_variant < 0 ? 0 : popc_variant;
   cfg->cap = list_cap_for(k);
   const uint64_t ntiles = (t.local_rows + 31) / 32;
-  uint32_t qp = qp_opt ? qp_opt : 8;
+  // queries sharing one pass: by default as many as amortise the HBM stream (the scan is then
+  // bound by the popcount pipes); callers that want the HBM-bound regime ask for 1..2
+  uint32_t qp = qp_opt ? qp_opt : 16;
   if (qp > nq) qp = nq;
   if (qp < 1) qp = 1;
+  // automatic variant: the TMA ring wins while the pass is memory-bound, the LDG kernel's
+  // 32 resident warps win once it is popcount-bound (measured crossover at 6..8 queries per pass)
+  cfg->variant = variant <= 0 ? (qp <= 6 ? 2 : 1) : variant;
   cfg->stages = 0; cfg->tiles_per_warp = 0;
   cfg->interleave = interleave ? 1u : 0u;
   uint64_t max_chunks;
