@@ -552,6 +552,39 @@ __device__ __forceinline__ void rank_tile2(const uint32_t (&ra)[W32], const uint
   }
 }
 
+// Register-resident queries (TMA variant, <= 4 queries per pass): the CTA's queries are loaded
+// into registers once, thresholds are re-read once per stage, so the inner loop touches shared
+// memory only for the rows themselves.  NR rows (tiles) are ranked together.
+template <int W32, bool EUCLID, int PV, int NQ, int NR>
+__device__ __forceinline__ void rank_reg(const uint32_t (&rows)[NR][W32], const uint32_t (&rowid)[NR],
+                                         const double (&ni)[NR], const uint32_t (&qreg)[NQ][W32],
+                                         const uint32_t (&tau)[NQ], const double* s_lut, uint32_t hash_num,
+                                         int warp, int lane) {
+  uint32_t key[NQ][NR];
+  bool any = false;
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+      const uint32_t d = hamming_rq<W32, PV>(rows[r], qreg[q]);
+      uint32_t kk = d;
+      if (EUCLID) {
+        const double l2 = s_lut[q * (hash_num + 1) + d];
+        kk = float_key(__double2float_rn(__dmul_rn(ni[r], __dsub_rn(ni[r], l2))));
+      }
+      key[q][r] = kk;
+      any = any || (kk <= tau[q]);
+    }
+  }
+  if (__any_sync(FULL_MASK, any)) {
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+#pragma unroll
+      for (int r = 0; r < NR; ++r) stash_push(q, key[q][r], rowid[r], key[q][r] <= tau[q], warp, lane);
+    }
+  }
+}
+
 // shared prologue: query blocks, euclid LUT, list control
 template <int W32, bool EUCLID>
 __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* smem, const SmemPlan& sp, ListCtl& L,
@@ -658,7 +691,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
 // and the memory pipeline runs ahead of the popcount work by several stages.
 // ---------------------------------------------------------------------------
 #ifndef JBN_TMA_CW
-#define JBN_TMA_CW 16
+#define JBN_TMA_CW 15   // 15 consumer warps + 1 producer warp = 512 threads: 128 registers per thread at 1 CTA/SM
 #endif
 static const int TMA_CONSUMER_WARPS = JBN_TMA_CW;
 static const int TMA_THREADS = (TMA_CONSUMER_WARPS + 1) * 32;
@@ -724,7 +757,7 @@ __device__ __forceinline__ void load_row_smem(const unsigned char* stage, uint32
   }
 }
 
-template <int W32, bool EUCLID, int PV>
+template <int W32, bool EUCLID, int PV, int NQ>
 __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, uint32_t stages, uint32_t tiles_per_warp) {
   unsigned char* smem = g_smem;
   const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0);
@@ -791,10 +824,47 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
     // ---- consumers: warp w owns tiles 2w, 2w+1 (+ 2*16 per further pair) of every stage ----
     uint32_t s = 0, ph = 0;
     uint64_t t0 = t_first;
+    constexpr int NQR = NQ > 0 ? NQ : 1;
+    constexpr uint32_t QS = W32 + 4;
+    uint32_t qreg[NQR][W32];
+    if (NQ > 0) {
+#pragma unroll
+      for (int q = 0; q < NQR; ++q) load_query<W32>(s_q + q * QS, qreg[q]);
+    }
     for (uint32_t it = 0; it < iters; ++it, t0 += t_stride) {
       mbar_wait(full_bar + s, ph);
       const unsigned char* stage = ring + s * stage_bytes;
       const float* nstage = nring + (size_t)s * stage_tiles * 32;
+      if (NQ > 0) {
+        uint32_t tau[NQR];
+#pragma unroll
+        for (int q = 0; q < NQR; ++q) tau[q] = *reinterpret_cast<const volatile uint32_t*>(s_q + q * QS + W32);
+        for (uint32_t j = 0; j < tiles_per_warp; j += 2) {
+          const uint32_t tis = (j * TMA_CONSUMER_WARPS) + 2 * warp;
+          const uint64_t t = t0 + tis;
+          if (t >= t_end) break;
+          const uint32_t rowa = (uint32_t)(t * 32 + lane);
+          if (NQ <= 2 && t + 1 < t_end) {
+            uint32_t rows[2][W32];
+            load_row_smem<W32>(stage, tis, lane, rows[0]);
+            load_row_smem<W32>(stage, tis + 1, lane, rows[1]);
+            const uint32_t rowid[2] = {rowa, rowa + 32};
+            double ni[2] = {0.0, 0.0};
+            if (EUCLID) { ni[0] = (double)nstage[tis * 32 + lane]; ni[1] = (double)nstage[(tis + 1) * 32 + lane]; }
+            rank_reg<W32, EUCLID, PV, NQR, 2>(rows, rowid, ni, qreg, tau, s_lut, a.hash_num, warp, lane);
+          } else {
+            const uint32_t ntile = (t + 1 < t_end) ? 2u : 1u;
+            for (uint32_t u = 0; u < ntile; ++u) {
+              uint32_t rows[1][W32];
+              load_row_smem<W32>(stage, tis + u, lane, rows[0]);
+              const uint32_t rowid[1] = {rowa + 32 * u};
+              double ni[1] = {0.0};
+              if (EUCLID) ni[0] = (double)nstage[(tis + u) * 32 + lane];
+              rank_reg<W32, EUCLID, PV, NQR, 1>(rows, rowid, ni, qreg, tau, s_lut, a.hash_num, warp, lane);
+            }
+          }
+        }
+      } else
       for (uint32_t j = 0; j < tiles_per_warp; j += 2) {
         const uint32_t tis = (j * TMA_CONSUMER_WARPS) + 2 * warp;
         const uint64_t t = t0 + tis;
@@ -1067,9 +1137,9 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
     // one CTA per SM; ring of >= 2 stages of ~32 KB; the rest of shared memory for the lists
     const size_t budget = 226 * 1024;
     uint32_t tpw = 2;  // consumer warps take tiles in pairs
-    while ((size_t)TMA_CONSUMER_WARPS * tpw * t.w32 * 128 < 64 * 1024) tpw <<= 1;
-    while (qp > 1 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) --qp;
+    while ((size_t)TMA_CONSUMER_WARPS * tpw * t.w32 * 128 < 48 * 1024) tpw <<= 1;
     while (tpw > 2 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) tpw >>= 1;
+    while (qp > 1 && plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) --qp;
     if (plan_tma(qp, t.w32, cfg->cap, euclid, t.hash_num, 2, tpw).total > budget) {
       // the ring does not fit beside the lists (very wide rows / very large k): stream with LDG instead
       return plan_scan(t, euclid, nq, k, 1, popc_variant, qp_opt, interleave, num_sms, cfg);
@@ -1100,14 +1170,30 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
   return true;
 }
 
+template <int W32, bool EUCLID, int PV, int NQ>
+static cudaError_t launch_tma_t(const ScanArgs& a, const ScanConfig& cfg, dim3 grid, cudaStream_t s) {
+  auto kern = scan_tma_kernel<W32, EUCLID, PV, NQ>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem_bytes);
+  if (e != cudaSuccess) return e;
+  kern<<<grid, TMA_THREADS, cfg.smem_bytes, s>>>(a, cfg.stages, cfg.tiles_per_warp);
+  return cudaGetLastError();
+}
+
 template <int W32, bool EUCLID, int PV>
 static cudaError_t launch_scan_t(const ScanArgs& a, const ScanConfig& cfg, dim3 grid, cudaStream_t s) {
   if (cfg.variant == 2) {
-    auto kern = scan_tma_kernel<W32, EUCLID, PV>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem_bytes);
-    if (e != cudaSuccess) return e;
-    kern<<<grid, TMA_THREADS, cfg.smem_bytes, s>>>(a, cfg.stages, cfg.tiles_per_warp);
-    return cudaGetLastError();
+    // register-resident queries for the common signature widths when every group is full
+    if ((W32 == 8 || W32 == 16) && (PV == 1 || PV == 3) && a.qp <= 4 && a.nq % a.qp == 0) {
+      constexpr int W = (W32 == 8 || W32 == 16) ? W32 : 16;
+      constexpr int P = (PV == 1 || PV == 3) ? PV : 1;
+      switch (a.qp) {
+        case 1: return launch_tma_t<W, EUCLID, P, 1>(a, cfg, grid, s);
+        case 2: return launch_tma_t<W, EUCLID, P, 2>(a, cfg, grid, s);
+        case 3: return launch_tma_t<W, EUCLID, P, 3>(a, cfg, grid, s);
+        default: return launch_tma_t<W, EUCLID, P, 4>(a, cfg, grid, s);
+      }
+    }
+    return launch_tma_t<W32, EUCLID, PV, 0>(a, cfg, grid, s);
   }
   auto kern = scan_ldg_kernel<W32, EUCLID, PV>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem_bytes);
