@@ -330,8 +330,11 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
   if (pages > 1) CK(h->b_floor.ensure((size_t)nq * 8));
   CK(h->b_tau.ensure((size_t)nq_launch * 8));
   CK(h->b_hist.ensure(hist_scratch_bytes(nq_launch, h->hash_num)));
-  for (uint32_t q0 = 0; q0 < nq; q0 += nq_launch) {
-    const uint32_t nql = std::min(nq_launch, nq - q0);
+  for (uint32_t q0 = 0, nql = 0; q0 < nq; q0 += nql) {
+    nql = std::min(nq_launch, nq - q0);
+    // keep every launch made of full groups (they run the register-resident kernels); a
+    // remainder smaller than one group gets a launch of its own
+    if (nql > cfg.qp && nql % cfg.qp) nql -= nql % cfg.qp;
     for (uint32_t p = 0; p < pages; ++p) {
       const uint32_t kthis = std::min(kpage, keff - p * kpage);
       const uint64_t* floor = (p == 0) ? nullptr : h->b_floor.as<uint64_t>() + q0;

@@ -1128,8 +1128,8 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
   if (qp > nq) qp = nq;
   if (qp < 1) qp = 1;
   // automatic variant: the TMA ring wins while the pass is memory-bound, the LDG kernel's
-  // 32 resident warps win once it is popcount-bound (measured crossover at 6..8 queries per pass)
-  cfg->variant = variant <= 0 ? (qp <= 6 ? 2 : 1) : variant;
+  // 32 resident warps win once it is popcount-bound (measured crossover between 4 and 8 queries per pass)
+  cfg->variant = variant <= 0 ? (qp <= 4 ? 2 : 1) : variant;
   cfg->stages = 0; cfg->tiles_per_warp = 0;
   cfg->interleave = interleave ? 1u : 0u;
   uint64_t max_chunks;
