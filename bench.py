@@ -363,7 +363,8 @@ def run_b200(a):
     micro = {}
     try:
         prof = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json")))
-        traffic = prof.get("dram_bytes_per_launch")
+        if prof.get("algorithmic_bytes_per_pass") == local_rows * row_bytes:   # captured on this very workload
+            traffic = prof["dram_bytes_per_pass"] * (st["scan_passes"] / float(max(1, st["scan_launches"])))
     except Exception:
         pass
     try:
