@@ -154,6 +154,18 @@ int jubann_query_sig_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, cons
 int jubann_set_rows_sig_dev(jubann_t* h, uint64_t n, uint64_t first_row_index,
                             const uint64_t* d_sigs, const float* d_norms, void* stream);
 
+/* Device-resident forms of jubann_hash_csr / jubann_set_rows_csr (same reference functions:
+ * lsh_function::random_projection + binarize, euclid_lsh::calc_norm, minhash::hash, then
+ * column_table::add): the CSR batch is already in device memory (indptr[n+1] starting at 0,
+ * nnz = indptr[n]); rows are stored at first_row_index .. first_row_index + n - 1.  For
+ * lsh / euclid_lsh the stream is synchronised once per call (features never seen before get
+ * their projection-cache rows first). */
+int jubann_hash_csr_dev(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d_indptr, const uint32_t* d_seed32,
+                        const uint64_t* d_keyhash64, const float* d_vals, uint64_t* d_out_sigs, float* d_out_norms,
+                        void* stream);
+int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, uint64_t nnz, const uint64_t* d_indptr,
+                            const uint32_t* d_seed32, const uint64_t* d_keyhash64, const float* d_vals, void* stream);
+
 /* No counterpart in the reference.  Same inputs, outputs and results as
  * jubann_query_sig_dev, for callers that may not allocate device memory once they are
  * running: a server whose GPU memory is parcelled out at start-up by its own pool, RPC

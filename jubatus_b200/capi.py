@@ -18,7 +18,7 @@ EXPORTS = [
     "jubann_query_sig", "jubann_query_csr", "jubann_query_rows", "jubann_query_sig_dev",
     "jubann_set_rows_sig_dev", "jubann_scan_local_dev", "jubann_merge_dev",
     "jubann_diff_record_bytes", "jubann_diff_pack_dev", "jubann_diff_apply_dev", "jubann_stats",
-    "jubann_stats_reset", "jubann_query_sig_noalloc_dev",
+    "jubann_stats_reset", "jubann_query_sig_noalloc_dev", "jubann_hash_csr_dev", "jubann_set_rows_csr_dev",
 ]
 
 
@@ -76,6 +76,8 @@ def load_library():
         "jubann_query_sig_noalloc_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp,
                                          _vp],
         "jubann_set_rows_sig_dev": [H, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp],
+        "jubann_hash_csr_dev": [H, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+        "jubann_set_rows_csr_dev": [H, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp, _vp, _vp],
         "jubann_scan_local_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, _vp, _vp, _vp],
         "jubann_merge_dev": [H, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp, ctypes.c_uint32,
                              _vp, _vp, _vp, _vp],
@@ -253,6 +255,17 @@ class Engine(object):
     def set_rows_sig_dev(self, n, first_row_index, d_sigs, d_norms=0, stream=0):
         _check(self._lib.jubann_set_rows_sig_dev(self._h, int(n), int(first_row_index), _vp(d_sigs),
                                                  _vp(d_norms) if d_norms else None, _vp(stream) if stream else None))
+
+    def hash_csr_dev(self, n, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, d_out_sigs, d_out_norms, stream=0):
+        _check(self._lib.jubann_hash_csr_dev(self._h, int(n), int(nnz), _vp(d_indptr), _vp(d_seed32) if d_seed32 else None,
+                                             _vp(d_keyhash64) if d_keyhash64 else None, _vp(d_vals), _vp(d_out_sigs),
+                                             _vp(d_out_norms), _vp(stream) if stream else None))
+
+    def set_rows_csr_dev(self, n, first_row_index, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, stream=0):
+        _check(self._lib.jubann_set_rows_csr_dev(self._h, int(n), int(first_row_index), int(nnz), _vp(d_indptr),
+                                                 _vp(d_seed32) if d_seed32 else None,
+                                                 _vp(d_keyhash64) if d_keyhash64 else None, _vp(d_vals),
+                                                 _vp(stream) if stream else None))
 
     def scan_local_dev(self, nq, d_qsigs, d_qnorms, k, d_cand_key, d_cand_index, stream=0):
         _check(self._lib.jubann_scan_local_dev(self._h, int(nq), _vp(d_qsigs), _vp(d_qnorms) if d_qnorms else None,

@@ -192,17 +192,19 @@ void free_cache(jubann_t* h) {
 
 // CSR already on the device -> signatures (+norms) on the device
 int hash_device(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d_indptr, const uint32_t* d_seed,
-                const uint64_t* d_keyhash, const float* d_vals, uint64_t* d_sigs, float* d_norms) {
+                const uint64_t* d_keyhash, const float* d_vals, uint64_t* d_sigs, float* d_norms,
+                cudaStream_t st = nullptr, bool use_handle_stream = true) {
+  if (use_handle_stream) st = h->stream;
   int launches = 0;
   if (h->method == MINHASH) {
-    CK(launch_signature_minhash(h->hash_num, n, d_indptr, d_keyhash, d_vals, d_sigs, d_norms, h->w64, h->stream));
+    CK(launch_signature_minhash(h->hash_num, n, d_indptr, d_keyhash, d_vals, d_sigs, d_norms, h->w64, st));
     ++launches;
   } else {
     int rc = ensure_cache(h);
     if (rc) return rc;
-    CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, h->stream, &launches));
-    CK(cudaMemcpyAsync(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, st, &launches));
+    CK(cudaMemcpyAsync(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     if (h->h_counters[2]) {
       return fail(JUBANN_E_CACHE_FULL,
                   "projection cache full: more than %u distinct features (raise option cache_slots, then clear)",
@@ -210,11 +212,11 @@ int hash_device(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d_indptr,
     }
     const uint32_t nfill = h->h_counters[1];
     if (nfill) {
-      CK(launch_cache_fill(h->cache, nfill, h->num_sms, h->stream, &launches));
-      CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, h->stream));
+      CK(launch_cache_fill(h->cache, nfill, h->num_sms, st, &launches));
+      CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, st));
     }
     CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, n, d_indptr, d_seed, d_vals, d_sigs, d_norms,
-                            h->w64, h->stream));
+                            h->w64, st));
     ++launches;
   }
   h->kernel_launches += launches;
@@ -803,6 +805,41 @@ int jubann_query_sig_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, cons
   if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
   return query_device(h, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count, nullptr, nullptr,
                       static_cast<cudaStream_t>(stream));
+}
+
+int jubann_hash_csr_dev(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d_indptr, const uint32_t* d_seed32,
+                        const uint64_t* d_keyhash64, const float* d_vals, uint64_t* d_out_sigs, float* d_out_norms,
+                        void* stream) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!d_indptr || !d_out_sigs || !d_out_norms || (nnz && !d_vals)) return fail(JUBANN_E_INVALID, "null argument");
+  if (h->method == MINHASH ? (nnz && !d_keyhash64) : (nnz && !d_seed32)) return fail(JUBANN_E_INVALID, "missing feature hashes for this method");
+  Guard g(h);
+  return hash_device(h, n, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, d_out_sigs, d_out_norms,
+                     static_cast<cudaStream_t>(stream), false);
+}
+
+int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, uint64_t nnz, const uint64_t* d_indptr,
+                            const uint32_t* d_seed32, const uint64_t* d_keyhash64, const float* d_vals, void* stream) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (n == 0) return 0;
+  if (!d_indptr || (nnz && !d_vals)) return fail(JUBANN_E_INVALID, "null argument");
+  if (h->method == MINHASH ? (nnz && !d_keyhash64) : (nnz && !d_seed32)) return fail(JUBANN_E_INVALID, "missing feature hashes for this method");
+  Guard g(h);
+  if (first_row_index > h->global_rows) return fail(JUBANN_E_RANGE, "row index skips past the table end");
+  rc = grow_to(h, std::max(h->global_rows, first_row_index + n));
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CK(h->b_sigs.ensure(n * h->w64 * 8));
+  CK(h->b_norms.ensure(n * 4));
+  rc = hash_device(h, n, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, h->b_sigs.as<uint64_t>(), h->b_norms.as<float>(), st, false);
+  if (rc) return rc;
+  CK(launch_scatter_rows(view(h), n, nullptr, first_row_index, h->b_sigs.as<uint64_t>(),
+                         h->method == EUCLID_LSH ? h->b_norms.as<float>() : nullptr, h->shard_rank, h->shard_count, st));
+  h->kernel_launches += 1;
+  return 0;
 }
 
 int jubann_scan_local_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms, uint32_t k,

@@ -138,3 +138,35 @@ def test_set_rows_csr_then_query_end_to_end(oracle, feature_tables):
     from gpu_util import assert_same_ranking
     assert_same_ranking(got, want, nq, k)
     assert got[1][0][0] == 0.0      # query 0 is an exact duplicate of a stored row
+
+
+@pytest.mark.parametrize("method,hash_num", [("lsh", 512), ("euclid_lsh", 256), ("minhash", 128)])
+def test_device_resident_csr_entry_points(feature_tables, method, hash_num):
+    # jubann_hash_csr_dev / jubann_set_rows_csr_dev give what the host-buffer calls give
+    import torch
+    from jubatus_b200 import Engine
+    s32, k64 = feature_tables
+    n = 500
+    ids, vals = w.synth_rows(w.MASTER_SEED, 77, n)
+    indptr, seed32, keyhash, v = w.to_csr(ids, vals, s32, k64)
+    dev = torch.device("cuda:0")
+    d_ip = torch.from_numpy(indptr.view(np.int64)).to(dev)
+    d_s = torch.from_numpy(seed32.view(np.int32)).to(dev)
+    d_k = torch.from_numpy(keyhash.view(np.int64)).to(dev)
+    d_v = torch.from_numpy(v).to(dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    with Engine(method, hash_num, cache_slots=1 << 17) as e:
+        want, wnorm = e.hash_csr(indptr, seed32, keyhash, v)
+        sigs = torch.zeros((n, e.w64), dtype=torch.int64, device=dev)
+        norms = torch.zeros(n, dtype=torch.float32, device=dev)
+        e.hash_csr_dev(n, len(v), d_ip.data_ptr(), d_s.data_ptr() if method != "minhash" else 0,
+                       d_k.data_ptr() if method == "minhash" else 0, d_v.data_ptr(), sigs.data_ptr(), norms.data_ptr(), stream)
+        torch.cuda.synchronize()
+        assert np.array_equal(sigs.cpu().numpy().view(np.uint64), want)
+        assert np.array_equal(norms.cpu().numpy(), wnorm)
+        e.set_rows_csr_dev(n, 0, len(v), d_ip.data_ptr(), d_s.data_ptr() if method != "minhash" else 0,
+                           d_k.data_ptr() if method == "minhash" else 0, d_v.data_ptr(), stream)
+        torch.cuda.synchronize()
+        stored, snorm = e.get_rows_sig(np.arange(n))
+        assert e.size() == (n, n)
+        assert np.array_equal(stored, want) and np.array_equal(snorm, wnorm)
