@@ -46,6 +46,9 @@ def parse_args():
                     help="queries sharing one streaming pass in the headline run (2 = HBM-bound regime; 0 = library default)")
     ap.add_argument("--popc-variant", type=int, default=-1)
     ap.add_argument("--scan-variant", type=int, default=0)
+    ap.add_argument("--table", default="datums", choices=["datums", "words"],
+                    help="datums: rows are synthetic sparse datums hashed by the signature kernel (end to end); "
+                         "words: uniform random signature words (scan-only fill)")
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     return ap.parse_args()
@@ -250,33 +253,88 @@ def run_b200(a):
     eng.set_option("reserve_rows", a.rows)
     stream = torch.cuda.current_stream().cuda_stream
 
-    # ---- table: uniform random signature words, written straight into the shard's slab ----
-    chunk = 4_000_000
-    gen = torch.Generator(device=dev)
-    keep_rows = {}
-    for r0 in range(0, a.rows, chunk):
-        n = min(chunk, a.rows - r0)
-        gen.manual_seed(TABLE_SEED + r0)   # every rank generates the same global rows
-        sig = torch.randint(-2 ** 63, 2 ** 63 - 1, (n, w64), dtype=torch.int64, device=dev, generator=gen)
-        nrm = (torch.rand(n, device=dev, generator=gen) + 0.5) if euclid else None
-        eng.set_rows_sig_dev(n, r0, sig.data_ptr(), nrm.data_ptr() if euclid else 0, stream)
-        if r0 == 0:
-            keep_rows = sig[:4096].clone()
+    nnz = 100
+    nsets = 4
+    minhash = a.method == "minhash"
+    if a.table == "words":
+        # ---- table: uniform random signature words, written straight into the shard's slab ----
+        chunk = 4_000_000
+        gen = torch.Generator(device=dev)
+        for r0 in range(0, a.rows, chunk):
+            n = min(chunk, a.rows - r0)
+            gen.manual_seed(TABLE_SEED + r0)   # every rank generates the same global rows
+            sig = torch.randint(-2 ** 63, 2 ** 63 - 1, (n, w64), dtype=torch.int64, device=dev, generator=gen)
+            nrm = (torch.rand(n, device=dev, generator=gen) + 0.5) if euclid else None
+            eng.set_rows_sig_dev(n, r0, sig.data_ptr(), nrm.data_ptr() if euclid else 0, stream)
+            if r0 == 0:
+                keep_rows = sig[:4096].clone()
+            torch.cuda.synchronize()
+            del sig, nrm
+
+        def queries(seed):
+            q = torch.from_numpy(workload.random_signatures(seed, a.nq, w64).view(np.int64)).clone()
+            q[::8] = keep_rows[(torch.arange(0, a.nq, 8) * 13) % keep_rows.shape[0]].cpu()
+            return q
+
+        h_q = [queries(1000 + i).pin_memory() for i in range(nsets)]
+        d_q = [x.to(dev) for x in h_q]
+        h_qn = [torch.ones(a.nq, dtype=torch.float32).pin_memory() for _ in range(nsets)] if euclid else None
+        d_qn = [x.to(dev) for x in h_qn] if euclid else None
+        h_csr = None
+    else:
+        # ---- table: synthetic sparse datums (100 of 2^20 hashed features, values 1 + U[0,1)), hashed on
+        # the device by the signature kernel and stored: set_row end to end ----
+        s32, k64 = workload.feature_tables(20)
+        d_s32 = torch.from_numpy(s32.view(np.int32)).to(dev)
+        d_k64 = torch.from_numpy(k64.view(np.int64)).to(dev)
+        chunk = 1_000_000
+        gen = torch.Generator(device=dev)
+        t_build = time.time()
+        for r0 in range(0, a.rows, chunk):
+            n = min(chunk, a.rows - r0)
+            gen.manual_seed(TABLE_SEED + r0)   # every rank generates (and hashes) the same global rows
+            ids = torch.randint(0, 1 << 20, (n, nnz), device=dev, generator=gen)
+            vals = (torch.rand((n, nnz), device=dev, generator=gen) + 1.0)
+            flat = ids.reshape(-1)
+            seed = None if minhash else d_s32[flat].contiguous()
+            keyh = d_k64[flat].contiguous() if minhash else None
+            indptr = torch.arange(n + 1, device=dev, dtype=torch.int64) * nnz
+            eng.set_rows_csr_dev(n, r0, n * nnz, indptr.data_ptr(), seed.data_ptr() if seed is not None else 0,
+                                 keyh.data_ptr() if keyh is not None else 0, vals.reshape(-1).data_ptr(), stream)
+            if r0 == 0:
+                keep_ids, keep_vals = ids[:4096].clone(), vals[:4096].clone()
+            torch.cuda.synchronize()
+            del ids, vals, flat, seed, keyh, indptr
+        t_build = time.time() - t_build
+
+        # queries: datums from another stream; every 8th is an exact copy of a stored datum
+        def query_csr(seed_):
+            g2 = torch.Generator(device=dev); g2.manual_seed(seed_)
+            ids = torch.randint(0, 1 << 20, (a.nq, nnz), device=dev, generator=g2)
+            vals = torch.rand((a.nq, nnz), device=dev, generator=g2) + 1.0
+            src = (torch.arange(0, a.nq, 8, device=dev) * 13) % keep_ids.shape[0]
+            ids[::8], vals[::8] = keep_ids[src], keep_vals[src]
+            flat = ids.reshape(-1)
+            return {"indptr": (torch.arange(a.nq + 1, dtype=torch.int64) * nnz).pin_memory(),
+                    "seed": d_s32[flat].cpu().pin_memory(), "key": d_k64[flat].cpu().pin_memory(),
+                    "vals": vals.reshape(-1).cpu().pin_memory()}
+
+        h_csr = [query_csr(1000 + i) for i in range(nsets)]
+        d_csr = [{k_: v.to(dev) for k_, v in c.items()} for c in h_csr]
+        d_q = [torch.zeros((a.nq, w64), dtype=torch.int64, device=dev) for _ in range(nsets)]
+        d_qn = [torch.zeros(a.nq, dtype=torch.float32, device=dev) for _ in range(nsets)]
+        for i in range(nsets):   # query signatures resident in HBM for the device-timed region
+            c = d_csr[i]
+            eng.hash_csr_dev(a.nq, a.nq * nnz, c["indptr"].data_ptr(), 0 if minhash else c["seed"].data_ptr(),
+                             c["key"].data_ptr() if minhash else 0, c["vals"].data_ptr(), d_q[i].data_ptr(),
+                             d_qn[i].data_ptr(), stream)
         torch.cuda.synchronize()
-        del sig, nrm
+        h_q = [x.cpu().pin_memory() for x in d_q]
+        h_qn = [x.cpu().pin_memory() for x in d_qn] if euclid else None
+        if not euclid:
+            d_qn = None
     assert eng.size()[0] == a.rows
 
-    # ---- queries (same on every rank): random words, every 8th an exact copy of a stored row ----
-    def queries(seed):
-        q = torch.from_numpy(workload.random_signatures(seed, a.nq, w64).view(np.int64)).clone()
-        q[::8] = keep_rows[(torch.arange(0, a.nq, 8) * 13) % keep_rows.shape[0]].cpu()
-        return q
-
-    nsets = 4
-    h_q = [queries(1000 + i).pin_memory() for i in range(nsets)]
-    d_q = [x.to(dev) for x in h_q]
-    h_qn = [torch.ones(a.nq, dtype=torch.float32).pin_memory() for _ in range(nsets)] if euclid else None
-    d_qn = [x.to(dev) for x in h_qn] if euclid else None
     d_idx = torch.zeros((a.nq, a.k), dtype=torch.int64, device=dev)
     d_score = torch.zeros((a.nq, a.k), dtype=torch.float32, device=dev)
     d_count = torch.zeros(a.nq, dtype=torch.int32, device=dev)
@@ -341,7 +399,7 @@ def run_b200(a):
     got_score = d_score.cpu().numpy()
     assert int(d_count.min().item()) == min(a.k, a.rows)
     if not euclid:
-        planted = ((np.arange(0, a.nq, 8) * 13) % keep_rows.shape[0])
+        planted = ((np.arange(0, a.nq, 8) * 13) % 4096)
         assert (got_score[::8, 0] == 0).all() and (got_idx[::8, 0] == planted).all(), "planted rows not found"
         assert (np.diff(got_score, axis=1) >= 0).all()
 
@@ -420,21 +478,39 @@ def run_b200(a):
     h2d = a.nq * w64 * 8 + (a.nq * 4 if euclid else 0)
     d2h = a.nq * a.k * 12 + a.nq * 4
 
+    if h_csr is not None:
+        h2d = a.nq * nnz * (4 + (8 if minhash else 4)) + (a.nq + 1) * 8
+
     def step_e2e(i):
         qn_h = h_qn[i % nsets].data_ptr() if euclid else 0
-        if G == 1:
+        if G == 1 and h_csr is not None:
+            # neighbor_row_from_datum as the adapter calls it: host CSR of the query datums in, ids/scores out
+            c = h_csr[i % nsets]
+            eng.query_csr_ptr(a.nq, c["indptr"].data_ptr(), 0 if minhash else c["seed"].data_ptr(),
+                              c["key"].data_ptr() if minhash else 0, c["vals"].data_ptr(), a.k, 0, h_idx.data_ptr(),
+                              h_score.data_ptr(), h_count.data_ptr())
+        elif G == 1:
             eng.query_sig_ptr(a.nq, h_q[i % nsets].data_ptr(), qn_h, a.k, 0, h_idx.data_ptr(), h_score.data_ptr(),
                               h_count.data_ptr())
         else:
-            d_q[i % nsets].copy_(h_q[i % nsets], non_blocking=True)
-            if euclid:
-                d_qn[i % nsets].copy_(h_qn[i % nsets], non_blocking=True)
+            if h_csr is not None:
+                c, dc = h_csr[i % nsets], d_csr[i % nsets]
+                for k_ in ("indptr", "vals", "key" if minhash else "seed"):
+                    dc[k_].copy_(c[k_], non_blocking=True)
+                eng.hash_csr_dev(a.nq, a.nq * nnz, dc["indptr"].data_ptr(), 0 if minhash else dc["seed"].data_ptr(),
+                                 dc["key"].data_ptr() if minhash else 0, dc["vals"].data_ptr(), d_q[i % nsets].data_ptr(),
+                                 (d_qn[i % nsets] if euclid else scratch_norm).data_ptr(), stream)
+            else:
+                d_q[i % nsets].copy_(h_q[i % nsets], non_blocking=True)
+                if euclid:
+                    d_qn[i % nsets].copy_(h_qn[i % nsets], non_blocking=True)
             step_device(i)
             h_idx.copy_(d_idx, non_blocking=True)
             h_score.copy_(d_score, non_blocking=True)
             h_count.copy_(d_count, non_blocking=True)
             torch.cuda.synchronize()
 
+    scratch_norm = torch.zeros(a.nq, dtype=torch.float32, device=dev)
     e2e_steps = max(2, a.steps // 2)
     for i in range(2):
         step_e2e(i)
@@ -445,8 +521,8 @@ def run_b200(a):
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e = {"value": e2e_steps * a.nq / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-           "steps": e2e_steps, "api": "jubann_query_sig (host buffers)" if G == 1 else
-           "H2D + jubann_scan_local_dev + NCCL all_gather + jubann_merge_dev + D2H"}
+           "steps": e2e_steps, "api": ("jubann_query_csr (host CSR of the query datums -> ids/scores)" if h_csr is not None else "jubann_query_sig (host buffers)") if G == 1 else
+           "H2D + (jubann_hash_csr_dev) + jubann_scan_local_dev + NCCL all_gather + jubann_merge_dev + D2H"}
     step_device(e2e_steps - 1)          # same query set as the last end-to-end step
     torch.cuda.synchronize()
     assert np.array_equal(h_idx.numpy(), d_idx.cpu().numpy()), "host-buffer path and device path disagree"
@@ -455,7 +531,9 @@ def run_b200(a):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": G, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "u32", "data": "synthetic (uniform random signature words, scan-only fill; queries random + planted exact copies)",
+        "dtype": "u32", "data": ("synthetic sparse datums (100 of 2^20 hashed features) hashed by the signature kernel; queries are datums, "
+                                 "every 8th an exact copy of a stored one" if a.table == "datums" else
+                                 "synthetic (uniform random signature words, scan-only fill; queries random + planted exact copies)"),
         "config": {"workload": workload_name(a), "parallelism": "rows sharded round-robin over %d GPU(s)" % G,
                    "cache": "table %.1f GB per GPU >> 126 MB L2, streamed once per pass (inputs larger than L2)" % (local_rows * row_bytes / 1e9),
                    "queries_per_pass": qp_eff},

@@ -237,6 +237,12 @@ class Engine(object):
                                           int(k), int(flags), _vp(out_idx_ptr), _vp(out_score_ptr),
                                           _vp(out_count_ptr)))
 
+    def query_csr_ptr(self, nq, indptr_ptr, seed32_ptr, keyhash_ptr, vals_ptr, k, flags, out_idx_ptr, out_score_ptr,
+                      out_count_ptr):
+        _check(self._lib.jubann_query_csr(self._h, int(nq), _vp(indptr_ptr), _vp(seed32_ptr) if seed32_ptr else None,
+                                          _vp(keyhash_ptr) if keyhash_ptr else None, _vp(vals_ptr), int(k), int(flags),
+                                          _vp(out_idx_ptr), _vp(out_score_ptr), _vp(out_count_ptr)))
+
     # -- device-pointer entry points -----------------------------------------
     def query_sig_dev(self, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count, stream=0):
         _check(self._lib.jubann_query_sig_dev(self._h, int(nq), _vp(d_qsigs), _vp(d_qnorms) if d_qnorms else None,
