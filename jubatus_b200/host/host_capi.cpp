@@ -236,6 +236,20 @@ int jubahost_mix_pair(void* ha, void* hb) {
     return 0;
   });
 }
+int jubahost_enable_batching(void* h, uint64_t max_batch, uint64_t max_wait_us) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->serv) throw jubatus_exception("batching: nearest_neighbor server only");
+    b->serv->enable_batching(max_batch, max_wait_us);
+    return 0;
+  });
+}
+int jubahost_batch_stats(void* h, uint64_t* batches, uint64_t* queries) {
+  host_box* b = static_cast<host_box*>(h);
+  *batches = b->serv ? b->serv->batches_run() : 0;
+  *queries = b->serv ? b->serv->queries_batched() : 0;
+  return 0;
+}
 int jubahost_calc_score_datum(void* h, const char* const* nkeys, const double* nvals, uint64_t nn, float* score) {
   host_box* b = static_cast<host_box*>(h);
   return guarded([&]() {

@@ -30,6 +30,8 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <chrono>
+#include <condition_variable>
 #include <limits>
 #include <map>
 #include <memory>
@@ -644,6 +646,84 @@ class nearest_neighbor {
 };
 }  // namespace driver
 
+// ---------------------------------------------------------------------------------------
+// query_batcher: turns the server's call pattern -- N RPC worker threads each asking for one
+// query without the model lock (NOLOCK_, nearest_neighbor_impl.cpp:75-102; --thread,
+// server_util.cpp:155) -- into the batched launches the kernels are measured at.
+// The first thread to arrive leads: it waits until `max_batch` requests have queued or `max_wait`
+// has passed, takes the whole queue, runs ONE neighbor_rows call per distinct (size, similar)
+// and hands every follower its own result.
+// ---------------------------------------------------------------------------------------
+class query_batcher {
+ public:
+  query_batcher(gpu_nearest_neighbor* nn, size_t max_batch, std::chrono::microseconds max_wait)
+      : nn_(nn), max_batch_(max_batch < 1 ? 1 : max_batch), max_wait_(max_wait), leader_(false), batches_(0), queries_(0) {}
+
+  neighbor_result query(const sfv_t& q, uint64_t ret_num, bool similar) {
+    request r;
+    r.q = &q; r.ret_num = ret_num; r.similar = similar; r.done = false;
+    std::unique_lock<std::mutex> lk(mu_);
+    queue_.push_back(&r);
+    if (queue_.size() >= max_batch_) cv_.notify_all();
+    while (!r.done) {
+      if (!leader_) {
+        leader_ = true;   // lead one batch
+        const std::chrono::steady_clock::time_point deadline = std::chrono::steady_clock::now() + max_wait_;
+        while (queue_.size() < max_batch_ && cv_.wait_until(lk, deadline) != std::cv_status::timeout) {}
+        std::vector<request*> batch;
+        batch.swap(queue_);
+        lk.unlock();
+        run(batch);
+        lk.lock();
+        for (size_t i = 0; i < batch.size(); ++i) batch[i]->done = true;
+        ++batches_; queries_ += batch.size();
+        leader_ = false;
+        cv_.notify_all();
+      } else {
+        cv_.wait(lk);
+      }
+    }
+    if (!r.error.empty()) throw jubatus_exception(r.error);
+    return r.result;
+  }
+  uint64_t batches() const { return batches_; }
+  uint64_t queries() const { return queries_; }
+
+ private:
+  struct request {
+    const sfv_t* q; uint64_t ret_num; bool similar; bool done;
+    neighbor_result result; std::string error;
+  };
+  void run(const std::vector<request*>& batch) {
+    std::vector<bool> taken(batch.size(), false);
+    for (size_t i = 0; i < batch.size(); ++i) {
+      if (taken[i]) continue;
+      std::vector<size_t> members;
+      std::vector<sfv_t> qs;
+      for (size_t j = i; j < batch.size(); ++j) {
+        if (!taken[j] && batch[j]->ret_num == batch[i]->ret_num && batch[j]->similar == batch[i]->similar) {
+          taken[j] = true; members.push_back(j); qs.push_back(*batch[j]->q);
+        }
+      }
+      try {
+        std::vector<neighbor_result> out;
+        nn_->neighbor_rows(qs, out, batch[i]->ret_num, batch[i]->similar);
+        for (size_t m = 0; m < members.size(); ++m) batch[members[m]]->result.swap(out[m]);
+      } catch (const std::exception& e) {
+        for (size_t m = 0; m < members.size(); ++m) batch[members[m]]->error = e.what();
+      }
+    }
+  }
+  gpu_nearest_neighbor* nn_;
+  size_t max_batch_;
+  std::chrono::microseconds max_wait_;
+  std::mutex mu_;
+  std::condition_variable cv_;
+  std::vector<request*> queue_;
+  bool leader_;
+  uint64_t batches_, queries_;
+};
+
 // jubatus::server::nearest_neighbor_serv: config -> engine, RPC-named pass-throughs
 class nearest_neighbor_serv {
  public:
@@ -670,9 +750,24 @@ class nearest_neighbor_serv {
   bool clear() { check_set_config(); update_row_cnt_ = 0; nearest_neighbor_->clear(); return true; }
   bool set_row(const std::string& id, const datum& d) { check_set_config(); ++update_row_cnt_; nearest_neighbor_->set_row(id, d); return true; }
   neighbor_result neighbor_row_from_id(const std::string& id, size_t size) { check_set_config(); return nearest_neighbor_->neighbor_row_from_id(id, size); }
-  neighbor_result neighbor_row_from_datum(const datum& d, size_t size) { check_set_config(); return nearest_neighbor_->neighbor_row_from_datum(d, size); }
+  neighbor_result neighbor_row_from_datum(const datum& d, size_t size) {
+    check_set_config();
+    if (batcher_) { sfv_t v; nearest_neighbor_->converter().convert(d, v); return batcher_->query(v, size, false); }
+    return nearest_neighbor_->neighbor_row_from_datum(d, size);
+  }
   neighbor_result similar_row_from_id(const std::string& id, size_t n) { check_set_config(); return nearest_neighbor_->similar_row(id, n); }
-  neighbor_result similar_row_from_datum(const datum& d, size_t n) { check_set_config(); return nearest_neighbor_->similar_row(d, n); }
+  neighbor_result similar_row_from_datum(const datum& d, size_t n) {
+    check_set_config();
+    if (batcher_) { sfv_t v; nearest_neighbor_->converter().convert(d, v); return batcher_->query(v, n, true); }
+    return nearest_neighbor_->similar_row(d, n);
+  }
+  // coalesce concurrent *_from_datum calls into batched device launches (off by default)
+  void enable_batching(size_t max_batch, uint64_t max_wait_us) {
+    check_set_config();
+    batcher_.reset(new query_batcher(nearest_neighbor_->engine(), max_batch, std::chrono::microseconds(max_wait_us)));
+  }
+  uint64_t batches_run() const { return batcher_ ? batcher_->batches() : 0; }
+  uint64_t queries_batched() const { return batcher_ ? batcher_->queries() : 0; }
   std::vector<std::string> get_all_rows() const { check_set_config(); return nearest_neighbor_->get_all_rows(); }
   uint64_t update_row_cnt() const { return update_row_cnt_; }
   driver::nearest_neighbor* get_driver() { check_set_config(); return nearest_neighbor_.get(); }
@@ -684,6 +779,7 @@ class nearest_neighbor_serv {
   std::string config_;
   uint64_t update_row_cnt_;
   std::shared_ptr<driver::nearest_neighbor> nearest_neighbor_;
+  std::shared_ptr<query_batcher> batcher_;
 };
 
 // ---------------------------------------------------------------------------------------

@@ -58,6 +58,8 @@ def _load():
     lib.jubahost_get_all_rows.argtypes = [_vp, _vp, ctypes.c_uint64, _vp]
     lib.jubahost_get_signature.argtypes = [_vp, ctypes.c_char_p, _vp, _vp]
     lib.jubahost_mix_pair.argtypes = [_vp, _vp]
+    lib.jubahost_enable_batching.argtypes = [_vp, ctypes.c_uint64, ctypes.c_uint64]
+    lib.jubahost_batch_stats.argtypes = [_vp, _vp, _vp]
     lib.jubahost_calc_score_datum.argtypes = [_vp, _vp, _vp, ctypes.c_uint64, _vp]
     lib.jubahost_calc_score_id.argtypes = [_vp, ctypes.c_char_p, _vp]
     lib.jubahost_lof_params.argtypes = [_vp, ctypes.c_char_p, _vp, _vp]
@@ -242,6 +244,17 @@ class NearestNeighbor(_HostHandle):
 
     def similar_row_from_datum(self, d, ret_num):
         return self._query_datum(d, ret_num, 1)
+
+    def enable_batching(self, max_batch=64, max_wait_us=200):
+        """Coalesce concurrent *_from_datum calls (one per RPC worker thread in the server) into
+        batched device launches."""
+        if self._lib.jubahost_enable_batching(self._h, int(max_batch), int(max_wait_us)):
+            _raise()
+
+    def batch_stats(self):
+        b, q = ctypes.c_uint64(), ctypes.c_uint64()
+        self._lib.jubahost_batch_stats(self._h, ctypes.byref(b), ctypes.byref(q))
+        return {"batches": b.value, "queries": q.value}
 
     def delete_row(self, row_id):
         """column_table::delete_row (what an unlearner calls)."""

@@ -166,3 +166,72 @@ def test_anomaly_light_lof(oracle):
     assert abs(an.calc_score(q) - ora.calc_score(sfv_of(ids[5][:6], vals[5][:6]))) <= 1e-5
     with pytest.raises(nn.JubatusError):
         nn.Anomaly(json.dumps({"method": "lof", "converter": CONVERTER, "parameter": {"method": "lsh", "parameter": {}}}))
+
+
+def test_concurrent_queries_are_coalesced_by_the_batcher(oracle):
+    # the server answers queries from several RPC worker threads without the model lock
+    # (nearest_neighbor_impl.cpp:75-102); the batcher turns them into batched launches
+    import threading
+    hash_num, n, k = 128, 400, 10
+    ids, vals = w.synth_rows(w.MASTER_SEED, 300, n, nnz=12, nfeat_log2=9)
+    cli = nn.NearestNeighbor(config("lsh", hash_num))
+    cli.set_rows(["r%d" % r for r in range(n)], [datum_of(ids[r], vals[r]) for r in range(n)])
+    want = [cli.neighbor_row_from_datum(datum_of(ids[r][:9], vals[r][:9]), k) for r in range(64)]
+    cli.enable_batching(max_batch=16, max_wait_us=20000)
+    got = [None] * 64
+    errors = []
+
+    def worker(t):
+        try:
+            for r in range(t, 64, 8):
+                got[r] = cli.neighbor_row_from_datum(datum_of(ids[r][:9], vals[r][:9]), k)
+        except Exception as e:   # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    assert got == want
+    st = cli.batch_stats()
+    assert st["queries"] == 64 and st["batches"] < 64     # several queries shared a launch
+    assert cli.similar_row_from_datum(datum_of(ids[0], vals[0]), 1)[0] == ("r0", 1.0)
+
+
+def test_engine_is_thread_safe_at_the_c_abi(oracle):
+    # concurrent queries + one writer on one handle: every answer must be the exact ranking of
+    # the table either before or after the write (calls are serialised inside the library)
+    import threading
+    from jubatus_b200 import Engine
+    rng = np.random.RandomState(0)
+    hash_num, n, k = 256, 30000, 20
+    rows = rng.randint(0, 2 ** 62, size=(n, 4), dtype=np.int64).astype(np.uint64)
+    q = rows[:32].copy()
+    new_row = rows[:1] ^ np.uint64(0xFFFFFFFF)
+    before = oracle.scan_batch("lsh", q, None, rows, None, hash_num, k, threads=4)[:3]
+    after = oracle.scan_batch("lsh", q, None, np.concatenate([rows, new_row]), None, hash_num, k, threads=4)[:3]
+    with Engine("lsh", hash_num) as e:
+        e.set_rows_sig(np.arange(n), rows)
+        out = [[] for _ in range(8)]
+
+        def worker(t):
+            for _ in range(10):
+                out[t].append(e.query_sig(q[t * 4:(t + 1) * 4], None, k))
+
+        ts = [threading.Thread(target=worker, args=(t,)) for t in range(8)]
+        for t in ts:
+            t.start()
+        e.set_rows_sig([n], new_row)
+        for t in ts:
+            t.join()
+        assert e.size() == (n + 1, n + 1)
+        for t in range(8):
+            sl = slice(t * 4, (t + 1) * 4)
+            for g in out[t]:
+                ok_b = np.array_equal(g[0], before[0][sl]) and np.array_equal(g[1], before[1][sl])
+                ok_a = np.array_equal(g[0], after[0][sl]) and np.array_equal(g[1], after[1][sl])
+                assert ok_b or ok_a, t
+        final = e.query_sig(q, None, k)
+        assert np.array_equal(final[0], after[0]) and np.array_equal(final[1], after[1])
