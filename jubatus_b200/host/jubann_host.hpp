@@ -36,6 +36,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <shared_mutex>
 #include <stdexcept>
 #include <string>
 #include <unordered_map>
@@ -479,7 +480,7 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
       : method_(method), hash_num_(hash_num), table_(table), my_id_(my_id), mixable_(table.get()) {}
 
   std::string type() const { return method_; }
-  void clear() { table_->clear(); }
+  void clear() { std::unique_lock<std::shared_mutex> lk(rw_); table_->clear(); }
   std::shared_ptr<device_table> get_table() { return table_; }
   std::shared_ptr<const device_table> get_const_table() const { return table_; }
   mixable_versioned_table* get_mixable() { return &mixable_; }
@@ -495,6 +496,8 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
     if (ids.empty()) return;
     csr_batch b;
     for (size_t i = 0; i < sfvs.size(); ++i) b.add(sfvs[i]);
+    // like column_table's own rw-mutex: writers exclusive, the lock-free RPC readers shared
+    std::unique_lock<std::shared_mutex> lk(rw_);
     std::vector<uint64_t> idx = table_->assign(ids, my_id_);
     const jubann_api& a = table_->api();
     a.check(a.set_rows_csr(table_->handle(), idx.size(), idx.data(), b.indptr.data(), b.seed32.data(),
@@ -517,6 +520,7 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
                      bool similar) const {
     csr_batch b;
     for (size_t i = 0; i < queries.size(); ++i) b.add(queries[i]);
+    std::shared_lock<std::shared_mutex> lk(rw_);
     const uint32_t k = clamp_k(ret_num);
     std::vector<uint64_t> oi(queries.size() * std::max<uint32_t>(k, 1));
     std::vector<float> os(oi.size());
@@ -529,6 +533,7 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
   // unknown ids give an empty result, not an error
   void neighbor_rows_from_ids(const std::vector<std::string>& query_ids, std::vector<neighbor_result>& out,
                               uint64_t ret_num, bool similar) const {
+    std::shared_lock<std::shared_mutex> lk(rw_);
     std::vector<uint64_t> rows;
     std::vector<bool> known(query_ids.size());
     for (size_t i = 0; i < query_ids.size(); ++i) {
@@ -547,8 +552,8 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
     }
     emit(query_ids.size(), k, oi, os, oc, known, out);
   }
-  void get_all_row_ids(std::vector<std::string>& ids) const { ids = table_->get_all_row_ids(); }
-  bool delete_row(const std::string& id) { return table_->delete_row(id); }
+  void get_all_row_ids(std::vector<std::string>& ids) const { std::shared_lock<std::shared_mutex> lk(rw_); ids = table_->get_all_row_ids(); }
+  bool delete_row(const std::string& id) { std::unique_lock<std::shared_mutex> lk(rw_); return table_->delete_row(id); }
 
  private:
   uint32_t clamp_k(uint64_t ret_num) const {
@@ -571,6 +576,7 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
   std::shared_ptr<device_table> table_;
   std::string my_id_;
   mixable_versioned_table mixable_;
+  mutable std::shared_mutex rw_;
 };
 
 // {"hash_num": int [, "threads": int]}; unknown keys are rejected (config_cast_check)
