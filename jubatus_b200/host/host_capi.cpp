@@ -236,6 +236,31 @@ int jubahost_mix_pair(void* ha, void* hb) {
     return 0;
   });
 }
+// driver->pack(): returns the blob size; copies it when the buffer is large enough
+int64_t jubahost_pack(void* h, char* buf, uint64_t cap) {
+  host_box* b = static_cast<host_box*>(h);
+  int64_t n = -1;
+  int rc = guarded([&]() {
+    std::string blob = b->nn()->pack();
+    if (blob.size() <= cap) memcpy(buf, blob.data(), blob.size());
+    n = static_cast<int64_t>(blob.size());
+    return 0;
+  });
+  return rc ? -1 : n;
+}
+int jubahost_unpack(void* h, const char* buf, uint64_t n) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() { b->nn()->unpack(std::string(buf, n)); return 0; });
+}
+int jubahost_dump_json(void* h, char* buf, uint64_t cap) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    std::string j = b->nn()->get_table()->dump_json();
+    if (j.size() + 1 > cap) throw jubatus_exception("buffer too small");
+    memcpy(buf, j.c_str(), j.size() + 1);
+    return 0;
+  });
+}
 int jubahost_enable_batching(void* h, uint64_t max_batch, uint64_t max_wait_us) {
   host_box* b = static_cast<host_box*>(h);
   return guarded([&]() {

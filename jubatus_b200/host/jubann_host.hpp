@@ -28,6 +28,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include <algorithm>
 #include <chrono>
@@ -381,7 +382,70 @@ class device_table {
   }
   uint64_t clock() const { return clock_; }
 
+  // column_table::dump_json as the server's get_status uses it (nearest_neighbor_serv.cpp:72-73):
+  // a short description, not the rows.
+  std::string dump_json() const {
+    return "{\"rows\":" + std::to_string(keys_.size()) + ",\"hash_num\":" + std::to_string(hash_num_) +
+           ",\"clock\":" + std::to_string(clock_) + ",\"columns\":[\"bit_vector(" + std::to_string(hash_num_) +
+           ")\"],\"storage\":\"device\"}";
+  }
+
+  // column_table::pack / unpack (driver->pack / unpack, framework/save_load.cpp:129,280).  The
+  // reference writes msgpack; this is a self-describing little-endian blob with the same content
+  // (keys, versions, clock, columns) -- not byte-compatible with a .jubatus model file.
+  std::string pack() const {
+    std::string out;
+    put_u64(out, 0x314E4E4142554Aull);   // "JUBANN1"
+    put_u64(out, hash_num_); put_u64(out, clock_); put_u64(out, keys_.size());
+    std::vector<uint64_t> idx(keys_.size());
+    for (size_t i = 0; i < idx.size(); ++i) idx[i] = i;
+    std::vector<uint64_t> sigs(idx.size() * w64_);
+    std::vector<float> norms(idx.size());
+    if (!idx.empty()) api_->check(api_->get_rows_sig(h_, idx.size(), idx.data(), sigs.data(), norms.data()));
+    for (size_t i = 0; i < keys_.size(); ++i) {
+      put_str(out, keys_[i]); put_str(out, versions_[i].first); put_u64(out, versions_[i].second);
+    }
+    out.append(reinterpret_cast<const char*>(sigs.data()), sigs.size() * 8);
+    out.append(reinterpret_cast<const char*>(norms.data()), norms.size() * 4);
+    return out;
+  }
+  void unpack(const std::string& blob) {
+    size_t p = 0;
+    if (get_u64(blob, p) != 0x314E4E4142554Aull) throw jubatus_exception("unpack: not a jubann table blob");
+    if (get_u64(blob, p) != hash_num_) throw jubatus_exception("unpack: hash_num differs from the configured engine");
+    const uint64_t clock = get_u64(blob, p), n = get_u64(blob, p);
+    std::vector<std::string> keys(n);
+    std::vector<version_t> versions(n);
+    for (uint64_t i = 0; i < n; ++i) {
+      keys[i] = get_str(blob, p); versions[i].first = get_str(blob, p); versions[i].second = get_u64(blob, p);
+    }
+    if (blob.size() < p + n * w64_ * 8 + n * 4) throw jubatus_exception("unpack: truncated blob");
+    clear();
+    if (n) {
+      std::vector<uint64_t> idx(n);
+      for (uint64_t i = 0; i < n; ++i) idx[i] = i;
+      std::vector<uint64_t> sigs(n * w64_);
+      std::vector<float> norms(n);
+      memcpy(sigs.data(), blob.data() + p, n * w64_ * 8);
+      memcpy(norms.data(), blob.data() + p + n * w64_ * 8, n * 4);
+      api_->check(api_->set_rows_sig(h_, n, idx.data(), sigs.data(), norms.data()));
+    }
+    keys_.swap(keys); versions_.swap(versions); clock_ = clock;
+    for (uint64_t i = 0; i < n; ++i) index_[keys_[i]] = i;
+  }
+
  private:
+  static void put_u64(std::string& o, uint64_t v) { o.append(reinterpret_cast<const char*>(&v), 8); }
+  static void put_str(std::string& o, const std::string& s) { put_u64(o, s.size()); o.append(s); }
+  static uint64_t get_u64(const std::string& b, size_t& p) {
+    if (b.size() < p + 8) throw jubatus_exception("unpack: truncated blob");
+    uint64_t v; memcpy(&v, b.data() + p, 8); p += 8; return v;
+  }
+  static std::string get_str(const std::string& b, size_t& p) {
+    const uint64_t n = get_u64(b, p);
+    if (b.size() < p + n) throw jubatus_exception("unpack: truncated blob");
+    std::string s(b.data() + p, n); p += n; return s;
+  }
   std::shared_ptr<jubann_api> api_;
   jubann_t* h_;
   uint32_t hash_num_, w64_;
@@ -553,6 +617,9 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
     emit(query_ids.size(), k, oi, os, oc, known, out);
   }
   void get_all_row_ids(std::vector<std::string>& ids) const { std::shared_lock<std::shared_mutex> lk(rw_); ids = table_->get_all_row_ids(); }
+  // nearest_neighbor_base::pack / unpack delegate to the table
+  std::string pack() const { std::shared_lock<std::shared_mutex> lk(rw_); return table_->pack(); }
+  void unpack(const std::string& blob) { std::unique_lock<std::shared_mutex> lk(rw_); table_->unpack(blob); }
   bool delete_row(const std::string& id) { std::unique_lock<std::shared_mutex> lk(rw_); return table_->delete_row(id); }
 
  private:

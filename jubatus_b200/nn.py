@@ -58,6 +58,10 @@ def _load():
     lib.jubahost_get_all_rows.argtypes = [_vp, _vp, ctypes.c_uint64, _vp]
     lib.jubahost_get_signature.argtypes = [_vp, ctypes.c_char_p, _vp, _vp]
     lib.jubahost_mix_pair.argtypes = [_vp, _vp]
+    lib.jubahost_pack.restype = ctypes.c_int64
+    lib.jubahost_pack.argtypes = [_vp, _vp, ctypes.c_uint64]
+    lib.jubahost_unpack.argtypes = [_vp, _vp, ctypes.c_uint64]
+    lib.jubahost_dump_json.argtypes = [_vp, _vp, ctypes.c_uint64]
     lib.jubahost_enable_batching.argtypes = [_vp, ctypes.c_uint64, ctypes.c_uint64]
     lib.jubahost_batch_stats.argtypes = [_vp, _vp, _vp]
     lib.jubahost_calc_score_datum.argtypes = [_vp, _vp, _vp, ctypes.c_uint64, _vp]
@@ -204,6 +208,28 @@ class _HostHandle(object):
         if rc < 0:
             _raise()
         return None if rc else (sig, norm.value)
+
+    def pack(self):
+        """driver->pack(): the table (keys, versions, clock, columns) as one blob (save RPC payload)."""
+        n = self._lib.jubahost_pack(self._h, None, 0)
+        if n < 0:
+            _raise()
+        buf = ctypes.create_string_buffer(int(n))
+        if self._lib.jubahost_pack(self._h, buf, n) != n:
+            _raise()
+        return buf.raw
+
+    def unpack(self, blob):
+        """driver->unpack(): replace the table by a packed one (load RPC)."""
+        if self._lib.jubahost_unpack(self._h, blob, len(blob)):
+            _raise()
+
+    def get_status(self):
+        """Engine part of get_status: {'data': table.dump_json()} (nearest_neighbor_serv.cpp:69-75)."""
+        buf = ctypes.create_string_buffer(1024)
+        if self._lib.jubahost_dump_json(self._h, buf, 1024):
+            _raise()
+        return {"data": buf.value.decode()}
 
     def mix_with(self, other):
         """One push_mixer round between two in-process servers (push_mixer.cpp:335-408)."""

@@ -235,3 +235,27 @@ def test_engine_is_thread_safe_at_the_c_abi(oracle):
                 assert ok_b or ok_a, t
         final = e.query_sig(q, None, k)
         assert np.array_equal(final[0], after[0]) and np.array_equal(final[1], after[1])
+
+
+def test_pack_unpack_roundtrip_and_status(oracle):
+    hash_num, n, k = 64, 120, 10
+    ids, vals = w.synth_rows(w.MASTER_SEED, 1200, n, nnz=10, nfeat_log2=8)
+    a = nn.NearestNeighbor(config("euclid_lsh", hash_num), my_id="A")
+    for r in range(n):
+        a.set_row("r%d" % r, datum_of(ids[r], vals[r]))
+    a.delete_row("r3")
+    st = json.loads(a.get_status()["data"])
+    assert st["rows"] == n - 1 and st["hash_num"] == hash_num
+    blob = a.pack()
+    b = nn.NearestNeighbor(config("euclid_lsh", hash_num), my_id="B")
+    b.set_row("junk", datum_of(ids[0], vals[0]))
+    b.unpack(blob)
+    assert b.get_all_rows() == a.get_all_rows()
+    for r in ("r0", "r50", "r119"):
+        assert b.neighbor_row_from_id(r, k) == a.neighbor_row_from_id(r, k)
+    b.set_row("new", datum_of(ids[5], vals[5]))          # the clock continues where the saved table stopped
+    assert b.size() == n
+    with pytest.raises(nn.JubatusError):
+        nn.NearestNeighbor(config("euclid_lsh", 128)).unpack(blob)   # config mismatch is refused, as load does
+    with pytest.raises(nn.JubatusError):
+        b.unpack(blob[:40])
