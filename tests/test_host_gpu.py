@@ -259,3 +259,26 @@ def test_pack_unpack_roundtrip_and_status(oracle):
         nn.NearestNeighbor(config("euclid_lsh", 128)).unpack(blob)   # config mismatch is refused, as load does
     with pytest.raises(nn.JubatusError):
         b.unpack(blob[:40])
+
+
+def test_baseline_config1_lsh64_10k_rows_k10(oracle, feature_tables):
+    """BASELINE.json config 1: jubanearest_neighbor method=lsh hash_num=64, 10k synthetic sparse rows
+    (100 nnz out of 2^20 features), neighbor_row_from_datum k=10 -- the standalone CPU server is the
+    oracle engine here (the real binary cannot be built), the GPU answers through the same RPC names."""
+    n, nq, k, hash_num = 10000, 200, 10, 64
+    ids, vals = w.synth_rows(w.MASTER_SEED, 0, n)
+    qids, qvals = w.make_queries(w.MASTER_SEED, nq, ids, vals)
+    cli = nn.NearestNeighbor(config("lsh", hash_num))
+    ora = oracle.OracleNN("lsh", hash_num)
+    cli.set_rows(["%d" % r for r in range(n)], [datum_of(ids[r], vals[r]) for r in range(n)])
+    for r in range(n):
+        ora.set_row("%d" % r, sfv_of(ids[r], vals[r]))
+    # signatures: all bits equal on this data set (tolerance would allow 1e-4)
+    diff = sum(bin(int(a ^ b)).count("1") for r in range(0, n, 50)
+               for a, b in zip(cli.get_signature("%d" % r, hash_num)[0], ora.get_signature("%d" % r)[0]))
+    assert diff == 0
+    for j in range(nq):
+        got = cli.neighbor_row_from_datum(datum_of(qids[j], qvals[j]), k)
+        want = ora.neighbor_row_from_datum(sfv_of(qids[j], qvals[j]), k)
+        assert got == want, j
+    assert cli.neighbor_row_from_datum(datum_of(qids[0], qvals[0]), 1)[0][1] == 0.0   # query 0 is a stored row
