@@ -259,6 +259,9 @@ struct ListCtl {
   uint32_t nq, q0, hist_stride;
   uint32_t* ghist;     // global: [nq] bound words | [nq][hist_stride] counts; nullptr when unused
 };
+#ifndef JBN_REFRESH_MOD
+#define JBN_REFRESH_MOD 4   // every JBN_REFRESH_MOD-th warp re-derives the shared bound after a flush
+#endif
 __shared__ ListCtl s_L;   // written once by the prologue, read by the rare-path functions
 
 __device__ __forceinline__ unsigned long long* sm_u64(uint32_t off) { return reinterpret_cast<unsigned long long*>(g_smem + off); }
@@ -357,25 +360,38 @@ __device__ __noinline__ void hist_refresh(uint32_t q, int lane) {
   const volatile uint32_t* h = s_L.ghist + s_L.nq + (size_t)gq * s_L.hist_stride;
   const uint32_t cur = *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride);
   const uint32_t limit = min(cur, s_L.hist_stride - 1);   // only a bound below the current one is of interest
+  const uint32_t k = s_L.k;
   uint32_t run = 0;
-  for (uint32_t base = 0; base <= limit; base += 32) {
-    const uint32_t d = base + lane;
-    uint32_t v = (d <= limit) ? h[d] : 0u;
+  // eight 32-bin blocks per round, their loads all in flight together (one L2 round trip per
+  // 256 distances instead of one per 32)
+  for (uint32_t base0 = 0; base0 <= limit; base0 += 256) {
+    uint32_t v[8];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t n = __shfl_up_sync(FULL_MASK, v, o);
-      if (lane >= o) v += n;
+    for (int j = 0; j < 8; ++j) {
+      const uint32_t d = base0 + 32u * j + lane;
+      v[j] = (d <= limit) ? h[d] : 0u;
     }
-    const unsigned hit = __ballot_sync(FULL_MASK, run + v >= s_L.k);
-    if (hit) {
-      const uint32_t D = base + (__ffs(hit) - 1);
-      if (lane == 0 && D < cur) {
-        apply_shared_bound(q, D);
-        atomicMin(s_L.ghist + gq, D);   // publish for CTAs that insert rarely
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint32_t tot = __reduce_add_sync(FULL_MASK, v[j]);
+      if (run + tot >= k) {   // the crossing is inside this block: locate it with one prefix scan
+        uint32_t x = v[j];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t n = __shfl_up_sync(FULL_MASK, x, o);
+          if (lane >= o) x += n;
+        }
+        const unsigned hit = __ballot_sync(FULL_MASK, run + x >= k);
+        const uint32_t D = base0 + 32u * j + (__ffs(hit) - 1);
+        if (lane == 0 && D < cur) {
+          apply_shared_bound(q, D);
+          atomicMin(s_L.ghist + gq, D);   // publish for CTAs that insert rarely
+        }
+        __syncwarp();
+        return;
       }
-      break;
+      run += tot;
     }
-    run += __shfl_sync(FULL_MASK, v, 31);
   }
   __syncwarp();
 }
@@ -399,7 +415,7 @@ __device__ __noinline__ void stash_flush(int warp, int lane) {
     const uint32_t qcur = __shfl_sync(FULL_MASK, q, __ffs(todo) - 1);
     const bool sel = have && q == qcur;
     list_offer(qcur, (uint32_t)(key >> 32), (uint32_t)key, sel, lane);
-    if (s_L.ghist) hist_refresh(qcur, lane);
+    if (s_L.ghist && (warp % JBN_REFRESH_MOD) == 0) hist_refresh(qcur, lane);
     todo &= ~__ballot_sync(FULL_MASK, sel);
   }
 }
