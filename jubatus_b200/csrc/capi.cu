@@ -322,16 +322,17 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
   ScanConfig cfg;
   if (!plan_scan(t, euclid, nq, kpage, h->variant_opt, h->popc_variant_opt, h->qp_opt, h->interleave_opt, h->num_sms, &cfg))
     return fail(JUBANN_E_INVALID, "cannot plan a scan for k=%u", kpage);
-  // queries per launch bounded by candidate scratch (<= 256 MiB)
+  // queries per launch bounded by candidate + shared-histogram scratch (<= 256 MiB)
   const size_t per_query = (size_t)cfg.nchunks * kpage * 8;
-  uint32_t nq_launch = (uint32_t)std::max<size_t>(cfg.qp, ((size_t)256 << 20) / per_query);
+  const size_t hist_per_query = hist_scratch_bytes(1, h->hash_num, euclid);
+  uint32_t nq_launch = (uint32_t)std::max<size_t>(cfg.qp, ((size_t)256 << 20) / (per_query + hist_per_query));
   nq_launch = std::max(cfg.qp, nq_launch / cfg.qp * cfg.qp);
   nq_launch = std::min(nq_launch, (nq + cfg.qp - 1) / cfg.qp * cfg.qp);
   if (nq_launch / cfg.qp > 65535u) nq_launch = 65535u * cfg.qp;
   CK(h->b_cand.ensure((size_t)nq_launch * per_query));
   if (pages > 1) CK(h->b_floor.ensure((size_t)nq * 8));
   CK(h->b_tau.ensure((size_t)nq_launch * 8));
-  CK(h->b_hist.ensure(hist_scratch_bytes(nq_launch, h->hash_num)));
+  CK(h->b_hist.ensure(hist_scratch_bytes(nq_launch, h->hash_num, euclid)));
   for (uint32_t q0 = 0, nql = 0; q0 < nq; q0 += nql) {
     nql = std::min(nq_launch, nq - q0);
     // keep every launch made of full groups (they run the register-resident kernels); a

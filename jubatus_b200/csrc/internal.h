@@ -69,8 +69,8 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
 uint32_t max_k_per_pass();
 // d_hist_scratch (nullable, hamming engines): hist_scratch_bytes(nq, hash_num) of scratch for the
 // distance histogram all CTAs share to derive a GPU-wide bound
-uint32_t hist_stride_for(uint32_t hash_num);
-size_t hist_scratch_bytes(uint32_t nq, uint32_t hash_num);
+uint32_t hist_stride_for(uint32_t hash_num, bool euclid);
+size_t hist_scratch_bytes(uint32_t nq, uint32_t hash_num, bool euclid);
 void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages);  // tuning experiments; 0 = automatic
 
 // cand: [nq][nchunks][k] keys ((key_hi << 32) | local row) in no particular order, KEY_SENTINEL padded.

@@ -121,7 +121,7 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
     if (!plan_scan(hi.table, hi.euclid, nq, keff, hi.variant, hi.popc_variant, hi.qp, hi.interleave, hi.num_sms, &cfg))
       return set_error(JUBANN_E_INVALID, "no-alloc query: cannot plan a scan for this k");
     const uint64_t need = (uint64_t)nq * cfg.nchunks * keff * 8ull + (uint64_t)nq * 8ull +   // lists + one threshold per query
-                          hist_scratch_bytes(nq, hi.table.hash_num);                          // + shared distance histogram
+                          (hi.euclid ? 0 : hist_scratch_bytes(nq, hi.table.hash_num, false));  // + shared distance histogram (hamming engines)
     if (need > (uint64_t)JUBANN_NOALLOC_SCRATCH_BYTES) {
       snprintf(msg, sizeof(msg),
                "no-alloc query: %u queries x %u table chunks x k=%u need %llu bytes of scratch, the fixed array holds %llu; "
@@ -139,7 +139,9 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   if (e != cudaSuccess) return cuda_error("cudaMemsetAsync(out_count)", e);
   if (keff == 0) return 0;
   uint64_t* tau_scratch = static_cast<uint64_t*>(scratch) + (size_t)nq * cfg.nchunks * keff;
-  uint32_t* hist_scratch = reinterpret_cast<uint32_t*>(tau_scratch + nq);
+  // euclid_lsh's two-level score histogram (257 KiB per query) does not fit this fixed array: that
+  // engine runs here with each CTA's own bound only
+  uint32_t* hist_scratch = hi.euclid ? nullptr : reinterpret_cast<uint32_t*>(tau_scratch + nq);
   e = launch_scan(hi.table, hi.euclid, cfg, d_qsigs, d_qnorms, hi.coslut, nq, keff, nullptr, tau_scratch, hist_scratch,
                   static_cast<uint64_t*>(scratch), s);
   if (e != cudaSuccess) return cuda_error("scan launch (no-alloc)", e);

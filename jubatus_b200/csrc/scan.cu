@@ -39,7 +39,7 @@ struct ScanArgs {
   const float* qnorms;
   const double* coslut;
   const uint64_t* floor_keys;
-  uint32_t* ghist;            // hamming only: [nq] shared bound words, then [nq][hist_stride] distance counts (nullable)
+  uint32_t* ghist;            // [nq] shared bound words, then [nq][hist_stride] bin counts (nullable)
   uint32_t hist_stride;
   const uint64_t* tau_init;   // per query: exclusive upper bound of admissible keys from the sample pre-pass (nullable)
   uint64_t* cand;
@@ -237,6 +237,31 @@ __host__ __device__ __forceinline__ uint32_t tau_hi_of(unsigned long long tau) {
   return tau ? (uint32_t)((tau - 1ull) >> 32) : 0u;
 }
 
+// euclid_lsh fast reject.  A row with norm n at Hamming distance d scores n * (n - c_d) with
+// c_d = 2 * norm_q * cos(pi d / hash_num): a parabola in n.  It can reach the list only while its
+// float score is <= T (the list's current bound), i.e. while n lies between the roots of
+// n^2 - c_d n - T = 0.  The hot loop therefore needs no double arithmetic at all: one float
+// lookup by d (the upper root) and one compare against the row norm; the exact score is computed
+// only for the rare rows below it (rows under the lower root are rejected there as well, by the
+// exact comparison).  The bound can only err towards admitting a row: T is replaced by the next
+// float above it (anything smaller may still round to T) plus 1e-14 * (c^2 + |T|), which covers
+// the two double roundings of the exact score and the rounding of the discriminant; the root is
+// moved up by 1e-14 * (|c| + sqrt(disc)) and rounded up to float.  A non-finite c or T disables
+// the filter for that entry (+inf); a negative discriminant means no norm is admissible (-inf).
+__device__ __forceinline__ float euclid_bound(double c, uint32_t tau_hi) {
+  const float Tf = key_float(tau_hi);
+  if (!(fabsf(Tf) < INFINITY) || !(fabs(c) < (double)INFINITY)) return INFINITY;
+  const float Tn = __uint_as_float(Tf >= 0.0f ? __float_as_uint(Tf + 0.0f) + 1u : __float_as_uint(Tf) - 1u);  // next float up
+  if (!(fabsf(Tn) < INFINITY)) return INFINITY;
+  const double T2 = (double)Tn;
+  const double T4 = T2 + (1e-14 * (c * c + fabs(T2)) + 1e-300);
+  const double disc = c * c + 4.0 * T4;
+  if (!(disc == disc) || !(disc < (double)INFINITY)) return INFINITY;
+  if (disc < 0.0) return -INFINITY;
+  const double sq = sqrt(disc);
+  return __double2float_ru(0.5 * (c + sq) + (1e-14 * (fabs(c) + sq) + 1e-300));
+}
+
 // ---------------------------------------------------------------------------
 // per-(CTA, query) candidate list
 // ---------------------------------------------------------------------------
@@ -258,6 +283,11 @@ struct ListCtl {
   uint32_t has_floor;
   uint32_t nq, q0, hist_stride;
   uint32_t* ghist;     // global: [nq] bound words | [nq][hist_stride] counts; nullptr when unused
+  // euclid only
+  uint32_t bnd_off;    // float [qp][hash_num + 1]: norm above which a row at that distance cannot be admitted
+  uint32_t hash_num;
+  const double* coslut;   // global: cos(pi * d / hash_num)
+  const float* qnorms;    // global: query norms
 };
 #ifndef JBN_REFRESH_MOD
 #define JBN_REFRESH_MOD 4   // every JBN_REFRESH_MOD-th warp re-derives the shared bound after a flush
@@ -267,12 +297,24 @@ __shared__ ListCtl s_L;   // written once by the prologue, read by the rare-path
 __device__ __forceinline__ unsigned long long* sm_u64(uint32_t off) { return reinterpret_cast<unsigned long long*>(g_smem + off); }
 __device__ __forceinline__ uint32_t* sm_u32(uint32_t off) { return reinterpret_cast<uint32_t*>(g_smem + off); }
 
+// euclid: recompute query q's norm bounds for its current (tightened) threshold.  One full warp.
+// Readers may see a mix of old and new entries: the bounds only ever shrink, so any mix still
+// admits every admissible norm.
+__device__ __noinline__ void euclid_bounds_update(uint32_t q, int lane) {
+  const uint32_t th = *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride);
+  const double two_nq = (double)(2.0f * s_L.qnorms[s_L.q0 + q]);
+  float* b = reinterpret_cast<float*>(g_smem + s_L.bnd_off) + (size_t)q * (s_L.hash_num + 1);
+  for (uint32_t d = lane; d <= s_L.hash_num; d += 32) b[d] = euclid_bound(__dmul_rn(two_nq, s_L.coslut[d]), th);
+  __syncwarp();
+}
+
 // Keep the k smallest of the cnt (distinct) keys of list q and tighten the threshold to the
 // k-th smallest.  No sort: the k-th smallest key is found by a most-significant-bit-first search
 // (count keys below a trial value, one warp reduction per bit), then the survivors are packed to
 // the front in place.  Called by one full warp that holds lock q (or after the CTA-wide barrier
 // at the end).  Returns the new count; the survivors are NOT ordered.
-__device__ __noinline__ uint32_t list_compact(uint32_t q, uint32_t cnt, int lane) {
+template <bool EUCLID>
+__device__ __noinline__ uint32_t list_compact(uint32_t q, uint32_t cnt, int lane, bool last = false) {
   const uint32_t cap = s_L.cap, k = s_L.k;
   unsigned long long* a = sm_u64(s_L.list_off) + (size_t)q * cap;
   if (cnt <= k) return cnt;
@@ -305,10 +347,12 @@ __device__ __noinline__ uint32_t list_compact(uint32_t q, uint32_t cnt, int lane
     atomicMin(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride, tau_hi_of(prefix));
   }
   __syncwarp();
+  if (EUCLID && !last) euclid_bounds_update(q, lane);
   return w;
 }
 
 // Warp-uniform slow path: lanes with cand != 0 offer (key_hi, row).
+template <bool EUCLID>
 __device__ __noinline__ void list_offer(uint32_t q, uint32_t key_hi, uint32_t row, bool cand, int lane) {
   const unsigned long long key = ((unsigned long long)key_hi << 32) | row;
   volatile unsigned long long* tau_p = sm_u64(s_L.tau_off) + q;
@@ -336,7 +380,7 @@ __device__ __noinline__ void list_offer(uint32_t q, uint32_t key_hi, uint32_t ro
     }
     cnt += __popc(m);
     __syncwarp();
-    if (cnt > s_L.cap - 32) cnt = list_compact(q, cnt, lane);
+    if (cnt > s_L.cap - 32) cnt = list_compact<EUCLID>(q, cnt, lane);
     if (lane == 0) *cnt_p = cnt;
   }
   __syncwarp();
@@ -346,16 +390,70 @@ __device__ __noinline__ void list_offer(uint32_t q, uint32_t key_hi, uint32_t ro
   }
 }
 
-// Hamming only.  Every inserted candidate is also counted in a histogram of distances shared
-// by all CTAs (global memory).  If the counts of distances <= D add up to k, k rows with
-// distance <= D exist, so no key with distance > D can be in the top k: (D + 1) << 32 is a valid
-// bound for every CTA.  Unlike a CTA's own k-th best it reflects what the whole GPU has seen.
-__device__ __forceinline__ void apply_shared_bound(uint32_t q, uint32_t D) {
-  atomicMin(sm_u64(s_L.tau_off) + q, ((unsigned long long)D + 1ull) << 32);
-  atomicMin(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride, D);
+// Every inserted candidate is also counted in a histogram shared by all CTAs (global memory).
+// If the counts of the bins up to B add up to k, k rows with a key inside those bins exist, so
+// no key above bin B can be in the top k: a valid bound for every CTA, and unlike a CTA's own
+// k-th best it reflects what the whole GPU has seen.
+//   hamming engines: one bin per distance (key_hi = distance).
+//   euclid_lsh: key_hi is the order-preserving image of the float score; its upper 16 bits (sign,
+//   exponent, 7 mantissa bits: steps of under 1 % of the score) index 65536 fine bins, summarised
+//   by 256 coarse bins (upper 8 bits) so that a refresh reads two short runs instead of a long one.
+static const uint32_t EUCLID_COARSE_BINS = 256, EUCLID_FINE_BINS = 65536;
+__device__ __forceinline__ void apply_shared_bound(uint32_t q, uint32_t key_hi) {
+  atomicMin(sm_u64(s_L.tau_off) + q, ((unsigned long long)key_hi + 1ull) << 32);
+  atomicMin(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride, key_hi);
+}
+template <bool EUCLID>
+__device__ __forceinline__ void hist_count(uint32_t gq, uint32_t key_hi) {
+  uint32_t* h = s_L.ghist + s_L.nq + (size_t)gq * s_L.hist_stride;
+  if (EUCLID) {
+    atomicAdd(h + EUCLID_COARSE_BINS + (key_hi >> 16), 1u);   // fine first, then its coarse summary
+    atomicAdd(h + (key_hi >> 24), 1u);
+  } else {
+    atomicAdd(h + key_hi, 1u);
+  }
 }
 
-__device__ __noinline__ void hist_refresh(uint32_t q, int lane) {
+// First bin b in [first, last] at which `run` + (counts of first..b) reaches k, or 0xFFFFFFFF;
+// `run` is advanced to the count of the bins before the returned one (or past `last`).  Eight
+// 32-bin blocks per round with their loads all in flight together (one L2 round trip per 256
+// bins).  `first` is a multiple of 32.
+__device__ __forceinline__ uint32_t hist_find(const volatile uint32_t* h, uint32_t first, uint32_t last, uint32_t& run,
+                                              uint32_t k, int lane) {
+  for (uint32_t base0 = first; base0 <= last; base0 += 256) {
+    uint32_t v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint32_t d = base0 + 32u * j + lane;
+      v[j] = (d <= last) ? h[d] : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint32_t tot = __reduce_add_sync(FULL_MASK, v[j]);
+      if (run + tot >= k) {   // the crossing is inside this block: locate it with one prefix scan
+        uint32_t x = v[j];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t n = __shfl_up_sync(FULL_MASK, x, o);
+          if (lane >= o) x += n;
+        }
+        const unsigned hit = __ballot_sync(FULL_MASK, run + x >= k);
+        const int l = __ffs(hit) - 1;
+        run += __shfl_sync(FULL_MASK, x - v[j], l);
+        return base0 + 32u * j + l;
+      }
+      run += tot;
+    }
+  }
+  return 0xFFFFFFFFu;
+}
+
+template <bool EUCLID>
+__device__ __noinline__ void hist_refresh(uint32_t q, int lane);
+
+// hamming engines: one bin per distance
+template <>
+__device__ __noinline__ void hist_refresh<false>(uint32_t q, int lane) {
   const uint32_t gq = s_L.q0 + q;
   const volatile uint32_t* h = s_L.ghist + s_L.nq + (size_t)gq * s_L.hist_stride;
   const uint32_t cur = *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride);
@@ -396,7 +494,32 @@ __device__ __noinline__ void hist_refresh(uint32_t q, int lane) {
   __syncwarp();
 }
 
+// euclid_lsh: coarse bins locate the 256 fine bins in which the count reaches k
+template <>
+__device__ __noinline__ void hist_refresh<true>(uint32_t q, int lane) {
+  const uint32_t gq = s_L.q0 + q;
+  const volatile uint32_t* h = s_L.ghist + s_L.nq + (size_t)gq * s_L.hist_stride;
+  const uint32_t cur = *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride);
+  const uint32_t last16 = cur >> 16;
+  uint32_t run = 0;
+  const uint32_t C = hist_find(h, 0, last16 >> 8, run, s_L.k, lane);
+  if (C == 0xFFFFFFFFu) return;
+  const uint32_t word = hist_find(h + EUCLID_COARSE_BINS, C << 8, min((C << 8) | 0xFFu, last16), run, s_L.k, lane);
+  if (word == 0xFFFFFFFFu) return;
+  const uint32_t bound = (word << 16) | 0xFFFFu;   // every key of that fine bin stays admissible
+  if (bound < cur) {
+    if (lane == 0) {
+      apply_shared_bound(q, bound);
+      atomicMin(s_L.ghist + gq, word);   // publish for CTAs that insert rarely
+    }
+    __syncwarp();
+    euclid_bounds_update(q, lane);
+  }
+  __syncwarp();
+}
+
 // Insert everything this warp has stashed (grouped by query, one list_offer per distinct query).
+template <bool EUCLID>
 __device__ __noinline__ void stash_flush(int warp, int lane) {
   unsigned char* base = g_smem + s_L.stash_off + (size_t)warp * (32 * 8 + 32 * 4 + 16);
   unsigned long long* skey = reinterpret_cast<unsigned long long*>(base);
@@ -409,30 +532,56 @@ __device__ __noinline__ void stash_flush(int warp, int lane) {
   const uint32_t q = have ? sq[lane] : 0xFFFFFFFFu;
   __syncwarp();
   if (lane == 0) *scnt = 0;
-  if (s_L.ghist && have) atomicAdd(s_L.ghist + s_L.nq + (size_t)(s_L.q0 + q) * s_L.hist_stride + (uint32_t)(key >> 32), 1u);
+  if (s_L.ghist && have) hist_count<EUCLID>(s_L.q0 + q, (uint32_t)(key >> 32));
   unsigned todo = __ballot_sync(FULL_MASK, have);
   while (todo) {
     const uint32_t qcur = __shfl_sync(FULL_MASK, q, __ffs(todo) - 1);
     const bool sel = have && q == qcur;
-    list_offer(qcur, (uint32_t)(key >> 32), (uint32_t)key, sel, lane);
-    if (s_L.ghist && (warp % JBN_REFRESH_MOD) == 0) hist_refresh(qcur, lane);
+    list_offer<EUCLID>(qcur, (uint32_t)(key >> 32), (uint32_t)key, sel, lane);
+    if (s_L.ghist && (warp % JBN_REFRESH_MOD) == 0) hist_refresh<EUCLID>(qcur, lane);
     todo &= ~__ballot_sync(FULL_MASK, sel);
   }
 }
 
 // One warp per CTA polls the bounds other CTAs have published (a coalesced read of nqp words).
+template <bool EUCLID>
 __device__ __forceinline__ void poll_shared_bounds(const ListCtl& L, uint32_t nqp, int lane) {
   if (L.ghist == nullptr) return;
-  for (uint32_t q = lane; q < nqp; q += 32) {
-    const uint32_t D = *reinterpret_cast<const volatile uint32_t*>(L.ghist + L.q0 + q);
-    if (D < *reinterpret_cast<const volatile uint32_t*>(sm_u32(L.tauhi_off) + (size_t)q * L.tau_stride)) {
-      atomicMin(sm_u64(L.tau_off) + q, ((unsigned long long)D + 1ull) << 32);
-      atomicMin(sm_u32(L.tauhi_off) + (size_t)q * L.tau_stride, D);
+  if (!EUCLID) {
+    for (uint32_t q = lane; q < nqp; q += 32) {
+      const uint32_t D = *reinterpret_cast<const volatile uint32_t*>(L.ghist + L.q0 + q);
+      if (D < *reinterpret_cast<const volatile uint32_t*>(sm_u32(L.tauhi_off) + (size_t)q * L.tau_stride)) {
+        atomicMin(sm_u64(L.tau_off) + q, ((unsigned long long)D + 1ull) << 32);
+        atomicMin(sm_u32(L.tauhi_off) + (size_t)q * L.tau_stride, D);
+      }
+    }
+    return;
+  }
+  for (uint32_t qb = 0; qb < nqp; qb += 32) {
+    const uint32_t q = qb + lane;
+    bool tighter = false;
+    if (q < nqp) {
+      const uint32_t word = *reinterpret_cast<const volatile uint32_t*>(L.ghist + L.q0 + q);
+      const uint32_t bound = (word << 16) | 0xFFFFu;
+      tighter = bound < *reinterpret_cast<const volatile uint32_t*>(sm_u32(L.tauhi_off) + (size_t)q * L.tau_stride);
+      if (tighter) {
+        atomicMin(sm_u64(L.tau_off) + q, ((unsigned long long)bound + 1ull) << 32);
+        atomicMin(sm_u32(L.tauhi_off) + (size_t)q * L.tau_stride, bound);
+      }
+    }
+    {   // the norm bounds of the tightened queries follow
+      unsigned m = __ballot_sync(FULL_MASK, tighter);
+      while (m) {
+        const int l = __ffs(m) - 1;
+        m &= m - 1;
+        euclid_bounds_update(qb + l, lane);
+      }
     }
   }
 }
 
 // Warp-uniform: lanes with cand offer (key_hi, row) for query q; admissible ones are stashed.
+template <bool EUCLID>
 __device__ __noinline__ void stash_push(uint32_t q, uint32_t key_hi, uint32_t row, bool cand, int warp, int lane) {
   const unsigned long long key = ((unsigned long long)key_hi << 32) | row;
   bool pass = cand && row < s_L.local_rows &&
@@ -444,7 +593,7 @@ __device__ __noinline__ void stash_push(uint32_t q, uint32_t key_hi, uint32_t ro
   volatile uint32_t* scnt = reinterpret_cast<uint32_t*>(base + 32 * 8 + 32 * 4);
   uint32_t n = *scnt;
   if (n + __popc(m) > 32) {   // no room: insert what is stashed now
-    stash_flush(warp, lane);
+    stash_flush<EUCLID>(warp, lane);
     n = 0;
   }
   if (pass) {
@@ -456,6 +605,22 @@ __device__ __noinline__ void stash_push(uint32_t q, uint32_t key_hi, uint32_t ro
   if (lane == 0) *scnt = n + __popc(m);
   __syncwarp();
 }
+
+// euclid slow path, warp-uniform: lanes with cand compute the exact score of (row, query q) --
+// double arithmetic with one rounding per operation, narrowed to float: the same values as the
+// CPU engine -- and offer it.
+__device__ __noinline__ void euclid_offer(uint32_t q, uint32_t d, float nif, uint32_t row, bool cand, int warp, int lane) {
+  if (!__any_sync(FULL_MASK, cand)) return;
+  uint32_t key = 0;
+  if (cand) {
+    const double ni = (double)nif;
+    const float two_nq = 2.0f * s_L.qnorms[s_L.q0 + q];
+    const double l2 = __dmul_rn((double)two_nq, s_L.coslut[d]);
+    key = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l2))));
+  }
+  stash_push<true>(q, key, row, cand, warp, lane);
+}
+__device__ __forceinline__ bool norm_inside(float n, float hi) { return !(n > hi); }   // NaN norms go to the exact path
 
 __device__ __forceinline__ uint32_t stash_count(const ListCtl& L, int warp) {
   return *reinterpret_cast<const volatile uint32_t*>(g_smem + L.stash_off + (size_t)warp * (32 * 8 + 32 * 4 + 16) + 32 * 8 + 32 * 4);
@@ -483,7 +648,7 @@ __host__ __device__ inline SmemPlan plan_smem(uint32_t qp, uint32_t w32, uint32_
   SmemPlan p;
   size_t o = base;
   p.q_off = o; o = align16(o + (size_t)qp * q_stride(w32) * 4);
-  p.lut_off = o; if (euclid) o = align16(o + (size_t)qp * (hash_num + 1) * 8);
+  p.lut_off = o; if (euclid) o = align16(o + (size_t)qp * (hash_num + 1) * 4);
   p.list_off = o; o = align16(o + (size_t)qp * cap * 8);
   p.tau_off = o; o = align16(o + (size_t)qp * 8);
   p.floor_off = o; o = align16(o + (size_t)qp * 8);
@@ -499,42 +664,43 @@ __host__ __device__ inline SmemPlan plan_smem(uint32_t qp, uint32_t w32, uint32_
 // one tile (lane = row) against the CTA's queries
 // ---------------------------------------------------------------------------
 template <int W32, bool EUCLID, int PV>
-__device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t row, double ni, uint32_t nqp,
-                                          const uint32_t* s_q, const double* s_lut, uint32_t hash_num,
+__device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t row, float ni, uint32_t nqp,
+                                          const uint32_t* s_q, const float* s_bnd, uint32_t hash_num,
                                           const ListCtl& L, int lane) {
   constexpr uint32_t QS = W32 + 4;
+  const int warp = threadIdx.x >> 5;
   uint32_t q = 0;
   for (; q + 2 <= nqp; q += 2) {  // two independent distance chains in flight
     const uint32_t* b0 = s_q + q * QS;
     const uint32_t* b1 = b0 + QS;
     const uint32_t d0 = hamming<W32, PV>(cur, b0);
     const uint32_t d1 = hamming<W32, PV>(cur, b1);
-    uint32_t k0 = d0, k1 = d1;
     if (EUCLID) {
-      // score = norm_i * (norm_i - 2*norm_q*cos(theta)), evaluated in double with one rounding
-      // per operation, then narrowed to float: the same values as the CPU engine
-      const double l0 = s_lut[q * (hash_num + 1) + d0];
-      const double l1 = s_lut[(q + 1) * (hash_num + 1) + d1];
-      k0 = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l0))));
-      k1 = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l1))));
-    }
-    const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
-    const bool c1 = k1 <= *reinterpret_cast<const volatile uint32_t*>(b1 + W32);
-    if (__any_sync(FULL_MASK, c0 || c1)) {
-      stash_push(q, k0, row, c0, threadIdx.x >> 5, lane);
-      stash_push(q + 1, k1, row, c1, threadIdx.x >> 5, lane);
+      const bool c0 = norm_inside(ni, s_bnd[q * (hash_num + 1) + d0]);
+      const bool c1 = norm_inside(ni, s_bnd[(q + 1) * (hash_num + 1) + d1]);
+      if (__any_sync(FULL_MASK, c0 || c1)) {
+        euclid_offer(q, d0, ni, row, c0, warp, lane);
+        euclid_offer(q + 1, d1, ni, row, c1, warp, lane);
+      }
+    } else {
+      const bool c0 = d0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
+      const bool c1 = d1 <= *reinterpret_cast<const volatile uint32_t*>(b1 + W32);
+      if (__any_sync(FULL_MASK, c0 || c1)) {
+        stash_push<false>(q, d0, row, c0, warp, lane);
+        stash_push<false>(q + 1, d1, row, c1, warp, lane);
+      }
     }
   }
   if (q < nqp) {
     const uint32_t* b0 = s_q + q * QS;
     const uint32_t d0 = hamming<W32, PV>(cur, b0);
-    uint32_t k0 = d0;
     if (EUCLID) {
-      const double l0 = s_lut[q * (hash_num + 1) + d0];
-      k0 = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l0))));
+      const bool c0 = norm_inside(ni, s_bnd[q * (hash_num + 1) + d0]);
+      if (__any_sync(FULL_MASK, c0)) euclid_offer(q, d0, ni, row, c0, warp, lane);
+    } else {
+      const bool c0 = d0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
+      if (__any_sync(FULL_MASK, c0)) stash_push<false>(q, d0, row, c0, warp, lane);
     }
-    const bool c0 = k0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
-    if (__any_sync(FULL_MASK, c0)) stash_push(q, k0, row, c0, threadIdx.x >> 5, lane);
   }
 }
 
@@ -542,9 +708,10 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
 // serves two rows, and the two distance chains are independent
 template <int W32, bool EUCLID, int PV>
 __device__ __forceinline__ void rank_tile2(const uint32_t (&ra)[W32], const uint32_t (&rb)[W32], uint32_t rowa,
-                                           uint32_t rowb, double nia, double nib, uint32_t nqp, const uint32_t* s_q,
-                                           const double* s_lut, uint32_t hash_num, const ListCtl& L, int lane) {
+                                           uint32_t rowb, float nia, float nib, uint32_t nqp, const uint32_t* s_q,
+                                           const float* s_bnd, uint32_t hash_num, const ListCtl& L, int lane) {
   constexpr uint32_t QS = W32 + 4;
+  const int warp = threadIdx.x >> 5;
   const uint32_t* b0 = s_q;
 #pragma unroll 2
   for (uint32_t q = 0; q < nqp; ++q, b0 += QS) {
@@ -552,63 +719,66 @@ __device__ __forceinline__ void rank_tile2(const uint32_t (&ra)[W32], const uint
     load_query<W32>(b0, qw);
     const uint32_t da = hamming_rq<W32, PV>(ra, qw);
     const uint32_t db = hamming_rq<W32, PV>(rb, qw);
-    uint32_t ka = da, kb = db;
     if (EUCLID) {
-      const double la = s_lut[q * (hash_num + 1) + da];
-      const double lb = s_lut[q * (hash_num + 1) + db];
-      ka = float_key(__double2float_rn(__dmul_rn(nia, __dsub_rn(nia, la))));
-      kb = float_key(__double2float_rn(__dmul_rn(nib, __dsub_rn(nib, lb))));
-    }
-    const uint32_t tau = *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
-    const bool ca = ka <= tau, cb = kb <= tau;
-    if (__any_sync(FULL_MASK, ca || cb)) {
-      stash_push(q, ka, rowa, ca, threadIdx.x >> 5, lane);
-      stash_push(q, kb, rowb, cb, threadIdx.x >> 5, lane);
+      const bool ca = norm_inside(nia, s_bnd[q * (hash_num + 1) + da]);
+      const bool cb = norm_inside(nib, s_bnd[q * (hash_num + 1) + db]);
+      if (__any_sync(FULL_MASK, ca || cb)) {
+        euclid_offer(q, da, nia, rowa, ca, warp, lane);
+        euclid_offer(q, db, nib, rowb, cb, warp, lane);
+      }
+    } else {
+      const uint32_t tau = *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
+      const bool ca = da <= tau, cb = db <= tau;
+      if (__any_sync(FULL_MASK, ca || cb)) {
+        stash_push<false>(q, da, rowa, ca, warp, lane);
+        stash_push<false>(q, db, rowb, cb, warp, lane);
+      }
     }
   }
 }
 
 // Register-resident queries (TMA variant, <= 4 queries per pass): the CTA's queries are loaded
 // into registers once, thresholds are re-read once per stage, so the inner loop touches shared
-// memory only for the rows themselves.  NR rows (tiles) are ranked together.
+// memory only for the rows themselves (and, for euclid, the norm intervals).  NR rows (tiles)
+// are ranked together.
 template <int W32, bool EUCLID, int PV, int NQ, int NR>
 __device__ __forceinline__ void rank_reg(const uint32_t (&rows)[NR][W32], const uint32_t (&rowid)[NR],
-                                         const double (&ni)[NR], const uint32_t (&qreg)[NQ][W32],
-                                         const uint32_t (&tau)[NQ], const double* s_lut, uint32_t hash_num,
+                                         const float (&ni)[NR], const uint32_t (&qreg)[NQ][W32],
+                                         const uint32_t (&tau)[NQ], const float* s_bnd, uint32_t hash_num,
                                          int warp, int lane) {
-  uint32_t key[NQ][NR];
+  uint32_t dist[NQ][NR];
   bool any = false;
 #pragma unroll
   for (int q = 0; q < NQ; ++q) {
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
       const uint32_t d = hamming_rq<W32, PV>(rows[r], qreg[q]);
-      uint32_t kk = d;
-      if (EUCLID) {
-        const double l2 = s_lut[q * (hash_num + 1) + d];
-        kk = float_key(__double2float_rn(__dmul_rn(ni[r], __dsub_rn(ni[r], l2))));
-      }
-      key[q][r] = kk;
-      any = any || (kk <= tau[q]);
+      dist[q][r] = d;
+      any = any || (EUCLID ? norm_inside(ni[r], s_bnd[q * (hash_num + 1) + d]) : (d <= tau[q]));
     }
   }
   if (__any_sync(FULL_MASK, any)) {
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
 #pragma unroll
-      for (int r = 0; r < NR; ++r) stash_push(q, key[q][r], rowid[r], key[q][r] <= tau[q], warp, lane);
+      for (int r = 0; r < NR; ++r) {
+        if (EUCLID)
+          euclid_offer(q, dist[q][r], ni[r], rowid[r], norm_inside(ni[r], s_bnd[q * (hash_num + 1) + dist[q][r]]), warp, lane);
+        else
+          stash_push<false>(q, dist[q][r], rowid[r], dist[q][r] <= tau[q], warp, lane);
+      }
     }
   }
 }
 
-// shared prologue: query blocks, euclid LUT, list control
+// shared prologue: query blocks, euclid norm intervals, list control
 template <int W32, bool EUCLID>
 __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* smem, const SmemPlan& sp, ListCtl& L,
-                                              uint32_t*& s_q, double*& s_lut, uint32_t q0, uint32_t nqp, int tid,
+                                              uint32_t*& s_q, float*& s_bnd, uint32_t q0, uint32_t nqp, int tid,
                                               int nthreads) {
   constexpr uint32_t QS = W32 + 4;
   s_q = reinterpret_cast<uint32_t*>(smem + sp.q_off);
-  s_lut = reinterpret_cast<double*>(smem + sp.lut_off);
+  s_bnd = reinterpret_cast<float*>(smem + sp.lut_off);
   L.list_off = (uint32_t)sp.list_off; L.tau_off = (uint32_t)sp.tau_off; L.floor_off = (uint32_t)sp.floor_off;
   L.cnt_off = (uint32_t)sp.cnt_off; L.lock_off = (uint32_t)sp.lock_off;
   L.tauhi_off = (uint32_t)(sp.q_off + W32 * 4);
@@ -616,7 +786,9 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
   L.tau_stride = QS;
   L.local_rows = (uint32_t)a.local_rows;
   L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr) ? 1u : 0u;
-  L.nq = a.nq; L.q0 = q0; L.hist_stride = a.hist_stride; L.ghist = EUCLID ? nullptr : a.ghist;
+  L.nq = a.nq; L.q0 = q0; L.hist_stride = a.hist_stride; L.ghist = a.ghist;
+  L.bnd_off = (uint32_t)sp.lut_off; L.hash_num = a.hash_num;
+  L.coslut = EUCLID ? a.coslut : nullptr; L.qnorms = EUCLID ? a.qnorms : nullptr;
   if (tid == 0) s_L = L;
   if ((uint32_t)tid < STASH_WARPS) *reinterpret_cast<uint32_t*>(smem + sp.stash_off + (size_t)tid * STASH_BYTES + STASH * 12) = 0u;
   for (uint32_t i = tid; i < nqp * QS; i += nthreads) {
@@ -629,7 +801,8 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
     for (uint32_t i = tid; i < nqp * hn; i += nthreads) {
       uint32_t q = i / hn, h = i % hn;
       float two_nq = 2.0f * a.qnorms[q0 + q];
-      s_lut[i] = __dmul_rn((double)two_nq, a.coslut[h]);
+      s_bnd[i] = euclid_bound(__dmul_rn((double)two_nq, a.coslut[h]),
+                               tau_hi_of(a.tau_init ? a.tau_init[q0 + q] : KEY_SENTINEL));
     }
   }
   if ((uint32_t)tid < nqp) {
@@ -651,8 +824,8 @@ __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
   const uint32_t nqp = min(a.qp, a.nq - q0);
   ListCtl L;
   uint32_t* s_q;
-  double* s_lut;
-  scan_prologue<W32, EUCLID>(a, smem, sp, L, s_q, s_lut, q0, nqp, tid, SCAN_THREADS);
+  float* s_bnd;
+  scan_prologue<W32, EUCLID>(a, smem, sp, L, s_q, s_bnd, q0, nqp, tid, SCAN_THREADS);
   __syncthreads();
 
   uint64_t t, t_end, t_step;
@@ -679,17 +852,17 @@ __global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
       load_row<W32>(a.slab, tn, lane, nxt);
       if (EUCLID) nnxt = ld_stream_f32(a.norms + tn * 32 + lane);
     }
-    rank_tile<W32, EUCLID, PV>(cur, (uint32_t)(t * 32 + lane), (double)ncur, nqp, s_q, s_lut, a.hash_num, L, lane);
-    if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush(warp, lane);   // the next tile's loads are already in flight
-    if (warp == 0 && ((++poll_tick) & 7u) == 0u) poll_shared_bounds(L, nqp, lane);
+    rank_tile<W32, EUCLID, PV>(cur, (uint32_t)(t * 32 + lane), ncur, nqp, s_q, s_bnd, a.hash_num, L, lane);
+    if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush<EUCLID>(warp, lane);   // the next tile's loads are already in flight
+    if (warp == 0 && ((++poll_tick) & 7u) == 0u) poll_shared_bounds<EUCLID>(L, nqp, lane);
 #pragma unroll
     for (int w = 0; w < W32; ++w) cur[w] = nxt[w];
     ncur = nnxt;
   }
-  if (stash_count(L, warp)) stash_flush(warp, lane);
+  if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane);
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += SCAN_WARPS) {
-    uint32_t n = list_compact(q, sm_u32(L.cnt_off)[q], lane);
+    uint32_t n = list_compact<EUCLID>(q, sm_u32(L.cnt_off)[q], lane, true);
     const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
                               ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
@@ -791,8 +964,8 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
   const size_t stage_bytes = stage_tiles * tile_bytes;
   ListCtl L;
   uint32_t* s_q;
-  double* s_lut;
-  scan_prologue<W32, EUCLID>(a, smem, sp, L, s_q, s_lut, q0, nqp, tid, TMA_THREADS);
+  float* s_bnd;
+  scan_prologue<W32, EUCLID>(a, smem, sp, L, s_q, s_bnd, q0, nqp, tid, TMA_THREADS);
   if (tid == 0) {
     for (uint32_t s = 0; s < stages; ++s) {
       mbar_init(full_bar + s, 1);
@@ -865,18 +1038,18 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
             load_row_smem<W32>(stage, tis, lane, rows[0]);
             load_row_smem<W32>(stage, tis + 1, lane, rows[1]);
             const uint32_t rowid[2] = {rowa, rowa + 32};
-            double ni[2] = {0.0, 0.0};
-            if (EUCLID) { ni[0] = (double)nstage[tis * 32 + lane]; ni[1] = (double)nstage[(tis + 1) * 32 + lane]; }
-            rank_reg<W32, EUCLID, PV, NQR, 2>(rows, rowid, ni, qreg, tau, s_lut, a.hash_num, warp, lane);
+            float ni[2] = {0.0f, 0.0f};
+            if (EUCLID) { ni[0] = nstage[tis * 32 + lane]; ni[1] = nstage[(tis + 1) * 32 + lane]; }
+            rank_reg<W32, EUCLID, PV, NQR, 2>(rows, rowid, ni, qreg, tau, s_bnd, a.hash_num, warp, lane);
           } else {
             const uint32_t ntile = (t + 1 < t_end) ? 2u : 1u;
             for (uint32_t u = 0; u < ntile; ++u) {
               uint32_t rows[1][W32];
               load_row_smem<W32>(stage, tis + u, lane, rows[0]);
               const uint32_t rowid[1] = {rowa + 32 * u};
-              double ni[1] = {0.0};
-              if (EUCLID) ni[0] = (double)nstage[(tis + u) * 32 + lane];
-              rank_reg<W32, EUCLID, PV, NQR, 1>(rows, rowid, ni, qreg, tau, s_lut, a.hash_num, warp, lane);
+              float ni[1] = {0.0f};
+              if (EUCLID) ni[0] = nstage[(tis + u) * 32 + lane];
+              rank_reg<W32, EUCLID, PV, NQR, 1>(rows, rowid, ni, qreg, tau, s_bnd, a.hash_num, warp, lane);
             }
           }
         }
@@ -887,30 +1060,33 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
         if (t >= t_end) break;
         uint32_t ra[W32];
         load_row_smem<W32>(stage, tis, lane, ra);
-        double nia = 0.0;
-        if (EUCLID) nia = (double)nstage[tis * 32 + lane];
+        float nia = 0.0f;
+        if (EUCLID) nia = nstage[tis * 32 + lane];
         const uint32_t rowa = (uint32_t)(t * 32 + lane);
         if (t + 1 < t_end) {
           uint32_t rb[W32];
           load_row_smem<W32>(stage, tis + 1, lane, rb);
-          double nib = 0.0;
-          if (EUCLID) nib = (double)nstage[(tis + 1) * 32 + lane];
-          rank_tile2<W32, EUCLID, PV>(ra, rb, rowa, rowa + 32, nia, nib, nqp, s_q, s_lut, a.hash_num, L, lane);
+          float nib = 0.0f;
+          if (EUCLID) nib = nstage[(tis + 1) * 32 + lane];
+          rank_tile2<W32, EUCLID, PV>(ra, rb, rowa, rowa + 32, nia, nib, nqp, s_q, s_bnd, a.hash_num, L, lane);
         } else {
-          rank_tile<W32, EUCLID, PV>(ra, rowa, nia, nqp, s_q, s_lut, a.hash_num, L, lane);
+          rank_tile<W32, EUCLID, PV>(ra, rowa, nia, nqp, s_q, s_bnd, a.hash_num, L, lane);
         }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_bar + s);   // release the stage first ...
-      if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush(warp, lane);   // ... then do the slow insertions
-      if (warp == 0) poll_shared_bounds(L, nqp, lane);
+      if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush<EUCLID>(warp, lane);   // ... then do the slow insertions
+      // euclid: a tighter bound means recomputing that query's norm bounds, so poll less often
+      // and take turns (a warp that lags holds up the whole ring)
+      if (EUCLID ? ((it & 7u) == 7u && (uint32_t)warp == (it >> 3) % TMA_CONSUMER_WARPS) : (warp == 0))
+        poll_shared_bounds<EUCLID>(L, nqp, lane);
       if (++s == stages) { s = 0; ph ^= 1u; }
     }
-    if (stash_count(L, warp)) stash_flush(warp, lane);
+    if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane);
   }
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += TMA_CONSUMER_WARPS + 1) {
-    uint32_t n = list_compact(q, sm_u32(L.cnt_off)[q], lane);
+    uint32_t n = list_compact<EUCLID>(q, sm_u32(L.cnt_off)[q], lane, true);
     const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
                               ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
@@ -1117,8 +1293,12 @@ __global__ void __launch_bounds__(TAU_THREADS) tau_init_kernel(ScanArgs a, uint3
 // host side
 // ---------------------------------------------------------------------------
 uint32_t max_k_per_pass() { return MAX_CAP / 2; }
-uint32_t hist_stride_for(uint32_t hash_num) { return (hash_num + 1 + 31) / 32 * 32; }
-size_t hist_scratch_bytes(uint32_t nq, uint32_t hash_num) { return ((size_t)nq + (size_t)nq * hist_stride_for(hash_num)) * 4; }
+uint32_t hist_stride_for(uint32_t hash_num, bool euclid) {
+  return euclid ? EUCLID_COARSE_BINS + EUCLID_FINE_BINS : (hash_num + 1 + 31) / 32 * 32;
+}
+size_t hist_scratch_bytes(uint32_t nq, uint32_t hash_num, bool euclid) {
+  return ((size_t)nq + (size_t)nq * hist_stride_for(hash_num, euclid)) * 4;
+}
 
 static uint32_t g_tma_tpw_override = 0, g_tma_stages_override = 0;
 void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages) {
@@ -1253,7 +1433,7 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   a.ntiles = (t.local_rows + 31) / 32;
   a.qsigs = d_qsigs; a.qnorms = d_qnorms; a.coslut = d_coslut; a.floor_keys = d_floor_keys;
   a.tau_init = nullptr;
-  a.ghist = nullptr; a.hist_stride = hist_stride_for(t.hash_num);
+  a.ghist = nullptr; a.hist_stride = hist_stride_for(t.hash_num, euclid);
   a.cand = d_cand;
   a.nq = nq; a.k = k; a.cap = cfg.cap; a.qp = cfg.qp; a.w64 = t.w64; a.hash_num = t.hash_num;
   a.tiles_per_chunk = cfg.tiles_per_chunk; a.nchunks = cfg.nchunks;
@@ -1274,7 +1454,7 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
       a.tau_init = d_tau_scratch;
     }
   }
-  if (d_hist_scratch && !euclid && t.local_rows >= (1u << 16)) {
+  if (d_hist_scratch && t.local_rows >= (1u << 16)) {
     cudaError_t e = cudaMemsetAsync(d_hist_scratch, 0xFF, (size_t)nq * 4, s);   // published bounds: none yet
     if (e == cudaSuccess) e = cudaMemsetAsync(d_hist_scratch + nq, 0, (size_t)nq * a.hist_stride * 4, s);
     if (e != cudaSuccess) return e;
