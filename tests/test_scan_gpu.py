@@ -241,3 +241,41 @@ def test_sample_prepass_bound_is_safe(oracle, method, hash_num, n, k, scan_varia
         got = e.query_sig(q, qn, k)
     want = oracle.scan_batch(method, q, qn, rows, norms, hash_num, k, threads=4)[:3]
     assert_same_ranking(got, want, nq, k)
+
+
+@pytest.mark.parametrize("scan_variant", [1, 2])
+@pytest.mark.parametrize("qp", [1, 2, 4, 16])
+@pytest.mark.parametrize("hash_num,n,k", [(256, 150000, 100), (64, 90000, 7), (512, 70000, 300)])
+def test_euclid_norm_bound_filter_adversarial(oracle, hash_num, n, k, qp, scan_variant):
+    """euclid_lsh rows are pre-filtered by a float bound on the row norm per Hamming distance and by a
+    GPU-wide histogram of score keys (tables >= 65536 rows); both may only ever let too much
+    through.  Norms over six decades, zero norms, blocks of equal norms (ties by row index),
+    near-copies of the queries (negative scores) and thresholds that cross zero."""
+    from jubatus_b200 import SIMILAR
+    rng = np.random.RandomState(hash_num * 7 + k + qp)
+    nq = 16
+    rows = random_rows(rng, n, hash_num)
+    q = random_rows(rng, nq, hash_num)
+    norms = np.exp(rng.uniform(np.log(1e-3), np.log(1e3), n)).astype(np.float32)
+    norms[rng.randint(0, n, n // 50)] = 0.0
+    norms[1000:3000] = np.float32(0.75)
+    qn = np.exp(rng.uniform(np.log(1e-2), np.log(1e2), nq)).astype(np.float32)
+    qn[3] = 0.0
+    w = rows.shape[1]
+    for j in range(nq // 2):      # plant near-copies with norms around the query's: negative scores
+        for c in range(40):
+            r = rng.randint(0, n)
+            rows[r] = q[j]
+            flip = rng.randint(0, hash_num, rng.randint(0, 6))
+            for b in flip:
+                rows[r, b // 64] ^= np.uint64(1) << np.uint64(b % 64)
+            norms[r] = np.float32(qn[j] * rng.uniform(0.3, 2.5))
+    assert rows.shape[1] == w
+    with _engine("euclid_lsh", hash_num, scan_variant=scan_variant, queries_per_pass=qp) as e:
+        e.set_rows_sig(np.arange(n), rows, norms)
+        got = e.query_sig(q, qn, k)
+        got_sim = e.query_sig(q, qn, k, SIMILAR)
+    want = oracle.scan_batch("euclid_lsh", q, qn, rows, norms, hash_num, k, threads=4)[:3]
+    assert_same_ranking(got, want, nq, k)
+    want_sim = oracle.scan_batch("euclid_lsh", q, qn, rows, norms, hash_num, k, similar=True, threads=4)[:3]
+    assert_same_ranking(got_sim, want_sim, nq, k)
