@@ -174,7 +174,7 @@ int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, u
  * candidate lists) is a fixed array of JUBANN_NOALLOC_SCRATCH_BYTES inside the library image
  * instead of a buffer grown with cudaMalloc; every GPU that loads the library holds it until
  * exit.  This call allocates and frees nothing.  It needs nq * (chunks * min(k, rows) + 1) * 8
- * + nq * (hash_num + 33) * 4 bytes (chunks <= 2 per SM); a larger request, or k above 2048,
+ * + nq * (hash_num + 33) * 4 bytes (that term for lsh / minhash only; chunks <= 2 per SM); a larger request, or k above 2048,
  * returns JUBANN_E_INVALID
  * with a message.  The first call on a device looks up the array's address
  * (cudaGetSymbolAddress): make it at start-up, before any stream capture.  Calls share the

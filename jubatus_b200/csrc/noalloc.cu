@@ -16,7 +16,7 @@
 //  * The array is part of the library image: every GPU that loads libjubann.so holds
 //    JUBANN_NOALLOC_SCRATCH_BYTES (32 MiB) of device memory until the process exits,
 //    whether or not this entry point is ever called.
-//  * A call needs  nq * (chunks * min(k, rows) + 1) * 8 + nq * (hash_num + 33) * 4  bytes of it (chunks = CTAs along the
+//  * A call needs  nq * (chunks * min(k, rows) + 1) * 8 + nq * (hash_num + 33) * 4  bytes of it (second term: lsh / minhash only) (chunks = CTAs along the
 //    table, at most 2 per SM).  A request that does not fit, or k above the single-pass
 //    limit of 2048, is refused with JUBANN_E_INVALID and a message; nothing is launched.
 //  * The first call on a device looks up the array's device address
