@@ -30,6 +30,14 @@ def _nvcc():
     raise RuntimeError("nvcc not found")
 
 
+def _cxx():
+    """The host compiler nvcc itself uses (g++ on PATH), so that every library of the process shares
+    one dynamic libstdc++.  ($CXX in this image is a wrapper that links libstdc++ statically; a
+    second, older copy of the runtime inside the host library crashed in iostream code once
+    libjubann.so had pulled in the system one.)"""
+    return shutil.which("g++") or os.environ.get("CXX") or "g++"
+
+
 def _newer(target, deps):
     if not os.path.exists(target):
         return True
@@ -79,7 +87,7 @@ def build_host(verbose=False):
     deps = srcs + [os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith(".hpp")]
     deps.append(os.path.join(ROOT, "include", "jubann.h"))
     if _newer(HOST_LIB, deps):
-        cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
+        cxx = _cxx()
         _run([cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", "-Wall", "-I", os.path.join(ROOT, "include"),
               "-o", HOST_LIB] + srcs + ["-ldl"])
     return HOST_LIB
@@ -87,7 +95,10 @@ def build_host(verbose=False):
 
 def build_oracle():
     """Test infrastructure: the CPU oracle (building the checker is not using it)."""
-    _run(["make", "-C", os.path.join(ROOT, "oracle")])
+    _run(["make", "-C", os.path.join(ROOT, "oracle"), "CXX=" + _cxx()])
+    # oracle/_ref: the reference's own crc32.cpp, compiled where it lies (only in the container
+    # that has /root/reference; the GPU box uses the prebuilt file that travelled with the snapshot)
+    _run(["make", "-C", os.path.join(ROOT, "oracle"), "CXX=" + _cxx(), "ref"])
 
 
 def build_all(verbose=False):

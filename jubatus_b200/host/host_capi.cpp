@@ -6,6 +6,8 @@
 
 #include <string.h>
 
+#include <sstream>
+
 using namespace jubatus_b200;
 
 namespace {
@@ -251,6 +253,80 @@ int64_t jubahost_pack(void* h, char* buf, uint64_t cap) {
 int jubahost_unpack(void* h, const char* buf, uint64_t n) {
   host_box* b = static_cast<host_box*>(h);
   return guarded([&]() { b->nn()->unpack(std::string(buf, n)); return 0; });
+}
+// ---- model files (nearest_neighbor kind): server_base::save / load / load_file ----
+uint32_t jubahost_crc32(const char* data, uint64_t n, uint32_t crc) { return model_file::calc_crc32(data, n, crc); }
+int jubahost_set_storage(void* h, const char* datadir, const char* eth, int port) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->serv) throw jubatus_exception("model files are served by the nearest_neighbor kind");
+    b->serv->set_storage(datadir, eth, port);
+    return 0;
+  });
+}
+int jubahost_save(void* h, const char* id, char* path_buf, uint64_t cap) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->serv) throw jubatus_exception("model files are served by the nearest_neighbor kind");
+    std::map<std::string, std::string> r = b->serv->save(id);
+    const std::string out = r.begin()->first + "\n" + r.begin()->second;
+    if (out.size() + 1 > cap) throw jubatus_exception("path buffer too small");
+    memcpy(path_buf, out.c_str(), out.size() + 1);
+    return 0;
+  });
+}
+int jubahost_load(void* h, const char* id) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->serv) throw jubatus_exception("model files are served by the nearest_neighbor kind");
+    b->serv->load(id);
+    return 0;
+  });
+}
+int jubahost_load_file(void* h, const char* path) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->serv) throw jubatus_exception("model files are served by the nearest_neighbor kind");
+    b->serv->load_file(path);
+    return 0;
+  });
+}
+int jubahost_get_config(void* h, char* buf, uint64_t cap) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->serv) throw jubatus_exception("get_config is served by the nearest_neighbor kind");
+    const std::string c = b->serv->get_config();
+    if (c.size() + 1 > cap) throw jubatus_exception("config buffer too small");
+    memcpy(buf, c.c_str(), c.size() + 1);
+    return 0;
+  });
+}
+// container only, no engine: write / check a model file around an arbitrary payload (CPU tests)
+int64_t jubahost_model_write(const char* type, const char* id, const char* config, uint64_t user_data_version,
+                             const char* payload, uint64_t payload_n, uint64_t timestamp, char* out, uint64_t cap) {
+  int64_t n = -1;
+  int rc = guarded([&]() {
+    std::ostringstream os;
+    model_file::save(os, type, id, config, user_data_version, std::string(payload, payload_n), timestamp);
+    const std::string f = os.str();
+    if (f.size() <= cap) memcpy(out, f.data(), f.size());
+    n = static_cast<int64_t>(f.size());
+    return 0;
+  });
+  return rc ? -1 : n;
+}
+int64_t jubahost_model_read(const char* file, uint64_t file_n, const char* expected_type, const char* expected_config,
+                            int overwrite_config, uint64_t user_data_version, char* payload, uint64_t cap) {
+  int64_t n = -1;
+  int rc = guarded([&]() {
+    std::istringstream is(std::string(file, file_n));
+    model_file::system_data sd;
+    const std::string p = model_file::load(is, expected_type, expected_config, overwrite_config != 0, user_data_version, &sd);
+    if (p.size() <= cap) memcpy(payload, p.data(), p.size());
+    n = static_cast<int64_t>(p.size());
+    return 0;
+  });
+  return rc ? -1 : n;
 }
 int jubahost_dump_json(void* h, char* buf, uint64_t cap) {
   host_box* b = static_cast<host_box*>(h);

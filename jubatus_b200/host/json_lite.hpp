@@ -5,6 +5,8 @@
 #ifndef JUBANN_HOST_JSON_LITE_HPP_
 #define JUBANN_HOST_JSON_LITE_HPP_
 
+#include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <map>
 #include <memory>
@@ -127,6 +129,55 @@ class parser {
 };
 
 inline ptr parse(const std::string& s) { return parser(s).parse(); }
+
+// Canonical text of a value: no whitespace, object keys sorted (the reference's json object is a
+// std::map, so re-serialising two configs that differ in spacing or key order gives equal text:
+// compare_config, framework/save_load.cpp:102-109).
+inline void dump_to(const value& v, std::string& out) {
+  switch (v.kind) {
+    case value::NUL: out += "null"; break;
+    case value::BOOL: out += v.b ? "true" : "false"; break;
+    case value::NUM: {
+      char buf[40];
+      if (v.is_integer) snprintf(buf, sizeof(buf), "%lld", static_cast<long long>(v.num));
+      else snprintf(buf, sizeof(buf), "%.17g", v.num);
+      out += buf;
+      break;
+    }
+    case value::STR: {
+      out.push_back('"');
+      for (size_t i = 0; i < v.str.size(); ++i) {
+        const unsigned char c = static_cast<unsigned char>(v.str[i]);
+        if (c == '"' || c == '\\') { out.push_back('\\'); out.push_back(static_cast<char>(c)); }
+        else if (c < 0x20) { char buf[8]; snprintf(buf, sizeof(buf), "\\u%04x", c); out += buf; }
+        else out.push_back(static_cast<char>(c));
+      }
+      out.push_back('"');
+      break;
+    }
+    case value::ARR:
+      out.push_back('[');
+      for (size_t i = 0; i < v.arr.size(); ++i) { if (i) out.push_back(','); dump_to(*v.arr[i], out); }
+      out.push_back(']');
+      break;
+    case value::OBJ: {
+      std::vector<size_t> order(v.obj.size());
+      for (size_t i = 0; i < order.size(); ++i) order[i] = i;
+      std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return v.obj[a].first < v.obj[b].first; });
+      out.push_back('{');
+      for (size_t i = 0; i < order.size(); ++i) {
+        if (i) out.push_back(',');
+        value k; k.kind = value::STR; k.str = v.obj[order[i]].first;
+        dump_to(k, out);
+        out.push_back(':');
+        dump_to(*v.obj[order[i]].second, out);
+      }
+      out.push_back('}');
+      break;
+    }
+  }
+}
+inline std::string dump(const ptr& v) { std::string out; if (v) dump_to(*v, out); return out; }
 
 }  // namespace json
 }  // namespace jubatus_b200

@@ -33,6 +33,7 @@
 #include <algorithm>
 #include <chrono>
 #include <condition_variable>
+#include <fstream>
 #include <limits>
 #include <map>
 #include <memory>
@@ -47,6 +48,7 @@
 
 #include "jubann.h"
 #include "json_lite.hpp"
+#include "model_file.hpp"
 
 namespace jubatus_b200 {
 
@@ -712,6 +714,8 @@ class nearest_neighbor {
   std::vector<std::string> get_all_rows() { std::vector<std::string> r; nn_->get_all_row_ids(r); return r; }
   void clear() { nn_->clear(); }
   mixable_versioned_table* get_mixable() { return nn_->get_mixable(); }
+  std::string pack() const { return nn_->pack(); }                 // driver->pack, save_load.cpp:129
+  void unpack(const std::string& blob) { nn_->unpack(blob); }      // driver->unpack, save_load.cpp:280
   const datum_to_fv_converter& converter() const { return *converter_; }
  private:
   std::shared_ptr<gpu_nearest_neighbor> nn_;
@@ -844,7 +848,68 @@ class nearest_neighbor_serv {
   std::vector<std::string> get_all_rows() const { check_set_config(); return nearest_neighbor_->get_all_rows(); }
   uint64_t update_row_cnt() const { return update_row_cnt_; }
   driver::nearest_neighbor* get_driver() { check_set_config(); return nearest_neighbor_.get(); }
+
+  // ---- model files (framework/server_base.cpp:135-212, framework/save_load.cpp) ----
+  // where `save(id)` / `load(id)` put their file: <datadir>/<eth>_<port>_<type>_<id>.jubatus
+  // (build_local_path, server_base.cpp:41-50; defaults of server_util.cpp: /tmp, port 9199)
+  void set_storage(const std::string& datadir, const std::string& eth, int port) { datadir_ = datadir; eth_ = eth; port_ = port; }
+  static const char* type() { return "nearest_neighbor"; }
+  uint64_t user_data_version() const { return 1; }   // nearest_neighbor_serv.cpp:77-79
+  std::string local_path(const std::string& id) const {
+    std::ostringstream p; p << datadir_ << '/' << eth_ << '_' << port_ << '_' << type() << '_' << id << ".jubatus";
+    return p.str();
+  }
+  // returns {server identifier "<eth>_<port>" -> path}, like the `save` RPC
+  std::map<std::string, std::string> save(const std::string& id) {
+    check_set_config();
+    if (id.empty()) throw jubatus_exception("empty id is not allowed");
+    const std::string path = local_path(id);
+    {
+      std::ofstream ofs(path.c_str(), std::ios::binary | std::ios::trunc);
+      if (!ofs) throw jubatus_exception("cannot open output file: " + path);
+      try {
+        model_file::save(ofs, type(), id, config_, user_data_version(), nearest_neighbor_->pack());
+        ofs.close();
+        if (!ofs) throw std::ios_base::failure("close");
+      } catch (const std::ios_base::failure&) {
+        remove(path.c_str());   // no dirty model file is left behind (server_base.cpp:170-182)
+        throw jubatus_exception("cannot write output file: " + path);
+      }
+    }
+    last_saved_path_ = path;
+    std::map<std::string, std::string> ret;
+    std::ostringstream ident; ident << eth_ << '_' << port_;
+    ret[ident.str()] = path;
+    return ret;
+  }
+  // `load` RPC: the file must carry this server's type and (semantically) its config
+  bool load(const std::string& id) {
+    if (id.empty()) throw jubatus_exception("empty id is not allowed");
+    load_file_impl(local_path(id), false);
+    return true;
+  }
+  // --model_file at start-up: the file's config replaces the current one (server_base.cpp:207-209)
+  void load_file(const std::string& path) { load_file_impl(path, true); }
+  const std::string& last_saved_path() const { return last_saved_path_; }
+  const std::string& last_loaded_path() const { return last_loaded_path_; }
  private:
+  void load_file_impl(const std::string& path, bool overwrite_config) {
+    std::ifstream ifs(path.c_str(), std::ios::binary);
+    if (!ifs) throw jubatus_exception("cannot open input file: " + path);
+    model_file::system_data sd;
+    std::string blob;
+    try {
+      if (!overwrite_config) check_set_config();
+      blob = model_file::load(ifs, type(), config_, overwrite_config, user_data_version(), &sd);
+    } catch (const model_file::format_error& e) {
+      throw jubatus_exception(e.what());
+    } catch (const std::ios_base::failure&) {
+      throw jubatus_exception("cannot read input file: " + path);
+    }
+    if (overwrite_config) set_config(sd.config);
+    nearest_neighbor_->unpack(blob);
+    last_loaded_path_ = path;
+  }
   void check_set_config() const { if (!nearest_neighbor_) throw config_exception("config is not set"); }
   std::shared_ptr<jubann_api> api_;
   std::string my_id_;
@@ -853,6 +918,8 @@ class nearest_neighbor_serv {
   uint64_t update_row_cnt_;
   std::shared_ptr<driver::nearest_neighbor> nearest_neighbor_;
   std::shared_ptr<query_batcher> batcher_;
+  std::string datadir_ = "/tmp", eth_ = "127.0.0.1", last_saved_path_, last_loaded_path_;
+  int port_ = 9199;
 };
 
 // ---------------------------------------------------------------------------------------

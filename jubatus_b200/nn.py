@@ -67,12 +67,56 @@ def _load():
     lib.jubahost_calc_score_datum.argtypes = [_vp, _vp, _vp, ctypes.c_uint64, _vp]
     lib.jubahost_calc_score_id.argtypes = [_vp, ctypes.c_char_p, _vp]
     lib.jubahost_lof_params.argtypes = [_vp, ctypes.c_char_p, _vp, _vp]
+    lib.jubahost_crc32.restype = ctypes.c_uint32
+    lib.jubahost_crc32.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_uint32]
+    lib.jubahost_set_storage.argtypes = [_vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int]
+    lib.jubahost_save.argtypes = [_vp, ctypes.c_char_p, _vp, ctypes.c_uint64]
+    lib.jubahost_load.argtypes = [_vp, ctypes.c_char_p]
+    lib.jubahost_load_file.argtypes = [_vp, ctypes.c_char_p]
+    lib.jubahost_get_config.argtypes = [_vp, _vp, ctypes.c_uint64]
+    lib.jubahost_model_write.restype = ctypes.c_int64
+    lib.jubahost_model_write.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_char_p,
+                                         ctypes.c_uint64, ctypes.c_uint64, _vp, ctypes.c_uint64]
+    lib.jubahost_model_read.restype = ctypes.c_int64
+    lib.jubahost_model_read.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int,
+                                        ctypes.c_uint64, _vp, ctypes.c_uint64]
     _lib = lib
     return lib
 
 
 def _raise():
     raise JubatusError(_load().jubahost_last_error().decode("utf-8", "replace"))
+
+
+def crc32(data, crc=0):
+    """common::calc_crc32 (jubatus/server/common/crc32.cpp:25-52), chainable."""
+    return int(_load().jubahost_crc32(data, len(data), crc))
+
+
+def model_write(server_type, model_id, config, user_data_version, payload, timestamp=0):
+    """framework::save_server's container (save_load.cpp:113-166) around `payload`; returns the file bytes."""
+    lib = _load()
+    args = (server_type.encode(), model_id.encode(), config.encode(), user_data_version, payload, len(payload), timestamp)
+    n = lib.jubahost_model_write(*args, None, 0)
+    if n < 0:
+        _raise()
+    buf = ctypes.create_string_buffer(int(n))
+    if lib.jubahost_model_write(*args, buf, n) != n:
+        _raise()
+    return buf.raw
+
+
+def model_read(blob, expected_type, expected_config, overwrite_config=False, user_data_version=1):
+    """framework::load_server's checks (save_load.cpp:168-283); returns the driver payload."""
+    lib = _load()
+    args = (blob, len(blob), expected_type.encode(), expected_config.encode(), 1 if overwrite_config else 0, user_data_version)
+    n = lib.jubahost_model_read(*args, None, 0)
+    if n < 0:
+        _raise()
+    buf = ctypes.create_string_buffer(max(1, int(n)))
+    if lib.jubahost_model_read(*args, buf, n) != n:
+        _raise()
+    return buf.raw[:n]
 
 
 class Datum(object):
@@ -270,6 +314,34 @@ class NearestNeighbor(_HostHandle):
 
     def similar_row_from_datum(self, d, ret_num):
         return self._query_datum(d, ret_num, 1)
+
+    # ---- save / load RPCs (framework/server_base.cpp:135-212) ----
+    def set_storage(self, datadir, eth="127.0.0.1", port=9199):
+        if self._lib.jubahost_set_storage(self._h, datadir.encode(), eth.encode(), port):
+            _raise()
+
+    def save(self, model_id):
+        """-> {"<eth>_<port>": path} like the save RPC."""
+        buf = ctypes.create_string_buffer(4096)
+        if self._lib.jubahost_save(self._h, model_id.encode(), buf, 4096):
+            _raise()
+        ident, path = buf.value.decode().split("\n", 1)
+        return {ident: path}
+
+    def load(self, model_id):
+        if self._lib.jubahost_load(self._h, model_id.encode()):
+            _raise()
+        return True
+
+    def load_file(self, path):
+        if self._lib.jubahost_load_file(self._h, path.encode()):
+            _raise()
+
+    def get_config(self):
+        buf = ctypes.create_string_buffer(1 << 16)
+        if self._lib.jubahost_get_config(self._h, buf, 1 << 16):
+            _raise()
+        return buf.value.decode()
 
     def enable_batching(self, max_batch=64, max_wait_us=200):
         """Coalesce concurrent *_from_datum calls (one per RPC worker thread in the server) into

@@ -282,3 +282,61 @@ def test_baseline_config1_lsh64_10k_rows_k10(oracle, feature_tables):
         want = ora.neighbor_row_from_datum(sfv_of(qids[j], qvals[j]), k)
         assert got == want, j
     assert cli.neighbor_row_from_datum(datum_of(qids[0], qvals[0]), 1)[0][1] == 0.0   # query 0 is a stored row
+
+
+def test_save_load_rpcs_write_the_reference_model_file_container(tmp_path):
+    """save / load / load_file (framework/server_base.cpp:135-212) through the ".jubatus" container of
+    framework/save_load.cpp; the header is re-read here independently of the library."""
+    import struct
+    import zlib
+    hash_num, n, k = 128, 300, 10
+    ids, vals = w.synth_rows(w.MASTER_SEED, 77, n, nnz=12, nfeat_log2=9)
+    cfg = config("lsh", hash_num)
+    a = nn.NearestNeighbor(cfg, my_id="A")
+    a.set_storage(str(tmp_path), "10.0.0.7", 9199)
+    for r in range(n):
+        a.set_row("r%d" % r, datum_of(ids[r], vals[r]))
+    want = {r: a.neighbor_row_from_id(r, k) for r in ("r0", "r17", "r299")}
+    with pytest.raises(nn.JubatusError, match="empty id is not allowed"):
+        a.save("")
+    out = a.save("snap1")
+    path = str(tmp_path / "10.0.0.7_9199_nearest_neighbor_snap1.jubatus")     # build_local_path, server_base.cpp:41-50
+    assert out == {"10.0.0.7_9199": path}
+    f = open(path, "rb").read()
+    fmt, major, minor, maint, crc, sys_n, user_n = struct.unpack(">QIIIIQQ", f[8:48])
+    assert f[:8] == b"jubatus\0" and (fmt, major, minor, maint) == (1, 0, 9, 2) and 48 + sys_n + user_n == len(f)
+    assert crc == zlib.crc32(f[48:], zlib.crc32(f[32:48], zlib.crc32(f[:28])))
+    # load into the same server after clear
+    a.clear()
+    assert a.size() == 0
+    assert a.load("snap1") is True
+    assert a.size() == n
+    for r, res in want.items():
+        assert a.neighbor_row_from_id(r, k) == res
+    # a server with another config refuses the file on `load` ...
+    b = nn.NearestNeighbor(config("lsh", 64), my_id="B")
+    b.set_storage(str(tmp_path), "10.0.0.7", 9199)
+    with pytest.raises(nn.JubatusError, match="server config mismatched"):
+        b.load("snap1")
+    # ... and takes the file's config with load_file (--model_file at start-up)
+    b.load_file(path)
+    assert json.loads(b.get_config()) == json.loads(cfg)
+    assert b.size() == n
+    for r, res in want.items():
+        assert b.neighbor_row_from_id(r, k) == res
+    b.set_row("extra", datum_of(ids[1], vals[1]))
+    assert b.size() == n + 1
+    # same config written differently is the same config
+    c = nn.NearestNeighbor(json.dumps(json.loads(cfg), indent=4, sort_keys=True), my_id="C")
+    c.set_storage(str(tmp_path), "10.0.0.7", 9199)
+    assert c.load("snap1") and c.size() == n
+    # damage is detected before anything is unpacked
+    g = bytearray(f)
+    g[len(g) // 2] ^= 0x10
+    bad = tmp_path / "10.0.0.7_9199_nearest_neighbor_bad.jubatus"
+    bad.write_bytes(bytes(g))
+    with pytest.raises(nn.JubatusError, match="invalid crc32 checksum"):
+        a.load("bad")
+    assert a.size() == n
+    with pytest.raises(nn.JubatusError, match="cannot open input file"):
+        a.load("nope")
