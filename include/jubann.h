@@ -79,7 +79,7 @@ int jubann_destroy(jubann_t* h);
  * feature seeds held by the projection cache, default 2^20), "queries_per_pass" (how many
  * queries share one streaming pass over the table; 0 = automatic), "scan_variant"
  * (0 = automatic, 1 = LDG streaming, 2 = TMA bulk-copy pipeline), "popc_variant" (0 = one
- * POPC per word, 1..4 = carry-save adder trees), "scan_order" (1 = CTAs take turns over
+ * POPC per word, 1..4 = carry-save adder trees of growing depth, default 3), "scan_order" (1 = CTAs take turns over
  * consecutive tile groups so the whole GPU sweeps one front, 0 = one contiguous range per CTA),
  * "reserve_rows" (allocate the slab for this
  * many global rows up front; may be set at any time). */

@@ -68,7 +68,7 @@ struct jubann {
   // options
   uint32_t qp_opt = 0;
   int variant_opt = 0;
-  int popc_variant_opt = 1;   // 5 carry-save adders, 11 POPC per 512-bit pair: best measured on B200
+  int popc_variant_opt = 3;   // 7 carry-save adders, 9 POPC per 512-bit pair: best measured on B200 (1: 5 adders, 11 POPC)
   int interleave_opt = 1;
   // staging (grow-only)
   DevBuf b_indptr, b_seed, b_keyhash, b_vals, b_rowidx, b_sigs, b_norms;

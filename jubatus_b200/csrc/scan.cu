@@ -89,11 +89,15 @@ __device__ __forceinline__ void load_row(const unsigned char* slab, uint64_t til
 // PV 0: one POPC per word.  PV 1/2: carry-save adders (3 words -> sum + carry, two LOP3)
 // so fewer words reach the quarter-rate POPC pipe.
 // ---------------------------------------------------------------------------
-#define CSA(h, l, a, b, c)                         \
-  {                                                \
-    uint32_t a_ = (a), b_ = (b), c_ = (c);         \
-    l = a_ ^ b_ ^ c_;                              \
-    h = (a_ & b_) | (a_ & c_) | (b_ & c_);         \
+// Written as the two LOP3 themselves (sum = 0x96, carry = majority 0xE8).  Left as C expressions,
+// the compiler re-derives sum and carry from the six raw operands (row and query words) when
+// several rows and queries share registers: 8 LOP3 per adder instead of 3 XOR + 2, measured
+// 42 instead of 26 LOP3 per 512-bit pair in the register-resident kernels.
+#define CSA(h, l, a, b, c)                                                                      \
+  {                                                                                             \
+    uint32_t a_ = (a), b_ = (b), c_ = (c);                                                      \
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(l) : "r"(a_), "r"(b_), "r"(c_));                \
+    asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(h) : "r"(a_), "r"(b_), "r"(c_));                \
   }
 
 template <int PV>
