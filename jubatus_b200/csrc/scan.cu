@@ -1243,6 +1243,89 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32
   if (threadIdx.x == 0 && o.out_count) o.out_count[q] = s_count;
 }
 
+// Latency path of the list reduction: when all nlists * k candidates of a query fit in shared
+// memory, find the k-th smallest key by a most-significant-bit-first search over the whole set
+// (one block-wide count per bit), then sort only the k survivors.  The streaming variant above
+// sorts 2 * half keys per 256 candidates read, which is what a single small query spent most of
+// its time in.
+static const int MSEL_THREADS = 1024;
+static const uint32_t MSEL_MAX_KEYS = 24576;   // 192 KB of keys
+__global__ void __launch_bounds__(MSEL_THREADS) merge_select_kernel(const unsigned long long* cand, uint32_t nlists,
+                                                                    uint32_t k, uint32_t kp, MergeOut o) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem);   // [M]
+  unsigned long long* top = keys + (size_t)nlists * k;                       // [kp], kp = pow2 >= k
+  __shared__ uint32_t s_cnt[2];
+  __shared__ uint32_t s_pos;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const uint32_t q = blockIdx.x;
+  const uint32_t M = nlists * k;
+  const unsigned long long* src = cand + (size_t)q * M;
+  unsigned long long mx = 0;
+  uint32_t valid = 0;
+  for (uint32_t i = tid; i < M; i += MSEL_THREADS) {
+    const unsigned long long v = src[i];
+    keys[i] = v;
+    if (v != KEY_SENTINEL) { mx = max(mx, v); ++valid; }
+  }
+  for (uint32_t i = tid; i < kp; i += MSEL_THREADS) top[i] = KEY_SENTINEL;
+  if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_pos = 0; }
+  // block-wide max and number of real keys
+#pragma unroll
+  for (int ofs = 16; ofs > 0; ofs >>= 1) mx = max(mx, __shfl_xor_sync(FULL_MASK, mx, ofs));
+  __shared__ unsigned long long s_mx;
+  __shared__ uint32_t s_valid;
+  if (tid == 0) { s_mx = 0; s_valid = 0; }
+  __syncthreads();
+  if (lane == 0) atomicMax(&s_mx, mx);
+  valid = __reduce_add_sync(FULL_MASK, valid);
+  if (lane == 0 && valid) atomicAdd(&s_valid, valid);
+  __syncthreads();
+  const uint32_t nvalid = s_valid;
+  const uint32_t want = min(k, nvalid);
+  unsigned long long kth = KEY_SENTINEL;   // keys <= kth are the answer
+  if (nvalid > k) {
+    unsigned long long prefix = 0;
+    int round = 0;
+    for (int bit = 63 - __clzll((long long)(s_mx | 1ull)); bit >= 0; --bit, ++round) {
+      const unsigned long long trial = prefix | (1ull << bit);
+      uint32_t c = 0;
+      for (uint32_t i = tid; i < M; i += MSEL_THREADS) c += (keys[i] < trial) ? 1u : 0u;
+      c = __reduce_add_sync(FULL_MASK, c);
+      if (lane == 0 && c) atomicAdd(&s_cnt[round & 1], c);
+      __syncthreads();
+      const uint32_t total = s_cnt[round & 1];
+      if (total < k) prefix = trial;   // fewer than k keys below trial: the k-th smallest is >= trial
+      __syncthreads();                 // everyone has read the counter ...
+      if (tid == 0) s_cnt[round & 1] = 0;   // ... before it is reused two rounds later
+    }
+    kth = prefix;
+  }
+  for (uint32_t i = tid; i < M; i += MSEL_THREADS) {
+    const unsigned long long v = keys[i];
+    if (v != KEY_SENTINEL && v <= kth) top[atomicAdd(&s_pos, 1u)] = v;   // exactly `want` keys (keys are distinct)
+  }
+  __syncthreads();
+  block_bitonic_sort(top, kp, tid, MSEL_THREADS);
+  for (uint32_t j = tid; j < want; j += MSEL_THREADS) {
+    const unsigned long long key = top[j];
+    const uint32_t key_hi = (uint32_t)(key >> 32);
+    const uint64_t gidx = (uint64_t)(uint32_t)key * o.shard_count + o.shard_rank;
+    if (o.cand_key) {  // unused slots were pre-filled with sentinels by the host
+      o.cand_key[(size_t)q * o.kout + o.col0 + j] = key_hi;
+      o.cand_index[(size_t)q * o.kout + o.col0 + j] = gidx;
+    }
+    if (o.out_index) {
+      o.out_index[(size_t)q * o.kout + o.col0 + j] = gidx;
+      o.out_score[(size_t)q * o.kout + o.col0 + j] = final_score(key_hi, o, q);
+    }
+  }
+  if (tid == 0) {
+    if (o.out_count) o.out_count[q] = (o.count_accumulate ? o.out_count[q] : 0u) + want;
+    if (o.last_key) o.last_key[q] = want ? top[want - 1] : KEY_SENTINEL;
+  }
+}
+
 // ---------------------------------------------------------------------------
 // sample pre-pass: an admissible-key bound per query before the scan starts.
 // One CTA per query ranks the first S rows and takes the k-th smallest ordering key t;
@@ -1413,6 +1496,53 @@ static cudaError_t launch_scan_pv(const ScanArgs& a, const ScanConfig& cfg, dim3
   }
 }
 
+// Hamming engines: the k-th smallest distance of the sample needs no sort, distances are small
+// integers -- count them in shared memory and walk the counts.  The same CTA also resets its
+// query's part of the shared histogram (saves two memset nodes per launch on the latency path).
+static const int TAUH_THREADS = 512;
+__global__ void __launch_bounds__(TAUH_THREADS) tau_init_hamming_kernel(ScanArgs a, uint32_t S, unsigned long long* tau_out) {
+  __shared__ uint32_t hist[1025 + 31];
+  __shared__ uint32_t s_found;
+  const uint32_t q = blockIdx.x;
+  const uint32_t bins = a.hash_num + 1;
+  for (uint32_t i = threadIdx.x; i < bins + 31; i += TAUH_THREADS) hist[i] = 0;
+  if (threadIdx.x == 0) s_found = 0xFFFFFFFFu;
+  if (a.ghist) {
+    if (threadIdx.x == 0) a.ghist[q] = 0xFFFFFFFFu;
+    uint32_t* g = a.ghist + a.nq + (size_t)q * a.hist_stride;
+    for (uint32_t i = threadIdx.x; i < a.hist_stride; i += TAUH_THREADS) g[i] = 0;
+  }
+  __syncthreads();
+  const uint32_t* qw = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)q * a.w64);
+  for (uint32_t i = threadIdx.x; i < S; i += TAUH_THREADS) {
+    uint32_t d = 0;
+    for (uint32_t w = 0; w < 2 * a.w64; ++w)
+      d += __popc(*reinterpret_cast<const uint32_t*>(a.slab + word_offset(a.w32, i, w)) ^ qw[w]);
+    atomicAdd(&hist[d], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    uint32_t run = 0;
+    for (uint32_t base = 0; base < bins; base += 32) {
+      uint32_t v = hist[base + lane];   // bins beyond hash_num are zero
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(FULL_MASK, v, o);
+        if (lane >= o) v += n;
+      }
+      const unsigned hit = __ballot_sync(FULL_MASK, run + v >= a.k);
+      if (hit) { if (lane == 0) s_found = base + (__ffs(hit) - 1); break; }
+      run += __shfl_sync(FULL_MASK, v, 31);
+    }
+    __syncwarp();
+    if (lane == 0) {
+      const uint32_t t = (a.k <= S) ? s_found : 0xFFFFFFFFu;
+      tau_out[q] = (t == 0xFFFFFFFFu) ? KEY_SENTINEL : (((unsigned long long)t + 1ull) << 32);
+    }
+  }
+}
+
 template <bool EUCLID>
 static cudaError_t launch_scan_w(uint32_t w32, const ScanArgs& a, const ScanConfig& cfg, dim3 grid,
                                  cudaStream_t s) {
@@ -1443,26 +1573,34 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   a.tiles_per_chunk = cfg.tiles_per_chunk; a.nchunks = cfg.nchunks;
   a.w32 = t.w32;
   a.interleave = cfg.interleave;
+  const bool use_hist = d_hist_scratch && t.local_rows >= (1u << 16);
+  if (use_hist) a.ghist = d_hist_scratch;
+  bool hist_cleared = false;
   // sample pre-pass (not with a pagination floor: the bound would not hold for keys above it),
   // worthwhile only when the table is much larger than the sample
   if (d_tau_scratch && !d_floor_keys) {
     uint64_t S = std::max<uint64_t>(2048, 4ull * k);
     if (S > 8192) S = 8192;
     if (t.local_rows >= 16 * S && k <= S) {
-      uint32_t SP = 1;
-      while (SP < S) SP <<= 1;
-      if (euclid) tau_init_kernel<true><<<nq, TAU_THREADS, SP * 4, s>>>(a, (uint32_t)S, SP, reinterpret_cast<unsigned long long*>(d_tau_scratch));
-      else tau_init_kernel<false><<<nq, TAU_THREADS, SP * 4, s>>>(a, (uint32_t)S, SP, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+      if (euclid) {
+        uint32_t SP = 1;
+        while (SP < S) SP <<= 1;
+        ScanArgs b = a;
+        b.ghist = nullptr;
+        tau_init_kernel<true><<<nq, TAU_THREADS, SP * 4, s>>>(b, (uint32_t)S, SP, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+      } else {
+        tau_init_hamming_kernel<<<nq, TAUH_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+        hist_cleared = use_hist;
+      }
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
       a.tau_init = d_tau_scratch;
     }
   }
-  if (d_hist_scratch && t.local_rows >= (1u << 16)) {
+  if (use_hist && !hist_cleared) {
     cudaError_t e = cudaMemsetAsync(d_hist_scratch, 0xFF, (size_t)nq * 4, s);   // published bounds: none yet
     if (e == cudaSuccess) e = cudaMemsetAsync(d_hist_scratch + nq, 0, (size_t)nq * a.hist_stride * 4, s);
     if (e != cudaSuccess) return e;
-    a.ghist = d_hist_scratch;
   }
   dim3 grid(cfg.nchunks, (nq + cfg.qp - 1) / cfg.qp, 1);
   return euclid ? launch_scan_w<true>(t.w32, a, cfg, grid, s) : launch_scan_w<false>(t.w32, a, cfg, grid, s);
@@ -1470,6 +1608,17 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
 
 cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nlists, uint32_t k,
                                const MergeOut& out, cudaStream_t s) {
+  if ((uint64_t)nlists * k <= MSEL_MAX_KEYS) {
+    uint32_t kp = 32;
+    while (kp < k) kp <<= 1;
+    const size_t smem_sel = ((size_t)nlists * k + kp) * 8;
+    if (smem_sel <= 220 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(merge_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sel);
+      if (e != cudaSuccess) return e;
+      merge_select_kernel<<<nq, MSEL_THREADS, smem_sel, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
+      return cudaGetLastError();
+    }
+  }
   uint32_t half = 2 * MERGE_THREADS;
   while (half < k) half <<= 1;
   const size_t smem = (size_t)2 * half * 8;

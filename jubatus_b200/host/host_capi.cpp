@@ -153,12 +153,18 @@ int jubahost_set_rows(void* h, uint64_t n, const char* const* ids, const uint64_
                       const double* nvals) {
   host_box* b = static_cast<host_box*>(h);
   return guarded([&]() {
-    if (!b->serv) throw jubatus_exception("set_rows: nearest_neighbor server only");
+    if (!b->serv && !b->lof) throw jubatus_exception("set_rows: nearest_neighbor and anomaly servers only");
     std::vector<std::string> vid(n);
     std::vector<datum> ds(n);
     for (uint64_t i = 0; i < n; ++i) {
       vid[i] = ids[i];
       for (uint64_t j = offs[i]; j < offs[i + 1]; ++j) ds[i].add_number(nkeys[j], nvals[j]);
+    }
+    if (b->lof) {   // anomaly: bulk load (light_lof::set_rows_bulk)
+      std::vector<sfv_t> v(n);
+      for (uint64_t i = 0; i < n; ++i) b->conv().convert(ds[i], v[i]);
+      b->lof->set_rows_bulk(vid, v);
+      return 0;
     }
     b->serv->get_driver()->set_rows(vid, ds);
     return 0;

@@ -1021,6 +1021,31 @@ class light_lof {
       lrd_[ids[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
     }
   }
+  // Bulk load for a table that is built in one go (benchmarks, restoring from raw data): rows go
+  // in through the batched set_rows, then kdist for every row, then lrd for every row, each in
+  // batched device calls.  Unlike a sequence of set_row calls no row keeps a stale parameter.
+  void set_rows_bulk(const std::vector<std::string>& ids, const std::vector<sfv_t>& sfvs, size_t batch = 4096) {
+    nn_->set_rows(ids, sfvs);
+    for (size_t i = 0; i < ids.size(); ++i) { kdist_[ids[i]] = -1.0f; lrd_[ids[i]] = -1.0f; }
+    std::vector<std::string> all;
+    nn_->get_all_row_ids(all);
+    std::vector<neighbor_result> nn;
+    for (size_t b = 0; b < all.size(); b += batch) {
+      std::vector<std::string> part(all.begin() + b, all.begin() + std::min(all.size(), b + batch));
+      nn_->neighbor_rows_from_ids(part, nn, nn_num_, false);
+      for (size_t i = 0; i < part.size(); ++i) kdist_[part[i]] = nn[i].empty() ? 0.0f : nn[i].back().second;
+    }
+    for (size_t b = 0; b < all.size(); b += batch) {
+      std::vector<std::string> part(all.begin() + b, all.begin() + std::min(all.size(), b + batch));
+      nn_->neighbor_rows_from_ids(part, nn, nn_num_, false);
+      for (size_t i = 0; i < part.size(); ++i) {
+        const size_t length = std::min<size_t>(nn[i].size(), nn_num_);
+        float sum_reach = 0.0f;
+        for (size_t j = 0; j < length; ++j) sum_reach += std::max(nn[i][j].second, kdist_[nn[i][j].first]);
+        lrd_[part[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
+      }
+    }
+  }
   bool get_row_parameter(const std::string& id, float* kdist, float* lrd) const {
     std::unordered_map<std::string, float>::const_iterator a = kdist_.find(id), b = lrd_.find(id);
     if (a == kdist_.end() || b == lrd_.end()) return false;

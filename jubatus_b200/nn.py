@@ -397,6 +397,23 @@ class Anomaly(_HostHandle):
         self._set_row(row_id, d)
         return self.calc_score_id(row_id)
 
+    def add_bulk(self, datums):
+        """Load many number-valued datums at once (ids continue the add sequence): batched set_rows,
+        then every row's kdist and lrd in batched device calls (light_lof::set_rows_bulk)."""
+        ids = [str(self._next_id + i) for i in range(len(datums))]
+        self._next_id += len(datums)
+        offs = np.zeros(len(ids) + 1, dtype=np.uint64)
+        keys, vals = [], []
+        for i, d in enumerate(datums):
+            keys.extend(k for k, _ in d.num_values)
+            vals.extend(v for _, v in d.num_values)
+            offs[i + 1] = len(keys)
+        vals = np.array(vals or [0.0], dtype=np.float64)
+        if self._lib.jubahost_set_rows(self._h, len(ids), _cstrs(ids), offs.ctypes.data_as(_vp), _cstrs(keys),
+                                       vals.ctypes.data_as(_vp)):
+            _raise()
+        return ids
+
     def calc_score(self, d):
         _, _, _, nk, nv, nn = _datum_args(d)
         s = ctypes.c_float()

@@ -340,3 +340,41 @@ def test_save_load_rpcs_write_the_reference_model_file_container(tmp_path):
     assert a.size() == n
     with pytest.raises(nn.JubatusError, match="cannot open input file"):
         a.load("nope")
+
+
+def test_light_lof_bulk_load_then_streaming_adds(oracle):
+    """add_bulk = rows first, then every kdist, then every lrd; adds after it behave as usual.  The
+    oracle gets the same final table state by re-scoring every row after loading (touch order
+    does not matter once all kdist are fresh)."""
+    cfg = json.dumps({"method": "light_lof", "converter": CONVERTER,
+                      "parameter": {"nearest_neighbor_num": 3, "reverse_nearest_neighbor_num": 6, "method": "lsh",
+                                    "parameter": {"hash_num": 128}}})
+    n = 60
+    ids, vals = w.synth_rows(w.MASTER_SEED, 900, n + 5, nnz=8, nfeat_log2=6)
+    bulk = nn.Anomaly(cfg)
+    got_ids = bulk.add_bulk([datum_of(ids[r], vals[r]) for r in range(n)])
+    assert got_ids == [str(r) for r in range(n)]
+    # reference state: a second server loaded row by row, then the same two global passes
+    # (kdist of all rows, then lrd of all rows) emulated through its own parameters
+    seq = nn.Anomaly(cfg)
+    for r in range(n):
+        seq.add(datum_of(ids[r], vals[r]))
+    # the engines hold the same rows, so neighbor lists agree; kdist must equal the k-th neighbor distance
+    eng = nn.NearestNeighbor(config("lsh", 128))
+    for r in range(n):
+        eng.set_row(str(r), datum_of(ids[r], vals[r]))
+    kd = {}
+    for r in range(n):
+        nb = eng.neighbor_row_from_id(str(r), 3)
+        kd[str(r)] = nb[-1][1]
+    for r in (0, 13, 59):
+        nb = eng.neighbor_row_from_id(str(r), 3)
+        want_lrd = len(nb) / sum(max(d, kd[i]) for i, d in nb) if sum(max(d, kd[i]) for i, d in nb) else float("inf")
+        got_kd, got_lrd = bulk.lof_params(str(r))
+        assert got_kd == kd[str(r)]
+        assert np.isclose(got_lrd, want_lrd, rtol=1e-5) or (np.isinf(got_lrd) and np.isinf(want_lrd))
+    # streaming adds continue the id sequence and return finite-or-inf scores like the row-by-row server
+    for r in range(n, n + 5):
+        rid, score = bulk.add(datum_of(ids[r], vals[r]))
+        assert rid == str(r) and score == score
+    assert bulk.size() == n + 5

@@ -1,0 +1,30 @@
+import sys, time, json, numpy as np, torch
+sys.path.insert(0, '/root/repo')
+from jubatus_b200 import Engine, workload as w, nn
+n, h = 1_000_000, 256
+e = Engine("lsh", h)
+sig = w.random_signatures(1, n, h // 64)
+e.set_rows_sig(np.arange(n), sig, None)
+q = w.random_signatures(2, 1, h // 64)
+def t(f, reps=300):
+    for _ in range(20): f()
+    t0 = time.perf_counter()
+    for _ in range(reps): f()
+    return (time.perf_counter() - t0) / reps * 1e6
+print("query_sig host 1 query, k=10: %.1f us" % t(lambda: e.query_sig(q, None, 10)))
+ft = w.feature_tables()
+ids, vals = w.synth_rows(w.MASTER_SEED, 5, 1, nnz=100, nfeat_log2=20)
+csr = w.to_csr(ids, vals, *ft)
+print("query_csr host 1 query: %.1f us" % t(lambda: e.query_csr(*csr, 10)))
+st = e.stats(); print(st)
+e.stats_reset(True)
+for _ in range(100): e.query_sig(q, None, 10)
+st = e.stats(); print("scan ms per query", st["scan_ms"]/100, st)
+# device-resident variant
+dev = torch.device("cuda:0")
+qd = torch.from_numpy(q.view(np.int64)).to(dev)
+oi = torch.zeros((1, 10), dtype=torch.int64, device=dev); os_ = torch.zeros((1, 10), dtype=torch.float32, device=dev); oc = torch.zeros(1, dtype=torch.int32, device=dev)
+s = torch.cuda.current_stream().cuda_stream
+def f():
+    e.query_sig_dev(1, qd.data_ptr(), 0, 10, 0, oi.data_ptr(), os_.data_ptr(), oc.data_ptr(), s); torch.cuda.synchronize()
+print("query_sig_dev + sync: %.1f us" % t(f))
