@@ -1248,8 +1248,9 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32
 // (one block-wide count per bit), then sort only the k survivors.  The streaming variant above
 // sorts 2 * half keys per 256 candidates read, which is what a single small query spent most of
 // its time in.
-static const int MSEL_THREADS = 1024;
 static const uint32_t MSEL_MAX_KEYS = 24576;   // 192 KB of keys
+// THREADS: 128 for small candidate sets (block barriers are what a round costs), 1024 otherwise
+template <int MSEL_THREADS>
 __global__ void __launch_bounds__(MSEL_THREADS) merge_select_kernel(const unsigned long long* cand, uint32_t nlists,
                                                                     uint32_t k, uint32_t kp, MergeOut o) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -1257,37 +1258,50 @@ __global__ void __launch_bounds__(MSEL_THREADS) merge_select_kernel(const unsign
   unsigned long long* top = keys + (size_t)nlists * k;                       // [kp], kp = pow2 >= k
   __shared__ uint32_t s_cnt[2];
   __shared__ uint32_t s_pos;
+  __shared__ unsigned long long s_or, s_and;
+  __shared__ uint32_t s_valid;
   const int tid = threadIdx.x, lane = tid & 31;
   const uint32_t q = blockIdx.x;
   const uint32_t M = nlists * k;
   const unsigned long long* src = cand + (size_t)q * M;
-  unsigned long long mx = 0;
+  unsigned long long vor = 0, vand = ~0ull;
   uint32_t valid = 0;
-  for (uint32_t i = tid; i < M; i += MSEL_THREADS) {
-    const unsigned long long v = src[i];
-    keys[i] = v;
-    if (v != KEY_SENTINEL) { mx = max(mx, v); ++valid; }
+  for (uint32_t base = 0; base < M; base += 4 * MSEL_THREADS) {   // four loads in flight per thread
+    unsigned long long v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t i = base + j * MSEL_THREADS + tid;
+      v[j] = i < M ? src[i] : KEY_SENTINEL;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t i = base + j * MSEL_THREADS + tid;
+      if (i < M) keys[i] = v[j];
+      if (v[j] != KEY_SENTINEL) { vor |= v[j]; vand &= v[j]; ++valid; }
+    }
   }
   for (uint32_t i = tid; i < kp; i += MSEL_THREADS) top[i] = KEY_SENTINEL;
-  if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_pos = 0; }
-  // block-wide max and number of real keys
+  if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_pos = 0; s_or = 0; s_and = ~0ull; s_valid = 0; }
 #pragma unroll
-  for (int ofs = 16; ofs > 0; ofs >>= 1) mx = max(mx, __shfl_xor_sync(FULL_MASK, mx, ofs));
-  __shared__ unsigned long long s_mx;
-  __shared__ uint32_t s_valid;
-  if (tid == 0) { s_mx = 0; s_valid = 0; }
-  __syncthreads();
-  if (lane == 0) atomicMax(&s_mx, mx);
+  for (int ofs = 16; ofs > 0; ofs >>= 1) {
+    vor |= __shfl_xor_sync(FULL_MASK, vor, ofs);
+    vand &= __shfl_xor_sync(FULL_MASK, vand, ofs);
+  }
   valid = __reduce_add_sync(FULL_MASK, valid);
-  if (lane == 0 && valid) atomicAdd(&s_valid, valid);
+  __syncthreads();
+  if (lane == 0 && valid) { atomicOr(&s_or, vor); atomicAnd(&s_and, vand); atomicAdd(&s_valid, valid); }
   __syncthreads();
   const uint32_t nvalid = s_valid;
   const uint32_t want = min(k, nvalid);
   unsigned long long kth = KEY_SENTINEL;   // keys <= kth are the answer
   if (nvalid > k) {
+    // bits on which all keys agree (the unused high bits of the row index, most of the distance)
+    // are the k-th key's too and cost no round
+    const unsigned long long all_or = s_or, all_and = s_and, varying = all_or ^ all_and;
     unsigned long long prefix = 0;
     int round = 0;
-    for (int bit = 63 - __clzll((long long)(s_mx | 1ull)); bit >= 0; --bit, ++round) {
+    for (int bit = 63 - __clzll((long long)(all_or | 1ull)); bit >= 0; --bit) {
+      if (!((varying >> bit) & 1ull)) { prefix |= all_and & (1ull << bit); continue; }
       const unsigned long long trial = prefix | (1ull << bit);
       uint32_t c = 0;
       for (uint32_t i = tid; i < M; i += MSEL_THREADS) c += (keys[i] < trial) ? 1u : 0u;
@@ -1298,6 +1312,7 @@ __global__ void __launch_bounds__(MSEL_THREADS) merge_select_kernel(const unsign
       if (total < k) prefix = trial;   // fewer than k keys below trial: the k-th smallest is >= trial
       __syncthreads();                 // everyone has read the counter ...
       if (tid == 0) s_cnt[round & 1] = 0;   // ... before it is reused two rounds later
+      ++round;
     }
     kth = prefix;
   }
@@ -1312,6 +1327,92 @@ __global__ void __launch_bounds__(MSEL_THREADS) merge_select_kernel(const unsign
     const uint32_t key_hi = (uint32_t)(key >> 32);
     const uint64_t gidx = (uint64_t)(uint32_t)key * o.shard_count + o.shard_rank;
     if (o.cand_key) {  // unused slots were pre-filled with sentinels by the host
+      o.cand_key[(size_t)q * o.kout + o.col0 + j] = key_hi;
+      o.cand_index[(size_t)q * o.kout + o.col0 + j] = gidx;
+    }
+    if (o.out_index) {
+      o.out_index[(size_t)q * o.kout + o.col0 + j] = gidx;
+      o.out_score[(size_t)q * o.kout + o.col0 + j] = final_score(key_hi, o, q);
+    }
+  }
+  if (tid == 0) {
+    if (o.out_count) o.out_count[q] = (o.count_accumulate ? o.out_count[q] : 0u) + want;
+    if (o.last_key) o.last_key[q] = want ? top[want - 1] : KEY_SENTINEL;
+  }
+}
+
+// Smallest candidate sets (a single query with a small k: nlists * k <= 128 * KPT): the keys live in
+// registers, a round of the bit search is KPT compares, one warp reduction, one shared atomic
+// and one barrier (three counters in rotation), so the kernel is no longer a chain of
+// shared-memory latencies.
+static const int MSMALL_THREADS = 128;
+template <int KPT>
+__global__ void __launch_bounds__(MSMALL_THREADS) merge_small_kernel(const unsigned long long* cand, uint32_t nlists,
+                                                                     uint32_t k, uint32_t kp, MergeOut o) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  unsigned long long* top = reinterpret_cast<unsigned long long*>(smem);   // [kp], kp = pow2 >= k
+  __shared__ uint32_t s_cnt[3];
+  __shared__ uint32_t s_pos, s_valid;
+  __shared__ unsigned long long s_or, s_and;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const uint32_t q = blockIdx.x;
+  const uint32_t M = nlists * k;
+  const unsigned long long* src = cand + (size_t)q * M;
+  unsigned long long r[KPT];
+#pragma unroll
+  for (int j = 0; j < KPT; ++j) {
+    const uint32_t i = j * MSMALL_THREADS + tid;
+    r[j] = i < M ? src[i] : KEY_SENTINEL;
+  }
+  unsigned long long vor = 0, vand = ~0ull;
+  uint32_t valid = 0;
+#pragma unroll
+  for (int j = 0; j < KPT; ++j)
+    if (r[j] != KEY_SENTINEL) { vor |= r[j]; vand &= r[j]; ++valid; }
+  for (uint32_t i = tid; i < kp; i += MSMALL_THREADS) top[i] = KEY_SENTINEL;
+  if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_cnt[2] = 0; s_pos = 0; s_or = 0; s_and = ~0ull; s_valid = 0; }
+#pragma unroll
+  for (int ofs = 16; ofs > 0; ofs >>= 1) {
+    vor |= __shfl_xor_sync(FULL_MASK, vor, ofs);
+    vand &= __shfl_xor_sync(FULL_MASK, vand, ofs);
+  }
+  valid = __reduce_add_sync(FULL_MASK, valid);
+  __syncthreads();
+  if (lane == 0 && valid) { atomicOr(&s_or, vor); atomicAnd(&s_and, vand); atomicAdd(&s_valid, valid); }
+  __syncthreads();
+  const uint32_t nvalid = s_valid;
+  const uint32_t want = min(k, nvalid);
+  unsigned long long kth = KEY_SENTINEL;
+  if (nvalid > k) {
+    const unsigned long long all_or = s_or, all_and = s_and, varying = all_or ^ all_and;
+    unsigned long long prefix = 0;
+    uint32_t round = 0;
+    for (int bit = 63 - __clzll((long long)(all_or | 1ull)); bit >= 0; --bit) {
+      if (!((varying >> bit) & 1ull)) { prefix |= all_and & (1ull << bit); continue; }
+      const unsigned long long trial = prefix | (1ull << bit);
+      uint32_t c = 0;
+#pragma unroll
+      for (int j = 0; j < KPT; ++j) c += (r[j] < trial) ? 1u : 0u;
+      c = __reduce_add_sync(FULL_MASK, c);
+      const uint32_t slot = round % 3u;
+      if (lane == 0 && c) atomicAdd(&s_cnt[slot], c);
+      if (tid == 0) s_cnt[(round + 1u) % 3u] = 0;   // last read two rounds ago, behind a barrier
+      __syncthreads();
+      if (s_cnt[slot] < k) prefix = trial;
+      ++round;
+    }
+    kth = prefix;
+  }
+#pragma unroll
+  for (int j = 0; j < KPT; ++j)
+    if (r[j] != KEY_SENTINEL && r[j] <= kth) top[atomicAdd(&s_pos, 1u)] = r[j];   // exactly `want` keys
+  __syncthreads();
+  block_bitonic_sort(top, kp, tid, MSMALL_THREADS);
+  for (uint32_t j = tid; j < want; j += MSMALL_THREADS) {
+    const unsigned long long key = top[j];
+    const uint32_t key_hi = (uint32_t)(key >> 32);
+    const uint64_t gidx = (uint64_t)(uint32_t)key * o.shard_count + o.shard_rank;
+    if (o.cand_key) {
       o.cand_key[(size_t)q * o.kout + o.col0 + j] = key_hi;
       o.cand_index[(size_t)q * o.kout + o.col0 + j] = gidx;
     }
@@ -1499,7 +1600,7 @@ static cudaError_t launch_scan_pv(const ScanArgs& a, const ScanConfig& cfg, dim3
 // Hamming engines: the k-th smallest distance of the sample needs no sort, distances are small
 // integers -- count them in shared memory and walk the counts.  The same CTA also resets its
 // query's part of the shared histogram (saves two memset nodes per launch on the latency path).
-static const int TAUH_THREADS = 512;
+static const int TAUH_THREADS = 1024;
 __global__ void __launch_bounds__(TAUH_THREADS) tau_init_hamming_kernel(ScanArgs a, uint32_t S, unsigned long long* tau_out) {
   __shared__ uint32_t hist[1025 + 31];
   __shared__ uint32_t s_found;
@@ -1512,12 +1613,31 @@ __global__ void __launch_bounds__(TAUH_THREADS) tau_init_hamming_kernel(ScanArgs
     uint32_t* g = a.ghist + a.nq + (size_t)q * a.hist_stride;
     for (uint32_t i = threadIdx.x; i < a.hist_stride; i += TAUH_THREADS) g[i] = 0;
   }
+  __shared__ uint32_t sq[32];
+  if (threadIdx.x < 32) {
+    const uint32_t* qw = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)q * a.w64);
+    sq[threadIdx.x] = threadIdx.x < 2 * a.w64 ? qw[threadIdx.x] : 0u;   // padding words of a row are zero
+  }
   __syncthreads();
-  const uint32_t* qw = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)q * a.w64);
   for (uint32_t i = threadIdx.x; i < S; i += TAUH_THREADS) {
     uint32_t d = 0;
-    for (uint32_t w = 0; w < 2 * a.w64; ++w)
-      d += __popc(*reinterpret_cast<const uint32_t*>(a.slab + word_offset(a.w32, i, w)) ^ qw[w]);
+    if (a.w32 == 2) {
+      const uint2 v = *reinterpret_cast<const uint2*>(a.slab + (size_t)i * 8);
+      d = __popc(v.x ^ sq[0]) + __popc(v.y ^ sq[1]);
+    } else {
+      // the row's 16-byte chunks are 512 bytes apart: issue all loads, then count
+      const uint32_t C = a.w32 >> 2;
+      const unsigned char* base = a.slab + ((size_t)(i >> 5) * C * 32 + (i & 31)) * 16;
+      uint4 v[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        if ((uint32_t)c < C) v[c] = *reinterpret_cast<const uint4*>(base + (size_t)c * 512);
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        if ((uint32_t)c < C)
+          d += __popc(v[c].x ^ sq[4 * c]) + __popc(v[c].y ^ sq[4 * c + 1]) + __popc(v[c].z ^ sq[4 * c + 2]) +
+               __popc(v[c].w ^ sq[4 * c + 3]);
+    }
     atomicAdd(&hist[d], 1u);
   }
   __syncthreads();
@@ -1581,6 +1701,8 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   if (d_tau_scratch && !d_floor_keys) {
     uint64_t S = std::max<uint64_t>(2048, 4ull * k);
     if (S > 8192) S = 8192;
+    // counting a sample is cheap for the hamming engines: take the largest one the table allows
+    if (!euclid && t.local_rows >= 16 * 8192) S = 8192;
     if (t.local_rows >= 16 * S && k <= S) {
       if (euclid) {
         uint32_t SP = 1;
@@ -1613,9 +1735,17 @@ cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nli
     while (kp < k) kp <<= 1;
     const size_t smem_sel = ((size_t)nlists * k + kp) * 8;
     if (smem_sel <= 220 * 1024) {
-      cudaError_t e = cudaFuncSetAttribute(merge_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sel);
+      const uint64_t M = (uint64_t)nlists * k;
+      if (M <= 128u * 32u && kp <= 1024) {
+        const size_t sm = (size_t)kp * 8;
+        if (M <= 128u * 4u) merge_small_kernel<4><<<nq, MSMALL_THREADS, sm, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
+        else if (M <= 128u * 16u) merge_small_kernel<16><<<nq, MSMALL_THREADS, sm, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
+        else merge_small_kernel<32><<<nq, MSMALL_THREADS, sm, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
+        return cudaGetLastError();
+      }
+      cudaError_t e = cudaFuncSetAttribute(merge_select_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sel);
       if (e != cudaSuccess) return e;
-      merge_select_kernel<<<nq, MSEL_THREADS, smem_sel, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
+      merge_select_kernel<1024><<<nq, 1024, smem_sel, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
       return cudaGetLastError();
     }
   }

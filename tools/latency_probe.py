@@ -28,3 +28,19 @@ s = torch.cuda.current_stream().cuda_stream
 def f():
     e.query_sig_dev(1, qd.data_ptr(), 0, 10, 0, oi.data_ptr(), os_.data_ptr(), oc.data_ptr(), s); torch.cuda.synchronize()
 print("query_sig_dev + sync: %.1f us" % t(f))
+# GPU-side span of one call (events on the launching stream)
+def span(k):
+    oi = torch.zeros((1, k), dtype=torch.int64, device=dev); os2 = torch.zeros((1, k), dtype=torch.float32, device=dev)
+    ts = []
+    for _ in range(200):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        e.query_sig_dev(1, qd.data_ptr(), 0, k, 0, oi.data_ptr(), os2.data_ptr(), oc.data_ptr(), s)
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1) * 1e3)
+    ts.sort()
+    return ts[len(ts) // 2]
+for k in (1, 10, 100):
+    print("k=%d GPU span of one query_sig_dev: %.1f us" % (k, span(k)))
