@@ -27,6 +27,10 @@ int fail(int code, const char* fmt, ...) {
   return code;
 }
 
+// Requests whose inputs and results fit this many bytes take the latency path: one pinned
+// staging buffer, one host->device copy, one device->host copy, one synchronisation.
+static const size_t SMALL_STAGE_BYTES = 1u << 20;
+
 struct DevBuf {
   void* p = nullptr;
   size_t cap = 0;
@@ -65,6 +69,7 @@ struct jubann {
   uint32_t cache_slots_opt = 1u << 20;
   double* d_coslut = nullptr;
   uint32_t* h_counters = nullptr;  // pinned
+  unsigned char* h_stage = nullptr;  // pinned, SMALL_STAGE_BYTES: small requests go through one copy each way
   // options
   uint32_t qp_opt = 0;
   int variant_opt = 0;
@@ -72,7 +77,7 @@ struct jubann {
   int interleave_opt = 1;
   // staging (grow-only)
   DevBuf b_indptr, b_seed, b_keyhash, b_vals, b_rowidx, b_sigs, b_norms;
-  DevBuf b_qsigs, b_qnorms, b_out_idx, b_out_score, b_out_count, b_cand, b_floor, b_tau, b_hist;
+  DevBuf b_qsigs, b_qnorms, b_out_idx, b_out_score, b_out_count, b_cand, b_floor, b_tau, b_hist, b_stage;
   // stats
   uint64_t kernel_launches = 0, scan_launches = 0, scan_passes = 0;
   bool time_scan = false;
@@ -429,6 +434,8 @@ int jubann_create(const char* method, uint32_t hash_num, int device, uint32_t sh
   if (ok) h->num_sms = prop.multiProcessorCount;
   ok = ok && cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess;
   ok = ok && cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 16) == cudaSuccess;
+  ok = ok && cudaMallocHost(reinterpret_cast<void**>(&h->h_stage), SMALL_STAGE_BYTES) == cudaSuccess;
+  ok = ok && h->b_stage.ensure(SMALL_STAGE_BYTES) == cudaSuccess;
   if (ok && m == EUCLID_LSH) {
     // cos(theta_h), theta_h = (float)(h * M_PI / (float)hash_num), evaluated in double by the host
     // libm so that the table holds the very values the CPU engine computes per row
@@ -463,8 +470,9 @@ int jubann_destroy(jubann_t* h) {
     free_cache(h);
     if (h->d_coslut) cudaFree(h->d_coslut);
     if (h->h_counters) cudaFreeHost(h->h_counters);
+    if (h->h_stage) cudaFreeHost(h->h_stage);
     DevBuf* bufs[] = {&h->b_indptr, &h->b_seed, &h->b_keyhash, &h->b_vals, &h->b_rowidx, &h->b_sigs, &h->b_norms,
-                      &h->b_qsigs, &h->b_qnorms, &h->b_out_idx, &h->b_out_score, &h->b_out_count, &h->b_cand, &h->b_floor, &h->b_tau, &h->b_hist};
+                      &h->b_qsigs, &h->b_qnorms, &h->b_out_idx, &h->b_out_score, &h->b_out_count, &h->b_cand, &h->b_floor, &h->b_tau, &h->b_hist, &h->b_stage};
     for (DevBuf* b : bufs) b->release();
     for (auto& ev : h->scan_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -717,6 +725,126 @@ static int ensure_query_outputs(jubann_t* h, uint64_t nq, uint32_t k) {
   return 0;
 }
 
+// ---- latency path ------------------------------------------------------------------------------
+// One RPC = one query is how the server calls this library (nearest_neighbor_impl.cpp:75-102), so
+// the fixed cost of a call matters as much as the scan.  A request that fits SMALL_STAGE_BYTES is
+// packed into the pinned staging buffer, copied in one piece, answered into the device staging
+// buffer and copied back in one piece: two copies and one synchronisation per call instead of
+// seven copies and three synchronisations.  Layout (256-byte aligned parts):
+//   in : CSR [indptr | vals | seed32 or keyhash64]   or   [qsigs | qnorms]
+//   dev: qsigs, qnorms (when hashed on the device)
+//   out: [out_index | out_score | out_count]
+static size_t up256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct SmallPlan {
+  size_t in_bytes, sig_off, norm_off, out_off, idx_off, score_off, count_off, out_bytes, total;
+};
+static SmallPlan small_plan(const jubann_t* h, uint64_t nq, uint32_t k, size_t in_bytes, bool dev_sigs) {
+  SmallPlan p;
+  p.in_bytes = up256(in_bytes);
+  size_t o = p.in_bytes;
+  p.sig_off = o; if (dev_sigs) o += up256(nq * h->w64 * 8);
+  p.norm_off = o; if (dev_sigs) o += up256(nq * 4);
+  p.out_off = o;
+  p.idx_off = o; o += up256(nq * (size_t)k * 8);
+  p.score_off = o; o += up256(nq * (size_t)k * 4);
+  p.count_off = o; o += up256(nq * 4);
+  p.out_bytes = o - p.out_off;
+  p.total = o;
+  return p;
+}
+
+// run the query and bring the results back; `also_counters`: read the projection-cache counters
+// in the same go (the resolve before it may have overflowed the cache)
+static int small_finish(jubann_t* h, const SmallPlan& p, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms,
+                        uint32_t k, uint32_t flags, bool also_counters, uint64_t* out_index, float* out_score,
+                        uint32_t* out_count) {
+  unsigned char* d = h->b_stage.as<unsigned char>();
+  int rc = query_device(h, nq, d_qsigs, d_qnorms, k, flags, reinterpret_cast<uint64_t*>(d + p.idx_off),
+                        reinterpret_cast<float*>(d + p.score_off), reinterpret_cast<uint32_t*>(d + p.count_off), nullptr,
+                        nullptr, h->stream);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(h->h_stage + p.out_off, d + p.out_off, p.out_bytes, cudaMemcpyDeviceToHost, h->stream));
+  if (also_counters) CK(cudaMemcpyAsync(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if (also_counters && h->h_counters[2]) {
+    return fail(JUBANN_E_CACHE_FULL,
+                "projection cache full: more than %u distinct features (raise option cache_slots, then clear)",
+                h->cache.slots);
+  }
+  if (k) {
+    memcpy(out_index, h->h_stage + p.idx_off, nq * (size_t)k * 8);
+    memcpy(out_score, h->h_stage + p.score_off, nq * (size_t)k * 4);
+  }
+  memcpy(out_count, h->h_stage + p.count_off, nq * 4);
+  return 0;
+}
+
+static int query_sig_small(jubann_t* h, uint64_t nq, const uint64_t* qsigs, const float* qnorms, uint32_t k,
+                           uint32_t flags, uint64_t* out_index, float* out_score, uint32_t* out_count, bool* taken) {
+  const size_t sig_b = up256(nq * h->w64 * 8), norm_b = h->method == EUCLID_LSH ? up256(nq * 4) : 0;
+  const SmallPlan p = small_plan(h, nq, k, sig_b + norm_b, false);
+  *taken = p.total <= SMALL_STAGE_BYTES;
+  if (!*taken) return 0;
+  memcpy(h->h_stage, qsigs, nq * h->w64 * 8);
+  if (norm_b) memcpy(h->h_stage + sig_b, qnorms, nq * 4);
+  unsigned char* d = h->b_stage.as<unsigned char>();
+  CK(cudaMemcpyAsync(d, h->h_stage, sig_b + norm_b, cudaMemcpyHostToDevice, h->stream));
+  return small_finish(h, p, nq, reinterpret_cast<const uint64_t*>(d), norm_b ? reinterpret_cast<const float*>(d + sig_b) : nullptr,
+                      k, flags, false, out_index, out_score, out_count);
+}
+
+static int query_csr_small(jubann_t* h, uint64_t nq, const uint64_t* indptr, const uint32_t* seed32,
+                           const uint64_t* keyhash64, const float* vals, uint32_t k, uint32_t flags,
+                           uint64_t* out_index, float* out_score, uint32_t* out_count, bool* taken) {
+  *taken = false;
+  const uint64_t base = indptr[0], nnz = indptr[nq] - base;
+  if (indptr[nq] < base || nnz > SMALL_STAGE_BYTES / 4) return 0;
+  const bool mh = h->method == MINHASH;
+  const size_t ip_b = up256((nq + 1) * 8), val_b = up256(nnz * 4), key_b = up256(nnz * (mh ? 8 : 4));
+  const SmallPlan p = small_plan(h, nq, k, ip_b + val_b + key_b, true);
+  if (p.total > SMALL_STAGE_BYTES) return 0;
+  if (mh) { if (!keyhash64 && nnz) return fail(JUBANN_E_INVALID, "minhash needs keyhash64"); }
+  else if (!seed32 && nnz) return fail(JUBANN_E_INVALID, "lsh/euclid_lsh need seed32");
+  if (!vals && nnz) return fail(JUBANN_E_INVALID, "vals is null");
+  *taken = true;
+  uint64_t* ip = reinterpret_cast<uint64_t*>(h->h_stage);
+  for (uint64_t i = 0; i <= nq; ++i) {
+    if (indptr[i] < base || (i && indptr[i] < indptr[i - 1])) return fail(JUBANN_E_INVALID, "indptr is not non-decreasing");
+    ip[i] = indptr[i] - base;
+  }
+  if (nnz) {
+    memcpy(h->h_stage + ip_b, vals + base, nnz * 4);
+    if (mh) memcpy(h->h_stage + ip_b + val_b, keyhash64 + base, nnz * 8);
+    else memcpy(h->h_stage + ip_b + val_b, seed32 + base, nnz * 4);
+  }
+  unsigned char* d = h->b_stage.as<unsigned char>();
+  CK(cudaMemcpyAsync(d, h->h_stage, ip_b + val_b + key_b, cudaMemcpyHostToDevice, h->stream));
+  const uint64_t* d_ip = reinterpret_cast<const uint64_t*>(d);
+  const float* d_vals = reinterpret_cast<const float*>(d + ip_b);
+  uint64_t* d_sigs = reinterpret_cast<uint64_t*>(d + p.sig_off);
+  float* d_norms = reinterpret_cast<float*>(d + p.norm_off);
+  int launches = 0;
+  bool counters = false;
+  if (mh) {
+    CK(launch_signature_minhash(h->hash_num, nq, d_ip, reinterpret_cast<const uint64_t*>(d + ip_b + val_b), d_vals, d_sigs,
+                                d_norms, h->w64, h->stream));
+    ++launches;
+  } else {
+    int rc = ensure_cache(h);
+    if (rc) return rc;
+    const uint32_t* d_seed = reinterpret_cast<const uint32_t*>(d + ip_b + val_b);
+    CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, h->stream, &launches));
+    CK(launch_cache_fill_queued(h->cache, nnz, h->num_sms, h->stream, &launches));
+    if (nnz) CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, h->stream));
+    CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, nq, d_ip, d_seed, d_vals, d_sigs, d_norms, h->w64, h->stream));
+    ++launches;
+    counters = nnz != 0;
+  }
+  h->kernel_launches += launches;
+  return small_finish(h, p, nq, d_sigs, d_norms, k, flags, counters, out_index, out_score, out_count);
+}
+
 int jubann_query_sig(jubann_t* h, uint64_t nq, const uint64_t* qsigs, const float* qnorms, uint32_t k,
                      uint32_t flags, uint64_t* out_index, float* out_score, uint32_t* out_count) {
   int rc = check_handle(h);
@@ -726,6 +854,11 @@ int jubann_query_sig(jubann_t* h, uint64_t nq, const uint64_t* qsigs, const floa
   if (h->method == EUCLID_LSH && !qnorms) return fail(JUBANN_E_INVALID, "euclid_lsh queries need norms");
   Guard g(h);
   if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
+  {
+    bool taken = false;
+    rc = query_sig_small(h, nq, qsigs, qnorms, k, flags, out_index, out_score, out_count, &taken);
+    if (rc || taken) return rc;
+  }
   CK(h->b_qsigs.ensure(nq * h->w64 * 8));
   CK(cudaMemcpyAsync(h->b_qsigs.p, qsigs, nq * h->w64 * 8, cudaMemcpyHostToDevice, h->stream));
   const float* dqn = nullptr;
@@ -751,6 +884,11 @@ int jubann_query_csr(jubann_t* h, uint64_t nq, const uint64_t* indptr, const uin
   if (!indptr || !out_count || (k && (!out_index || !out_score))) return fail(JUBANN_E_INVALID, "null argument");
   Guard g(h);
   if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
+  {
+    bool taken = false;
+    rc = query_csr_small(h, nq, indptr, seed32, keyhash64, vals, k, flags, out_index, out_score, out_count, &taken);
+    if (rc || taken) return rc;
+  }
   for (uint64_t r0 = 0; r0 < nq; r0 += CSR_CHUNK_ROWS) {
     const uint64_t r1 = std::min(nq, r0 + CSR_CHUNK_ROWS), m = r1 - r0;
     CsrDev d;

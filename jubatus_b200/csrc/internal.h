@@ -127,6 +127,7 @@ struct ProjCache {
 cudaError_t launch_cache_resolve(const ProjCache& c, const uint32_t* d_seed32, uint64_t nnz, int num_sms,
                                  cudaStream_t s, int* launches);
 cudaError_t launch_cache_fill(const ProjCache& c, uint32_t nfill, int num_sms, cudaStream_t s, int* launches);
+cudaError_t launch_cache_fill_queued(const ProjCache& c, uint64_t max_entries, int num_sms, cudaStream_t s, int* launches);
 cudaError_t launch_signature_lsh(const ProjCache& c, bool euclid, uint64_t n, const uint64_t* d_indptr,
                                  const uint32_t* d_seed32, const float* d_vals, uint64_t* d_sigs,
                                  float* d_norms, uint32_t w64, cudaStream_t s);

@@ -26,7 +26,7 @@ def main():
     key64 = d_k64[ids.reshape(-1)].contiguous()
     indptr = (torch.arange(n + 1, device=dev, dtype=torch.int64) * nnz_per).contiguous()
     stream = torch.cuda.current_stream().cuda_stream
-    for method, h in (("lsh", 512), ("lsh", 64), ("euclid_lsh", 256), ("minhash", 128)):
+    for method, h in (("lsh", 512), ("lsh", 64), ("lsh", 128), ("euclid_lsh", 256), ("minhash", 128)):
         with Engine(method, h) as e:
             w64 = (h + 63) // 64
             sigs = torch.zeros((n, w64), dtype=torch.int64, device=dev)
