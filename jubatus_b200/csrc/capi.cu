@@ -578,6 +578,8 @@ int jubann_hash_csr(jubann_t* h, uint64_t n, const uint64_t* indptr, const uint3
   return 0;
 }
 
+static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index, const uint64_t* indptr,
+                              const uint32_t* seed32, const uint64_t* keyhash64, const float* vals, bool* taken);
 int jubann_set_rows_csr(jubann_t* h, uint64_t n, const uint64_t* row_index, const uint64_t* indptr,
                         const uint32_t* seed32, const uint64_t* keyhash64, const float* vals) {
   int rc = check_handle(h);
@@ -590,6 +592,11 @@ int jubann_set_rows_csr(jubann_t* h, uint64_t n, const uint64_t* row_index, cons
   if (rc) return rc;
   rc = grow_to(h, new_global);
   if (rc) return rc;
+  {
+    bool taken = false;
+    rc = set_rows_csr_small(h, n, row_index, indptr, seed32, keyhash64, vals, &taken);
+    if (rc || taken) return rc;
+  }
   for (uint64_t r0 = 0; r0 < n; r0 += CSR_CHUNK_ROWS) {
     const uint64_t r1 = std::min(n, r0 + CSR_CHUNK_ROWS), m = r1 - r0;
     CsrDev d;
@@ -845,6 +852,69 @@ static int query_csr_small(jubann_t* h, uint64_t nq, const uint64_t* indptr, con
   return small_finish(h, p, nq, d_sigs, d_norms, k, flags, counters, out_index, out_score, out_count);
 }
 
+// set_row for a few rows (one RPC): CSR and row indices in one copy, the cache fill off the
+// device-side count, the scatter guarded by the overflow flag, one synchronisation.
+static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index, const uint64_t* indptr,
+                              const uint32_t* seed32, const uint64_t* keyhash64, const float* vals, bool* taken) {
+  *taken = false;
+  const uint64_t base = indptr[0], nnz = indptr[n] - base;
+  if (indptr[n] < base || nnz > SMALL_STAGE_BYTES / 4) return 0;
+  const bool mh = h->method == MINHASH;
+  const size_t ip_b = up256((n + 1) * 8), val_b = up256(nnz * 4), key_b = up256(nnz * (mh ? 8 : 4)), ri_b = up256(n * 8);
+  const size_t in_b = ip_b + val_b + key_b + ri_b;
+  const size_t sig_off = in_b, norm_off = sig_off + up256(n * h->w64 * 8), total = norm_off + up256(n * 4);
+  if (total > SMALL_STAGE_BYTES) return 0;
+  if (mh) { if (!keyhash64 && nnz) return fail(JUBANN_E_INVALID, "minhash needs keyhash64"); }
+  else if (!seed32 && nnz) return fail(JUBANN_E_INVALID, "lsh/euclid_lsh need seed32");
+  if (!vals && nnz) return fail(JUBANN_E_INVALID, "vals is null");
+  *taken = true;
+  uint64_t* ip = reinterpret_cast<uint64_t*>(h->h_stage);
+  for (uint64_t i = 0; i <= n; ++i) {
+    if (indptr[i] < base || (i && indptr[i] < indptr[i - 1])) return fail(JUBANN_E_INVALID, "indptr is not non-decreasing");
+    ip[i] = indptr[i] - base;
+  }
+  if (nnz) {
+    memcpy(h->h_stage + ip_b, vals + base, nnz * 4);
+    if (mh) memcpy(h->h_stage + ip_b + val_b, keyhash64 + base, nnz * 8);
+    else memcpy(h->h_stage + ip_b + val_b, seed32 + base, nnz * 4);
+  }
+  memcpy(h->h_stage + ip_b + val_b + key_b, row_index, n * 8);
+  unsigned char* d = h->b_stage.as<unsigned char>();
+  CK(cudaMemcpyAsync(d, h->h_stage, in_b, cudaMemcpyHostToDevice, h->stream));
+  const uint64_t* d_ip = reinterpret_cast<const uint64_t*>(d);
+  const float* d_vals = reinterpret_cast<const float*>(d + ip_b);
+  const uint64_t* d_ri = reinterpret_cast<const uint64_t*>(d + ip_b + val_b + key_b);
+  uint64_t* d_sigs = reinterpret_cast<uint64_t*>(d + sig_off);
+  float* d_norms = reinterpret_cast<float*>(d + norm_off);
+  int launches = 0;
+  const uint32_t* guard = nullptr;
+  if (mh) {
+    CK(launch_signature_minhash(h->hash_num, n, d_ip, reinterpret_cast<const uint64_t*>(d + ip_b + val_b), d_vals, d_sigs,
+                                d_norms, h->w64, h->stream));
+    ++launches;
+  } else {
+    int rc = ensure_cache(h);
+    if (rc) return rc;
+    const uint32_t* d_seed = reinterpret_cast<const uint32_t*>(d + ip_b + val_b);
+    CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, h->stream, &launches));
+    CK(launch_cache_fill_queued(h->cache, nnz, h->num_sms, h->stream, &launches));
+    if (nnz) CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, h->stream));
+    CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, n, d_ip, d_seed, d_vals, d_sigs, d_norms, h->w64, h->stream));
+    ++launches;
+    if (nnz) guard = h->cache.counters + 2;
+  }
+  CK(launch_scatter_rows(view(h), n, d_ri, 0, d_sigs, d_norms, h->shard_rank, h->shard_count, h->stream, guard));
+  h->kernel_launches += launches + 1;
+  if (guard) CK(cudaMemcpyAsync(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if (guard && h->h_counters[2]) {
+    return fail(JUBANN_E_CACHE_FULL,
+                "projection cache full: more than %u distinct features (raise option cache_slots, then clear)",
+                h->cache.slots);
+  }
+  return 0;
+}
+
 int jubann_query_sig(jubann_t* h, uint64_t nq, const uint64_t* qsigs, const float* qnorms, uint32_t k,
                      uint32_t flags, uint64_t* out_index, float* out_score, uint32_t* out_count) {
   int rc = check_handle(h);
@@ -919,6 +989,19 @@ int jubann_query_rows(jubann_t* h, uint64_t nq, const uint64_t* row_index, uint3
   if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "query_rows needs a single-shard handle");
   for (uint64_t r = 0; r < nq; ++r)
     if (row_index[r] >= h->global_rows) return fail(JUBANN_E_RANGE, "row index %llu out of range", (unsigned long long)row_index[r]);
+  {
+    const SmallPlan p = small_plan(h, nq, k, nq * 8, true);
+    if (p.total <= SMALL_STAGE_BYTES) {   // latency path: one copy each way
+      memcpy(h->h_stage, row_index, nq * 8);
+      unsigned char* d = h->b_stage.as<unsigned char>();
+      CK(cudaMemcpyAsync(d, h->h_stage, nq * 8, cudaMemcpyHostToDevice, h->stream));
+      uint64_t* d_sigs = reinterpret_cast<uint64_t*>(d + p.sig_off);
+      float* d_norms = reinterpret_cast<float*>(d + p.norm_off);
+      CK(launch_gather_rows(view(h), nq, reinterpret_cast<const uint64_t*>(d), d_sigs, d_norms, 0, 1, h->stream));
+      h->kernel_launches += 1;
+      return small_finish(h, p, nq, d_sigs, d_norms, k, flags, false, out_index, out_score, out_count);
+    }
+  }
   CK(h->b_rowidx.ensure(nq * 8));
   CK(h->b_qsigs.ensure(nq * h->w64 * 8));
   CK(h->b_qnorms.ensure(nq * 4));

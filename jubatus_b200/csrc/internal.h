@@ -103,7 +103,8 @@ cudaError_t launch_merge_parts(const uint32_t* d_cand_key, const uint64_t* d_can
 // rows given row-major ([n][w64] u64 words) -> slab at local slot (g / G) when g % G == rank
 cudaError_t launch_scatter_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                 uint64_t first_index, const uint64_t* d_sigs, const float* d_norms,
-                                uint32_t shard_rank, uint32_t shard_count, cudaStream_t s);
+                                uint32_t shard_rank, uint32_t shard_count, cudaStream_t s,
+                                const uint32_t* d_skip_if_nonzero = nullptr);
 cudaError_t launch_gather_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                uint64_t* d_sigs, float* d_norms, uint32_t shard_rank,
                                uint32_t shard_count, cudaStream_t s);

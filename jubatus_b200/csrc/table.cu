@@ -12,7 +12,10 @@ namespace jbn {
 // one thread per (row, 32-bit word): row-major ABI words -> tile-transposed slab
 __global__ void scatter_rows_kernel(TableView t, uint64_t n, const uint64_t* __restrict__ row_index,
                                     uint64_t first_index, const uint64_t* __restrict__ sigs,
-                                    const float* __restrict__ norms, uint32_t rank, uint32_t G) {
+                                    const float* __restrict__ norms, uint32_t rank, uint32_t G,
+                                    const uint32_t* skip_if_nonzero) {
+  // latency path: the projection cache overflowed in this very call, the signatures are not valid
+  if (skip_if_nonzero && *reinterpret_cast<const volatile uint32_t*>(skip_if_nonzero)) return;
   const uint64_t total = n * t.w32;
   unsigned char* slab = static_cast<unsigned char*>(t.slab);
   for (uint64_t e = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; e < total;
@@ -101,10 +104,11 @@ static unsigned grid_for(uint64_t total) {
 
 cudaError_t launch_scatter_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                 uint64_t first_index, const uint64_t* d_sigs, const float* d_norms,
-                                uint32_t shard_rank, uint32_t shard_count, cudaStream_t s) {
+                                uint32_t shard_rank, uint32_t shard_count, cudaStream_t s,
+                                const uint32_t* d_skip_if_nonzero) {
   if (n == 0) return cudaSuccess;
   scatter_rows_kernel<<<grid_for(n * t.w32), 256, 0, s>>>(t, n, d_row_index, first_index, d_sigs, d_norms,
-                                                          shard_rank, shard_count);
+                                                          shard_rank, shard_count, d_skip_if_nonzero);
   return cudaGetLastError();
 }
 cudaError_t launch_gather_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,

@@ -117,6 +117,30 @@ def test_cache_full_is_reported(feature_tables):
         assert ei.value.code == -4
 
 
+def test_cache_full_on_the_small_request_paths_leaves_the_table_alone(feature_tables):
+    # small requests do not read the cache counters back before hashing: the scatter is guarded on
+    # the device, the error surfaces with the results
+    from jubatus_b200 import Engine, JubannError
+    s32, k64 = feature_tables
+    with Engine("lsh", 64, cache_slots=150) as e:
+        ids, vals = w.synth_rows(w.MASTER_SEED, 0, 1)
+        e.set_rows_csr(np.arange(1, dtype=np.uint64), *w.to_csr(ids, vals, s32, k64))      # 100 features: fits
+        before = e.get_rows_sig(np.arange(1, dtype=np.uint64))[0].copy()
+        ids2, vals2 = w.synth_rows(w.MASTER_SEED, 7, 1)
+        csr2 = w.to_csr(ids2, vals2, s32, k64)
+        with pytest.raises(JubannError) as ei:
+            e.set_rows_csr(np.arange(1, dtype=np.uint64), *csr2)                            # 100 more: overflow
+        assert ei.value.code == -4
+        assert np.array_equal(e.get_rows_sig(np.arange(1, dtype=np.uint64))[0], before)      # row 0 not overwritten
+    with Engine("lsh", 64, cache_slots=150) as e:
+        ids, vals = w.synth_rows(w.MASTER_SEED, 0, 1)
+        e.set_rows_csr(np.arange(1, dtype=np.uint64), *w.to_csr(ids, vals, s32, k64))
+        ids2, vals2 = w.synth_rows(w.MASTER_SEED, 7, 1)
+        with pytest.raises(JubannError) as ei:
+            e.query_csr(*w.to_csr(ids2, vals2, s32, k64), 1)
+        assert ei.value.code == -4
+
+
 def test_set_rows_csr_then_query_end_to_end(oracle, feature_tables):
     # the whole path: datums -> signatures -> table -> neighbor_row_from_datum
     from jubatus_b200 import Engine

@@ -44,3 +44,7 @@ def span(k):
     return ts[len(ts) // 2]
 for k in (1, 10, 100):
     print("k=%d GPU span of one query_sig_dev: %.1f us" % (k, span(k)))
+# one set_row (100-feature datum hashed on the device, overwriting row 5) and one query by stored row
+ridx = np.array([5], dtype=np.uint64)
+print("set_rows_csr host 1 row: %.1f us" % t(lambda: e.set_rows_csr(ridx, *csr)))
+print("query_rows host 1 row, k=10: %.1f us" % t(lambda: e.query_rows(ridx, 10)))
