@@ -1513,7 +1513,8 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
   if (qp < 1) qp = 1;
   // automatic variant: the TMA ring wins while the pass is memory-bound, the LDG kernel's
   // 32 resident warps win once it is popcount-bound (measured crossover between 4 and 8 queries per pass)
-  cfg->variant = variant <= 0 ? (qp <= 4 ? 2 : 1) : variant;
+  // (a table that cannot give every SM a stage or two is not worth the ring's set-up either)
+  cfg->variant = variant <= 0 ? ((qp <= 4 && ntiles >= (uint64_t)num_sms * 32) ? 2 : 1) : variant;
   cfg->stages = 0; cfg->tiles_per_warp = 0;
   cfg->interleave = interleave ? 1u : 0u;
   uint64_t max_chunks;
@@ -1544,8 +1545,11 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
     max_chunks = (uint64_t)num_sms * 2;
   }
   cfg->qp = qp;
-  // at least 64 tiles per CTA
-  uint64_t nchunks = (ntiles + 63) / 64;
+  // at least 64 tiles per CTA; tables too small to give every SM that much are cut finer (down
+  // to one tile per warp) so that a single query is not left to a handful of SMs
+  uint64_t min_tiles = 64;
+  if (ntiles < (uint64_t)num_sms * 64) min_tiles = cfg->variant == 2 ? 32 : 16;
+  uint64_t nchunks = (ntiles + min_tiles - 1) / min_tiles;
   if (nchunks > max_chunks) nchunks = max_chunks;
   if (nchunks < 1) nchunks = 1;
   cfg->nchunks = (uint32_t)nchunks;
@@ -1703,7 +1707,10 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
     if (S > 8192) S = 8192;
     // counting a sample is cheap for the hamming engines: take the largest one the table allows
     if (!euclid && t.local_rows >= 16 * 8192) S = 8192;
-    if (t.local_rows >= 16 * S && k <= S) {
+    // small tables: a quarter of the rows at most (without any bound a CTA's first rows all go
+    // through the list, which is what a query on a 10^4-row table spent its time in)
+    while (S > 256 && t.local_rows < 4 * S) S >>= 1;
+    if (t.local_rows >= 4 * S && k <= S) {
       if (euclid) {
         uint32_t SP = 1;
         while (SP < S) SP <<= 1;

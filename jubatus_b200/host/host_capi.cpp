@@ -81,9 +81,15 @@ void* jubahost_create(const char* kind, const char* config_json, const char* lib
         if (key != "method" && key != "parameter" && key != "unlearner" && key != "unlearner_parameter")
           throw config_exception("unknown parameter key: " + key);
       }
-      if (p->find("unlearner")) throw config_exception("unlearner is not supported by this build");
+      std::shared_ptr<unlearner_base> unl;
+      if (json::ptr u = p->find("unlearner")) {
+        if (u->kind != json::value::STR) throw config_exception("\"unlearner\" must be a string");
+        unl = create_unlearner(u->str, p->find("unlearner_parameter"));
+      } else if (p->find("unlearner_parameter")) {
+        throw config_exception("\"unlearner_parameter\" without \"unlearner\"");
+      }
       b->engine = create_nearest_neighbor(im->str, p->find("parameter"), b->api, my_id ? my_id : "", device);
-      b->recommender.reset(new nearest_neighbor_recommender(b->engine));
+      b->recommender.reset(new nearest_neighbor_recommender(b->engine, unl));
     } else if (k == "anomaly") {
       // anomaly_serv.cpp:112-142 -> anomaly_factory; light_lof only
       if (m->str != "light_lof") throw unsupported_method(m->str);
@@ -95,13 +101,20 @@ void* jubahost_create(const char* kind, const char* config_json, const char* lib
           if (v->kind != json::value::NUM || !v->is_integer) throw config_exception("\"" + key + "\" must be an integer");
           (key == "nearest_neighbor_num" ? nn_num : rnn_num) = static_cast<int>(v->num);
         } else if (key == "unlearner" || key == "unlearner_parameter") {
-          throw config_exception("unlearner is not supported by this build");
+          // handled below
         } else if (key != "method" && key != "parameter") {
           throw config_exception("unknown parameter key: " + key);
         }
       }
+      std::shared_ptr<unlearner_base> unl;
+      if (json::ptr u = p->find("unlearner")) {
+        if (u->kind != json::value::STR) throw config_exception("\"unlearner\" must be a string");
+        unl = create_unlearner(u->str, p->find("unlearner_parameter"));
+      } else if (p->find("unlearner_parameter")) {
+        throw config_exception("\"unlearner_parameter\" without \"unlearner\"");
+      }
       b->engine = create_nearest_neighbor(im->str, p->find("parameter"), b->api, my_id ? my_id : "", device);
-      b->lof.reset(new light_lof(b->engine, nn_num, rnn_num));
+      b->lof.reset(new light_lof(b->engine, nn_num, rnn_num, unl));
     } else {
       throw jubatus_exception("unknown server kind: " + k);
     }
@@ -333,6 +346,27 @@ int64_t jubahost_model_read(const char* file, uint64_t file_n, const char* expec
     return 0;
   });
   return rc ? -1 : n;
+}
+// unlearner policy alone (CPU tests): touch ids in order, report "<position>:<victim>" per eviction
+int jubahost_unlearner_trace(const char* name, const char* param_json, const char* const* ids, uint64_t n, char* out,
+                             uint64_t cap, uint64_t* final_size) {
+  return guarded([&]() {
+    json::ptr param;
+    try { param = json::parse(param_json); } catch (const json::parse_error& e) { throw config_exception(e.what()); }
+    std::shared_ptr<unlearner_base> u = create_unlearner(name, param);
+    std::string log;
+    uint64_t pos = 0;
+    u->set_callback([&](const std::string& victim) { log += std::to_string(pos) + ":" + victim + "\n"; });
+    for (pos = 0; pos < n; ++pos) {
+      const std::string id(ids[pos]);
+      if (!id.empty() && id[0] == '-') u->remove(id.substr(1));   // "-x" removes x
+      else u->touch(id);
+    }
+    if (log.size() + 1 > cap) throw jubatus_exception("trace buffer too small");
+    memcpy(out, log.c_str(), log.size() + 1);
+    *final_size = u->size();
+    return 0;
+  });
 }
 int jubahost_dump_json(void* h, char* buf, uint64_t cap) {
   host_box* b = static_cast<host_box*>(h);

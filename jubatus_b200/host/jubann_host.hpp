@@ -34,6 +34,8 @@
 #include <chrono>
 #include <condition_variable>
 #include <fstream>
+#include <functional>
+#include <list>
 #include <limits>
 #include <map>
 #include <memory>
@@ -923,14 +925,152 @@ class nearest_neighbor_serv {
 };
 
 // ---------------------------------------------------------------------------------------
+// core::unlearner -- keeps the model at most `max_size` rows.  Config surface:
+// "unlearner": "lru" | "random", "unlearner_parameter": {"max_size": N [, "seed": S]}
+// (config/recommender/nearest_neighbor_recommender_euclid_lsh_unlearn_lru.json:21-24,
+// config/anomaly/light_lof_unlearn_lru.json:23-26).  touch(id) marks a row as just used; when a
+// new id would exceed max_size the policy picks a victim and the owner's callback deletes it
+// (column_table::delete_row: swap with the last row).  [core] unlearner/{lru,random}_unlearner --
+// restated from recall: lru evicts the least recently touched id, random a uniformly drawn one.
+// ---------------------------------------------------------------------------------------
+class unlearner_base {
+ public:
+  typedef std::function<void(const std::string&)> callback_t;
+  virtual ~unlearner_base() {}
+  virtual std::string type() const = 0;
+  virtual void clear() = 0;
+  virtual bool touch(const std::string& id) = 0;      // false: cannot make room (max_size 0 is rejected at construction)
+  virtual bool remove(const std::string& id) = 0;
+  virtual bool exists_in_memory(const std::string& id) const = 0;
+  virtual size_t size() const = 0;
+  void set_callback(const callback_t& cb) { callback_ = cb; }
+ protected:
+  callback_t callback_;
+};
+
+class lru_unlearner : public unlearner_base {
+ public:
+  explicit lru_unlearner(size_t max_size) : max_size_(max_size) {
+    if (max_size_ == 0) throw invalid_parameter("max_size must be a positive integer");
+  }
+  std::string type() const { return "lru_unlearner"; }
+  void clear() { lru_.clear(); pos_.clear(); }
+  bool touch(const std::string& id) {
+    std::unordered_map<std::string, std::list<std::string>::iterator>::iterator it = pos_.find(id);
+    if (it != pos_.end()) {
+      lru_.splice(lru_.begin(), lru_, it->second);   // most recently used first
+      return true;
+    }
+    if (lru_.size() >= max_size_) {
+      const std::string victim = lru_.back();
+      pos_.erase(victim);
+      lru_.pop_back();
+      if (callback_) callback_(victim);
+    }
+    lru_.push_front(id);
+    pos_[id] = lru_.begin();
+    return true;
+  }
+  bool remove(const std::string& id) {
+    std::unordered_map<std::string, std::list<std::string>::iterator>::iterator it = pos_.find(id);
+    if (it == pos_.end()) return false;
+    lru_.erase(it->second);
+    pos_.erase(it);
+    return true;
+  }
+  bool exists_in_memory(const std::string& id) const { return pos_.count(id) != 0; }
+  size_t size() const { return lru_.size(); }
+ private:
+  size_t max_size_;
+  std::list<std::string> lru_;
+  std::unordered_map<std::string, std::list<std::string>::iterator> pos_;
+};
+
+class random_unlearner : public unlearner_base {
+ public:
+  random_unlearner(size_t max_size, uint64_t seed) : max_size_(max_size), state_(seed ? seed : 0x9E3779B97F4A7C15ull) {
+    if (max_size_ == 0) throw invalid_parameter("max_size must be a positive integer");
+  }
+  std::string type() const { return "random_unlearner"; }
+  void clear() { ids_.clear(); pos_.clear(); }
+  bool touch(const std::string& id) {
+    if (pos_.count(id)) return true;
+    if (ids_.size() >= max_size_) {
+      const size_t v = static_cast<size_t>(next() % ids_.size());
+      const std::string victim = ids_[v];
+      ids_[v] = ids_.back();
+      pos_[ids_[v]] = v;
+      ids_.pop_back();
+      pos_.erase(victim);
+      if (callback_) callback_(victim);
+    }
+    pos_[id] = ids_.size();
+    ids_.push_back(id);
+    return true;
+  }
+  bool remove(const std::string& id) {
+    std::unordered_map<std::string, size_t>::iterator it = pos_.find(id);
+    if (it == pos_.end()) return false;
+    const size_t v = it->second;
+    ids_[v] = ids_.back();
+    pos_[ids_[v]] = v;
+    ids_.pop_back();
+    pos_.erase(id);
+    return true;
+  }
+  bool exists_in_memory(const std::string& id) const { return pos_.count(id) != 0; }
+  size_t size() const { return ids_.size(); }
+ private:
+  uint64_t next() {   // splitmix64
+    uint64_t z = (state_ += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+  }
+  size_t max_size_;
+  uint64_t state_;
+  std::vector<std::string> ids_;
+  std::unordered_map<std::string, size_t> pos_;
+};
+
+// create_unlearner(name, config) -- core::unlearner::create_unlearner
+inline std::shared_ptr<unlearner_base> create_unlearner(const std::string& name, const json::ptr& param) {
+  if (!param || param->kind != json::value::OBJ) throw config_exception("\"unlearner_parameter\" is required with \"unlearner\"");
+  int64_t max_size = -1, seed = 0;
+  for (size_t i = 0; i < param->obj.size(); ++i) {
+    const std::string& k = param->obj[i].first;
+    const json::ptr& v = param->obj[i].second;
+    if (k == "max_size" || k == "seed") {
+      if (v->kind != json::value::NUM || !v->is_integer) throw config_exception("\"" + k + "\" must be an integer");
+      (k == "max_size" ? max_size : seed) = static_cast<int64_t>(v->num);
+    } else if (k != "sticky_pattern") {
+      throw config_exception("unknown unlearner_parameter key: " + k);
+    } else {
+      throw config_exception("sticky_pattern is not supported by this build");
+    }
+  }
+  if (max_size <= 0) throw invalid_parameter("max_size must be a positive integer");
+  if (name == "lru") return std::shared_ptr<unlearner_base>(new lru_unlearner(static_cast<size_t>(max_size)));
+  if (name == "random") return std::shared_ptr<unlearner_base>(new random_unlearner(static_cast<size_t>(max_size), static_cast<uint64_t>(seed)));
+  throw unsupported_method("unlearner: " + name);
+}
+
+// ---------------------------------------------------------------------------------------
 // recommender::nearest_neighbor_recommender
 // ---------------------------------------------------------------------------------------
 class nearest_neighbor_recommender {
  public:
-  explicit nearest_neighbor_recommender(const std::shared_ptr<gpu_nearest_neighbor>& nn) : nn_(nn) {}
-  void clear() { orig_.clear(); nn_->clear(); }
+  explicit nearest_neighbor_recommender(const std::shared_ptr<gpu_nearest_neighbor>& nn,
+                                        const std::shared_ptr<unlearner_base>& unlearner = std::shared_ptr<unlearner_base>())
+      : nn_(nn), unlearner_(unlearner) {
+    // the victim leaves both the original rows and the engine's table
+    if (unlearner_) unlearner_->set_callback([this](const std::string& victim) { orig_.erase(victim); nn_->delete_row(victim); });
+  }
+  void clear() { orig_.clear(); nn_->clear(); if (unlearner_) unlearner_->clear(); }
+  const unlearner_base* get_unlearner() const { return unlearner_.get(); }
   // update_row merges the diff into the stored original row, then re-hashes the FULL row
   void update_row(const std::string& id, const sfv_t& diff) {
+    if (unlearner_ && !unlearner_->touch(id)) throw jubatus_exception("cannot add new row as number of sticky rows reached the maximum size of unlearner: " + id);
     std::vector<std::pair<std::string, float> >& row = orig_[id];
     for (size_t i = 0; i < diff.size(); ++i) {
       bool found = false;
@@ -939,7 +1079,7 @@ class nearest_neighbor_recommender {
     }
     nn_->set_row(id, row);
   }
-  void clear_row(const std::string& id) { orig_.erase(id); nn_->delete_row(id); }
+  void clear_row(const std::string& id) { orig_.erase(id); nn_->delete_row(id); if (unlearner_) unlearner_->remove(id); }
   void similar_row(const sfv_t& q, neighbor_result& ids, size_t n) const { nn_->similar_row(q, ids, n); }
   void neighbor_row(const sfv_t& q, neighbor_result& ids, size_t n) const { nn_->neighbor_row(q, ids, n); }
   // *_from_id re-hashes the stored original row (not the stored signature); unknown id -> empty
@@ -961,6 +1101,7 @@ class nearest_neighbor_recommender {
   std::string type() const { return "nearest_neighbor_recommender:" + nn_->type(); }
  private:
   std::shared_ptr<gpu_nearest_neighbor> nn_;
+  std::shared_ptr<unlearner_base> unlearner_;
   std::unordered_map<std::string, sfv_t> orig_;
 };
 
@@ -970,12 +1111,19 @@ class nearest_neighbor_recommender {
 // ---------------------------------------------------------------------------------------
 class light_lof {
  public:
-  light_lof(const std::shared_ptr<gpu_nearest_neighbor>& nn, int nearest_neighbor_num, int reverse_nearest_neighbor_num)
-      : nn_(nn), nn_num_(nearest_neighbor_num), rnn_num_(reverse_nearest_neighbor_num) {
+  light_lof(const std::shared_ptr<gpu_nearest_neighbor>& nn, int nearest_neighbor_num, int reverse_nearest_neighbor_num,
+            const std::shared_ptr<unlearner_base>& unlearner = std::shared_ptr<unlearner_base>())
+      : nn_(nn), nn_num_(nearest_neighbor_num), rnn_num_(reverse_nearest_neighbor_num), unlearner_(unlearner) {
     if (nn_num_ < 2) throw invalid_parameter("nearest_neighbor_num should be >= 2");
     if (rnn_num_ < nn_num_) throw invalid_parameter("reverse_nearest_neighbor_num should be >= nearest_neighbor_num");
+    // the victim leaves the engine's table and the (kdist, lrd) table; rows that had it as a
+    // neighbour keep their parameters until they are next re-scored
+    if (unlearner_) unlearner_->set_callback([this](const std::string& victim) {
+      nn_->delete_row(victim); kdist_.erase(victim); lrd_.erase(victim);
+    });
   }
-  void clear() { nn_->clear(); kdist_.clear(); lrd_.clear(); }
+  void clear() { nn_->clear(); kdist_.clear(); lrd_.clear(); if (unlearner_) unlearner_->clear(); }
+  const unlearner_base* get_unlearner() const { return unlearner_.get(); }
   static float calculate_lof(float lrd, const std::vector<float>& neighbor_lrds) {
     if (neighbor_lrds.empty()) return lrd == 0 ? 1.0f : std::numeric_limits<float>::infinity();
     float sum = 0.0f;
@@ -994,6 +1142,7 @@ class light_lof {
     return score_from_neighbors(nb);
   }
   bool set_row(const std::string& id, const sfv_t& sfv) {
+    if (unlearner_ && !unlearner_->touch(id)) throw jubatus_exception("no more space available to add new ID: " + id);
     std::vector<std::string> order;
     std::unordered_set<std::string> seen;
     if (nn_->get_table()->exact_match(id).first) collect_neighbors(id, order, seen);
@@ -1025,6 +1174,7 @@ class light_lof {
   // in through the batched set_rows, then kdist for every row, then lrd for every row, each in
   // batched device calls.  Unlike a sequence of set_row calls no row keeps a stale parameter.
   void set_rows_bulk(const std::vector<std::string>& ids, const std::vector<sfv_t>& sfvs, size_t batch = 4096) {
+    if (unlearner_) throw jubatus_exception("bulk load is not available with an unlearner (rows must arrive one by one)");
     nn_->set_rows(ids, sfvs);
     for (size_t i = 0; i < ids.size(); ++i) { kdist_[ids[i]] = -1.0f; lrd_[ids[i]] = -1.0f; }
     std::vector<std::string> all;
@@ -1079,6 +1229,7 @@ class light_lof {
   }
   std::shared_ptr<gpu_nearest_neighbor> nn_;
   int nn_num_, rnn_num_;
+  std::shared_ptr<unlearner_base> unlearner_;
   std::unordered_map<std::string, float> kdist_, lrd_;
 };
 

@@ -12,6 +12,7 @@ Each takes the server's JSON config string (config/*/*.json).  All arithmetic ha
 libjubann.so on the GPU; this module only marshals strings.
 """
 import ctypes
+import json
 import os
 
 import numpy as np
@@ -86,6 +87,20 @@ def _load():
 
 def _raise():
     raise JubatusError(_load().jubahost_last_error().decode("utf-8", "replace"))
+
+
+def unlearner_trace(name, param, ids):
+    """Run an unlearner policy ("lru" / "random") over a sequence of touched ids ("-x" removes x);
+    returns ([(position, victim), ...], final_size)."""
+    lib = _load()
+    buf = ctypes.create_string_buffer(1 << 20)
+    size = ctypes.c_uint64()
+    lib.jubahost_unlearner_trace.argtypes = [ctypes.c_char_p, ctypes.c_char_p, _vp, ctypes.c_uint64, _vp, ctypes.c_uint64, _vp]
+    if lib.jubahost_unlearner_trace(name.encode(), json.dumps(param).encode(), _cstrs(ids), len(ids), buf, 1 << 20,
+                                    ctypes.byref(size)):
+        _raise()
+    ev = [ln.split(":", 1) for ln in buf.value.decode().split("\n") if ln]
+    return [(int(a), b) for a, b in ev], int(size.value)
 
 
 def crc32(data, crc=0):

@@ -42,3 +42,29 @@ def test_shipped_config_schema_is_accepted_by_the_parser():
     cfg = {"method": "lsh", "parameter": {"hash_num": 64}, "converter": CONVERTER}
     sfv = nn.convert(json.dumps(cfg["converter"]), nn.Datum().add_number("key", 1.0))
     assert sfv == [("key@num", 1.0)]
+
+
+def test_unlearner_policies():
+    """core::unlearner lru / random (SURVEY 8f n4; config/*_unlearn_lru.json): the policy alone."""
+    ev, size = nn.unlearner_trace("lru", {"max_size": 3}, ["a", "b", "c", "a", "d", "e", "-a", "f", "g"])
+    # a b c | touch a | d evicts b (least recently used) | e evicts c | remove a | f fits | g evicts d
+    assert ev == [(4, "b"), (5, "c"), (8, "d")] and size == 3
+    ev, size = nn.unlearner_trace("lru", {"max_size": 2}, ["x", "x", "x", "y", "x", "z"])
+    assert ev == [(5, "y")] and size == 2
+    ids = [str(i) for i in range(50)]
+    ev1, size1 = nn.unlearner_trace("random", {"max_size": 5, "seed": 7}, ids)
+    ev2, _ = nn.unlearner_trace("random", {"max_size": 5, "seed": 7}, ids)
+    ev3, _ = nn.unlearner_trace("random", {"max_size": 5, "seed": 8}, ids)
+    assert size1 == 5 and len(ev1) == 45 and ev1 == ev2 and ev1 != ev3
+    alive = set()
+    for pos, i in enumerate(ids):            # a victim is always a row that is held at that moment
+        for p, v in ev1:
+            if p == pos:
+                assert v in alive
+                alive.discard(v)
+        alive.add(i)
+    assert len(alive) == 5
+    for name, param in (("lru", {"max_size": 0}), ("lru", {}), ("fifo", {"max_size": 3}), ("lru", {"max_size": 3, "bogus": 1}),
+                        ("lru", {"max_size": "3"})):
+        with pytest.raises(nn.JubatusError):
+            nn.unlearner_trace(name, param, ["a"])

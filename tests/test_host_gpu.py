@@ -378,3 +378,47 @@ def test_light_lof_bulk_load_then_streaming_adds(oracle):
         rid, score = bulk.add(datum_of(ids[r], vals[r]))
         assert rid == str(r) and score == score
     assert bulk.size() == n + 5
+
+
+def test_recommender_and_light_lof_with_unlearner():
+    """config/recommender/nearest_neighbor_recommender_euclid_lsh_unlearn_lru.json and
+    config/anomaly/light_lof_unlearn_lru.json: the model never holds more than max_size rows, the
+    least recently touched row goes first, and it leaves the device table as well."""
+    cfg = json.dumps({"method": "nearest_neighbor_recommender", "converter": CONVERTER,
+                      "parameter": {"method": "euclid_lsh", "parameter": {"hash_num": 64},
+                                    "unlearner": "lru", "unlearner_parameter": {"max_size": 5}}})
+    rec = nn.Recommender(cfg)
+    ids, vals = w.synth_rows(w.MASTER_SEED, 300, 12, nnz=10, nfeat_log2=7)
+    for r in range(5):
+        rec.update_row("u%d" % r, datum_of(ids[r], vals[r]))
+    rec.update_row("u0", datum_of(ids[0][:3], vals[0][:3]))          # touch u0: u1 is now the oldest
+    rec.update_row("u5", datum_of(ids[5], vals[5]))                   # evicts u1
+    assert sorted(rec.get_all_rows()) == ["u0", "u2", "u3", "u4", "u5"] and rec.size() == 5
+    assert rec.similar_row_from_id("u1", 3) == []
+    assert rec.similar_row_from_id("u5", 1)[0][0] == "u5"
+    rec.clear_row("u2")                                               # frees a place: nobody is evicted next
+    rec.update_row("u6", datum_of(ids[6], vals[6]))
+    assert sorted(rec.get_all_rows()) == ["u0", "u3", "u4", "u5", "u6"]
+    for r in range(7, 12):
+        rec.update_row("u%d" % r, datum_of(ids[r], vals[r]))
+    assert sorted(rec.get_all_rows()) == ["u10", "u11", "u7", "u8", "u9"]
+    # the datum query only ever sees rows that are still held
+    got = rec.similar_row_from_datum(datum_of(ids[3], vals[3]), 10)
+    assert len(got) == 5 and all(g[0] in ("u7", "u8", "u9", "u10", "u11") for g in got)
+
+    acfg = json.dumps({"method": "light_lof", "converter": CONVERTER,
+                       "parameter": {"nearest_neighbor_num": 3, "reverse_nearest_neighbor_num": 6, "method": "lsh",
+                                     "parameter": {"hash_num": 128},
+                                     "unlearner": "lru", "unlearner_parameter": {"max_size": 20}}})
+    an = nn.Anomaly(acfg)
+    ids, vals = w.synth_rows(w.MASTER_SEED, 500, 60, nnz=8, nfeat_log2=6)
+    for r in range(60):
+        rid, score = an.add(datum_of(ids[r], vals[r]))
+        assert rid == str(r) and score == score
+        assert an.size() == min(r + 1, 20)
+    assert an.lof_params("39") is None and an.lof_params("40") is not None   # rows 0..39 were unlearned
+    assert sorted(an.get_all_rows(), key=int) == [str(r) for r in range(40, 60)]
+    with pytest.raises(nn.JubatusError):
+        nn.Anomaly(acfg.replace('"lru"', '"nope"'))
+    with pytest.raises(nn.JubatusError):
+        nn.Anomaly(acfg.replace('{"max_size": 20}', '{"max_size": 0}'))

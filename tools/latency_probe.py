@@ -1,8 +1,20 @@
-import sys, time, json, numpy as np, torch
-sys.path.insert(0, '/root/repo')
-from jubatus_b200 import Engine, workload as w, nn
-n, h = 1_000_000, 256
-e = Engine("lsh", h)
+"""Per-call latency of the C-ABI entry points for one query / one row at a time (development
+measurement, not the bench): python tools/latency_probe.py [rows] [hash_num]"""
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from jubatus_b200 import Engine, workload as w  # noqa: E402
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+h = int(sys.argv[2]) if len(sys.argv) > 2 else 256
+print("table: %d rows x %d bits (lsh), k=10" % (n, h))
+opts = {"scan_variant": int(sys.argv[3])} if len(sys.argv) > 3 else {}
+e = Engine("lsh", h, **opts)
 sig = w.random_signatures(1, n, h // 64)
 e.set_rows_sig(np.arange(n), sig, None)
 q = w.random_signatures(2, 1, h // 64)
