@@ -20,6 +20,7 @@ struct host_box {
   std::shared_ptr<datum_to_fv_converter> converter;
   std::unique_ptr<nearest_neighbor_recommender> recommender;
   std::unique_ptr<light_lof> lof;
+  std::unique_ptr<nearest_neighbor_classifier> classifier;   // jubaclassifier, method NN
   gpu_nearest_neighbor* nn() { return serv ? serv->get_driver()->engine() : engine.get(); }
   const datum_to_fv_converter& conv() { return serv ? serv->get_driver()->converter() : *converter; }
 };
@@ -115,6 +116,33 @@ void* jubahost_create(const char* kind, const char* config_json, const char* lib
       }
       b->engine = create_nearest_neighbor(im->str, p->find("parameter"), b->api, my_id ? my_id : "", device);
       b->lof.reset(new light_lof(b->engine, nn_num, rnn_num, unl));
+    } else if (k == "classifier") {
+      // classifier_serv.cpp -> classifier_factory; only the NN method is on this path (config/classifier/nn.json)
+      if (m->str != "NN" && m->str != "nearest_neighbor") throw unsupported_method(m->str);
+      int nn_num = -1;
+      double alpha = -1.0;
+      for (size_t i = 0; i < p->obj.size(); ++i) {
+        const std::string& key = p->obj[i].first;
+        const json::ptr& v = p->obj[i].second;
+        if (key == "nearest_neighbor_num") {
+          if (v->kind != json::value::NUM || !v->is_integer) throw config_exception("\"nearest_neighbor_num\" must be an integer");
+          nn_num = static_cast<int>(v->num);
+        } else if (key == "local_sensitivity") {
+          if (v->kind != json::value::NUM) throw config_exception("\"local_sensitivity\" must be a number");
+          alpha = v->num;
+        } else if (key != "method" && key != "parameter" && key != "unlearner" && key != "unlearner_parameter") {
+          throw config_exception("unknown parameter key: " + key);
+        }
+      }
+      if (nn_num < 1) throw config_exception("\"nearest_neighbor_num\" is required and must be >= 1");
+      if (alpha < 0) throw config_exception("\"local_sensitivity\" is required and must be >= 0");
+      std::shared_ptr<unlearner_base> unl;
+      if (json::ptr u = p->find("unlearner")) {
+        if (u->kind != json::value::STR) throw config_exception("\"unlearner\" must be a string");
+        unl = create_unlearner(u->str, p->find("unlearner_parameter"));
+      }
+      b->engine = create_nearest_neighbor(im->str, p->find("parameter"), b->api, my_id ? my_id : "", device);
+      b->classifier.reset(new nearest_neighbor_classifier(b->engine, static_cast<size_t>(nn_num), static_cast<float>(alpha), unl));
     } else {
       throw jubatus_exception("unknown server kind: " + k);
     }
@@ -142,7 +170,8 @@ int jubahost_convert(const char* converter_json, const char* const* skeys, const
 int jubahost_clear(void* h) {
   host_box* b = static_cast<host_box*>(h);
   return guarded([&]() {
-    if (b->serv) b->serv->clear(); else if (b->recommender) b->recommender->clear(); else b->lof->clear();
+    if (b->serv) b->serv->clear(); else if (b->recommender) b->recommender->clear();
+    else if (b->classifier) b->classifier->clear(); else b->lof->clear();
     return 0;
   });
 }
@@ -367,6 +396,81 @@ int jubahost_unlearner_trace(const char* name, const char* param_json, const cha
     *final_size = u->size();
     return 0;
   });
+}
+// ---- jubaclassifier, method NN ----
+int jubahost_train(void* h, const char* label, const char* const* skeys, const char* const* svals, uint64_t ns,
+                   const char* const* nkeys, const double* nvals, uint64_t nn) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->classifier) throw jubatus_exception("train: classifier server only");
+    sfv_t v;
+    b->conv().convert(make_datum(skeys, svals, ns, nkeys, nvals, nn), v);
+    b->classifier->train(v, label);
+    return 0;
+  });
+}
+// classify over n number-valued datums (flattened like jubahost_set_rows); the result is one line
+// per datum: "label\tscore\tlabel\tscore..."
+int jubahost_classify(void* h, uint64_t n, const uint64_t* offs, const char* const* nkeys, const double* nvals, char* out,
+                      uint64_t cap) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->classifier) throw jubatus_exception("classify: classifier server only");
+    std::vector<sfv_t> v(n);
+    for (uint64_t i = 0; i < n; ++i) {
+      datum d;
+      for (uint64_t j = offs[i]; j < offs[i + 1]; ++j) d.add_number(nkeys[j], nvals[j]);
+      b->conv().convert(d, v[i]);
+    }
+    std::vector<nearest_neighbor_classifier::classify_result> res;
+    b->classifier->classify_batch(v, res);
+    std::string s;
+    char num[48];
+    for (size_t i = 0; i < res.size(); ++i) {
+      for (size_t j = 0; j < res[i].size(); ++j) {
+        snprintf(num, sizeof(num), "%.9g", static_cast<double>(res[i][j].second));
+        if (j) s += '\t';
+        s += res[i][j].first; s += '\t'; s += num;
+      }
+      s += '\n';
+    }
+    if (s.size() + 1 > cap) throw jubatus_exception("classify buffer too small");
+    memcpy(out, s.c_str(), s.size() + 1);
+    return 0;
+  });
+}
+int jubahost_get_labels(void* h, char* out, uint64_t cap) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->classifier) throw jubatus_exception("get_labels: classifier server only");
+    std::string s;
+    const std::map<std::string, uint64_t> l = b->classifier->get_labels();
+    for (std::map<std::string, uint64_t>::const_iterator it = l.begin(); it != l.end(); ++it)
+      s += it->first + "\t" + std::to_string(it->second) + "\n";
+    if (s.size() + 1 > cap) throw jubatus_exception("labels buffer too small");
+    memcpy(out, s.c_str(), s.size() + 1);
+    return 0;
+  });
+}
+int jubahost_set_label(void* h, const char* label) {
+  host_box* b = static_cast<host_box*>(h);
+  int r = 0;
+  int rc = guarded([&]() {
+    if (!b->classifier) throw jubatus_exception("set_label: classifier server only");
+    r = b->classifier->set_label(label) ? 1 : 0;
+    return 0;
+  });
+  return rc ? -1 : r;
+}
+int jubahost_delete_label(void* h, const char* label) {
+  host_box* b = static_cast<host_box*>(h);
+  int r = 0;
+  int rc = guarded([&]() {
+    if (!b->classifier) throw jubatus_exception("delete_label: classifier server only");
+    r = b->classifier->delete_label(label) ? 1 : 0;
+    return 0;
+  });
+  return rc ? -1 : r;
 }
 int jubahost_dump_json(void* h, char* buf, uint64_t cap) {
   host_box* b = static_cast<host_box*>(h);

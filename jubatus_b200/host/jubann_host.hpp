@@ -1106,6 +1106,79 @@ class nearest_neighbor_recommender {
 };
 
 // ---------------------------------------------------------------------------------------
+// classifier::nearest_neighbor_classifier -- method "NN" of jubaclassifier
+// (config/classifier/nn.json: {"method": "NN", "parameter": {"method": <engine>, "parameter":
+// {...}, "nearest_neighbor_num": k, "local_sensitivity": alpha}}; RPC surface classifier.idl:
+// train, classify, get_labels, set_label, delete_label, clear).  Restated from recall of
+// [core] classifier/nearest_neighbor_classifier.cpp: every training datum becomes a row whose id
+// is "<label>_<serial>"; classify asks for the k nearest rows and adds exp(-alpha * distance)
+// to the label each row carries; every known label is reported, unseen ones with score 0.
+// ---------------------------------------------------------------------------------------
+class nearest_neighbor_classifier {
+ public:
+  typedef std::vector<std::pair<std::string, float> > classify_result;   // (label, score), label order
+  nearest_neighbor_classifier(const std::shared_ptr<gpu_nearest_neighbor>& nn, size_t k, float alpha,
+                              const std::shared_ptr<unlearner_base>& unlearner = std::shared_ptr<unlearner_base>())
+      : nn_(nn), k_(k), alpha_(alpha), serial_(0), unlearner_(unlearner) {
+    if (k_ == 0) throw invalid_parameter("nearest_neighbor_num should be >= 1");
+    if (!(alpha_ >= 0.0f)) throw invalid_parameter("local_sensitivity should be >= 0");
+    if (unlearner_) unlearner_->set_callback([this](const std::string& victim) { forget(victim); });
+  }
+  void train(const sfv_t& fv, const std::string& label) {
+    const std::string id = label + "_" + std::to_string(serial_++);
+    if (unlearner_ && !unlearner_->touch(id)) throw jubatus_exception("no more space available to add new ID: " + id);
+    labels_[label] += 1;
+    nn_->set_row(id, fv);
+  }
+  void classify_with_scores(const sfv_t& fv, classify_result& scores) const {
+    neighbor_result ids;
+    nn_->neighbor_row(fv, ids, k_);
+    std::map<std::string, float> m;
+    for (std::map<std::string, uint64_t>::const_iterator it = labels_.begin(); it != labels_.end(); ++it) m[it->first] = 0.0f;
+    for (size_t i = 0; i < ids.size(); ++i) m[label_of(ids[i].first)] += expf(-alpha_ * ids[i].second);
+    scores.assign(m.begin(), m.end());
+  }
+  // one device call for a whole classify RPC (it takes a list of datums)
+  void classify_batch(const std::vector<sfv_t>& fvs, std::vector<classify_result>& out) const {
+    std::vector<neighbor_result> nb;
+    nn_->neighbor_rows(fvs, nb, k_, false);
+    out.resize(fvs.size());
+    for (size_t r = 0; r < fvs.size(); ++r) {
+      std::map<std::string, float> m;
+      for (std::map<std::string, uint64_t>::const_iterator it = labels_.begin(); it != labels_.end(); ++it) m[it->first] = 0.0f;
+      for (size_t i = 0; i < nb[r].size(); ++i) m[label_of(nb[r][i].first)] += expf(-alpha_ * nb[r][i].second);
+      out[r].assign(m.begin(), m.end());
+    }
+  }
+  std::map<std::string, uint64_t> get_labels() const { return labels_; }
+  bool set_label(const std::string& label) { return labels_.insert(std::make_pair(label, static_cast<uint64_t>(0))).second; }
+  // delete_label drops the label and every row trained with it
+  bool delete_label(const std::string& label) {
+    if (labels_.erase(label) == 0) return false;
+    std::vector<std::string> all;
+    nn_->get_all_row_ids(all);
+    for (size_t i = 0; i < all.size(); ++i)
+      if (label_of(all[i]) == label) { nn_->delete_row(all[i]); if (unlearner_) unlearner_->remove(all[i]); }
+    return true;
+  }
+  void clear() { nn_->clear(); labels_.clear(); serial_ = 0; if (unlearner_) unlearner_->clear(); }
+  gpu_nearest_neighbor* engine() { return nn_.get(); }
+  static std::string label_of(const std::string& id) { return id.substr(0, id.rfind('_')); }
+ private:
+  void forget(const std::string& id) {
+    nn_->delete_row(id);
+    std::map<std::string, uint64_t>::iterator it = labels_.find(label_of(id));
+    if (it != labels_.end() && it->second > 0) it->second -= 1;
+  }
+  std::shared_ptr<gpu_nearest_neighbor> nn_;
+  size_t k_;
+  float alpha_;
+  uint64_t serial_;
+  std::shared_ptr<unlearner_base> unlearner_;
+  std::map<std::string, uint64_t> labels_;
+};
+
+// ---------------------------------------------------------------------------------------
 // anomaly::light_lof -- the 1 + reverse_nearest_neighbor_num re-queries of one add() go to the
 // device as ONE batched call (they share the streaming passes)
 // ---------------------------------------------------------------------------------------

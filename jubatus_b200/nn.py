@@ -68,6 +68,11 @@ def _load():
     lib.jubahost_calc_score_datum.argtypes = [_vp, _vp, _vp, ctypes.c_uint64, _vp]
     lib.jubahost_calc_score_id.argtypes = [_vp, ctypes.c_char_p, _vp]
     lib.jubahost_lof_params.argtypes = [_vp, ctypes.c_char_p, _vp, _vp]
+    lib.jubahost_train.argtypes = [_vp, ctypes.c_char_p, _vp, _vp, ctypes.c_uint64, _vp, _vp, ctypes.c_uint64]
+    lib.jubahost_classify.argtypes = [_vp, ctypes.c_uint64, _vp, _vp, _vp, _vp, ctypes.c_uint64]
+    lib.jubahost_get_labels.argtypes = [_vp, _vp, ctypes.c_uint64]
+    lib.jubahost_set_label.argtypes = [_vp, ctypes.c_char_p]
+    lib.jubahost_delete_label.argtypes = [_vp, ctypes.c_char_p]
     lib.jubahost_crc32.restype = ctypes.c_uint32
     lib.jubahost_crc32.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_uint32]
     lib.jubahost_set_storage.argtypes = [_vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int]
@@ -447,3 +452,56 @@ class Anomaly(_HostHandle):
         if self._lib.jubahost_lof_params(self._h, row_id.encode(), ctypes.byref(kd), ctypes.byref(lrd)):
             return None
         return kd.value, lrd.value
+
+
+class Classifier(_HostHandle):
+    """jubaclassifier with method "NN" (config/classifier/nn.json): train / classify / get_labels /
+    set_label / delete_label / clear (classifier.idl:41-80)."""
+    kind = "classifier"
+
+    def train(self, labeled):
+        """labeled: [(label, Datum), ...]; returns the number trained."""
+        for label, d in labeled:
+            sk, sv, ns, nk, nv, n = _datum_args(d)
+            if self._lib.jubahost_train(self._h, label.encode(), sk, sv, ns, nk, nv.ctypes.data_as(_vp), n):
+                _raise()
+        return len(labeled)
+
+    def classify(self, datums):
+        """-> [[(label, score), ...] per datum], labels in sorted order."""
+        offs = np.zeros(len(datums) + 1, dtype=np.uint64)
+        keys, vals = [], []
+        for i, d in enumerate(datums):
+            assert not d.string_values
+            keys.extend(k for k, _ in d.num_values)
+            vals.extend(v for _, v in d.num_values)
+            offs[i + 1] = len(keys)
+        vals = np.array(vals or [0.0], dtype=np.float64)
+        buf = ctypes.create_string_buffer(1 << 22)
+        if self._lib.jubahost_classify(self._h, len(datums), offs.ctypes.data_as(_vp), _cstrs(keys), vals.ctypes.data_as(_vp),
+                                       buf, 1 << 22):
+            _raise()
+        out = []
+        lines = buf.value.decode().split("\n")[:len(datums)]
+        for ln in lines:
+            f = ln.split("\t") if ln else []
+            out.append([(f[i], float(f[i + 1])) for i in range(0, len(f), 2)])
+        return out
+
+    def get_labels(self):
+        buf = ctypes.create_string_buffer(1 << 20)
+        if self._lib.jubahost_get_labels(self._h, buf, 1 << 20):
+            _raise()
+        return {a: int(b) for a, b in (ln.split("\t") for ln in buf.value.decode().split("\n") if ln)}
+
+    def set_label(self, label):
+        r = self._lib.jubahost_set_label(self._h, label.encode())
+        if r < 0:
+            _raise()
+        return bool(r)
+
+    def delete_label(self, label):
+        r = self._lib.jubahost_delete_label(self._h, label.encode())
+        if r < 0:
+            _raise()
+        return bool(r)

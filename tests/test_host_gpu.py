@@ -422,3 +422,52 @@ def test_recommender_and_light_lof_with_unlearner():
         nn.Anomaly(acfg.replace('"lru"', '"nope"'))
     with pytest.raises(nn.JubatusError):
         nn.Anomaly(acfg.replace('{"max_size": 20}', '{"max_size": 0}'))
+
+
+def test_classifier_nn_method():
+    """jubaclassifier method "NN" (config/classifier/nn.json): votes exp(-local_sensitivity * distance)
+    of the nearest_neighbor_num nearest training rows, checked against the same engine queried
+    directly."""
+    import math
+    k, alpha, hash_num = 8, 1.0, 128
+    cfg = json.dumps({"method": "NN", "converter": CONVERTER,
+                      "parameter": {"method": "euclid_lsh", "parameter": {"hash_num": hash_num},
+                                    "nearest_neighbor_num": k, "local_sensitivity": alpha}})
+    clf = nn.Classifier(cfg)
+    eng = nn.NearestNeighbor(config("euclid_lsh", hash_num))
+    ids, vals = w.synth_rows(w.MASTER_SEED, 800, 90, nnz=10, nfeat_log2=7)
+    labels = ["spam", "ham", "eggs"]
+    assert clf.set_label("unused") is True and clf.set_label("unused") is False
+    serial = 0
+    for r in range(80):
+        lab = labels[r % 3]
+        assert clf.train([(lab, datum_of(ids[r], vals[r]))]) == 1
+        eng.set_row("%s_%d" % (lab, serial), datum_of(ids[r], vals[r]))
+        serial += 1
+    assert clf.get_labels() == {"spam": 27, "ham": 27, "eggs": 26, "unused": 0}
+    queries = [datum_of(ids[r], vals[r]) for r in range(80, 90)] + [datum_of(ids[4], vals[4])]
+    got = clf.classify(queries)
+    assert len(got) == len(queries)
+    for d, res in zip(queries, got):
+        want = {"spam": 0.0, "ham": 0.0, "eggs": 0.0, "unused": 0.0}
+        for rid, dist in eng.neighbor_row_from_datum(d, k):
+            want[rid.rsplit("_", 1)[0]] += math.exp(-alpha * dist)
+        assert [lab for lab, _ in res] == sorted(want)              # every known label, label order
+        for lab, score in res:
+            assert abs(score - want[lab]) <= 1e-5 * max(1.0, want[lab]), (lab, score, want[lab])
+    # a stored datum votes for its own label with weight exp(0) = 1 at least
+    own = dict(got[-1])
+    assert own[labels[4 % 3]] >= 1.0 - 1e-6
+    # delete_label removes the label and its rows; clear resets everything
+    assert clf.delete_label("ham") is True and clf.delete_label("ham") is False
+    assert clf.get_labels() == {"spam": 27, "eggs": 26, "unused": 0}
+    assert clf.size() == 53
+    assert all(lab != "ham" for lab, _ in clf.classify(queries[:1])[0])
+    clf.clear()
+    assert clf.get_labels() == {} and clf.size() == 0
+    for bad in ({"method": "AROW"}, {"parameter": {"method": "lsh", "parameter": {"hash_num": 64}, "local_sensitivity": 1}},
+                {"parameter": {"method": "lsh", "parameter": {"hash_num": 64}, "nearest_neighbor_num": 0, "local_sensitivity": 1}}):
+        c = json.loads(cfg)
+        c.update(bad)
+        with pytest.raises(nn.JubatusError):
+            nn.Classifier(json.dumps(c))
