@@ -440,7 +440,7 @@ def run_b200(a):
     if micro.get("popc_only_per_s"):
         roofline["int_frac_of_measured_popc_peak"] = popc32 / micro["popc_only_per_s"]
 
-    # ---- second regime, same table: the library's default of 16 queries per pass, where the scan
+    # ---- second regime, same table: the library's default of 32 queries per pass, where the scan
     # is bound by the popcount pipes instead of HBM (SURVEY 8d asks for both fractions) ----
     throughput_mode = None
     if a.qp:
@@ -466,7 +466,7 @@ def run_b200(a):
                            "hbm_frac": local_rows * row_bytes / (pass_ms * 1e-3) / 1e9 / peak,
                            "int_popc32_per_s": popc2,
                            "int_frac_of_measured_popc_peak": popc2 / micro["popc_only_per_s"] if micro.get("popc_only_per_s") else None,
-                           "note": "algorithmic popcounts (16 per 512-bit pair); the kernel issues 11 after carry-save adders"}
+                           "note": "algorithmic popcounts (16 per 512-bit pair); the kernel issues 9 after carry-save adders"}
         eng.set_option("queries_per_pass", a.qp)
         if a.scan_variant:
             eng.set_option("scan_variant", a.scan_variant)
