@@ -1243,112 +1243,17 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32
   if (threadIdx.x == 0 && o.out_count) o.out_count[q] = s_count;
 }
 
-// Latency path of the list reduction: when all nlists * k candidates of a query fit in shared
-// memory, find the k-th smallest key by a most-significant-bit-first search over the whole set
-// (one block-wide count per bit), then sort only the k survivors.  The streaming variant above
-// sorts 2 * half keys per 256 candidates read, which is what a single small query spent most of
-// its time in.
-static const uint32_t MSEL_MAX_KEYS = 24576;   // 192 KB of keys
-// THREADS: 128 for small candidate sets (block barriers are what a round costs), 1024 otherwise
-template <int MSEL_THREADS>
-__global__ void __launch_bounds__(MSEL_THREADS) merge_select_kernel(const unsigned long long* cand, uint32_t nlists,
-                                                                    uint32_t k, uint32_t kp, MergeOut o) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem);   // [M]
-  unsigned long long* top = keys + (size_t)nlists * k;                       // [kp], kp = pow2 >= k
-  __shared__ uint32_t s_cnt[2];
-  __shared__ uint32_t s_pos;
-  __shared__ unsigned long long s_or, s_and;
-  __shared__ uint32_t s_valid;
-  const int tid = threadIdx.x, lane = tid & 31;
-  const uint32_t q = blockIdx.x;
-  const uint32_t M = nlists * k;
-  const unsigned long long* src = cand + (size_t)q * M;
-  unsigned long long vor = 0, vand = ~0ull;
-  uint32_t valid = 0;
-  for (uint32_t base = 0; base < M; base += 4 * MSEL_THREADS) {   // four loads in flight per thread
-    unsigned long long v[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t i = base + j * MSEL_THREADS + tid;
-      v[j] = i < M ? src[i] : KEY_SENTINEL;
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t i = base + j * MSEL_THREADS + tid;
-      if (i < M) keys[i] = v[j];
-      if (v[j] != KEY_SENTINEL) { vor |= v[j]; vand &= v[j]; ++valid; }
-    }
-  }
-  for (uint32_t i = tid; i < kp; i += MSEL_THREADS) top[i] = KEY_SENTINEL;
-  if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_pos = 0; s_or = 0; s_and = ~0ull; s_valid = 0; }
-#pragma unroll
-  for (int ofs = 16; ofs > 0; ofs >>= 1) {
-    vor |= __shfl_xor_sync(FULL_MASK, vor, ofs);
-    vand &= __shfl_xor_sync(FULL_MASK, vand, ofs);
-  }
-  valid = __reduce_add_sync(FULL_MASK, valid);
-  __syncthreads();
-  if (lane == 0 && valid) { atomicOr(&s_or, vor); atomicAnd(&s_and, vand); atomicAdd(&s_valid, valid); }
-  __syncthreads();
-  const uint32_t nvalid = s_valid;
-  const uint32_t want = min(k, nvalid);
-  unsigned long long kth = KEY_SENTINEL;   // keys <= kth are the answer
-  if (nvalid > k) {
-    // bits on which all keys agree (the unused high bits of the row index, most of the distance)
-    // are the k-th key's too and cost no round
-    const unsigned long long all_or = s_or, all_and = s_and, varying = all_or ^ all_and;
-    unsigned long long prefix = 0;
-    int round = 0;
-    for (int bit = 63 - __clzll((long long)(all_or | 1ull)); bit >= 0; --bit) {
-      if (!((varying >> bit) & 1ull)) { prefix |= all_and & (1ull << bit); continue; }
-      const unsigned long long trial = prefix | (1ull << bit);
-      uint32_t c = 0;
-      for (uint32_t i = tid; i < M; i += MSEL_THREADS) c += (keys[i] < trial) ? 1u : 0u;
-      c = __reduce_add_sync(FULL_MASK, c);
-      if (lane == 0 && c) atomicAdd(&s_cnt[round & 1], c);
-      __syncthreads();
-      const uint32_t total = s_cnt[round & 1];
-      if (total < k) prefix = trial;   // fewer than k keys below trial: the k-th smallest is >= trial
-      __syncthreads();                 // everyone has read the counter ...
-      if (tid == 0) s_cnt[round & 1] = 0;   // ... before it is reused two rounds later
-      ++round;
-    }
-    kth = prefix;
-  }
-  for (uint32_t i = tid; i < M; i += MSEL_THREADS) {
-    const unsigned long long v = keys[i];
-    if (v != KEY_SENTINEL && v <= kth) top[atomicAdd(&s_pos, 1u)] = v;   // exactly `want` keys (keys are distinct)
-  }
-  __syncthreads();
-  block_bitonic_sort(top, kp, tid, MSEL_THREADS);
-  for (uint32_t j = tid; j < want; j += MSEL_THREADS) {
-    const unsigned long long key = top[j];
-    const uint32_t key_hi = (uint32_t)(key >> 32);
-    const uint64_t gidx = (uint64_t)(uint32_t)key * o.shard_count + o.shard_rank;
-    if (o.cand_key) {  // unused slots were pre-filled with sentinels by the host
-      o.cand_key[(size_t)q * o.kout + o.col0 + j] = key_hi;
-      o.cand_index[(size_t)q * o.kout + o.col0 + j] = gidx;
-    }
-    if (o.out_index) {
-      o.out_index[(size_t)q * o.kout + o.col0 + j] = gidx;
-      o.out_score[(size_t)q * o.kout + o.col0 + j] = final_score(key_hi, o, q);
-    }
-  }
-  if (tid == 0) {
-    if (o.out_count) o.out_count[q] = (o.count_accumulate ? o.out_count[q] : 0u) + want;
-    if (o.last_key) o.last_key[q] = want ? top[want - 1] : KEY_SENTINEL;
-  }
-}
-
-// Smallest candidate sets (a single query with a small k: nlists * k <= 128 * KPT): the keys live in
-// registers, a round of the bit search is KPT compares, one warp reduction, one shared atomic
-// and one barrier (three counters in rotation), so the kernel is no longer a chain of
-// shared-memory latencies.
-static const int MSMALL_THREADS = 128;
-template <int KPT>
-__global__ void __launch_bounds__(MSMALL_THREADS) merge_small_kernel(const unsigned long long* cand, uint32_t nlists,
-                                                                     uint32_t k, uint32_t kp, MergeOut o) {
+// List reduction when all nlists * k candidates of a query fit in registers (up to 24576 keys):
+// the k-th smallest key by a most-significant-bit-first search -- a round is KPT compares, one
+// warp reduction, one shared atomic and one barrier (three counters in rotation), and the bits
+// on which all keys agree (unused high bits of the row index, most of the distance) cost no
+// round -- then the k survivors are ordered by counting (each finds its rank among the others)
+// or, for large k, by a bitonic sort.  The streaming variant above sorts 2 * half keys per 256
+// candidates read, which is what a single small query spent most of its time in.
+static const uint32_t MSEL_MAX_KEYS = 24576;
+template <int KPT, int THREADS>
+__global__ void __launch_bounds__(THREADS) merge_small_kernel(const unsigned long long* cand, uint32_t nlists,
+                                                              uint32_t k, uint32_t kp, MergeOut o) {
   extern __shared__ __align__(16) unsigned char smem[];
   unsigned long long* top = reinterpret_cast<unsigned long long*>(smem);   // [kp], kp = pow2 >= k
   __shared__ uint32_t s_cnt[3];
@@ -1361,7 +1266,7 @@ __global__ void __launch_bounds__(MSMALL_THREADS) merge_small_kernel(const unsig
   unsigned long long r[KPT];
 #pragma unroll
   for (int j = 0; j < KPT; ++j) {
-    const uint32_t i = j * MSMALL_THREADS + tid;
+    const uint32_t i = j * THREADS + tid;
     r[j] = i < M ? src[i] : KEY_SENTINEL;
   }
   unsigned long long vor = 0, vand = ~0ull;
@@ -1369,7 +1274,7 @@ __global__ void __launch_bounds__(MSMALL_THREADS) merge_small_kernel(const unsig
 #pragma unroll
   for (int j = 0; j < KPT; ++j)
     if (r[j] != KEY_SENTINEL) { vor |= r[j]; vand &= r[j]; ++valid; }
-  for (uint32_t i = tid; i < kp; i += MSMALL_THREADS) top[i] = KEY_SENTINEL;
+  for (uint32_t i = tid; i < kp; i += THREADS) top[i] = KEY_SENTINEL;
   if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_cnt[2] = 0; s_pos = 0; s_or = 0; s_and = ~0ull; s_valid = 0; }
 #pragma unroll
   for (int ofs = 16; ofs > 0; ofs >>= 1) {
@@ -1407,12 +1312,26 @@ __global__ void __launch_bounds__(MSMALL_THREADS) merge_small_kernel(const unsig
   for (int j = 0; j < KPT; ++j)
     if (r[j] != KEY_SENTINEL && r[j] <= kth) top[atomicAdd(&s_pos, 1u)] = r[j];   // exactly `want` keys
   __syncthreads();
-  block_bitonic_sort(top, kp, tid, MSMALL_THREADS);
-  for (uint32_t j = tid; j < want; j += MSMALL_THREADS) {
-    const unsigned long long key = top[j];
+  unsigned long long* sorted = top;
+  if (kp <= 512) {
+    // order by counting: keys are distinct, so the number of smaller survivors is the position
+    unsigned long long* ord = top + kp;
+    for (uint32_t i = tid; i < want; i += THREADS) {
+      const unsigned long long v = top[i];
+      uint32_t rank = 0;
+      for (uint32_t j = 0; j < want; ++j) rank += (top[j] < v) ? 1u : 0u;
+      ord[rank] = v;
+    }
+    __syncthreads();
+    sorted = ord;
+  } else {
+    block_bitonic_sort(top, kp, tid, THREADS);
+  }
+  for (uint32_t j = tid; j < want; j += THREADS) {
+    const unsigned long long key = sorted[j];
     const uint32_t key_hi = (uint32_t)(key >> 32);
     const uint64_t gidx = (uint64_t)(uint32_t)key * o.shard_count + o.shard_rank;
-    if (o.cand_key) {
+    if (o.cand_key) {  // unused slots were pre-filled with sentinels by the host
       o.cand_key[(size_t)q * o.kout + o.col0 + j] = key_hi;
       o.cand_index[(size_t)q * o.kout + o.col0 + j] = gidx;
     }
@@ -1423,59 +1342,19 @@ __global__ void __launch_bounds__(MSMALL_THREADS) merge_small_kernel(const unsig
   }
   if (tid == 0) {
     if (o.out_count) o.out_count[q] = (o.count_accumulate ? o.out_count[q] : 0u) + want;
-    if (o.last_key) o.last_key[q] = want ? top[want - 1] : KEY_SENTINEL;
+    if (o.last_key) o.last_key[q] = want ? sorted[want - 1] : KEY_SENTINEL;
   }
 }
+
 
 // ---------------------------------------------------------------------------
 // sample pre-pass: an admissible-key bound per query before the scan starts.
 // One CTA per query ranks the first S rows and takes the k-th smallest ordering key t;
 // at least k rows have key_hi <= t, so every top-k key is below (t + 1) << 32.  Starting the
 // scan with this bound removes the warm-up in which every row of a CTA's first tiles is a
-// candidate and all warps queue on the list lock.
+// candidate and all warps queue on the list lock.  (tau_init_hamming_kernel and
+// tau_init_euclid_kernel, further down next to their launch site.)
 // ---------------------------------------------------------------------------
-static const int TAU_THREADS = 256;
-
-template <bool EUCLID>
-__global__ void __launch_bounds__(TAU_THREADS) tau_init_kernel(ScanArgs a, uint32_t S, uint32_t SP,
-                                                               unsigned long long* tau_out) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  uint32_t* keys = reinterpret_cast<uint32_t*>(smem);
-  const uint32_t q = blockIdx.x;
-  const uint32_t* qw = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)q * a.w64);
-  for (uint32_t i = threadIdx.x; i < SP; i += TAU_THREADS) {
-    uint32_t key = 0xFFFFFFFFu;
-    if (i < S) {
-      uint32_t d = 0;
-      for (uint32_t w = 0; w < 2 * a.w64; ++w)
-        d += __popc(*reinterpret_cast<const uint32_t*>(a.slab + word_offset(a.w32, i, w)) ^ qw[w]);
-      key = d;
-      if (EUCLID) {
-        const double ni = (double)a.norms[i];
-        const double l2 = __dmul_rn((double)(2.0f * a.qnorms[q]), a.coslut[d]);
-        key = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l2))));
-      }
-    }
-    keys[i] = key;
-  }
-  __syncthreads();
-  for (uint32_t size = 2; size <= SP; size <<= 1) {
-    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
-      for (uint32_t i = threadIdx.x; i < (SP >> 1); i += TAU_THREADS) {
-        uint32_t lo = ((i & ~(stride - 1)) << 1) | (i & (stride - 1));
-        uint32_t hi = lo | stride;
-        bool asc = ((lo & size) == 0);
-        uint32_t x = keys[lo], y = keys[hi];
-        if ((x > y) == asc && x != y) { keys[lo] = y; keys[hi] = x; }
-      }
-      __syncthreads();
-    }
-  }
-  if (threadIdx.x == 0) {
-    const uint32_t t = (a.k <= S) ? keys[a.k - 1] : 0xFFFFFFFFu;
-    tau_out[q] = (t == 0xFFFFFFFFu) ? KEY_SENTINEL : (((unsigned long long)t + 1ull) << 32);
-  }
-}
 
 // ---------------------------------------------------------------------------
 // host side
@@ -1667,6 +1546,80 @@ __global__ void __launch_bounds__(TAUH_THREADS) tau_init_hamming_kernel(ScanArgs
   }
 }
 
+// euclid_lsh: the sample's k-th smallest score key by an MSB-first bit search over keys held in
+// registers (one barrier per varying bit) instead of a bitonic sort of the whole sample.
+static const int TAUE_THREADS = 512, TAUE_KPT = 16;   // up to 8192 sample rows
+__global__ void __launch_bounds__(TAUE_THREADS) tau_init_euclid_kernel(ScanArgs a, uint32_t S, unsigned long long* tau_out) {
+  __shared__ uint32_t sq[32];
+  __shared__ uint32_t s_cnt[3];
+  __shared__ uint32_t s_or, s_and;
+  const uint32_t q = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (tid < 32) {
+    const uint32_t* qw = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)q * a.w64);
+    sq[tid] = (uint32_t)tid < 2 * a.w64 ? qw[tid] : 0u;
+  }
+  if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_cnt[2] = 0; s_or = 0; s_and = 0xFFFFFFFFu; }
+  __syncthreads();
+  const double two_nq = (double)(2.0f * a.qnorms[q]);
+  uint32_t r[TAUE_KPT];
+  uint32_t vor = 0, vand = 0xFFFFFFFFu;
+#pragma unroll
+  for (int j = 0; j < TAUE_KPT; ++j) {
+    const uint32_t i = j * TAUE_THREADS + tid;
+    uint32_t key = 0xFFFFFFFFu;
+    if (i < S) {
+      uint32_t d = 0;
+      if (a.w32 == 2) {
+        const uint2 v = *reinterpret_cast<const uint2*>(a.slab + (size_t)i * 8);
+        d = __popc(v.x ^ sq[0]) + __popc(v.y ^ sq[1]);
+      } else {
+        const uint32_t C = a.w32 >> 2;
+        const unsigned char* base = a.slab + ((size_t)(i >> 5) * C * 32 + (i & 31)) * 16;
+        uint4 v[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          if ((uint32_t)c < C) v[c] = *reinterpret_cast<const uint4*>(base + (size_t)c * 512);
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          if ((uint32_t)c < C)
+            d += __popc(v[c].x ^ sq[4 * c]) + __popc(v[c].y ^ sq[4 * c + 1]) + __popc(v[c].z ^ sq[4 * c + 2]) +
+                 __popc(v[c].w ^ sq[4 * c + 3]);
+      }
+      const double ni = (double)a.norms[i];
+      const double l2 = __dmul_rn(two_nq, a.coslut[d]);
+      key = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l2))));
+      vor |= key; vand &= key;
+    }
+    r[j] = key;
+  }
+  vor = __reduce_or_sync(FULL_MASK, vor);
+  vand = __reduce_and_sync(FULL_MASK, vand);
+  if (lane == 0) { atomicOr(&s_or, vor); atomicAnd(&s_and, vand); }
+  __syncthreads();
+  uint32_t t = 0xFFFFFFFFu;
+  if (a.k <= S) {
+    const uint32_t all_or = s_or, all_and = s_and, varying = all_or ^ all_and;
+    uint32_t prefix = 0, round = 0;
+    for (int bit = 31; bit >= 0; --bit) {
+      if (!((varying >> bit) & 1u)) { prefix |= all_and & (1u << bit); continue; }
+      const uint32_t trial = prefix | (1u << bit);
+      uint32_t c = 0;
+#pragma unroll
+      for (int j = 0; j < TAUE_KPT; ++j) c += (r[j] < trial) ? 1u : 0u;   // the padding keys (all ones) never count
+      c = __reduce_add_sync(FULL_MASK, c);
+      const uint32_t slot = round % 3u;
+      if (lane == 0 && c) atomicAdd(&s_cnt[slot], c);
+      if (tid == 0) s_cnt[(round + 1u) % 3u] = 0;
+      __syncthreads();
+      if (s_cnt[slot] < a.k) prefix = trial;
+      ++round;
+    }
+    t = prefix;   // the k-th smallest key of the sample
+  }
+  if (tid == 0) tau_out[q] = (t == 0xFFFFFFFFu) ? KEY_SENTINEL : (((unsigned long long)t + 1ull) << 32);
+}
+
 template <bool EUCLID>
 static cudaError_t launch_scan_w(uint32_t w32, const ScanArgs& a, const ScanConfig& cfg, dim3 grid,
                                  cudaStream_t s) {
@@ -1705,18 +1658,14 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   if (d_tau_scratch && !d_floor_keys) {
     uint64_t S = std::max<uint64_t>(2048, 4ull * k);
     if (S > 8192) S = 8192;
-    // counting a sample is cheap for the hamming engines: take the largest one the table allows
-    if (!euclid && t.local_rows >= 16 * 8192) S = 8192;
+    // ranking a sample is cheap (counting / bit search): take the largest one the table allows
+    if (t.local_rows >= 16 * 8192) S = 8192;
     // small tables: a quarter of the rows at most (without any bound a CTA's first rows all go
     // through the list, which is what a query on a 10^4-row table spent its time in)
     while (S > 256 && t.local_rows < 4 * S) S >>= 1;
     if (t.local_rows >= 4 * S && k <= S) {
       if (euclid) {
-        uint32_t SP = 1;
-        while (SP < S) SP <<= 1;
-        ScanArgs b = a;
-        b.ghist = nullptr;
-        tau_init_kernel<true><<<nq, TAU_THREADS, SP * 4, s>>>(b, (uint32_t)S, SP, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+        tau_init_euclid_kernel<<<nq, TAUE_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
       } else {
         tau_init_hamming_kernel<<<nq, TAUH_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
         hist_cleared = use_hist;
@@ -1737,24 +1686,19 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
 
 cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nlists, uint32_t k,
                                const MergeOut& out, cudaStream_t s) {
-  if ((uint64_t)nlists * k <= MSEL_MAX_KEYS) {
+  const uint64_t M = (uint64_t)nlists * k;
+  if (M <= MSEL_MAX_KEYS) {
     uint32_t kp = 32;
     while (kp < k) kp <<= 1;
-    const size_t smem_sel = ((size_t)nlists * k + kp) * 8;
-    if (smem_sel <= 220 * 1024) {
-      const uint64_t M = (uint64_t)nlists * k;
-      if (M <= 128u * 32u && kp <= 1024) {
-        const size_t sm = (size_t)kp * 8;
-        if (M <= 128u * 4u) merge_small_kernel<4><<<nq, MSMALL_THREADS, sm, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
-        else if (M <= 128u * 16u) merge_small_kernel<16><<<nq, MSMALL_THREADS, sm, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
-        else merge_small_kernel<32><<<nq, MSMALL_THREADS, sm, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
-        return cudaGetLastError();
-      }
-      cudaError_t e = cudaFuncSetAttribute(merge_select_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sel);
-      if (e != cudaSuccess) return e;
-      merge_select_kernel<1024><<<nq, 1024, smem_sel, s>>>(reinterpret_cast<const unsigned long long*>(d_cand), nlists, k, kp, out);
-      return cudaGetLastError();
-    }
+    const size_t sm = (size_t)kp * 8 * (kp <= 512 ? 2 : 1);
+    const unsigned long long* c = reinterpret_cast<const unsigned long long*>(d_cand);
+    if (M <= 128u * 4u) merge_small_kernel<4, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out);
+    else if (M <= 128u * 16u) merge_small_kernel<16, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out);
+    else if (M <= 128u * 32u) merge_small_kernel<32, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out);
+    else if (M <= 1024u * 8u) merge_small_kernel<8, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out);
+    else if (M <= 1024u * 16u) merge_small_kernel<16, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out);
+    else merge_small_kernel<24, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out);
+    return cudaGetLastError();
   }
   uint32_t half = 2 * MERGE_THREADS;
   while (half < k) half <<= 1;
