@@ -1548,7 +1548,7 @@ __global__ void __launch_bounds__(TAUH_THREADS) tau_init_hamming_kernel(ScanArgs
 
 // euclid_lsh: the sample's k-th smallest score key by an MSB-first bit search over keys held in
 // registers (one barrier per varying bit) instead of a bitonic sort of the whole sample.
-static const int TAUE_THREADS = 512, TAUE_KPT = 16;   // up to 8192 sample rows
+static const int TAUE_THREADS = 1024, TAUE_KPT = 8;   // up to 8192 sample rows
 __global__ void __launch_bounds__(TAUE_THREADS) tau_init_euclid_kernel(ScanArgs a, uint32_t S, unsigned long long* tau_out) {
   __shared__ uint32_t sq[32];
   __shared__ uint32_t s_cnt[3];
