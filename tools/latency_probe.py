@@ -1,5 +1,5 @@
 """Per-call latency of the C-ABI entry points for one query / one row at a time (development
-measurement, not the bench): python tools/latency_probe.py [rows] [hash_num]"""
+measurement, not the bench): python tools/latency_probe.py [rows] [hash_num] [scan_variant] [method]"""
 import os
 import sys
 import time
@@ -12,33 +12,38 @@ from jubatus_b200 import Engine, workload as w  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 h = int(sys.argv[2]) if len(sys.argv) > 2 else 256
-print("table: %d rows x %d bits (lsh), k=10" % (n, h))
+method = sys.argv[4] if len(sys.argv) > 4 else "lsh"
+euclid = method == "euclid_lsh"
+print("table: %d rows x %d bits (%s), k=10" % (n, h, method))
 opts = {"scan_variant": int(sys.argv[3])} if len(sys.argv) > 3 else {}
-e = Engine("lsh", h, **opts)
+e = Engine(method, h, **opts)
 sig = w.random_signatures(1, n, h // 64)
-e.set_rows_sig(np.arange(n), sig, None)
+norms = (np.random.RandomState(1).rand(n) * 3 + 0.5).astype(np.float32) if euclid else None
+e.set_rows_sig(np.arange(n), sig, norms)
 q = w.random_signatures(2, 1, h // 64)
+qn = np.array([1.3], dtype=np.float32) if euclid else None
 def t(f, reps=300):
     for _ in range(20): f()
     t0 = time.perf_counter()
     for _ in range(reps): f()
     return (time.perf_counter() - t0) / reps * 1e6
-print("query_sig host 1 query, k=10: %.1f us" % t(lambda: e.query_sig(q, None, 10)))
+print("query_sig host 1 query, k=10: %.1f us" % t(lambda: e.query_sig(q, qn, 10)))
 ft = w.feature_tables()
 ids, vals = w.synth_rows(w.MASTER_SEED, 5, 1, nnz=100, nfeat_log2=20)
 csr = w.to_csr(ids, vals, *ft)
 print("query_csr host 1 query: %.1f us" % t(lambda: e.query_csr(*csr, 10)))
 st = e.stats(); print(st)
 e.stats_reset(True)
-for _ in range(100): e.query_sig(q, None, 10)
+for _ in range(100): e.query_sig(q, qn, 10)
 st = e.stats(); print("scan ms per query", st["scan_ms"]/100, st)
 # device-resident variant
 dev = torch.device("cuda:0")
 qd = torch.from_numpy(q.view(np.int64)).to(dev)
+qnd = torch.from_numpy(qn).to(dev).data_ptr() if euclid else 0
 oi = torch.zeros((1, 10), dtype=torch.int64, device=dev); os_ = torch.zeros((1, 10), dtype=torch.float32, device=dev); oc = torch.zeros(1, dtype=torch.int32, device=dev)
 s = torch.cuda.current_stream().cuda_stream
 def f():
-    e.query_sig_dev(1, qd.data_ptr(), 0, 10, 0, oi.data_ptr(), os_.data_ptr(), oc.data_ptr(), s); torch.cuda.synchronize()
+    e.query_sig_dev(1, qd.data_ptr(), qnd, 10, 0, oi.data_ptr(), os_.data_ptr(), oc.data_ptr(), s); torch.cuda.synchronize()
 print("query_sig_dev + sync: %.1f us" % t(f))
 # GPU-side span of one call (events on the launching stream)
 def span(k):
@@ -48,7 +53,7 @@ def span(k):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         e0.record()
-        e.query_sig_dev(1, qd.data_ptr(), 0, k, 0, oi.data_ptr(), os2.data_ptr(), oc.data_ptr(), s)
+        e.query_sig_dev(1, qd.data_ptr(), qnd, k, 0, oi.data_ptr(), os2.data_ptr(), oc.data_ptr(), s)
         e1.record()
         torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1) * 1e3)
