@@ -220,6 +220,54 @@ __device__ __forceinline__ uint32_t hamming(const uint32_t (&r)[W32], const uint
   return hamming_rq<W32, PV>(r, q);
 }
 
+// Hamming distance with the XORs of the first-level adder triples hoisted out of the pair loop.
+// For a triple (x0, x1, x2), x_i = r_i ^ q_i, the adder's sum is (r0^r1^r2) ^ (q0^q1^q2): the two
+// halves are computed once per row and once per query, so the sum costs one LOP3; with x0 and x1
+// materialised the carry is a function of (x0, x1, sum) alone (x2 = sum ^ x0 ^ x1): four LOP3
+// per adder instead of five, 25 instead of 30 per 512-bit pair.  The ALU pipe is what binds
+// when many queries share a pass (80 % busy in the ncu capture of the 32-query kernel).
+// sq: the query block [W32 words | tau | pad3 | per 16-word block: 5 triples, pad3]
+#ifndef JBN_TRIPLES
+#define JBN_TRIPLES 1
+#endif
+template <int W32>
+__device__ __forceinline__ void row_triples(const uint32_t (&r)[W32], uint32_t (&rt)[(W32 / 16) * 5]) {
+#pragma unroll
+  for (int b = 0; b < W32 / 16; ++b)
+#pragma unroll
+    for (int g = 0; g < 5; ++g) rt[5 * b + g] = r[16 * b + 3 * g] ^ r[16 * b + 3 * g + 1] ^ r[16 * b + 3 * g + 2];
+}
+template <int W32>
+__device__ __forceinline__ uint32_t hamming_t(const uint32_t (&r)[W32], const uint32_t (&rt)[(W32 / 16) * 5],
+                                              const uint32_t* sq) {
+  uint32_t q[W32];
+  load_query<W32>(sq, q);
+  uint32_t d = 0;
+#pragma unroll
+  for (int b = 0; b < W32 / 16; ++b) {
+    const uint4 qa = *reinterpret_cast<const uint4*>(sq + W32 + 4 + 8 * b);
+    const uint32_t q4 = sq[W32 + 4 + 8 * b + 4];
+    const uint32_t qt[5] = {qa.x, qa.y, qa.z, qa.w, q4};
+    uint32_t o[7], t[7];
+#pragma unroll
+    for (int g = 0; g < 5; ++g) {
+      const uint32_t sum = rt[5 * b + g] ^ qt[g];
+      const uint32_t x0 = r[16 * b + 3 * g] ^ q[16 * b + 3 * g];
+      const uint32_t x1 = r[16 * b + 3 * g + 1] ^ q[16 * b + 3 * g + 1];
+      uint32_t carry;   // majority(x0, x1, sum ^ x0 ^ x1)
+      asm("lop3.b32 %0, %1, %2, %3, 0xD4;" : "=r"(carry) : "r"(x0), "r"(x1), "r"(sum));
+      o[g] = sum; t[g] = carry;
+    }
+    const uint32_t x15 = r[16 * b + 15] ^ q[16 * b + 15];
+    CSA(t[5], o[5], o[0], o[1], o[2]);
+    CSA(t[6], o[6], o[3], o[4], x15);
+    const uint32_t ones = __popc(o[5]) + __popc(o[6]);
+    const uint32_t twos = __popc(t[0]) + __popc(t[1]) + __popc(t[2]) + __popc(t[3]) + __popc(t[4]) + __popc(t[5]) + __popc(t[6]);
+    d += ones + 2 * twos;
+  }
+  return d;
+}
+
 // order-preserving image of a float (no NaN expected); -0 is folded into +0 first so that
 // equal scores tie exactly like operator< on float does in the reference heap
 __device__ __forceinline__ uint32_t float_key(float f) {
@@ -636,7 +684,9 @@ static const uint32_t STASH_FLUSH_AT = 16;
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 // a query's shared-memory block: W32 signature words, then the fast-reject threshold word
 // (tau_hi), padded to 16 bytes -- one base address serves the whole inner loop
-__host__ __device__ inline uint32_t q_stride(uint32_t w32) { return w32 + 4; }
+// ... then, for rows of 512 bits and more, the XOR of each of the query's first-level adder
+// triples (5 words per 16-word block, padded to 8): see hamming_t
+__host__ __device__ constexpr uint32_t q_stride(uint32_t w32) { return w32 + 4 + (w32 >= 16 ? (w32 / 16) * 8 : 0); }
 
 // per-warp stash of candidates whose list insertion is deferred until the warp has released
 // the stage it was reading (so a slow insertion never holds up the memory pipeline)
@@ -671,14 +721,24 @@ template <int W32, bool EUCLID, int PV>
 __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t row, float ni, uint32_t nqp,
                                           const uint32_t* s_q, const float* s_bnd, uint32_t hash_num,
                                           const ListCtl& L, int lane) {
-  constexpr uint32_t QS = W32 + 4;
+  constexpr uint32_t QS = q_stride(W32);
+  constexpr bool TRIPLES = JBN_TRIPLES && W32 >= 16 && PV == 3;
+  constexpr int NT = W32 >= 16 ? (W32 / 16) * 5 : 1;
   const int warp = threadIdx.x >> 5;
+  uint32_t rt[NT];
+  if constexpr (TRIPLES) row_triples<W32>(cur, rt);
   uint32_t q = 0;
   for (; q + 2 <= nqp; q += 2) {  // two independent distance chains in flight
     const uint32_t* b0 = s_q + q * QS;
     const uint32_t* b1 = b0 + QS;
-    const uint32_t d0 = hamming<W32, PV>(cur, b0);
-    const uint32_t d1 = hamming<W32, PV>(cur, b1);
+    uint32_t d0, d1;
+    if constexpr (TRIPLES) {
+      d0 = hamming_t<W32>(cur, rt, b0);
+      d1 = hamming_t<W32>(cur, rt, b1);
+    } else {
+      d0 = hamming<W32, PV>(cur, b0);
+      d1 = hamming<W32, PV>(cur, b1);
+    }
     if (EUCLID) {
       const bool c0 = norm_inside(ni, s_bnd[q * (hash_num + 1) + d0]);
       const bool c1 = norm_inside(ni, s_bnd[(q + 1) * (hash_num + 1) + d1]);
@@ -697,7 +757,8 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
   }
   if (q < nqp) {
     const uint32_t* b0 = s_q + q * QS;
-    const uint32_t d0 = hamming<W32, PV>(cur, b0);
+    uint32_t d0;
+    if constexpr (TRIPLES) d0 = hamming_t<W32>(cur, rt, b0); else d0 = hamming<W32, PV>(cur, b0);
     if (EUCLID) {
       const bool c0 = norm_inside(ni, s_bnd[q * (hash_num + 1) + d0]);
       if (__any_sync(FULL_MASK, c0)) euclid_offer(q, d0, ni, row, c0, warp, lane);
@@ -714,7 +775,7 @@ template <int W32, bool EUCLID, int PV>
 __device__ __forceinline__ void rank_tile2(const uint32_t (&ra)[W32], const uint32_t (&rb)[W32], uint32_t rowa,
                                            uint32_t rowb, float nia, float nib, uint32_t nqp, const uint32_t* s_q,
                                            const float* s_bnd, uint32_t hash_num, const ListCtl& L, int lane) {
-  constexpr uint32_t QS = W32 + 4;
+  constexpr uint32_t QS = q_stride(W32);
   const int warp = threadIdx.x >> 5;
   const uint32_t* b0 = s_q;
 #pragma unroll 2
@@ -780,7 +841,7 @@ template <int W32, bool EUCLID>
 __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* smem, const SmemPlan& sp, ListCtl& L,
                                               uint32_t*& s_q, float*& s_bnd, uint32_t q0, uint32_t nqp, int tid,
                                               int nthreads) {
-  constexpr uint32_t QS = W32 + 4;
+  constexpr uint32_t QS = q_stride(W32);
   s_q = reinterpret_cast<uint32_t*>(smem + sp.q_off);
   s_bnd = reinterpret_cast<float*>(smem + sp.lut_off);
   L.list_off = (uint32_t)sp.list_off; L.tau_off = (uint32_t)sp.tau_off; L.floor_off = (uint32_t)sp.floor_off;
@@ -798,7 +859,21 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
   for (uint32_t i = tid; i < nqp * QS; i += nthreads) {
     uint32_t q = i / QS, w = i % QS;
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)(q0 + q) * a.w64);
-    s_q[i] = (w < W32) ? ((w < 2 * a.w64) ? src[w] : 0u) : tau_hi_of(a.tau_init ? a.tau_init[q0 + q] : KEY_SENTINEL);
+    uint32_t v;
+    if (w < W32) {
+      v = (w < 2 * a.w64) ? src[w] : 0u;
+    } else if (w < W32 + 4) {
+      v = tau_hi_of(a.tau_init ? a.tau_init[q0 + q] : KEY_SENTINEL);   // word W32; the pad words carry the same
+    } else {   // XOR of the adder triple g of 16-word block b (hamming_t)
+      const uint32_t b = (w - W32 - 4) / 8, g = (w - W32 - 4) % 8;
+      v = 0u;
+      if (g < 5)
+        for (uint32_t j = 0; j < 3; ++j) {
+          const uint32_t ww = 16 * b + 3 * g + j;
+          if (ww < 2 * a.w64) v ^= src[ww];
+        }
+    }
+    s_q[i] = v;
   }
   if (EUCLID) {
     const uint32_t hn = a.hash_num + 1;
@@ -820,7 +895,11 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
 // variant 1: rows streamed with coalesced 128-bit LDG, one tile prefetched per warp
 // ---------------------------------------------------------------------------
 template <int W32, bool EUCLID, int PV>
-__global__ void __launch_bounds__(SCAN_THREADS, 2) scan_ldg_kernel(ScanArgs a) {
+// rows of 512 bits and more: one CTA per SM with 128 registers per thread (the row, its
+// prefetched successor, the adder triples and two queries fit without spilling: +16 % at 32
+// queries per pass, +17..42 % on 1024-bit rows); shorter rows: two CTAs per SM at 64 registers
+// (measured 13..33 % faster there than one)
+__global__ void __launch_bounds__(SCAN_THREADS, W32 >= 16 ? 1 : 2) scan_ldg_kernel(ScanArgs a) {
   unsigned char* smem = g_smem;
   const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1018,7 +1097,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
     uint32_t s = 0, ph = 0;
     uint64_t t0 = t_first;
     constexpr int NQR = NQ > 0 ? NQ : 1;
-    constexpr uint32_t QS = W32 + 4;
+    constexpr uint32_t QS = q_stride(W32);
     uint32_t qreg[NQR][W32];
     if (NQ > 0) {
 #pragma unroll
