@@ -1470,9 +1470,10 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
   if (qp > nq) qp = nq;
   if (qp < 1) qp = 1;
   // automatic variant: the TMA ring wins while the pass is memory-bound, the LDG kernel's
-  // 32 resident warps win once it is popcount-bound (measured crossover between 4 and 8 queries per pass)
+  // leaner inner loop wins once it is popcount-bound (measured crossover at 3-4 queries per pass)
   // (a table that cannot give every SM a stage or two is not worth the ring's set-up either)
-  cfg->variant = variant <= 0 ? ((qp <= 4 && ntiles >= (uint64_t)num_sms * 32) ? 2 : 1) : variant;
+  const uint32_t tma_max_qp = t.w32 >= 16 ? 3 : 4;   // 512-bit rows: the LDG kernel is ahead from 4 queries per pass on
+  cfg->variant = variant <= 0 ? ((qp <= tma_max_qp && ntiles >= (uint64_t)num_sms * 32) ? 2 : 1) : variant;
   cfg->stages = 0; cfg->tiles_per_warp = 0;
   cfg->interleave = interleave ? 1u : 0u;
   uint64_t max_chunks;
