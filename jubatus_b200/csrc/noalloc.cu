@@ -25,8 +25,9 @@
 //  * All calls on a device share the one array, and it keeps whatever the last call left in
 //    it.  The candidate slots need no clearing (every slot the merge kernel reads is written
 //    by the scan kernel of the same call); the part that must start from a known state -- the
-//    distance histogram and bound words the CTAs share -- is reset on the stream
-//    (cudaMemsetAsync) at the start of every call.  Two calls whose GPU work
+//    distance histogram and bound words the CTAs share -- is reset on the stream at the start
+//    of every call (by the sample pre-pass kernel, or by cudaMemsetAsync when that kernel does
+//    not run).  Two calls whose GPU work
 //    overlaps (different streams, different handles or threads) would overwrite each other's
 //    candidates -- run them on one stream or order them yourself.
 //  * Inputs and outputs are the caller's device buffers, exactly as for
