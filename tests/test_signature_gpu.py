@@ -194,3 +194,41 @@ def test_device_resident_csr_entry_points(feature_tables, method, hash_num):
         stored, snorm = e.get_rows_sig(np.arange(n))
         assert e.size() == (n, n)
         assert np.array_equal(stored, want) and np.array_equal(snorm, wnorm)
+
+
+@pytest.mark.parametrize("method,hash_num", [("lsh", 512), ("euclid_lsh", 256), ("minhash", 128), ("lsh", 64)])
+def test_small_request_path_equals_batch_path(feature_tables, method, hash_num):
+    """Requests under 1 MiB are staged in one copy and hashed without reading the cache counters
+    back; larger ones take the chunked path.  Same rows, same signatures, same answers; rows with
+    no features and empty requests included."""
+    from jubatus_b200 import Engine
+    s32, k64 = feature_tables
+    n_big = 6000                                   # 6000 x 100 features: > 1 MiB of CSR
+    ids, vals = w.synth_rows(w.MASTER_SEED, 4242, n_big)
+    indptr, seed32, keyhash, v = w.to_csr(ids, vals, s32, k64)
+    # rows 1 and 4 of the small request have no features at all
+    nnz = np.array([100, 0, 100, 37, 0, 100], dtype=np.uint64)
+    sip = np.concatenate([[0], np.cumsum(nnz)]).astype(np.uint64)
+    pick = np.concatenate([np.arange(r * 100, r * 100 + int(c)) for r, c in enumerate(nnz)]).astype(np.int64)
+    s_seed, s_key, s_val = seed32[pick], keyhash[pick], v[pick]
+    with Engine(method, hash_num) as big, Engine(method, hash_num) as small:
+        # the same six rows, once inside a large batch (rows 0..5 rebuilt with the ragged lengths)
+        rag_ip = np.concatenate([sip, sip[-1] + np.arange(1, n_big - 6 + 1, dtype=np.uint64) * np.uint64(100)])
+        rag_pick = np.concatenate([pick, np.arange(600, n_big * 100)])
+        big.set_rows_csr(np.arange(n_big, dtype=np.uint64), rag_ip, seed32[rag_pick], keyhash[rag_pick], v[rag_pick])
+        small.set_rows_csr(np.arange(6, dtype=np.uint64), sip, s_seed, s_key, s_val)
+        bs, bn = big.get_rows_sig(np.arange(6, dtype=np.uint64))
+        ss, sn = small.get_rows_sig(np.arange(6, dtype=np.uint64))
+        assert np.array_equal(bs, ss) and np.array_equal(bn.view(np.uint32), sn.view(np.uint32))
+        if method != "minhash":
+            assert not ss[1].any() and not ss[4].any()          # empty sfv -> all-zero signature
+        # queries: six datums through the small path against the whole batch through the large one
+        k = 5
+        got_small = big.query_csr(sip, s_seed, s_key, s_val, k)
+        q_ip = rag_ip[:n_big + 1]
+        got_big = big.query_csr(q_ip, seed32[rag_pick], keyhash[rag_pick], v[rag_pick], k)
+        for a, b in zip(got_small, got_big):
+            assert np.array_equal(np.asarray(a)[:6], np.asarray(b)[:6])
+        # an empty request is fine on both paths
+        e0 = small.query_csr(np.zeros(1, dtype=np.uint64), s_seed[:0], s_key[:0], s_val[:0], k)
+        assert len(e0[2]) == 0
