@@ -895,6 +895,9 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
 // variant 1: rows streamed with coalesced 128-bit LDG, one tile prefetched per warp
 // ---------------------------------------------------------------------------
 template <int W32, bool EUCLID, int PV>
+#ifndef JBN_V1_PAIR
+#define JBN_V1_PAIR 1
+#endif
 // rows of 512 bits and more: one CTA per SM with 128 registers per thread (the row, its
 // prefetched successor, the adder triples and two queries fit without spilling: +16 % at 32
 // queries per pass, +17..42 % on 1024-bit rows); shorter rows: two CTAs per SM at 64 registers
@@ -911,20 +914,60 @@ __global__ void __launch_bounds__(SCAN_THREADS, W32 >= 16 ? 1 : 2) scan_ldg_kern
   scan_prologue<W32, EUCLID>(a, smem, sp, L, s_q, s_bnd, q0, nqp, tid, SCAN_THREADS);
   __syncthreads();
 
+  // rows of <= 128 bits: a warp takes two adjacent tiles per step, so that every query word
+  // fetched from shared memory serves two rows (+6..11 % measured; at 256 bits the second row
+  // costs more in spilled registers than it saves)
+  constexpr bool PAIR = JBN_V1_PAIR && W32 <= 4;
+  constexpr uint64_t TPS = PAIR ? 2 : 1;   // tiles per warp and step
   uint64_t t, t_end, t_step;
   if (a.interleave) {
-    t = (uint64_t)blockIdx.x * SCAN_WARPS + warp;
+    t = ((uint64_t)blockIdx.x * SCAN_WARPS + warp) * TPS;
     t_end = a.ntiles;
-    t_step = (uint64_t)gridDim.x * SCAN_WARPS;
+    t_step = (uint64_t)gridDim.x * SCAN_WARPS * TPS;
   } else {
     const uint64_t t_begin = (uint64_t)blockIdx.x * a.tiles_per_chunk;
-    t = t_begin + warp;
+    t = t_begin + warp * TPS;
     t_end = min(a.ntiles, t_begin + (uint64_t)a.tiles_per_chunk);
-    t_step = SCAN_WARPS;
+    t_step = SCAN_WARPS * TPS;
   }
+  uint32_t poll_tick = 0;
+  if constexpr (PAIR) {
+    uint32_t ca[W32], cb[W32], na[W32], nb[W32];
+    float fa = 0.0f, fb = 0.0f, ga = 0.0f, gb = 0.0f;
+#pragma unroll
+    for (int w = 0; w < W32; ++w) { cb[w] = 0u; nb[w] = 0u; }
+    if (t < t_end) {
+      load_row<W32>(a.slab, t, lane, ca);
+      if (EUCLID) fa = ld_stream_f32(a.norms + t * 32 + lane);
+      if (t + 1 < t_end) {
+        load_row<W32>(a.slab, t + 1, lane, cb);
+        if (EUCLID) fb = ld_stream_f32(a.norms + (t + 1) * 32 + lane);
+      }
+    }
+    for (; t < t_end; t += t_step) {
+      const uint64_t tn = t + t_step;
+      if (tn < t_end) {
+        load_row<W32>(a.slab, tn, lane, na);
+        if (EUCLID) ga = ld_stream_f32(a.norms + tn * 32 + lane);
+        if (tn + 1 < t_end) {
+          load_row<W32>(a.slab, tn + 1, lane, nb);
+          if (EUCLID) gb = ld_stream_f32(a.norms + (tn + 1) * 32 + lane);
+        }
+      }
+      if (t + 1 < t_end)
+        rank_tile2<W32, EUCLID, PV>(ca, cb, (uint32_t)(t * 32 + lane), (uint32_t)(t * 32 + 32 + lane), fa, fb, nqp, s_q, s_bnd,
+                                    a.hash_num, L, lane);
+      else
+        rank_tile<W32, EUCLID, PV>(ca, (uint32_t)(t * 32 + lane), fa, nqp, s_q, s_bnd, a.hash_num, L, lane);
+      if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush<EUCLID>(warp, lane);
+      if (warp == 0 && ((++poll_tick) & 7u) == 0u) poll_shared_bounds<EUCLID>(L, nqp, lane);
+#pragma unroll
+      for (int w = 0; w < W32; ++w) { ca[w] = na[w]; cb[w] = nb[w]; }
+      fa = ga; fb = gb;
+    }
+  } else {
   uint32_t cur[W32], nxt[W32];
   float ncur = 0.0f, nnxt = 0.0f;
-  uint32_t poll_tick = 0;
   if (t < t_end) {
     load_row<W32>(a.slab, t, lane, cur);
     if (EUCLID) ncur = ld_stream_f32(a.norms + t * 32 + lane);
@@ -941,6 +984,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, W32 >= 16 ? 1 : 2) scan_ldg_kern
 #pragma unroll
     for (int w = 0; w < W32; ++w) cur[w] = nxt[w];
     ncur = nnxt;
+  }
   }
   if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane);
   __syncthreads();
