@@ -295,23 +295,28 @@ __host__ __device__ __forceinline__ uint32_t tau_hi_of(unsigned long long tau) {
 // n^2 - c_d n - T = 0.  The hot loop therefore needs no double arithmetic at all: one float
 // lookup by d (the upper root) and one compare against the row norm; the exact score is computed
 // only for the rare rows below it (rows under the lower root are rejected there as well, by the
-// exact comparison).  The bound can only err towards admitting a row: T is replaced by the next
-// float above it (anything smaller may still round to T) plus 1e-14 * (c^2 + |T|), which covers
-// the two double roundings of the exact score and the rounding of the discriminant; the root is
-// moved up by 1e-14 * (|c| + sqrt(disc)) and rounded up to float.  A non-finite c or T disables
-// the filter for that entry (+inf); a negative discriminant means no norm is admissible (-inf).
+// exact comparison).  The bound can only err towards admitting a row, and it is cheap enough to
+// recompute whenever a list tightens (float arithmetic with directed rounding, no double sqrt):
+//   T  -> two floats above it (anything below the next float may still round to T) plus
+//         1.5e-14 * c^2, which covers the two double roundings of the exact score;
+//   c  -> rounded up where it is added, away from zero where it is squared;
+//   every operation rounds towards +inf, and the result is moved one more float up.
+// A non-finite c or T disables the filter for that entry (+inf); a discriminant that is negative
+// even after rounding up means no norm is admissible at that distance (-inf).
 __device__ __forceinline__ float euclid_bound(double c, uint32_t tau_hi) {
   const float Tf = key_float(tau_hi);
   if (!(fabsf(Tf) < INFINITY) || !(fabs(c) < (double)INFINITY)) return INFINITY;
-  const float Tn = __uint_as_float(Tf >= 0.0f ? __float_as_uint(Tf + 0.0f) + 1u : __float_as_uint(Tf) - 1u);  // next float up
-  if (!(fabsf(Tn) < INFINITY)) return INFINITY;
-  const double T2 = (double)Tn;
-  const double T4 = T2 + (1e-14 * (c * c + fabs(T2)) + 1e-300);
-  const double disc = c * c + 4.0 * T4;
-  if (!(disc == disc) || !(disc < (double)INFINITY)) return INFINITY;
-  if (disc < 0.0) return -INFINITY;
-  const double sq = sqrt(disc);
-  return __double2float_ru(0.5 * (c + sq) + (1e-14 * (fabs(c) + sq) + 1e-300));
+  const float c_add = __double2float_ru(c);
+  const float c_mag = c >= 0.0 ? c_add : __double2float_rd(c);          // |c_mag| >= |c|
+  float Tu = Tf + 0.0f;                                                   // -0 -> +0
+  Tu = __uint_as_float(Tu >= 0.0f ? __float_as_uint(Tu) + 2u : (__float_as_uint(Tu) >= 0x80000002u ? __float_as_uint(Tu) - 2u : 1u));
+  Tu = __fadd_ru(Tu, __fmaf_ru(1.5e-14f, __fmul_ru(c_mag, c_mag), 1e-37f));
+  const float disc = __fmaf_ru(c_mag, c_mag, __fmul_ru(4.0f, Tu));
+  if (!(disc < INFINITY)) return INFINITY;                                // overflow or NaN: no filtering
+  if (disc < 0.0f) return -INFINITY;
+  const float hi = __fmul_ru(0.5f, __fadd_ru(c_add, __fsqrt_ru(disc)));
+  if (!(fabsf(hi) < INFINITY)) return INFINITY;
+  return __uint_as_float(hi >= 0.0f ? __float_as_uint(hi + 0.0f) + 1u : __float_as_uint(hi) - 1u);   // one more float up
 }
 
 // ---------------------------------------------------------------------------
@@ -1684,6 +1689,11 @@ __global__ void __launch_bounds__(TAUE_THREADS) tau_init_euclid_kernel(ScanArgs 
     sq[tid] = (uint32_t)tid < 2 * a.w64 ? qw[tid] : 0u;
   }
   if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_cnt[2] = 0; s_or = 0; s_and = 0xFFFFFFFFu; }
+  if (a.ghist) {   // this query's part of the shared histogram starts from zero, its bound word from "none"
+    if (tid == 0) a.ghist[q] = 0xFFFFFFFFu;
+    uint32_t* g = a.ghist + a.nq + (size_t)q * a.hist_stride;
+    for (uint32_t i = tid; i < a.hist_stride; i += TAUE_THREADS) g[i] = 0;
+  }
   __syncthreads();
   const double two_nq = (double)(2.0f * a.qnorms[q]);
   uint32_t r[TAUE_KPT];
@@ -1790,6 +1800,7 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
     if (t.local_rows >= 4 * S && k <= S) {
       if (euclid) {
         tau_init_euclid_kernel<<<nq, TAUE_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+        hist_cleared = use_hist;
       } else {
         tau_init_hamming_kernel<<<nq, TAUH_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
         hist_cleared = use_hist;
