@@ -179,6 +179,7 @@ struct jubann_api {
 class datum_to_fv_converter {
  public:
   struct rule { std::string key, type, sample_weight, global_weight; };
+  struct combination_rule { std::string key_left, key_right, type; };
   datum_to_fv_converter() : hash_max_size_(0) {}
 
   static std::shared_ptr<datum_to_fv_converter> from_config(const json::ptr& conv) {
@@ -207,6 +208,27 @@ class datum_to_fv_converter {
       if (r.sample_weight != "bin" && r.sample_weight != "tf") throw converter_exception("unknown sample_weight: " + r.sample_weight);
       if (r.global_weight != "bin") throw converter_exception("global_weight not supported by this build: " + r.global_weight);
       c->string_rules_.push_back(r);
+    }
+    // combination features (config/anomaly/light_lof_combinational_feature.json:15-18): "mul" and
+    // "add" of every pair of converted features whose keys match (key_left, key_right) in either
+    // order; [core] fv_converter/combination_feature*, restated from recall: pairs i < j in fv
+    // order, key "<left>&<right>/<type>"
+    json::ptr cr = conv->find("combination_rules");
+    if (cr) for (size_t i = 0; i < cr->arr.size(); ++i) {
+      combination_rule r;
+      r.key_left = str(cr->arr[i], "key_left"); r.key_right = str(cr->arr[i], "key_right"); r.type = str(cr->arr[i], "type");
+      if (r.type != "mul" && r.type != "add") throw converter_exception("unknown combination feature type: " + r.type);
+      c->combination_rules_.push_back(r);
+    }
+    // sections this build has no implementation for must be empty: ignoring a rule would change
+    // every signature silently
+    static const char* const unsupported[] = {"string_filter_types", "string_filter_rules", "num_filter_types",
+                                              "num_filter_rules", "string_types", "num_types", "binary_types",
+                                              "binary_rules", "combination_types"};
+    for (size_t j = 0; j < sizeof(unsupported) / sizeof(unsupported[0]); ++j) {
+      json::ptr v = conv->find(unsupported[j]);
+      if (v && (!v->arr.empty() || !v->obj.empty()))
+        throw converter_exception(std::string("converter section not supported by this build: ") + unsupported[j]);
     }
     json::ptr hm = conv->find("hash_max_size");
     if (hm && hm->kind == json::value::NUM) c->hash_max_size_ = static_cast<uint64_t>(hm->num);
@@ -241,6 +263,20 @@ class datum_to_fv_converter {
         }
       }
     }
+    if (!combination_rules_.empty()) {
+      const size_t n = out.size();
+      for (size_t r = 0; r < combination_rules_.size(); ++r) {
+        const combination_rule& cr = combination_rules_[r];
+        for (size_t i = 0; i < n; ++i)
+          for (size_t j = i + 1; j < n; ++j) {
+            const bool fwd = match(cr.key_left, out[i].first) && match(cr.key_right, out[j].first);
+            const bool rev = match(cr.key_left, out[j].first) && match(cr.key_right, out[i].first);
+            if (!fwd && !rev) continue;
+            const float v = cr.type == "mul" ? out[i].second * out[j].second : out[i].second + out[j].second;
+            out.push_back(std::make_pair(out[i].first + "&" + out[j].first + "/" + cr.type, v));
+          }
+      }
+    }
     if (hash_max_size_) {
       for (size_t i = 0; i < out.size(); ++i) out[i].first = std::to_string(calc_string_hash(out[i].first) % hash_max_size_);
     }
@@ -259,6 +295,7 @@ class datum_to_fv_converter {
     return pat == key;
   }
   std::vector<rule> num_rules_, string_rules_;
+  std::vector<combination_rule> combination_rules_;
   uint64_t hash_max_size_;
 };
 

@@ -68,3 +68,24 @@ def test_unlearner_policies():
                         ("lru", {"max_size": "3"})):
         with pytest.raises(nn.JubatusError):
             nn.unlearner_trace(name, param, ["a"])
+
+
+def test_combination_rules_and_unsupported_sections():
+    """config/anomaly/light_lof_combinational_feature.json:15-18: pairwise "mul" / "add" features over
+    the converted features; sections without an implementation must be empty (a silently ignored
+    rule would change every signature)."""
+    conv = dict(CONVERTER, combination_types={}, combination_rules=[{"key_left": "*", "key_right": "*", "type": "mul"}])
+    d = nn.Datum().add_string("s", "x").add_number("a", 2).add_number("b", 3)
+    sfv = nn.convert(json.dumps(conv), d)
+    assert sfv[:3] == [("s$x@str#bin/bin", 1.0), ("a@num", 2.0), ("b@num", 3.0)]
+    assert sfv[3:] == [("s$x@str#bin/bin&a@num/mul", 2.0), ("s$x@str#bin/bin&b@num/mul", 3.0), ("a@num&b@num/mul", 6.0)]
+    conv2 = dict(conv, combination_rules=[{"key_left": "a*", "key_right": "b*", "type": "add"}])
+    assert nn.convert(json.dumps(conv2), d)[3:] == [("a@num&b@num/add", 5.0)]
+    conv3 = dict(conv, combination_rules=[{"key_left": "b*", "key_right": "a*", "type": "add"}])   # either order matches
+    assert nn.convert(json.dumps(conv3), d)[3:] == [("a@num&b@num/add", 5.0)]
+    with pytest.raises(nn.JubatusError):
+        nn.convert(json.dumps(dict(conv, combination_rules=[{"key_left": "*", "key_right": "*", "type": "div"}])), d)
+    for section, value in (("num_filter_rules", [{"key": "*", "type": "f", "suffix": "_"}]), ("string_types", {"bigram": {"method": "ngram"}}),
+                           ("binary_rules", [{"key": "*", "type": "b"}]), ("combination_types", {"c": {"method": "dynamic"}})):
+        with pytest.raises(nn.JubatusError, match="not supported"):
+            nn.convert(json.dumps(dict(conv, **{section: value})), d)
