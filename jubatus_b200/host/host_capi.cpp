@@ -23,6 +23,7 @@ struct host_box {
   std::unique_ptr<nearest_neighbor_classifier> classifier;   // jubaclassifier, method NN
   gpu_nearest_neighbor* nn() { return serv ? serv->get_driver()->engine() : engine.get(); }
   const datum_to_fv_converter& conv() { return serv ? serv->get_driver()->converter() : *converter; }
+  datum_to_fv_converter& conv_mut() { return serv ? serv->get_driver()->converter_mut() : *converter; }
 };
 
 datum make_datum(const char* const* skeys, const char* const* svals, uint64_t ns, const char* const* nkeys,
@@ -172,6 +173,7 @@ int jubahost_clear(void* h) {
   return guarded([&]() {
     if (b->serv) b->serv->clear(); else if (b->recommender) b->recommender->clear();
     else if (b->classifier) b->classifier->clear(); else b->lof->clear();
+    if (!b->serv) b->converter->clear_weights();
     return 0;
   });
 }
@@ -185,7 +187,7 @@ int jubahost_set_row(void* h, const char* id, const char* const* skeys, const ch
     datum d = make_datum(skeys, svals, ns, nkeys, nvals, nn);
     if (b->serv) { b->serv->set_row(id, d); return 0; }
     sfv_t v;
-    b->conv().convert(d, v);
+    b->conv_mut().convert_and_update_weight(d, v);   // a stored row moves the global weights
     if (b->recommender) b->recommender->update_row(id, v); else b->lof->set_row(id, v);
     return 0;
   });
@@ -204,7 +206,7 @@ int jubahost_set_rows(void* h, uint64_t n, const char* const* ids, const uint64_
     }
     if (b->lof) {   // anomaly: bulk load (light_lof::set_rows_bulk)
       std::vector<sfv_t> v(n);
-      for (uint64_t i = 0; i < n; ++i) b->conv().convert(ds[i], v[i]);
+      for (uint64_t i = 0; i < n; ++i) b->conv_mut().convert_and_update_weight(ds[i], v[i]);
       b->lof->set_rows_bulk(vid, v);
       return 0;
     }
@@ -291,7 +293,7 @@ int64_t jubahost_pack(void* h, char* buf, uint64_t cap) {
   host_box* b = static_cast<host_box*>(h);
   int64_t n = -1;
   int rc = guarded([&]() {
-    std::string blob = b->nn()->pack();
+    std::string blob = b->serv ? b->serv->get_driver()->pack() : b->nn()->pack();   // the server's pack carries the converter weights too
     if (blob.size() <= cap) memcpy(buf, blob.data(), blob.size());
     n = static_cast<int64_t>(blob.size());
     return 0;
@@ -300,7 +302,10 @@ int64_t jubahost_pack(void* h, char* buf, uint64_t cap) {
 }
 int jubahost_unpack(void* h, const char* buf, uint64_t n) {
   host_box* b = static_cast<host_box*>(h);
-  return guarded([&]() { b->nn()->unpack(std::string(buf, n)); return 0; });
+  return guarded([&]() {
+    if (b->serv) b->serv->get_driver()->unpack(std::string(buf, n)); else b->nn()->unpack(std::string(buf, n));
+    return 0;
+  });
 }
 // ---- model files (nearest_neighbor kind): server_base::save / load / load_file ----
 uint32_t jubahost_crc32(const char* data, uint64_t n, uint32_t crc) { return model_file::calc_crc32(data, n, crc); }
@@ -376,6 +381,29 @@ int64_t jubahost_model_read(const char* file, uint64_t file_n, const char* expec
   });
   return rc ? -1 : n;
 }
+// converter with global weights (CPU tests): `n_update` string-valued datums (one string value each,
+// key skeys[i] / value svals[i]) are converted with convert_and_update_weight, then the last
+// (skeys[n_update], svals[n_update]) with convert; the latter's features come back.
+int jubahost_convert_weighted(const char* converter_json, const char* const* skeys, const char* const* svals,
+                              uint64_t n_update, char* keys_buf, uint64_t keys_cap, float* vals, uint64_t vals_cap,
+                              uint64_t* count) {
+  return guarded([&]() {
+    json::ptr root;
+    try { root = json::parse(converter_json); } catch (const json::parse_error& e) { throw config_exception(e.what()); }
+    std::shared_ptr<datum_to_fv_converter> c = datum_to_fv_converter::from_config(root);
+    sfv_t v;
+    for (uint64_t i = 0; i < n_update; ++i) { datum d; d.add_string(skeys[i], svals[i]); c->convert_and_update_weight(d, v); }
+    datum q; q.add_string(skeys[n_update], svals[n_update]);
+    c->convert(q, v);
+    std::string joined;
+    if (v.size() > vals_cap) throw jubatus_exception("values buffer too small");
+    for (size_t i = 0; i < v.size(); ++i) { joined += v[i].first; joined += '\n'; vals[i] = v[i].second; }
+    if (joined.size() + 1 > keys_cap) throw jubatus_exception("keys buffer too small");
+    memcpy(keys_buf, joined.c_str(), joined.size() + 1);
+    *count = v.size();
+    return 0;
+  });
+}
 // unlearner policy alone (CPU tests): touch ids in order, report "<position>:<victim>" per eviction
 int jubahost_unlearner_trace(const char* name, const char* param_json, const char* const* ids, uint64_t n, char* out,
                              uint64_t cap, uint64_t* final_size) {
@@ -404,7 +432,7 @@ int jubahost_train(void* h, const char* label, const char* const* skeys, const c
   return guarded([&]() {
     if (!b->classifier) throw jubatus_exception("train: classifier server only");
     sfv_t v;
-    b->conv().convert(make_datum(skeys, svals, ns, nkeys, nvals, nn), v);
+    b->conv_mut().convert_and_update_weight(make_datum(skeys, svals, ns, nkeys, nvals, nn), v);
     b->classifier->train(v, label);
     return 0;
   });

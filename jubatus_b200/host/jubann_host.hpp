@@ -24,6 +24,7 @@
 #ifndef JUBANN_HOST_HPP_
 #define JUBANN_HOST_HPP_
 
+#include <ctype.h>
 #include <dlfcn.h>
 #include <math.h>
 #include <stdint.h>
@@ -174,11 +175,106 @@ struct jubann_api {
 };
 
 // ---------------------------------------------------------------------------------------
-// datum -> sfv (the `num` and `str` rules the shipped configs use)
+// weight_manager -- global feature weights ([core] fv_converter/weight_manager, keyword_weights;
+// restated from recall).  A feature whose key ends in "/idf" is scaled by
+// log((documents + 1) / (documents_with_the_feature + 1)); "/bin" and everything else by 1.
+// Counts move only in convert_and_update_weight (set_row, update_row, add, train); queries read
+// them.  Features that end up with value 0 are dropped.  Counts are kept as (master, diff) so
+// that replicas can exchange diffs (get_diff / mix / put_diff, like the reference's mixable).
+// ---------------------------------------------------------------------------------------
+class weight_manager {
+ public:
+  struct counts {
+    uint64_t documents;
+    std::unordered_map<std::string, uint64_t> frequency;
+    counts() : documents(0) {}
+    void add(const counts& o) {
+      documents += o.documents;
+      for (std::unordered_map<std::string, uint64_t>::const_iterator it = o.frequency.begin(); it != o.frequency.end(); ++it)
+        frequency[it->first] += it->second;
+    }
+  };
+  void update_weight(const sfv_t& fv) {
+    ++diff_.documents;
+    for (size_t i = 0; i < fv.size(); ++i)
+      if (is_idf(fv[i].first)) diff_.frequency[fv[i].first] += 1;
+  }
+  double get_global_weight(const std::string& key) const {
+    if (!is_idf(key)) return 1.0;
+    const double n = static_cast<double>(master_.documents + diff_.documents);
+    const double df = static_cast<double>(lookup(master_, key) + lookup(diff_, key));
+    return log((n + 1.0) / (df + 1.0));
+  }
+  void get_weight(sfv_t& fv) const {
+    size_t w = 0;
+    for (size_t i = 0; i < fv.size(); ++i) {
+      const float v = static_cast<float>(fv[i].second * get_global_weight(fv[i].first));
+      if (v != 0.0f) { if (w != i) fv[w].first.swap(fv[i].first); fv[w].second = v; ++w; }
+    }
+    fv.resize(w);
+  }
+  void clear() { master_ = counts(); diff_ = counts(); }
+  // MIX: every replica's diff is summed and the sum lands in every master
+  void get_diff(counts& out) const { out = diff_; }
+  static void mix(const counts& lhs, counts& acc) { acc.add(lhs); }
+  void put_diff(const counts& mixed) { master_.add(mixed); diff_ = counts(); }
+  uint64_t documents() const { return master_.documents + diff_.documents; }
+  // save / load: master and diff folded together (a loaded model starts with an empty diff)
+  std::string pack() const {
+    counts all = master_;
+    all.add(diff_);
+    std::string b;
+    put64(b, all.documents);
+    put64(b, all.frequency.size());
+    std::vector<std::string> keys;
+    for (std::unordered_map<std::string, uint64_t>::const_iterator it = all.frequency.begin(); it != all.frequency.end(); ++it) keys.push_back(it->first);
+    std::sort(keys.begin(), keys.end());
+    for (size_t i = 0; i < keys.size(); ++i) { put64(b, keys[i].size()); b += keys[i]; put64(b, all.frequency[keys[i]]); }
+    return b;
+  }
+  void unpack(const std::string& b) {
+    size_t p = 0;
+    counts c;
+    c.documents = get64(b, p);
+    const uint64_t n = get64(b, p);
+    for (uint64_t i = 0; i < n; ++i) {
+      const uint64_t len = get64(b, p);
+      if (b.size() < p + len) throw jubatus_exception("unpack: truncated weights");
+      std::string key(b, p, len);
+      p += len;
+      c.frequency[key] = get64(b, p);
+    }
+    master_ = c;
+    diff_ = counts();
+  }
+ private:
+  static void put64(std::string& b, uint64_t v) { char t[8]; memcpy(t, &v, 8); b.append(t, 8); }
+  static uint64_t get64(const std::string& b, size_t& p) {
+    if (b.size() < p + 8) throw jubatus_exception("unpack: truncated weights");
+    uint64_t v; memcpy(&v, b.data() + p, 8); p += 8; return v;
+  }
+  static bool is_idf(const std::string& key) { return key.size() >= 4 && key.compare(key.size() - 4, 4, "/idf") == 0; }
+  static uint64_t lookup(const counts& c, const std::string& key) {
+    std::unordered_map<std::string, uint64_t>::const_iterator it = c.frequency.find(key);
+    return it == c.frequency.end() ? 0 : it->second;
+  }
+  counts master_, diff_;
+};
+
+// ---------------------------------------------------------------------------------------
+// datum -> sfv ([core] fv_converter/datum_to_fv_converter; the rule kinds the shipped configs of
+// this path use: config/nearest_neighbor/*.json, config/recommender/nearest_neighbor_recommender*.json,
+// config/anomaly/light_lof*.json, config/classifier/nn.json).
+//   string rules: type "str" (the whole value), "space" (split at white space) or a name from
+//     "string_types" with {"method": "ngram", "char_num": "N"} (character N-grams, UTF-8 aware);
+//     sample_weight bin | tf | log_tf; global_weight bin | idf.  Key:
+//     <key>$<token>@<type>#<sample_weight>/<global_weight>; tokens of one value in sorted order
+//     (the reference counts them in a std::map).
+//   num rules: num | log | str.      combination rules: mul | add.      hash_max_size.
 // ---------------------------------------------------------------------------------------
 class datum_to_fv_converter {
  public:
-  struct rule { std::string key, type, sample_weight, global_weight; };
+  struct rule { std::string key, type, sample_weight, global_weight; int ngram; bool space; };
   struct combination_rule { std::string key_left, key_right, type; };
   datum_to_fv_converter() : hash_max_size_(0) {}
 
@@ -194,19 +290,36 @@ class datum_to_fv_converter {
       for (size_t j = 0; j < sizeof(known) / sizeof(known[0]); ++j) ok = ok || conv->obj[i].first == known[j];
       if (!ok) throw config_exception("unknown converter key: " + conv->obj[i].first);
     }
+    // string_types: name -> ngram width (the only splitter method built here)
+    std::map<std::string, int> ngram_types;
+    json::ptr st = conv->find("string_types");
+    if (st) for (size_t i = 0; i < st->obj.size(); ++i) {
+      const json::ptr& t = st->obj[i].second;
+      json::ptr m = t ? t->find("method") : json::ptr();
+      if (!m || m->kind != json::value::STR) throw converter_exception("string type needs a \"method\": " + st->obj[i].first);
+      if (m->str != "ngram") throw converter_exception("string type method not supported by this build: " + m->str);
+      json::ptr n = t->find("char_num");
+      int width = 0;
+      if (n && n->kind == json::value::STR) width = atoi(n->str.c_str());
+      else if (n && n->kind == json::value::NUM) width = static_cast<int>(n->num);
+      if (width <= 0) throw converter_exception("ngram needs a positive \"char_num\": " + st->obj[i].first);
+      ngram_types[st->obj[i].first] = width;
+    }
     json::ptr nr = conv->find("num_rules");
     if (nr) for (size_t i = 0; i < nr->arr.size(); ++i) {
-      rule r; r.key = str(nr->arr[i], "key"); r.type = str(nr->arr[i], "type");
+      rule r; r.ngram = 0; r.space = false; r.key = str(nr->arr[i], "key"); r.type = str(nr->arr[i], "type");
       if (r.type != "num" && r.type != "log" && r.type != "str") throw converter_exception("unknown num feature type: " + r.type);
       c->num_rules_.push_back(r);
     }
     json::ptr sr = conv->find("string_rules");
     if (sr) for (size_t i = 0; i < sr->arr.size(); ++i) {
-      rule r; r.key = str(sr->arr[i], "key"); r.type = str(sr->arr[i], "type");
+      rule r; r.ngram = 0; r.space = false; r.key = str(sr->arr[i], "key"); r.type = str(sr->arr[i], "type");
       r.sample_weight = str(sr->arr[i], "sample_weight"); r.global_weight = str(sr->arr[i], "global_weight");
-      if (r.type != "str") throw converter_exception("string feature type not supported by this build: " + r.type);
-      if (r.sample_weight != "bin" && r.sample_weight != "tf") throw converter_exception("unknown sample_weight: " + r.sample_weight);
-      if (r.global_weight != "bin") throw converter_exception("global_weight not supported by this build: " + r.global_weight);
+      if (r.type == "space") r.space = true;
+      else if (ngram_types.count(r.type)) r.ngram = ngram_types[r.type];
+      else if (r.type != "str") throw converter_exception("unknown string feature type: " + r.type);
+      if (r.sample_weight != "bin" && r.sample_weight != "tf" && r.sample_weight != "log_tf") throw converter_exception("unknown sample_weight: " + r.sample_weight);
+      if (r.global_weight != "bin" && r.global_weight != "idf") throw converter_exception("global_weight not supported by this build: " + r.global_weight);
       c->string_rules_.push_back(r);
     }
     // combination features (config/anomaly/light_lof_combinational_feature.json:15-18): "mul" and
@@ -223,8 +336,8 @@ class datum_to_fv_converter {
     // sections this build has no implementation for must be empty: ignoring a rule would change
     // every signature silently
     static const char* const unsupported[] = {"string_filter_types", "string_filter_rules", "num_filter_types",
-                                              "num_filter_rules", "string_types", "num_types", "binary_types",
-                                              "binary_rules", "combination_types"};
+                                              "num_filter_rules", "num_types", "binary_types", "binary_rules",
+                                              "combination_types"};
     for (size_t j = 0; j < sizeof(unsupported) / sizeof(unsupported[0]); ++j) {
       json::ptr v = conv->find(unsupported[j]);
       if (v && (!v->arr.empty() || !v->obj.empty()))
@@ -235,21 +348,49 @@ class datum_to_fv_converter {
     return c;
   }
 
-  // strings first, then numbers, each in datum order and rule order (datum_to_fv_converter::convert)
+  // datum_to_fv_converter::convert: queries -- global weights are read, not moved
   void convert(const datum& d, sfv_t& out) const {
+    convert_unweighted(d, out);
+    weights_.get_weight(out);
+    finish(out);
+  }
+  // datum_to_fv_converter::convert_and_update_weight: everything that stores a row
+  void convert_and_update_weight(const datum& d, sfv_t& out) {
+    convert_unweighted(d, out);
+    weights_.update_weight(out);
+    weights_.get_weight(out);
+    finish(out);
+  }
+  weight_manager& weights() { return weights_; }
+  const weight_manager& weights() const { return weights_; }
+  void clear_weights() { weights_.clear(); }
+
+ private:
+  // strings first, then numbers, each in datum order and rule order
+  void convert_unweighted(const datum& d, sfv_t& out) const {
     out.clear();
     for (size_t r = 0; r < string_rules_.size(); ++r) {
-      std::map<std::string, float> tf;
-      std::vector<std::string> order;
-      for (size_t i = 0; i < d.string_values.size(); ++i) {
-        if (!match(string_rules_[r].key, d.string_values[i].first)) continue;
-        std::string f = d.string_values[i].first + "$" + d.string_values[i].second + "@" + string_rules_[r].type + "#" +
-                        string_rules_[r].sample_weight + "/" + string_rules_[r].global_weight;
-        if (tf.find(f) == tf.end()) order.push_back(f);
-        tf[f] += 1.0f;
+      const rule& sr = string_rules_[r];
+      const std::string suffix = "@" + sr.type + "#" + sr.sample_weight + "/" + sr.global_weight;
+      if (sr.ngram == 0 && !sr.space) {   // "str": the value is the token
+        std::map<std::string, float> tf;
+        std::vector<std::string> order;
+        for (size_t i = 0; i < d.string_values.size(); ++i) {
+          if (!match(sr.key, d.string_values[i].first)) continue;
+          std::string f = d.string_values[i].first + "$" + d.string_values[i].second + suffix;
+          if (tf.find(f) == tf.end()) order.push_back(f);
+          tf[f] += 1.0f;
+        }
+        for (size_t i = 0; i < order.size(); ++i) out.push_back(std::make_pair(order[i], sample_weight(sr, tf[order[i]])));
+        continue;
       }
-      for (size_t i = 0; i < order.size(); ++i)
-        out.push_back(std::make_pair(order[i], string_rules_[r].sample_weight == "bin" ? 1.0f : tf[order[i]]));
+      for (size_t i = 0; i < d.string_values.size(); ++i) {
+        if (!match(sr.key, d.string_values[i].first)) continue;
+        std::map<std::string, float> counter;   // sorted, like the reference's word counter
+        if (sr.space) split_space(d.string_values[i].second, counter); else split_ngram(d.string_values[i].second, sr.ngram, counter);
+        for (std::map<std::string, float>::const_iterator it = counter.begin(); it != counter.end(); ++it)
+          out.push_back(std::make_pair(d.string_values[i].first + "$" + it->first + suffix, sample_weight(sr, it->second)));
+      }
     }
     for (size_t r = 0; r < num_rules_.size(); ++r) {
       for (size_t i = 0; i < d.num_values.size(); ++i) {
@@ -277,12 +418,35 @@ class datum_to_fv_converter {
           }
       }
     }
+  }
+  void finish(sfv_t& out) const {
     if (hash_max_size_) {
       for (size_t i = 0; i < out.size(); ++i) out[i].first = std::to_string(calc_string_hash(out[i].first) % hash_max_size_);
     }
   }
-
- private:
+  static float sample_weight(const rule& r, float tf) {
+    if (r.sample_weight == "bin") return 1.0f;
+    if (r.sample_weight == "tf") return tf;
+    return static_cast<float>(log(1.0 + tf));   // log_tf
+  }
+  static size_t utf8_len(unsigned char c) { return c < 0x80 ? 1 : (c >> 5) == 0x6 ? 2 : (c >> 4) == 0xE ? 3 : (c >> 3) == 0x1E ? 4 : 1; }
+  static void split_ngram(const std::string& s, int n, std::map<std::string, float>& counter) {
+    std::vector<size_t> starts;   // byte offsets of the characters, plus the end
+    for (size_t p = 0; p < s.size(); p += utf8_len(static_cast<unsigned char>(s[p]))) starts.push_back(p);
+    starts.push_back(s.size());
+    const size_t chars = starts.size() - 1;
+    for (size_t i = 0; i + n <= chars; ++i) counter[s.substr(starts[i], std::min(starts[i + n], s.size()) - starts[i])] += 1.0f;
+  }
+  static void split_space(const std::string& s, std::map<std::string, float>& counter) {
+    size_t p = 0;
+    while (p < s.size()) {
+      while (p < s.size() && isspace(static_cast<unsigned char>(s[p]))) ++p;
+      size_t e = p;
+      while (e < s.size() && !isspace(static_cast<unsigned char>(s[e]))) ++e;
+      if (e > p) counter[s.substr(p, e - p)] += 1.0f;
+      p = e;
+    }
+  }
   static std::string str(const json::ptr& o, const char* k) {
     json::ptr v = o ? o->find(k) : json::ptr();
     if (!v || v->kind != json::value::STR) throw config_exception(std::string("rule needs a string \"") + k + "\"");
@@ -297,6 +461,7 @@ class datum_to_fv_converter {
   std::vector<rule> num_rules_, string_rules_;
   std::vector<combination_rule> combination_rules_;
   uint64_t hash_max_size_;
+  weight_manager weights_;
 };
 
 // ---------------------------------------------------------------------------------------
@@ -733,10 +898,10 @@ class nearest_neighbor {
       : nn_(nn), converter_(conv) {}
   std::shared_ptr<device_table> get_table() { return nn_->get_table(); }
   gpu_nearest_neighbor* engine() { return nn_.get(); }
-  void set_row(const std::string& id, const datum& d) { sfv_t v; converter_->convert(d, v); nn_->set_row(id, v); }
+  void set_row(const std::string& id, const datum& d) { sfv_t v; converter_->convert_and_update_weight(d, v); nn_->set_row(id, v); }
   void set_rows(const std::vector<std::string>& ids, const std::vector<datum>& ds) {
     std::vector<sfv_t> v(ds.size());
-    for (size_t i = 0; i < ds.size(); ++i) converter_->convert(ds[i], v[i]);
+    for (size_t i = 0; i < ds.size(); ++i) converter_->convert_and_update_weight(ds[i], v[i]);
     nn_->set_rows(ids, v);
   }
   neighbor_result neighbor_row_from_id(const std::string& id, size_t size) { neighbor_result r; nn_->neighbor_row(id, r, size); return r; }
@@ -751,10 +916,25 @@ class nearest_neighbor {
     return out;
   }
   std::vector<std::string> get_all_rows() { std::vector<std::string> r; nn_->get_all_row_ids(r); return r; }
-  void clear() { nn_->clear(); }
+  void clear() { nn_->clear(); converter_->clear_weights(); }
   mixable_versioned_table* get_mixable() { return nn_->get_mixable(); }
-  std::string pack() const { return nn_->pack(); }                 // driver->pack, save_load.cpp:129
-  void unpack(const std::string& blob) { nn_->unpack(blob); }      // driver->unpack, save_load.cpp:280
+  datum_to_fv_converter& converter_mut() { return *converter_; }
+  // driver->pack / unpack (save_load.cpp:129,280): the table, then the converter's global weights
+  std::string pack() const {
+    const std::string t = nn_->pack(), w = converter_->weights().pack();
+    std::string b("JUBANND1");
+    uint64_t n = t.size();
+    char len[8]; memcpy(len, &n, 8);
+    b.append(len, 8); b += t; b += w;
+    return b;
+  }
+  void unpack(const std::string& blob) {
+    if (blob.size() < 16 || blob.compare(0, 8, "JUBANND1") != 0) throw jubatus_exception("unpack: not a jubann driver blob");
+    uint64_t n; memcpy(&n, blob.data() + 8, 8);
+    if (blob.size() < 16 + n) throw jubatus_exception("unpack: truncated blob");
+    nn_->unpack(blob.substr(16, n));
+    converter_->weights().unpack(blob.substr(16 + n));
+  }
   const datum_to_fv_converter& converter() const { return *converter_; }
  private:
   std::shared_ptr<gpu_nearest_neighbor> nn_;

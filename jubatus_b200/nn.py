@@ -94,6 +94,24 @@ def _raise():
     raise JubatusError(_load().jubahost_last_error().decode("utf-8", "replace"))
 
 
+def convert_weighted(converter_json, stored, query):
+    """Feed `stored` [(key, string value), ...] through convert_and_update_weight (what set_row does),
+    then convert `query` (key, value) the way a query does; returns its [(feature, value), ...]."""
+    lib = _load()
+    pairs = list(stored) + [query]
+    cap = 1 << 18
+    buf = ctypes.create_string_buffer(cap)
+    vals = np.zeros(8192, dtype=np.float32)
+    cnt = ctypes.c_uint64()
+    lib.jubahost_convert_weighted.argtypes = [ctypes.c_char_p, _vp, _vp, ctypes.c_uint64, _vp, ctypes.c_uint64, _vp,
+                                              ctypes.c_uint64, _vp]
+    if lib.jubahost_convert_weighted(converter_json.encode(), _cstrs([k for k, _ in pairs]), _cstrs([v for _, v in pairs]),
+                                     len(stored), buf, cap, vals.ctypes.data_as(_vp), len(vals), ctypes.byref(cnt)):
+        _raise()
+    keys = buf.value.decode("utf-8").split("\n")[:cnt.value]
+    return [(k, float(vals[i])) for i, k in enumerate(keys)]
+
+
 def unlearner_trace(name, param, ids):
     """Run an unlearner policy ("lru" / "random") over a sequence of touched ids ("-x" removes x);
     returns ([(position, victim), ...], final_size)."""

@@ -85,7 +85,60 @@ def test_combination_rules_and_unsupported_sections():
     assert nn.convert(json.dumps(conv3), d)[3:] == [("a@num&b@num/add", 5.0)]
     with pytest.raises(nn.JubatusError):
         nn.convert(json.dumps(dict(conv, combination_rules=[{"key_left": "*", "key_right": "*", "type": "div"}])), d)
-    for section, value in (("num_filter_rules", [{"key": "*", "type": "f", "suffix": "_"}]), ("string_types", {"bigram": {"method": "ngram"}}),
+    for section, value in (("num_filter_rules", [{"key": "*", "type": "f", "suffix": "_"}]), ("string_types", {"morph": {"method": "dynamic", "path": "libmecab_splitter.so"}}),
                            ("binary_rules", [{"key": "*", "type": "b"}]), ("combination_types", {"c": {"method": "dynamic"}})):
         with pytest.raises(nn.JubatusError, match="not supported"):
             nn.convert(json.dumps(dict(conv, **{section: value})), d)
+
+
+def test_converter_sections_of_the_shipped_configs_parse():
+    """Every config the reference ships for the engines on this path (read from the reference tree
+    when it is there; the tree does not travel to the GPU box)."""
+    import glob
+    import os
+    root = "/root/reference/config"
+    paths = sorted(glob.glob(root + "/nearest_neighbor/*.json") + glob.glob(root + "/recommender/nearest_neighbor_recommender*.json") +
+                   glob.glob(root + "/anomaly/light_lof*.json") + [root + "/classifier/nn.json"])
+    paths = [p for p in paths if os.path.exists(p)]
+    if not paths:
+        pytest.skip("reference tree not present")
+    d = nn.Datum().add_string("name", "juba").add_number("age", 31).add_number("w", 0.5)
+    for p in paths:
+        cfg = json.load(open(p))
+        sfv = nn.convert(json.dumps(cfg["converter"]), d)
+        keys = [k for k, _ in sfv]
+        assert "age@num" in keys, p
+        # string features: "str" tokens everywhere but default.json (bigram/idf: weight 0 on an empty model)
+        assert "name$juba@str#bin/bin" in keys or p.endswith("nearest_neighbor/default.json"), p
+
+
+def test_string_types_sample_weights_and_idf():
+    """config/nearest_neighbor/default.json: bigram tokens, tf sample weight, idf global weight.
+    Stored rows move the document counts, queries only read them:
+    idf = log((documents + 1) / (documents with the feature + 1))."""
+    import math
+    conv = {"string_types": {"bigram": {"method": "ngram", "char_num": "2"}},
+            "string_rules": [{"key": "*", "type": "bigram", "sample_weight": "tf", "global_weight": "idf"}],
+            "num_types": {}, "num_rules": []}
+    got = nn.convert_weighted(json.dumps(conv), [("t", "abab"), ("t", "abc"), ("t", "xyz")], ("t", "abcab"))
+    want = [("t$ab@bigram#tf/idf", 2 * math.log(4 / 3)), ("t$bc@bigram#tf/idf", math.log(4 / 2)), ("t$ca@bigram#tf/idf", math.log(4 / 1))]
+    assert [k for k, _ in got] == [k for k, _ in want]            # tokens of a value in sorted order
+    for (_, g), (_, x) in zip(got, want):
+        assert abs(g - x) < 1e-6
+    # a feature every stored document has weighs log(1) = 0 and is dropped
+    got = nn.convert_weighted(json.dumps(conv), [("t", "ab"), ("t", "ab")], ("t", "abc"))
+    assert [k for k, _ in got] == ["t$bc@bigram#tf/idf"]
+    # bin / log_tf sample weights, the space splitter, multi-byte characters
+    conv2 = {"string_types": {"uni": {"method": "ngram", "char_num": 1}},
+             "string_rules": [{"key": "w*", "type": "space", "sample_weight": "log_tf", "global_weight": "bin"},
+                              {"key": "u*", "type": "uni", "sample_weight": "bin", "global_weight": "bin"}],
+             "num_rules": []}
+    got = nn.convert_weighted(json.dumps(conv2), [], ("words", "b a  b\tb"))
+    assert got[0][0] == "words$a@space#log_tf/bin" and abs(got[0][1] - math.log(2)) < 1e-6
+    assert got[1][0] == "words$b@space#log_tf/bin" and abs(got[1][1] - math.log(4)) < 1e-6
+    got = nn.convert_weighted(json.dumps(conv2), [], ("u", "aあa"))
+    assert got == [("u$a@uni#bin/bin", 1.0), ("u$あ@uni#bin/bin", 1.0)]
+    for bad in ({"string_types": {"m": {"method": "mecab"}}}, {"string_rules": [{"key": "*", "type": "nope", "sample_weight": "bin", "global_weight": "bin"}]},
+                {"string_rules": [{"key": "*", "type": "str", "sample_weight": "bin", "global_weight": "weight"}]}):
+        with pytest.raises(nn.JubatusError):
+            nn.convert_weighted(json.dumps(dict(conv, **bad)), [], ("t", "x"))

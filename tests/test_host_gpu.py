@@ -471,3 +471,34 @@ def test_classifier_nn_method():
         c.update(bad)
         with pytest.raises(nn.JubatusError):
             nn.Classifier(json.dumps(c))
+
+
+def test_default_config_bigram_idf_end_to_end(tmp_path):
+    """config/nearest_neighbor/default.json's converter (bigram tokens, tf x idf) in front of the
+    engine: stored rows move the document counts, the counts travel with the model file."""
+    conv = {"string_filter_types": {}, "string_filter_rules": [], "num_filter_types": {}, "num_filter_rules": [],
+            "string_types": {"bigram": {"method": "ngram", "char_num": "2"}},
+            "string_rules": [{"key": "*", "type": "bigram", "sample_weight": "tf", "global_weight": "idf"}],
+            "num_types": {}, "num_rules": [{"key": "*", "type": "num"}]}
+    cfg = json.dumps({"method": "lsh", "parameter": {"hash_num": 256}, "converter": conv})
+    a = nn.NearestNeighbor(cfg)
+    a.set_storage(str(tmp_path), "127.0.0.1", 9199)
+    texts = ["the quick brown fox", "the quick brown dog", "lorem ipsum dolor sit amet", "jubatus online learning",
+             "nearest neighbor search", "the lazy dog sleeps", "online machine learning framework", "quick sort"]
+    # a row is hashed with the weights of the moment it is stored (the first one sees an empty
+    # model: idf 0, all-zero signature), so every row is stored a second time once the counts exist
+    for _ in range(2):
+        for i, t in enumerate(texts):
+            a.set_row("t%d" % i, nn.Datum().add_string("text", t))
+    got = a.neighbor_row_from_datum(nn.Datum().add_string("text", "the quick brown fox jumps"), 3)
+    assert got[0][0] == "t0" and got[1][0] == "t1"
+    sim = a.similar_row_from_datum(nn.Datum().add_string("text", "online learning"), 2)
+    assert {sim[0][0], sim[1][0]} == {"t3", "t6"}
+    before = a.neighbor_row_from_datum(nn.Datum().add_string("text", "machine learning"), 4)
+    a.save("w")
+    b = nn.NearestNeighbor(cfg)
+    b.set_storage(str(tmp_path), "127.0.0.1", 9199)
+    b.load("w")
+    assert b.neighbor_row_from_datum(nn.Datum().add_string("text", "machine learning"), 4) == before   # same idf after load
+    b.clear()
+    assert b.size() == 0
