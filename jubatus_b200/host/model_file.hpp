@@ -16,8 +16,9 @@
 // JSON, not as text), user container arity, user data version.
 //
 // What is NOT the reference's: <driver pack>.  In the reference it is jubatus_core's msgpack
-// serialisation of column_table, which is not available here; this build stores the table as one
-// raw msgpack string holding the "JUBANN1" blob of device_table::pack().  A file written by the
+// serialisation of column_table, which is not available here; this build stores one raw msgpack
+// string holding driver::nearest_neighbor::pack() (the "JUBANN1" blob of device_table::pack()
+// followed by the converter's global-weight counts).  A file written by the
 // reference therefore passes every container check here and then fails in unpack with a clear
 // message (and the other way round).
 #ifndef JUBANN_MODEL_FILE_HPP_
