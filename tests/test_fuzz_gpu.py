@@ -16,9 +16,11 @@ KS = [1, 2, 3, 7, 10, 31, 33, 64, 100, 129, 170, 255, 500, 1025, 2048]
 
 
 def _cases():
-    rng = np.random.RandomState(20261107)
+    # JUBANN_FUZZ_SEED / JUBANN_FUZZ_CASES widen the hunt for a one-off run; the defaults are what CI runs
+    import os
+    rng = np.random.RandomState(int(os.environ.get("JUBANN_FUZZ_SEED", "20261107")))
     out = []
-    for i in range(160):
+    for i in range(int(os.environ.get("JUBANN_FUZZ_CASES", "160"))):
         method = ["lsh", "euclid_lsh", "minhash"][rng.randint(3)]
         n = SIZES[rng.randint(len(SIZES))]
         h = HASHES[rng.randint(len(HASHES))]
