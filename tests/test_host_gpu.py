@@ -502,3 +502,47 @@ def test_default_config_bigram_idf_end_to_end(tmp_path):
     assert b.neighbor_row_from_datum(nn.Datum().add_string("text", "machine learning"), 4) == before   # same idf after load
     b.clear()
     assert b.size() == 0
+
+
+@pytest.mark.parametrize("method,hash_num,seed", [("lsh", 128, 1), ("euclid_lsh", 64, 2), ("minhash", 64, 3), ("lsh", 512, 4)])
+def test_random_sequence_of_rpcs_matches_the_oracle_engine(oracle, method, hash_num, seed):
+    """A few hundred randomly interleaved set_row (new and overwriting), delete_row, *_from_id and
+    *_from_datum calls: ids, order and the row set must track the oracle's column_table
+    (swap-delete moves the last row into the hole, which changes tie order afterwards)."""
+    rng = np.random.RandomState(seed)
+    srv = nn.NearestNeighbor(config(method, hash_num))
+    ora = oracle.OracleNN(method, hash_num)
+    pool_ids, pool_vals = w.synth_rows(w.MASTER_SEED, 5000 + seed, 400, nnz=6, nfeat_log2=5)   # few features: many ties
+    live = []
+    for step in range(350):
+        op = rng.randint(0, 10)
+        r = int(rng.randint(0, 400))
+        if op <= 4 or not live:                       # set_row: new id or overwrite
+            rid = "r%d" % int(rng.randint(0, 120))
+            srv.set_row(rid, datum_of(pool_ids[r], pool_vals[r]))
+            ora.set_row(rid, sfv_of(pool_ids[r], pool_vals[r]))
+            if rid not in live:
+                live.append(rid)
+        elif op == 5:                                  # delete_row
+            rid = live[int(rng.randint(0, len(live)))]
+            assert srv.delete_row(rid) is True
+            ora.delete_row(rid)
+            live.remove(rid)
+            assert srv.delete_row(rid) is False      # already gone
+        elif op <= 7:                                  # query by id
+            rid = live[int(rng.randint(0, len(live)))]
+            k = int(rng.randint(1, 12))
+            if op == 6:
+                same(srv.neighbor_row_from_id(rid, k), ora.neighbor_row_from_id(rid, k), rel=1e-5)
+            else:
+                same(srv.similar_row_from_id(rid, k), ora.similar_row_from_id(rid, k), rel=1e-5)
+        else:                                          # query by datum
+            k = int(rng.randint(1, 12))
+            d, s = datum_of(pool_ids[r], pool_vals[r]), sfv_of(pool_ids[r], pool_vals[r])
+            if op == 8:
+                same(srv.neighbor_row_from_datum(d, k), ora.neighbor_row_from_datum(s, k), rel=1e-5)
+            else:
+                same(srv.similar_row_from_datum(d, k), ora.similar_row_from_datum(s, k), rel=1e-5)
+        if step % 50 == 49:
+            assert srv.get_all_rows() == ora.get_all_rows() and srv.size() == len(live)
+    assert srv.neighbor_row_from_id("never-stored", 3) == []
