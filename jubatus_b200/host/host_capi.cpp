@@ -285,6 +285,15 @@ int jubahost_mix_pair(void* ha, void* hb) {
     ma->pull(arg_b, from_a);
     mb->push(from_a);
     ma->push(from_b);
+    // the converters' global weights are the second mixable of the driver: every replica's
+    // count diff is summed and the sum goes into every master (linear_mixer.cpp:547-561,613-628)
+    weight_manager::counts da, db, acc;
+    a->conv_mut().weights().get_diff(da);
+    b->conv_mut().weights().get_diff(db);
+    weight_manager::mix(da, acc);
+    weight_manager::mix(db, acc);
+    a->conv_mut().weights().put_diff(acc);
+    b->conv_mut().weights().put_diff(acc);
     return 0;
   });
 }

@@ -546,3 +546,32 @@ def test_random_sequence_of_rpcs_matches_the_oracle_engine(oracle, method, hash_
         if step % 50 == 49:
             assert srv.get_all_rows() == ora.get_all_rows() and srv.size() == len(live)
     assert srv.neighbor_row_from_id("never-stored", 3) == []
+
+
+def test_mix_carries_the_converter_weights_too():
+    """Two replicas store different texts, MIX, and then weigh a query's features alike: the idf
+    counts are a mixable next to the table (every replica's diff summed into every master)."""
+    conv = {"string_types": {"bigram": {"method": "ngram", "char_num": "2"}},
+            "string_rules": [{"key": "*", "type": "bigram", "sample_weight": "tf", "global_weight": "idf"}],
+            "num_types": {}, "num_rules": []}
+    cfg = json.dumps({"method": "lsh", "parameter": {"hash_num": 128}, "converter": conv})
+    a, b = nn.NearestNeighbor(cfg, my_id="A"), nn.NearestNeighbor(cfg, my_id="B")
+    ta = ["alpha beta", "beta gamma", "gamma delta", "alpha delta"]
+    tb = ["omega psi", "psi chi", "chi phi", "alpha omega", "beta phi"]
+    for i, t in enumerate(ta):
+        a.set_row("a%d" % i, nn.Datum().add_string("t", t))
+    for i, t in enumerate(tb):
+        b.set_row("b%d" % i, nn.Datum().add_string("t", t))
+    a.mix_with(b)
+    assert sorted(a.get_all_rows()) == sorted(b.get_all_rows()) and a.size() == 9
+    # same rows (signatures travel as stored) and same document counts -> same scores on both
+    # (row order differs between the replicas, so ties may come out in another order)
+    for text in ("alpha beta gamma", "psi phi", "delta omega"):
+        q = nn.Datum().add_string("t", text)
+        ra, rb = a.similar_row_from_datum(q, 9), b.similar_row_from_datum(q, 9)
+        assert sorted(ra, key=lambda x: (-x[1], x[0])) == sorted(rb, key=lambda x: (-x[1], x[0]))
+        assert [s for _, s in ra] == [s for _, s in rb]
+    # a second MIX with nothing new changes nothing
+    before = a.similar_row_from_datum(nn.Datum().add_string("t", "alpha"), 9)
+    a.mix_with(b)
+    assert a.similar_row_from_datum(nn.Datum().add_string("t", "alpha"), 9) == before
