@@ -347,9 +347,10 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
       const uint32_t kthis = std::min(kpage, keff - p * kpage);
       const uint64_t* floor = (p == 0) ? nullptr : h->b_floor.as<uint64_t>() + q0;
       cudaEvent_t ea, eb;
+      int scan_kernels = 0;   // sample pre-pass (when it runs) + scan
       record_scan_begin(h, s, &ea, &eb);
       CK(launch_scan(t, euclid, cfg, d_qsigs + (size_t)q0 * h->w64, d_qnorms ? d_qnorms + q0 : nullptr,
-                     h->d_coslut, nql, kthis, floor, h->b_tau.as<uint64_t>(), h->b_hist.as<uint32_t>(), h->b_cand.as<uint64_t>(), s));
+                     h->d_coslut, nql, kthis, floor, h->b_tau.as<uint64_t>(), h->b_hist.as<uint32_t>(), h->b_cand.as<uint64_t>(), s, &scan_kernels));
       record_scan_end(h, s, ea, eb);
       MergeOut o{};
       o.kout = k; o.col0 = p * kpage;
@@ -367,7 +368,7 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
         o.out_count = d_out_count + q0;
       }
       CK(launch_merge_local(h->b_cand.as<uint64_t>(), nql, cfg.nchunks, kthis, o, s));
-      h->kernel_launches += 3;
+      h->kernel_launches += scan_kernels + 1;   // + the list reduction
       h->scan_launches += 1;
       h->scan_passes += (nql + cfg.qp - 1) / cfg.qp;
     }

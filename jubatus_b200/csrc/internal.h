@@ -79,7 +79,7 @@ void set_tma_geometry_override(uint32_t tiles_per_warp, uint32_t stages);  // tu
 cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, const uint64_t* d_qsigs,
                         const float* d_qnorms, const double* d_coslut, uint32_t nq, uint32_t k,
                         const uint64_t* d_floor_keys, uint64_t* d_tau_scratch, uint32_t* d_hist_scratch,
-                        uint64_t* d_cand, cudaStream_t s);
+                        uint64_t* d_cand, cudaStream_t s, int* kernels_launched = nullptr);
 
 // Per query: k smallest keys among nlists*k candidates.  If d_out_index != nullptr writes the
 // final (index, score, count) outputs at column offset `col0` of rows of width `kout`;

@@ -1770,7 +1770,7 @@ static cudaError_t launch_scan_w(uint32_t w32, const ScanArgs& a, const ScanConf
 cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, const uint64_t* d_qsigs,
                         const float* d_qnorms, const double* d_coslut, uint32_t nq, uint32_t k,
                         const uint64_t* d_floor_keys, uint64_t* d_tau_scratch, uint32_t* d_hist_scratch,
-                        uint64_t* d_cand, cudaStream_t s) {
+                        uint64_t* d_cand, cudaStream_t s, int* kernels_launched) {
   ScanArgs a;
   a.slab = static_cast<const unsigned char*>(t.slab);
   a.norms = t.norms;
@@ -1807,6 +1807,7 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
       }
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
+      if (kernels_launched) ++*kernels_launched;
       a.tau_init = d_tau_scratch;
     }
   }
@@ -1816,6 +1817,7 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
     if (e != cudaSuccess) return e;
   }
   dim3 grid(cfg.nchunks, (nq + cfg.qp - 1) / cfg.qp, 1);
+  if (kernels_launched) ++*kernels_launched;
   return euclid ? launch_scan_w<true>(t.w32, a, cfg, grid, s) : launch_scan_w<false>(t.w32, a, cfg, grid, s);
 }
 
