@@ -34,8 +34,17 @@
  *    in a ranking are broken by smaller global row index, exactly like the
  *    std::pair<dist, index> heap of ranking_hamming_bit_vectors.
  *  - Sharding: with shard_count G > 1 a handle stores only rows whose global index g
- *    satisfies g % G == shard_rank (local slot g / G).  Query entry points then return the
- *    shard-local top-k; jubann_merge_* combines the G candidate lists bit-exactly.
+ *    satisfies g % G == shard_rank (local slot g / G); it may be handed every row (it keeps
+ *    its own) or only its own.  Once the shards share a communicator (jubann_comm_init, or
+ *    jubann_create_multi) the query entry points answer for the whole table; without one,
+ *    jubann_scan_local_dev gives the shard-local top-k and jubann_merge_dev combines G such lists.
+ *  - Ordering: host-pointer entry points run on a stream of the handle and return when the
+ *    work is done.  _dev entry points enqueue on the caller's stream; work the handle does
+ *    afterwards on its own stream (any host-pointer call, growing the table) is ordered after
+ *    _dev writes by the library.  Two different caller streams are the caller's to order.
+ *  - A batch that names one destination row more than once stores the last entry (what
+ *    column_table::add does when applied in order).  Signature words are taken modulo
+ *    hash_num: bits at or above it are ignored (bit_vector keeps them zero).
  */
 #ifndef JUBANN_H_
 #define JUBANN_H_
@@ -48,13 +57,13 @@ extern "C" {
 
 typedef struct jubann jubann_t;
 
-#define JUBANN_ABI_VERSION 1
+#define JUBANN_ABI_VERSION 2
 
 #define JUBANN_OK 0
 #define JUBANN_E_INVALID (-1)      /* invalid_parameter / unsupported_method */
 #define JUBANN_E_CUDA (-2)         /* CUDA runtime error (sticky) */
 #define JUBANN_E_NOMEM (-3)        /* device or host allocation failed */
-#define JUBANN_E_CACHE_FULL (-4)   /* more distinct features than projection-cache slots */
+#define JUBANN_E_CACHE_FULL (-4)   /* (ABI 1; no longer returned: features beyond the cache are drawn on the spot) */
 #define JUBANN_E_RANGE (-5)        /* row index out of range */
 
 /* query flags */
@@ -76,7 +85,9 @@ int jubann_create(const char* method, uint32_t hash_num, int device, uint32_t sh
 int jubann_destroy(jubann_t* h);
 
 /* Tunables, to be set before the first row or query.  Names: "cache_slots" (distinct
- * feature seeds held by the projection cache, default 2^20), "queries_per_pass" (how many
+ * feature seeds whose random vectors the projection cache keeps, default 2^20; features met
+ * after it is full are never refused: their vectors are drawn on the spot, as
+ * lsh_function::random_projection does for every feature), "queries_per_pass" (how many
  * queries share one streaming pass over the table; 0 = automatic), "scan_variant"
  * (0 = automatic, 1 = LDG streaming, 2 = TMA bulk-copy pipeline), "popc_variant" (0 = one
  * POPC per word, 1..4 = carry-save adder trees of growing depth, default 3), "scan_order" (1 = CTAs take turns over
@@ -147,7 +158,8 @@ int jubann_query_rows(jubann_t* h, uint64_t nq, const uint64_t* row_index, uint3
 
 /* ---- device-pointer entry points (bench, torch.distributed / NCCL plumbing) ---- */
 
-/* Bytes of device scratch the _dev query needs for (nq, k); the library owns and grows it. */
+/* jubann_query_sig with device-resident queries and outputs; the library owns and grows the
+ * scratch it needs.  Collective on a sharded handle with a communicator (see below). */
 int jubann_query_sig_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms,
                          uint32_t k, uint32_t flags, uint64_t* d_out_index, float* d_out_score,
                          uint32_t* d_out_count, void* stream);
@@ -208,6 +220,53 @@ int jubann_diff_record_bytes(jubann_t* h, uint32_t* bytes);
 int jubann_diff_pack_dev(jubann_t* h, uint64_t n, const uint64_t* d_row_index, void* d_records,
                          void* stream);
 int jubann_diff_apply_dev(jubann_t* h, uint64_t n, const void* d_records, void* stream);
+
+/* ---- more than one GPU (NCCL over NVLink under this library) -------------------------------
+ *
+ * The reference spreads one model over servers with its proxy (framework/proxy.hpp:249-266
+ * broadcasts a query, aggregators.hpp:27-63 fold the answers) and keeps replicas in step with
+ * its mixers (framework/mixer/push_mixer.cpp:410-472, linear_mixer.cpp:547-561,613-628).  Here
+ * the GPUs of one box play those roles and the exchanges are collectives inside the library, so
+ * that the C++ host needs nothing but these calls.
+ *
+ * (1) One process, several GPUs -- SURVEY 8(b)'s jubann_create(..., devices[], ndev, ...):
+ * replaces create_nearest_neighbor + new column_table (nearest_neighbor_serv.cpp:98-109) by a
+ * table whose rows are sharded round-robin over devices[0..ndev).  The handle answers every
+ * host-pointer entry point above (set_option, clear, size, hash_csr, set_rows_*, get_rows_sig,
+ * move_row, truncate, query_*, stats); a query is: signatures to every GPU, shard-local scan,
+ * one all-gather of packed (key, global index) candidates, merge -- bit-exactly the single-table
+ * answer.  _dev entry points refuse such a handle. */
+int jubann_create_multi(const char* method, uint32_t hash_num, const int* devices, int ndev, jubann_t** out);
+
+/* (2) One process per GPU.  Rank 0 obtains an id (JUBANN_COMM_ID_BYTES bytes) and hands it to the
+ * other ranks by whatever transport the host has (the Jubatus servers: ZooKeeper, where they
+ * already register themselves -- common/membership.cpp; torchrun: the store); then every rank
+ * joins with its handle.  Collective: returns when all `world` ranks have called.  For a handle
+ * created with shard_rank/shard_count the communicator must have the same rank/world; from then
+ * on jubann_query_sig, jubann_query_csr and jubann_query_sig_dev are collective on such a handle:
+ * every rank makes the same call with the same queries and receives the same, global answer.
+ * Handles of replicas (shard_count 1) use the communicator for MIX. */
+#define JUBANN_COMM_ID_BYTES 128
+int jubann_comm_unique_id(void* id);
+int jubann_comm_init(jubann_t* h, const void* id, uint32_t rank, uint32_t world);
+int jubann_comm_info(jubann_t* h, uint32_t* rank, uint32_t* world);
+
+/* MIX between replicas as collectives (mixable_versioned_table get_diff / put_diff,
+ * linear_mixer.cpp:547-561,613-628; pull / push, push_mixer.cpp:410-472).  Every replica calls
+ * jubann_mix_allgather with the rows it has changed since the last round (row_index: n local
+ * rows) and an opaque blob the host has serialised for them (keys, owners, clocks: strings stay
+ * the host's business).  One all-gather of the counts and one of the payload -- the rows'
+ * signature records packed on the device, followed by the blob -- leave on every replica:
+ * out_rows[r] / out_blob_bytes[r] for each rank r, out_blobs[r] = rank r's blob (pinned memory
+ * owned by the handle, valid until the next MIX call), and the gathered records on the device.
+ * The host then decides, per gathered record, whether it is newer than what it holds (newer
+ * clock wins; unknown keys append) and calls jubann_mix_apply with the m records to store:
+ * record src_pos[e] of rank src_rank[e] goes to local row dst_row[e] (append when equal to the
+ * current size; if a row is named twice the later entry wins). */
+int jubann_mix_allgather(jubann_t* h, uint64_t n, const uint64_t* row_index, const void* blob, uint64_t blob_bytes,
+                         uint64_t* out_rows, uint64_t* out_blob_bytes, const void** out_blobs);
+int jubann_mix_apply(jubann_t* h, uint64_t m, const uint32_t* src_rank, const uint32_t* src_pos,
+                     const uint64_t* dst_row);
 
 /* Introspection for bench.py / tests: kernels launched by this handle since the last reset;
  * scan-kernel launches; streaming passes over the table (a launch covers several passes

@@ -76,7 +76,7 @@ def build_cuda(verbose=False):
             for o in outs:
                 print(o)
     if jobs or _newer(LIB, objs):
-        _run([nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+        _run([nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-ldl"])
     return LIB
 
 

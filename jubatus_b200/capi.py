@@ -19,7 +19,10 @@ EXPORTS = [
     "jubann_set_rows_sig_dev", "jubann_scan_local_dev", "jubann_merge_dev",
     "jubann_diff_record_bytes", "jubann_diff_pack_dev", "jubann_diff_apply_dev", "jubann_stats",
     "jubann_stats_reset", "jubann_query_sig_noalloc_dev", "jubann_hash_csr_dev", "jubann_set_rows_csr_dev",
+    "jubann_create_multi", "jubann_comm_unique_id", "jubann_comm_init", "jubann_comm_info",
+    "jubann_mix_allgather", "jubann_mix_apply",
 ]
+COMM_ID_BYTES = 128
 
 
 class JubannError(RuntimeError):
@@ -86,6 +89,13 @@ def load_library():
         "jubann_diff_apply_dev": [H, ctypes.c_uint64, _vp, _vp],
         "jubann_stats": [H, _u64p, _u64p, _u64p, ctypes.POINTER(ctypes.c_double)],
         "jubann_stats_reset": [H, ctypes.c_int],
+        "jubann_create_multi": [ctypes.c_char_p, ctypes.c_uint32, ctypes.POINTER(ctypes.c_int), ctypes.c_int,
+                                ctypes.POINTER(_vp)],
+        "jubann_comm_unique_id": [_vp],
+        "jubann_comm_init": [H, _vp, ctypes.c_uint32, ctypes.c_uint32],
+        "jubann_comm_info": [H, _u32p, _u32p],
+        "jubann_mix_allgather": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint64, _vp, _vp, _vp],
+        "jubann_mix_apply": [H, ctypes.c_uint64, _vp, _vp, _vp],
     }
     for name, argtypes in sig.items():
         fn = getattr(lib, name)
@@ -117,11 +127,18 @@ class Engine(object):
     (config/nearest_neighbor/*.json `parameter.hash_num`).
     """
 
-    def __init__(self, method, hash_num, device=0, shard_rank=0, shard_count=1, **options):
+    def __init__(self, method, hash_num, device=0, shard_rank=0, shard_count=1, devices=None, **options):
         self._lib = load_library()
         self._h = _vp()
-        _check(self._lib.jubann_create(method.encode(), int(hash_num), int(device), int(shard_rank),
-                                       int(shard_count), ctypes.byref(self._h)))
+        if devices is not None:   # one process, several GPUs: rows sharded over the device list
+            devs = (ctypes.c_int * len(devices))(*[int(d) for d in devices])
+            _check(self._lib.jubann_create_multi(method.encode(), int(hash_num), devs, len(devices),
+                                                 ctypes.byref(self._h)))
+            device = devices[0] if len(devices) else 0
+        else:
+            _check(self._lib.jubann_create(method.encode(), int(hash_num), int(device), int(shard_rank),
+                                           int(shard_count), ctypes.byref(self._h)))
+        self.devices = None if devices is None else [int(d) for d in devices]
         self.method = method
         self.hash_num = int(hash_num)
         self.w64 = (self.hash_num + 63) // 64
@@ -295,6 +312,42 @@ class Engine(object):
 
     def diff_apply_dev(self, n, d_records, stream=0):
         _check(self._lib.jubann_diff_apply_dev(self._h, int(n), _vp(d_records), _vp(stream) if stream else None))
+
+    # -- collectives under the C-ABI -------------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        """The id rank 0 hands to the other ranks (bytes of length COMM_ID_BYTES)."""
+        buf = (ctypes.c_ubyte * COMM_ID_BYTES)()
+        _check(load_library().jubann_comm_unique_id(ctypes.cast(buf, _vp)))
+        return bytes(buf)
+
+    def comm_init(self, comm_id, rank, world):
+        buf = (ctypes.c_ubyte * COMM_ID_BYTES).from_buffer_copy(bytes(comm_id)) if comm_id is not None else None
+        _check(self._lib.jubann_comm_init(self._h, ctypes.cast(buf, _vp) if buf is not None else None, int(rank), int(world)))
+
+    def comm_info(self):
+        r, w = ctypes.c_uint32(), ctypes.c_uint32()
+        _check(self._lib.jubann_comm_info(self._h, ctypes.byref(r), ctypes.byref(w)))
+        return r.value, w.value
+
+    def mix_allgather(self, row_index, blob):
+        """One MIX round's exchange: returns (rows per rank, [blob of every rank])."""
+        _, world = self.comm_info()
+        row_index = _arr(row_index, np.uint64)
+        blob = bytes(blob)
+        rows = np.zeros(world, dtype=np.uint64)
+        sizes = np.zeros(world, dtype=np.uint64)
+        ptrs = (ctypes.c_void_p * world)()
+        _check(self._lib.jubann_mix_allgather(self._h, len(row_index), _ptr(row_index), ctypes.c_char_p(blob) if blob else None,
+                                              len(blob), _ptr(rows), _ptr(sizes), ctypes.cast(ptrs, _vp)))
+        blobs = [ctypes.string_at(ptrs[r], int(sizes[r])) if sizes[r] else b"" for r in range(world)]
+        return rows, blobs
+
+    def mix_apply(self, src_rank, src_pos, dst_row):
+        src_rank = _arr(src_rank, np.uint32)
+        src_pos = _arr(src_pos, np.uint32)
+        dst_row = _arr(dst_row, np.uint64)
+        _check(self._lib.jubann_mix_apply(self._h, len(dst_row), _ptr(src_rank), _ptr(src_pos), _ptr(dst_row)))
 
     # -- stats ---------------------------------------------------------------
     def stats(self):

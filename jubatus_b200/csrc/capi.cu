@@ -1,8 +1,7 @@
 // extern "C" surface of libjubann.so (declared in include/jubann.h): handle, device
 // memory, batching and error plumbing around the kernels in scan.cu / signature.cu /
 // table.cu.  No CPU fallback: every entry point needs a CUDA device.
-#include "../../include/jubann.h"
-#include "internal.h"
+#include "handle.h"
 
 #include <math.h>
 #include <stdarg.h>
@@ -10,13 +9,13 @@
 #include <string.h>
 
 #include <algorithm>
+#include <unordered_set>
 
 using namespace jbn;
 
-namespace {
-
 thread_local std::string g_last_error;
 
+namespace jbn {
 int fail(int code, const char* fmt, ...) {
   char buf[512];
   va_list ap;
@@ -27,93 +26,11 @@ int fail(int code, const char* fmt, ...) {
   return code;
 }
 
-// Requests whose inputs and results fit this many bytes take the latency path: one pinned
-// staging buffer, one host->device copy, one device->host copy, one synchronisation.
-static const size_t SMALL_STAGE_BYTES = 1u << 20;
-
-struct DevBuf {
-  void* p = nullptr;
-  size_t cap = 0;
-  cudaError_t ensure(size_t bytes) {
-    if (bytes <= cap) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr; cap = 0;
-    size_t want = std::max(bytes, (size_t)4096);
-    cudaError_t e = cudaMalloc(&p, want);
-    if (e == cudaSuccess) cap = want;
-    return e;
-  }
-  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
-  template <typename T> T* as() { return static_cast<T*>(p); }
-};
-
-}  // namespace
-
-struct jubann {
-  std::mutex mu;
-  int device = 0;
-  Method method = LSH;
-  uint32_t hash_num = 0, w64 = 0, w32 = 0;
-  uint32_t shard_rank = 0, shard_count = 1;
-  int num_sms = 148;
-  cudaStream_t stream = nullptr;
-  // table
-  void* slab = nullptr;
-  float* norms = nullptr;
-  uint64_t cap_rows = 0;     // local capacity (multiple of 32)
-  uint64_t local_rows = 0;
-  uint64_t global_rows = 0;
-  // projection cache
-  ProjCache cache{};
-  bool cache_ready = false;
-  uint32_t cache_slots_opt = 1u << 20;
-  double* d_coslut = nullptr;
-  uint32_t* h_counters = nullptr;  // pinned
-  unsigned char* h_stage = nullptr;  // pinned, SMALL_STAGE_BYTES: small requests go through one copy each way
-  // options
-  uint32_t qp_opt = 0;
-  int variant_opt = 0;
-  int popc_variant_opt = 3;   // 7 carry-save adders, 9 POPC per 512-bit pair: best measured on B200 (1: 5 adders, 11 POPC)
-  int interleave_opt = 1;
-  // staging (grow-only)
-  DevBuf b_indptr, b_seed, b_keyhash, b_vals, b_rowidx, b_sigs, b_norms;
-  DevBuf b_qsigs, b_qnorms, b_out_idx, b_out_score, b_out_count, b_cand, b_floor, b_tau, b_hist, b_stage;
-  // stats
-  uint64_t kernel_launches = 0, scan_launches = 0, scan_passes = 0;
-  bool time_scan = false;
-  std::vector<std::pair<cudaEvent_t, cudaEvent_t> > scan_events;
-  double scan_ms = 0.0;
-  // sticky error
-  bool cuda_failed = false;
-  std::string sticky;
-};
-
-namespace {
-
 int cuda_fail(jubann_t* h, cudaError_t e, const char* what) {
   h->cuda_failed = true;
   h->sticky = std::string(what) + ": " + cudaGetErrorString(e);
   return fail(JUBANN_E_CUDA, "%s", h->sticky.c_str());
 }
-
-#define CK(call)                                                    \
-  do {                                                              \
-    cudaError_t e_ = (call);                                        \
-    if (e_ != cudaSuccess) return cuda_fail(h, e_, #call);          \
-  } while (0)
-
-struct Guard {
-  jubann_t* h;
-  std::unique_lock<std::mutex> lk;
-  int prev_dev = -1;
-  explicit Guard(jubann_t* hh) : h(hh), lk(hh->mu) {
-    cudaGetDevice(&prev_dev);
-    if (prev_dev != h->device) cudaSetDevice(h->device);
-  }
-  ~Guard() {
-    if (prev_dev >= 0 && prev_dev != h->device) cudaSetDevice(prev_dev);
-  }
-};
 
 int check_handle(jubann_t* h) {
   if (!h) return fail(JUBANN_E_INVALID, "null handle");
@@ -131,6 +48,13 @@ TableView view(jubann_t* h) {
 uint64_t local_count(uint64_t global_rows, uint32_t rank, uint32_t G) {
   return global_rows > rank ? (global_rows - rank + G - 1) / G : 0;
 }
+}  // namespace jbn
+
+namespace jbn {
+
+// Requests whose inputs and results fit this many bytes take the latency path: one pinned
+// staging buffer, one host->device copy, one device->host copy, one synchronisation.
+static const size_t SMALL_STAGE_BYTES = 1u << 20;
 
 // grow the slab (and norm column) to hold `rows` local rows; contents are preserved
 int ensure_rows(jubann_t* h, uint64_t rows) {
@@ -193,16 +117,17 @@ void free_cache(jubann_t* h) {
   if (c.fill_list) cudaFree(c.fill_list);
   c = ProjCache{};
   h->cache_ready = false;
+  h->cache_used_ub = 0;
 }
 
 // CSR already on the device -> signatures (+norms) on the device
 int hash_device(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d_indptr, const uint32_t* d_seed,
                 const uint64_t* d_keyhash, const float* d_vals, uint64_t* d_sigs, float* d_norms,
-                cudaStream_t st = nullptr, bool use_handle_stream = true) {
+                cudaStream_t st, bool use_handle_stream) {
   if (use_handle_stream) st = h->stream;
   int launches = 0;
   if (h->method == MINHASH) {
-    CK(launch_signature_minhash(h->hash_num, n, d_indptr, d_keyhash, d_vals, d_sigs, d_norms, h->w64, st));
+    CK(launch_signature_minhash(h->hash_num, n, d_indptr, d_keyhash, d_vals, d_sigs, d_norms, h->w64, h->num_sms, st));
     ++launches;
   } else {
     int rc = ensure_cache(h);
@@ -210,28 +135,21 @@ int hash_device(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d_indptr,
     CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, st, &launches));
     CK(cudaMemcpyAsync(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    if (h->h_counters[2]) {
-      return fail(JUBANN_E_CACHE_FULL,
-                  "projection cache full: more than %u distinct features (raise option cache_slots, then clear)",
-                  h->cache.slots);
-    }
+    // a full cache is not an error: features without a row are drawn on the spot by the
+    // signature kernel, as the reference draws every feature (h_counters[2] counts them)
     const uint32_t nfill = h->h_counters[1];
+    h->cache_used_ub = h->h_counters[0];
     if (nfill) {
       CK(launch_cache_fill(h->cache, nfill, h->num_sms, st, &launches));
       CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, st));
     }
     CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, n, d_indptr, d_seed, d_vals, d_sigs, d_norms,
-                            h->w64, st));
+                            h->w64, h->num_sms, h->cache_used_ub >= h->cache.slots, st));
     ++launches;
   }
   h->kernel_launches += launches;
   return 0;
 }
-
-struct CsrDev {
-  uint64_t nnz;
-  const uint64_t* indptr; const uint32_t* seed; const uint64_t* keyhash; const float* vals;
-};
 
 // stage rows [r0, r1) of a host CSR batch on the device (indptr rebased to 0)
 int stage_csr(jubann_t* h, uint64_t r0, uint64_t r1, const uint64_t* indptr, const uint32_t* seed32,
@@ -267,24 +185,72 @@ int stage_csr(jubann_t* h, uint64_t r0, uint64_t r1, const uint64_t* indptr, con
 
 const uint64_t CSR_CHUNK_ROWS = 1u << 18;
 
-// validates row indices (append or overwrite, no holes) and returns the new global size
+// validates row indices (append or overwrite, no holes) and returns the new global size.
+// A shard of a sharded table may be handed every row (it keeps its own) or only the rows it owns:
+// what must not skip is the shard's own slots.
 int check_row_indices(jubann_t* h, uint64_t n, const uint64_t* row_index, uint64_t* new_global) {
   uint64_t g = h->global_rows;
-  for (uint64_t r = 0; r < n; ++r) {
-    if (row_index[r] > g) return fail(JUBANN_E_RANGE, "row index %llu skips past the table end %llu", (unsigned long long)row_index[r], (unsigned long long)g);
-    if (row_index[r] == g) ++g;
+  if (h->shard_count == 1) {
+    for (uint64_t r = 0; r < n; ++r) {
+      if (row_index[r] > g) return fail(JUBANN_E_RANGE, "row index %llu skips past the table end %llu", (unsigned long long)row_index[r], (unsigned long long)g);
+      if (row_index[r] == g) ++g;
+    }
+    *new_global = g;
+    return 0;
   }
+  const uint32_t G = h->shard_count, rank = h->shard_rank;
+  uint64_t loc = h->local_rows;
+  for (uint64_t r = 0; r < n; ++r) {
+    const uint64_t idx = row_index[r];
+    if (idx == IDX_SENTINEL) return fail(JUBANN_E_RANGE, "row index out of range");
+    if (idx % G == rank) {
+      const uint64_t i = idx / G;
+      if (i > loc) return fail(JUBANN_E_RANGE, "row index %llu skips past the end of shard %u (%llu local rows)", (unsigned long long)idx, rank, (unsigned long long)loc);
+      if (i == loc) ++loc;
+    }
+    if (idx >= g) g = idx + 1;
+  }
+  if (local_count(g, rank, G) != loc)
+    return fail(JUBANN_E_RANGE, "rows owned by shard %u are missing from the batch (table would end at %llu)", rank, (unsigned long long)g);
   *new_global = g;
   return 0;
 }
 
-int grow_to(jubann_t* h, uint64_t new_global) {
+// Capacity first, sizes last: a set_rows call that fails half way (allocation, CUDA error) leaves
+// global_rows / local_rows as they were, so no row that was never stored becomes queryable.
+int reserve_global(jubann_t* h, uint64_t new_global) {
   const uint64_t nl = local_count(new_global, h->shard_rank, h->shard_count);
   if (nl > 0xFFFFFFF0ull) return fail(JUBANN_E_RANGE, "more than 2^32-16 rows per shard are not supported");
-  int rc = ensure_rows(h, nl);
-  if (rc) return rc;
+  return ensure_rows(h, nl);
+}
+void commit_global(jubann_t* h, uint64_t new_global) {
+  if (new_global <= h->global_rows) return;
   h->global_rows = new_global;
-  h->local_rows = nl;
+  h->local_rows = local_count(new_global, h->shard_rank, h->shard_count);
+}
+// view of the table as it will be once `new_global` rows are committed (for the scatter of a
+// batch that appends: the kernel only needs the slab, but keep local_rows truthful)
+static TableView view_grown(jubann_t* h, uint64_t new_global) {
+  TableView t = view(h);
+  t.local_rows = std::max<uint64_t>(t.local_rows, local_count(new_global, h->shard_rank, h->shard_count));
+  return t;
+}
+
+void strike_repeated_rows(uint64_t* idx, uint64_t n) {
+  if (n < 2) return;
+  bool increasing = true;
+  for (uint64_t r = 1; r < n && increasing; ++r) increasing = idx[r] > idx[r - 1];
+  if (increasing) return;   // the common batch: appends / distinct rows in order
+  std::unordered_set<uint64_t> seen;
+  seen.reserve((size_t)n * 2);
+  for (uint64_t r = n; r-- > 0;)
+    if (idx[r] != IDX_SENTINEL && !seen.insert(idx[r]).second) idx[r] = IDX_SENTINEL;   // a later entry wins
+}
+
+int order_after_caller_stream(jubann_t* h, cudaStream_t st) {
+  if (st == h->stream) return 0;
+  CK(cudaEventRecord(h->dev_write_event, st));
+  CK(cudaStreamWaitEvent(h->stream, h->dev_write_event, 0));
   return 0;
 }
 
@@ -376,13 +342,34 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
   return 0;
 }
 
-}  // namespace
+}  // namespace jbn
+
+// multi-device handles forward to comm.cu under the group's own lock
+#define GROUP_DISPATCH(expr)                              \
+  if (!h->shards.empty()) {                               \
+    std::lock_guard<std::mutex> group_lock(h->mu);        \
+    return (expr);                                        \
+  }
+#define NOT_FOR_GROUPS()                                  \
+  if (!h->shards.empty())                                 \
+    return fail(JUBANN_E_INVALID, "device-pointer entry points address one GPU: use the shard handles or the host-pointer entry points")
+
+// final answers for a query batch already on the device: the plain scan for a whole table, the
+// collective one for a shard whose handle has a communicator
+static int answer_device(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms, uint32_t k,
+                         uint32_t flags, uint64_t* d_out_index, float* d_out_score, uint32_t* d_out_count,
+                         cudaStream_t s) {
+  if (h->shard_count == 1)
+    return query_device(h, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count, nullptr, nullptr, s);
+  return sharded_query_device(h, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count, s);
+}
 
 namespace jbn {
 int set_error(int code, const char* message) { return fail(code, "%s", message); }
 int handle_info(jubann* h, HandleInfo* out) {
   int rc = check_handle(h);
   if (rc) return rc;
+  NOT_FOR_GROUPS();
   out->table = view(h);
   out->device = h->device;
   out->euclid = (h->method == EUCLID_LSH);
@@ -434,6 +421,7 @@ int jubann_create(const char* method, uint32_t hash_num, int device, uint32_t sh
   ok = ok && cudaGetDeviceProperties(&prop, device) == cudaSuccess;
   if (ok) h->num_sms = prop.multiProcessorCount;
   ok = ok && cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&h->dev_write_event, cudaEventDisableTiming) == cudaSuccess;
   ok = ok && cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 16) == cudaSuccess;
   ok = ok && cudaMallocHost(reinterpret_cast<void**>(&h->h_stage), SMALL_STAGE_BYTES) == cudaSuccess;
   ok = ok && h->b_stage.ensure(SMALL_STAGE_BYTES) == cudaSuccess;
@@ -463,9 +451,16 @@ int jubann_create(const char* method, uint32_t hash_num, int device, uint32_t sh
 
 int jubann_destroy(jubann_t* h) {
   if (!h) return 0;
+  if (!h->shards.empty()) {   // multi-device handle: the shards own everything
+    comm_destroy(h);
+    delete h;
+    return 0;
+  }
   {
     Guard g(h);
     cudaStreamSynchronize(h->stream);
+    comm_destroy(h);
+    if (h->dev_write_event) cudaEventDestroy(h->dev_write_event);
     if (h->slab) cudaFree(h->slab);
     if (h->norms) cudaFree(h->norms);
     free_cache(h);
@@ -486,6 +481,7 @@ int jubann_set_option(jubann_t* h, const char* name, int64_t value) {
   int rc = check_handle(h);
   if (rc) return rc;
   if (!name) return fail(JUBANN_E_INVALID, "option name is null");
+  GROUP_DISPATCH(group_set_option(h, name, value));
   Guard g(h);
   if (!strcmp(name, "cache_slots")) {
     if (value < 1 || value > (1ll << 28)) return fail(JUBANN_E_INVALID, "cache_slots out of range");
@@ -536,6 +532,7 @@ int jubann_set_option(jubann_t* h, const char* name, int64_t value) {
 int jubann_clear(jubann_t* h) {
   int rc = check_handle(h);
   if (rc) return rc;
+  GROUP_DISPATCH(group_clear(h));
   Guard g(h);
   CK(cudaStreamSynchronize(h->stream));
   if (h->slab) CK(cudaMemsetAsync(h->slab, 0, slab_bytes(h->w32, h->cap_rows), h->stream));
@@ -543,13 +540,17 @@ int jubann_clear(jubann_t* h) {
   CK(cudaStreamSynchronize(h->stream));
   h->local_rows = 0;
   h->global_rows = 0;
-  if (h->cache_ready && h->h_counters[2]) free_cache(h);  // a cache that overflowed is rebuilt
+  if (h->cache_ready) {   // a cache that ran full is rebuilt, so that the next table's features get the rows
+    CK(cudaMemcpy(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost));
+    if (h->h_counters[0] >= h->cache.slots) free_cache(h);
+  }
   return 0;
 }
 
 int jubann_size(jubann_t* h, uint64_t* global_rows, uint64_t* local_rows) {
   int rc = check_handle(h);
   if (rc) return rc;
+  GROUP_DISPATCH(group_size(h, global_rows, local_rows));
   Guard g(h);
   if (global_rows) *global_rows = h->global_rows;
   if (local_rows) *local_rows = h->local_rows;
@@ -562,6 +563,7 @@ int jubann_hash_csr(jubann_t* h, uint64_t n, const uint64_t* indptr, const uint3
   if (rc) return rc;
   if (n == 0) return 0;
   if (!indptr || !out_sigs) return fail(JUBANN_E_INVALID, "null argument");
+  GROUP_DISPATCH(group_hash_csr(h, n, indptr, seed32, keyhash64, vals, out_sigs, out_norms));
   Guard g(h);
   for (uint64_t r0 = 0; r0 < n; r0 += CSR_CHUNK_ROWS) {
     const uint64_t r1 = std::min(n, r0 + CSR_CHUNK_ROWS), m = r1 - r0;
@@ -579,23 +581,40 @@ int jubann_hash_csr(jubann_t* h, uint64_t n, const uint64_t* indptr, const uint3
   return 0;
 }
 
-static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index, const uint64_t* indptr,
-                              const uint32_t* seed32, const uint64_t* keyhash64, const float* vals, bool* taken);
+// A batch may name the same destination row twice (the host's set_rows with a repeated id, a MIX
+// round in which two replicas updated one key): column_table::add applied in order lets the last
+// one win.  Returns row_index itself when no row repeats, else a copy in `tmp` with the earlier
+// entries struck out.
+static const uint64_t* last_wins(const uint64_t* row_index, uint64_t n, std::vector<uint64_t>& tmp) {
+  bool increasing = true;
+  for (uint64_t r = 1; r < n && increasing; ++r) increasing = row_index[r] > row_index[r - 1];
+  if (increasing) return row_index;
+  tmp.assign(row_index, row_index + n);
+  strike_repeated_rows(tmp.data(), n);
+  return tmp.data();
+}
+
+static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index, uint64_t new_global,
+                              const uint64_t* indptr, const uint32_t* seed32, const uint64_t* keyhash64,
+                              const float* vals, bool* taken);
 int jubann_set_rows_csr(jubann_t* h, uint64_t n, const uint64_t* row_index, const uint64_t* indptr,
                         const uint32_t* seed32, const uint64_t* keyhash64, const float* vals) {
   int rc = check_handle(h);
   if (rc) return rc;
   if (n == 0) return 0;
   if (!row_index || !indptr) return fail(JUBANN_E_INVALID, "null argument");
+  GROUP_DISPATCH(group_set_rows_csr(h, n, row_index, indptr, seed32, keyhash64, vals));
   Guard g(h);
   uint64_t new_global;
   rc = check_row_indices(h, n, row_index, &new_global);
   if (rc) return rc;
-  rc = grow_to(h, new_global);
+  rc = reserve_global(h, new_global);   // capacity only: the sizes move once every row is stored
   if (rc) return rc;
+  std::vector<uint64_t> tmp;
+  row_index = last_wins(row_index, n, tmp);
   {
     bool taken = false;
-    rc = set_rows_csr_small(h, n, row_index, indptr, seed32, keyhash64, vals, &taken);
+    rc = set_rows_csr_small(h, n, row_index, new_global, indptr, seed32, keyhash64, vals, &taken);
     if (rc || taken) return rc;
   }
   for (uint64_t r0 = 0; r0 < n; r0 += CSR_CHUNK_ROWS) {
@@ -609,11 +628,12 @@ int jubann_set_rows_csr(jubann_t* h, uint64_t n, const uint64_t* row_index, cons
     CK(cudaMemcpyAsync(h->b_rowidx.p, row_index + r0, m * 8, cudaMemcpyHostToDevice, h->stream));
     rc = hash_device(h, m, d.nnz, d.indptr, d.seed, d.keyhash, d.vals, h->b_sigs.as<uint64_t>(), h->b_norms.as<float>());
     if (rc) return rc;
-    CK(launch_scatter_rows(view(h), m, h->b_rowidx.as<uint64_t>(), 0, h->b_sigs.as<uint64_t>(),
-                           h->b_norms.as<float>(), h->shard_rank, h->shard_count, h->stream));
+    CK(launch_scatter_rows(view_grown(h, new_global), m, h->b_rowidx.as<uint64_t>(), 0, h->b_sigs.as<uint64_t>(),
+                           h->b_norms.as<float>(), h->shard_rank, h->shard_count, h->num_sms, h->stream));
     h->kernel_launches += 1;
     CK(cudaStreamSynchronize(h->stream));
   }
+  commit_global(h, new_global);
   return 0;
 }
 
@@ -623,12 +643,15 @@ int jubann_set_rows_sig(jubann_t* h, uint64_t n, const uint64_t* row_index, cons
   if (rc) return rc;
   if (n == 0) return 0;
   if (!row_index || !sigs) return fail(JUBANN_E_INVALID, "null argument");
+  GROUP_DISPATCH(group_set_rows_sig(h, n, row_index, sigs, norms));
   Guard g(h);
   uint64_t new_global;
   rc = check_row_indices(h, n, row_index, &new_global);
   if (rc) return rc;
-  rc = grow_to(h, new_global);
+  rc = reserve_global(h, new_global);
   if (rc) return rc;
+  std::vector<uint64_t> tmp;
+  row_index = last_wins(row_index, n, tmp);
   CK(h->b_sigs.ensure(n * h->w64 * 8));
   CK(h->b_rowidx.ensure(n * 8));
   CK(cudaMemcpyAsync(h->b_sigs.p, sigs, n * h->w64 * 8, cudaMemcpyHostToDevice, h->stream));
@@ -639,10 +662,11 @@ int jubann_set_rows_sig(jubann_t* h, uint64_t n, const uint64_t* row_index, cons
     CK(cudaMemcpyAsync(h->b_norms.p, norms, n * 4, cudaMemcpyHostToDevice, h->stream));
     dn = h->b_norms.as<float>();
   }
-  CK(launch_scatter_rows(view(h), n, h->b_rowidx.as<uint64_t>(), 0, h->b_sigs.as<uint64_t>(), dn,
-                         h->shard_rank, h->shard_count, h->stream));
+  CK(launch_scatter_rows(view_grown(h, new_global), n, h->b_rowidx.as<uint64_t>(), 0, h->b_sigs.as<uint64_t>(), dn,
+                         h->shard_rank, h->shard_count, h->num_sms, h->stream));
   h->kernel_launches += 1;
   CK(cudaStreamSynchronize(h->stream));
+  commit_global(h, new_global);
   return 0;
 }
 
@@ -652,14 +676,18 @@ int jubann_set_rows_sig_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, c
   if (rc) return rc;
   if (n == 0) return 0;
   if (!d_sigs) return fail(JUBANN_E_INVALID, "null argument");
+  NOT_FOR_GROUPS();
   Guard g(h);
   if (first_row_index > h->global_rows) return fail(JUBANN_E_RANGE, "row index skips past the table end");
-  rc = grow_to(h, std::max(h->global_rows, first_row_index + n));
+  const uint64_t new_global = std::max(h->global_rows, first_row_index + n);
+  rc = reserve_global(h, new_global);
   if (rc) return rc;
-  CK(launch_scatter_rows(view(h), n, nullptr, first_row_index, d_sigs, h->method == EUCLID_LSH ? d_norms : nullptr,
-                         h->shard_rank, h->shard_count, static_cast<cudaStream_t>(stream)));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CK(launch_scatter_rows(view_grown(h, new_global), n, nullptr, first_row_index, d_sigs, h->method == EUCLID_LSH ? d_norms : nullptr,
+                         h->shard_rank, h->shard_count, h->num_sms, st));
   h->kernel_launches += 1;
-  return 0;
+  commit_global(h, new_global);
+  return order_after_caller_stream(h, st);
 }
 
 int jubann_get_rows_sig(jubann_t* h, uint64_t n, const uint64_t* row_index, uint64_t* out_sigs,
@@ -668,6 +696,7 @@ int jubann_get_rows_sig(jubann_t* h, uint64_t n, const uint64_t* row_index, uint
   if (rc) return rc;
   if (n == 0) return 0;
   if (!row_index || !out_sigs) return fail(JUBANN_E_INVALID, "null argument");
+  GROUP_DISPATCH(group_get_rows_sig(h, n, row_index, out_sigs, out_norms));
   Guard g(h);
   for (uint64_t r = 0; r < n; ++r)
     if (row_index[r] >= h->global_rows) return fail(JUBANN_E_RANGE, "row index %llu out of range", (unsigned long long)row_index[r]);
@@ -676,7 +705,7 @@ int jubann_get_rows_sig(jubann_t* h, uint64_t n, const uint64_t* row_index, uint
   CK(h->b_rowidx.ensure(n * 8));
   CK(cudaMemcpyAsync(h->b_rowidx.p, row_index, n * 8, cudaMemcpyHostToDevice, h->stream));
   CK(launch_gather_rows(view(h), n, h->b_rowidx.as<uint64_t>(), h->b_sigs.as<uint64_t>(), h->b_norms.as<float>(),
-                        h->shard_rank, h->shard_count, h->stream));
+                        h->shard_rank, h->shard_count, h->num_sms, h->stream));
   h->kernel_launches += 1;
   CK(cudaMemcpyAsync(out_sigs, h->b_sigs.p, n * h->w64 * 8, cudaMemcpyDeviceToHost, h->stream));
   if (out_norms) CK(cudaMemcpyAsync(out_norms, h->b_norms.p, n * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -687,6 +716,7 @@ int jubann_get_rows_sig(jubann_t* h, uint64_t n, const uint64_t* row_index, uint
 int jubann_move_row(jubann_t* h, uint64_t src_index, uint64_t dst_index) {
   int rc = check_handle(h);
   if (rc) return rc;
+  GROUP_DISPATCH(group_move_row(h, src_index, dst_index));
   Guard g(h);
   if (src_index >= h->global_rows || dst_index >= h->global_rows) return fail(JUBANN_E_RANGE, "row index out of range");
   if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "move_row is the single-shard fast path; sharded hosts use get_rows_sig + set_rows_sig");
@@ -697,9 +727,9 @@ int jubann_move_row(jubann_t* h, uint64_t src_index, uint64_t dst_index) {
   const uint64_t idx[2] = {src_index, dst_index};
   CK(cudaMemcpyAsync(h->b_rowidx.p, idx, 16, cudaMemcpyHostToDevice, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  CK(launch_gather_rows(view(h), 1, h->b_rowidx.as<uint64_t>(), h->b_sigs.as<uint64_t>(), h->b_norms.as<float>(), 0, 1, h->stream));
+  CK(launch_gather_rows(view(h), 1, h->b_rowidx.as<uint64_t>(), h->b_sigs.as<uint64_t>(), h->b_norms.as<float>(), 0, 1, h->num_sms, h->stream));
   CK(launch_scatter_rows(view(h), 1, h->b_rowidx.as<uint64_t>() + 1, 0, h->b_sigs.as<uint64_t>(),
-                         h->method == EUCLID_LSH ? h->b_norms.as<float>() : nullptr, 0, 1, h->stream));
+                         h->method == EUCLID_LSH ? h->b_norms.as<float>() : nullptr, 0, 1, h->num_sms, h->stream));
   h->kernel_launches += 2;
   CK(cudaStreamSynchronize(h->stream));
   return 0;
@@ -708,6 +738,7 @@ int jubann_move_row(jubann_t* h, uint64_t src_index, uint64_t dst_index) {
 int jubann_truncate(jubann_t* h, uint64_t new_global_rows) {
   int rc = check_handle(h);
   if (rc) return rc;
+  GROUP_DISPATCH(group_truncate(h, new_global_rows));
   Guard g(h);
   if (new_global_rows > h->global_rows) return fail(JUBANN_E_RANGE, "truncate cannot grow the table");
   h->global_rows = new_global_rows;
@@ -762,24 +793,16 @@ static SmallPlan small_plan(const jubann_t* h, uint64_t nq, uint32_t k, size_t i
   return p;
 }
 
-// run the query and bring the results back; `also_counters`: read the projection-cache counters
-// in the same go (the resolve before it may have overflowed the cache)
+// run the query and bring the results back
 static int small_finish(jubann_t* h, const SmallPlan& p, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms,
-                        uint32_t k, uint32_t flags, bool also_counters, uint64_t* out_index, float* out_score,
+                        uint32_t k, uint32_t flags, uint64_t* out_index, float* out_score,
                         uint32_t* out_count) {
   unsigned char* d = h->b_stage.as<unsigned char>();
-  int rc = query_device(h, nq, d_qsigs, d_qnorms, k, flags, reinterpret_cast<uint64_t*>(d + p.idx_off),
-                        reinterpret_cast<float*>(d + p.score_off), reinterpret_cast<uint32_t*>(d + p.count_off), nullptr,
-                        nullptr, h->stream);
+  int rc = answer_device(h, nq, d_qsigs, d_qnorms, k, flags, reinterpret_cast<uint64_t*>(d + p.idx_off),
+                         reinterpret_cast<float*>(d + p.score_off), reinterpret_cast<uint32_t*>(d + p.count_off), h->stream);
   if (rc) return rc;
   CK(cudaMemcpyAsync(h->h_stage + p.out_off, d + p.out_off, p.out_bytes, cudaMemcpyDeviceToHost, h->stream));
-  if (also_counters) CK(cudaMemcpyAsync(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  if (also_counters && h->h_counters[2]) {
-    return fail(JUBANN_E_CACHE_FULL,
-                "projection cache full: more than %u distinct features (raise option cache_slots, then clear)",
-                h->cache.slots);
-  }
   if (k) {
     memcpy(out_index, h->h_stage + p.idx_off, nq * (size_t)k * 8);
     memcpy(out_score, h->h_stage + p.score_off, nq * (size_t)k * 4);
@@ -799,7 +822,7 @@ static int query_sig_small(jubann_t* h, uint64_t nq, const uint64_t* qsigs, cons
   unsigned char* d = h->b_stage.as<unsigned char>();
   CK(cudaMemcpyAsync(d, h->h_stage, sig_b + norm_b, cudaMemcpyHostToDevice, h->stream));
   return small_finish(h, p, nq, reinterpret_cast<const uint64_t*>(d), norm_b ? reinterpret_cast<const float*>(d + sig_b) : nullptr,
-                      k, flags, false, out_index, out_score, out_count);
+                      k, flags, out_index, out_score, out_count);
 }
 
 static int query_csr_small(jubann_t* h, uint64_t nq, const uint64_t* indptr, const uint32_t* seed32,
@@ -833,10 +856,9 @@ static int query_csr_small(jubann_t* h, uint64_t nq, const uint64_t* indptr, con
   uint64_t* d_sigs = reinterpret_cast<uint64_t*>(d + p.sig_off);
   float* d_norms = reinterpret_cast<float*>(d + p.norm_off);
   int launches = 0;
-  bool counters = false;
   if (mh) {
     CK(launch_signature_minhash(h->hash_num, nq, d_ip, reinterpret_cast<const uint64_t*>(d + ip_b + val_b), d_vals, d_sigs,
-                                d_norms, h->w64, h->stream));
+                                d_norms, h->w64, h->num_sms, h->stream));
     ++launches;
   } else {
     int rc = ensure_cache(h);
@@ -845,18 +867,20 @@ static int query_csr_small(jubann_t* h, uint64_t nq, const uint64_t* indptr, con
     CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, h->stream, &launches));
     CK(launch_cache_fill_queued(h->cache, nnz, h->num_sms, h->stream, &launches));
     if (nnz) CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, h->stream));
-    CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, nq, d_ip, d_seed, d_vals, d_sigs, d_norms, h->w64, h->stream));
+    h->cache_used_ub += nnz;   // the count is not read back on this path: every feature may have been new
+    CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, nq, d_ip, d_seed, d_vals, d_sigs, d_norms, h->w64, h->num_sms,
+                            h->cache_used_ub >= h->cache.slots, h->stream));
     ++launches;
-    counters = nnz != 0;
   }
   h->kernel_launches += launches;
-  return small_finish(h, p, nq, d_sigs, d_norms, k, flags, counters, out_index, out_score, out_count);
+  return small_finish(h, p, nq, d_sigs, d_norms, k, flags, out_index, out_score, out_count);
 }
 
 // set_row for a few rows (one RPC): CSR and row indices in one copy, the cache fill off the
-// device-side count, the scatter guarded by the overflow flag, one synchronisation.
-static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index, const uint64_t* indptr,
-                              const uint32_t* seed32, const uint64_t* keyhash64, const float* vals, bool* taken) {
+// device-side count, one synchronisation.
+static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index, uint64_t new_global,
+                              const uint64_t* indptr, const uint32_t* seed32, const uint64_t* keyhash64,
+                              const float* vals, bool* taken) {
   *taken = false;
   const uint64_t base = indptr[0], nnz = indptr[n] - base;
   if (indptr[n] < base || nnz > SMALL_STAGE_BYTES / 4) return 0;
@@ -888,10 +912,9 @@ static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index
   uint64_t* d_sigs = reinterpret_cast<uint64_t*>(d + sig_off);
   float* d_norms = reinterpret_cast<float*>(d + norm_off);
   int launches = 0;
-  const uint32_t* guard = nullptr;
   if (mh) {
     CK(launch_signature_minhash(h->hash_num, n, d_ip, reinterpret_cast<const uint64_t*>(d + ip_b + val_b), d_vals, d_sigs,
-                                d_norms, h->w64, h->stream));
+                                d_norms, h->w64, h->num_sms, h->stream));
     ++launches;
   } else {
     int rc = ensure_cache(h);
@@ -900,19 +923,15 @@ static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index
     CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, h->stream, &launches));
     CK(launch_cache_fill_queued(h->cache, nnz, h->num_sms, h->stream, &launches));
     if (nnz) CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, h->stream));
-    CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, n, d_ip, d_seed, d_vals, d_sigs, d_norms, h->w64, h->stream));
+    h->cache_used_ub += nnz;
+    CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, n, d_ip, d_seed, d_vals, d_sigs, d_norms, h->w64, h->num_sms,
+                            h->cache_used_ub >= h->cache.slots, h->stream));
     ++launches;
-    if (nnz) guard = h->cache.counters + 2;
   }
-  CK(launch_scatter_rows(view(h), n, d_ri, 0, d_sigs, d_norms, h->shard_rank, h->shard_count, h->stream, guard));
+  CK(launch_scatter_rows(view_grown(h, new_global), n, d_ri, 0, d_sigs, d_norms, h->shard_rank, h->shard_count, h->num_sms, h->stream));
   h->kernel_launches += launches + 1;
-  if (guard) CK(cudaMemcpyAsync(h->h_counters, h->cache.counters, 16, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  if (guard && h->h_counters[2]) {
-    return fail(JUBANN_E_CACHE_FULL,
-                "projection cache full: more than %u distinct features (raise option cache_slots, then clear)",
-                h->cache.slots);
-  }
+  commit_global(h, new_global);
   return 0;
 }
 
@@ -923,8 +942,8 @@ int jubann_query_sig(jubann_t* h, uint64_t nq, const uint64_t* qsigs, const floa
   if (nq == 0) return 0;
   if (!qsigs || !out_count || (k && (!out_index || !out_score))) return fail(JUBANN_E_INVALID, "null argument");
   if (h->method == EUCLID_LSH && !qnorms) return fail(JUBANN_E_INVALID, "euclid_lsh queries need norms");
+  GROUP_DISPATCH(group_query_sig(h, nq, qsigs, qnorms, k, flags, out_index, out_score, out_count));
   Guard g(h);
-  if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
   {
     bool taken = false;
     rc = query_sig_small(h, nq, qsigs, qnorms, k, flags, out_index, out_score, out_count, &taken);
@@ -940,8 +959,8 @@ int jubann_query_sig(jubann_t* h, uint64_t nq, const uint64_t* qsigs, const floa
   }
   rc = ensure_query_outputs(h, nq, k);
   if (rc) return rc;
-  rc = query_device(h, nq, h->b_qsigs.as<uint64_t>(), dqn, k, flags, h->b_out_idx.as<uint64_t>(),
-                    h->b_out_score.as<float>(), h->b_out_count.as<uint32_t>(), nullptr, nullptr, h->stream);
+  rc = answer_device(h, nq, h->b_qsigs.as<uint64_t>(), dqn, k, flags, h->b_out_idx.as<uint64_t>(),
+                     h->b_out_score.as<float>(), h->b_out_count.as<uint32_t>(), h->stream);
   if (rc) return rc;
   return query_host_outputs(h, nq, k, out_index, out_score, out_count);
 }
@@ -953,8 +972,8 @@ int jubann_query_csr(jubann_t* h, uint64_t nq, const uint64_t* indptr, const uin
   if (rc) return rc;
   if (nq == 0) return 0;
   if (!indptr || !out_count || (k && (!out_index || !out_score))) return fail(JUBANN_E_INVALID, "null argument");
+  GROUP_DISPATCH(group_query_csr(h, nq, indptr, seed32, keyhash64, vals, k, flags, out_index, out_score, out_count));
   Guard g(h);
-  if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
   {
     bool taken = false;
     rc = query_csr_small(h, nq, indptr, seed32, keyhash64, vals, k, flags, out_index, out_score, out_count, &taken);
@@ -971,8 +990,8 @@ int jubann_query_csr(jubann_t* h, uint64_t nq, const uint64_t* indptr, const uin
     if (rc) return rc;
     rc = ensure_query_outputs(h, m, k);
     if (rc) return rc;
-    rc = query_device(h, m, h->b_qsigs.as<uint64_t>(), h->b_qnorms.as<float>(), k, flags, h->b_out_idx.as<uint64_t>(),
-                      h->b_out_score.as<float>(), h->b_out_count.as<uint32_t>(), nullptr, nullptr, h->stream);
+    rc = answer_device(h, m, h->b_qsigs.as<uint64_t>(), h->b_qnorms.as<float>(), k, flags, h->b_out_idx.as<uint64_t>(),
+                       h->b_out_score.as<float>(), h->b_out_count.as<uint32_t>(), h->stream);
     if (rc) return rc;
     rc = query_host_outputs(h, m, k, out_index + r0 * k, out_score + r0 * k, out_count + r0);
     if (rc) return rc;
@@ -986,6 +1005,7 @@ int jubann_query_rows(jubann_t* h, uint64_t nq, const uint64_t* row_index, uint3
   if (rc) return rc;
   if (nq == 0) return 0;
   if (!row_index || !out_count || (k && (!out_index || !out_score))) return fail(JUBANN_E_INVALID, "null argument");
+  GROUP_DISPATCH(group_query_rows(h, nq, row_index, k, flags, out_index, out_score, out_count));
   Guard g(h);
   if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "query_rows needs a single-shard handle");
   for (uint64_t r = 0; r < nq; ++r)
@@ -998,16 +1018,16 @@ int jubann_query_rows(jubann_t* h, uint64_t nq, const uint64_t* row_index, uint3
       CK(cudaMemcpyAsync(d, h->h_stage, nq * 8, cudaMemcpyHostToDevice, h->stream));
       uint64_t* d_sigs = reinterpret_cast<uint64_t*>(d + p.sig_off);
       float* d_norms = reinterpret_cast<float*>(d + p.norm_off);
-      CK(launch_gather_rows(view(h), nq, reinterpret_cast<const uint64_t*>(d), d_sigs, d_norms, 0, 1, h->stream));
+      CK(launch_gather_rows(view(h), nq, reinterpret_cast<const uint64_t*>(d), d_sigs, d_norms, 0, 1, h->num_sms, h->stream));
       h->kernel_launches += 1;
-      return small_finish(h, p, nq, d_sigs, d_norms, k, flags, false, out_index, out_score, out_count);
+      return small_finish(h, p, nq, d_sigs, d_norms, k, flags, out_index, out_score, out_count);
     }
   }
   CK(h->b_rowidx.ensure(nq * 8));
   CK(h->b_qsigs.ensure(nq * h->w64 * 8));
   CK(h->b_qnorms.ensure(nq * 4));
   CK(cudaMemcpyAsync(h->b_rowidx.p, row_index, nq * 8, cudaMemcpyHostToDevice, h->stream));
-  CK(launch_gather_rows(view(h), nq, h->b_rowidx.as<uint64_t>(), h->b_qsigs.as<uint64_t>(), h->b_qnorms.as<float>(), 0, 1, h->stream));
+  CK(launch_gather_rows(view(h), nq, h->b_rowidx.as<uint64_t>(), h->b_qsigs.as<uint64_t>(), h->b_qnorms.as<float>(), 0, 1, h->num_sms, h->stream));
   h->kernel_launches += 1;
   rc = ensure_query_outputs(h, nq, k);
   if (rc) return rc;
@@ -1024,10 +1044,10 @@ int jubann_query_sig_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, cons
   if (rc) return rc;
   if (nq == 0) return 0;
   if (!d_qsigs || !d_out_count || (k && (!d_out_index || !d_out_score))) return fail(JUBANN_E_INVALID, "null argument");
+  NOT_FOR_GROUPS();
   Guard g(h);
-  if (h->shard_count != 1) return fail(JUBANN_E_INVALID, "sharded handles answer through scan_local_dev + merge_dev");
-  return query_device(h, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count, nullptr, nullptr,
-                      static_cast<cudaStream_t>(stream));
+  return answer_device(h, nq, d_qsigs, d_qnorms, k, flags, d_out_index, d_out_score, d_out_count,
+                       static_cast<cudaStream_t>(stream));
 }
 
 int jubann_hash_csr_dev(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d_indptr, const uint32_t* d_seed32,
@@ -1038,6 +1058,7 @@ int jubann_hash_csr_dev(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d
   if (n == 0) return 0;
   if (!d_indptr || !d_out_sigs || !d_out_norms || (nnz && !d_vals)) return fail(JUBANN_E_INVALID, "null argument");
   if (h->method == MINHASH ? (nnz && !d_keyhash64) : (nnz && !d_seed32)) return fail(JUBANN_E_INVALID, "missing feature hashes for this method");
+  NOT_FOR_GROUPS();
   Guard g(h);
   return hash_device(h, n, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, d_out_sigs, d_out_norms,
                      static_cast<cudaStream_t>(stream), false);
@@ -1050,19 +1071,22 @@ int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, u
   if (n == 0) return 0;
   if (!d_indptr || (nnz && !d_vals)) return fail(JUBANN_E_INVALID, "null argument");
   if (h->method == MINHASH ? (nnz && !d_keyhash64) : (nnz && !d_seed32)) return fail(JUBANN_E_INVALID, "missing feature hashes for this method");
+  NOT_FOR_GROUPS();
   Guard g(h);
   if (first_row_index > h->global_rows) return fail(JUBANN_E_RANGE, "row index skips past the table end");
-  rc = grow_to(h, std::max(h->global_rows, first_row_index + n));
+  const uint64_t new_global = std::max(h->global_rows, first_row_index + n);
+  rc = reserve_global(h, new_global);
   if (rc) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   CK(h->b_sigs.ensure(n * h->w64 * 8));
   CK(h->b_norms.ensure(n * 4));
   rc = hash_device(h, n, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, h->b_sigs.as<uint64_t>(), h->b_norms.as<float>(), st, false);
   if (rc) return rc;
-  CK(launch_scatter_rows(view(h), n, nullptr, first_row_index, h->b_sigs.as<uint64_t>(),
-                         h->method == EUCLID_LSH ? h->b_norms.as<float>() : nullptr, h->shard_rank, h->shard_count, st));
+  CK(launch_scatter_rows(view_grown(h, new_global), n, nullptr, first_row_index, h->b_sigs.as<uint64_t>(),
+                         h->method == EUCLID_LSH ? h->b_norms.as<float>() : nullptr, h->shard_rank, h->shard_count, h->num_sms, st));
   h->kernel_launches += 1;
-  return 0;
+  commit_global(h, new_global);
+  return order_after_caller_stream(h, st);
 }
 
 int jubann_scan_local_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms, uint32_t k,
@@ -1071,6 +1095,7 @@ int jubann_scan_local_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, con
   if (rc) return rc;
   if (nq == 0 || k == 0) return 0;
   if (!d_qsigs || !d_cand_key || !d_cand_index) return fail(JUBANN_E_INVALID, "null argument");
+  NOT_FOR_GROUPS();
   Guard g(h);
   return query_device(h, nq, d_qsigs, d_qnorms, k, 0, nullptr, nullptr, nullptr, d_cand_key, d_cand_index,
                       static_cast<cudaStream_t>(stream));
@@ -1083,6 +1108,7 @@ int jubann_merge_dev(jubann_t* h, uint64_t nq, uint32_t k, uint32_t parts, const
   if (rc) return rc;
   if (nq == 0) return 0;
   if (!d_out_count) return fail(JUBANN_E_INVALID, "null argument");
+  NOT_FOR_GROUPS();
   Guard g(h);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (k == 0 || parts == 0) { CK(cudaMemsetAsync(d_out_count, 0, nq * 4, s)); return 0; }
@@ -1110,8 +1136,9 @@ int jubann_diff_pack_dev(jubann_t* h, uint64_t n, const uint64_t* d_row_index, v
   if (rc) return rc;
   if (n == 0) return 0;
   if (!d_row_index || !d_records) return fail(JUBANN_E_INVALID, "null argument");
+  NOT_FOR_GROUPS();
   Guard g(h);
-  CK(launch_diff_pack(view(h), n, d_row_index, d_records, 8 + 8 * h->w64 + 8, h->shard_rank, h->shard_count,
+  CK(launch_diff_pack(view(h), n, d_row_index, d_records, 8 + 8 * h->w64 + 8, h->shard_rank, h->shard_count, h->num_sms,
                       static_cast<cudaStream_t>(stream)));
   h->kernel_launches += 1;
   return 0;
@@ -1122,17 +1149,19 @@ int jubann_diff_apply_dev(jubann_t* h, uint64_t n, const void* d_records, void* 
   if (rc) return rc;
   if (n == 0) return 0;
   if (!d_records) return fail(JUBANN_E_INVALID, "null argument");
+  NOT_FOR_GROUPS();
   Guard g(h);
-  CK(launch_diff_apply(view(h), n, d_records, 8 + 8 * h->w64 + 8, h->shard_rank, h->shard_count,
-                       static_cast<cudaStream_t>(stream)));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CK(launch_diff_apply(view(h), n, d_records, 8 + 8 * h->w64 + 8, h->shard_rank, h->shard_count, h->num_sms, st));
   h->kernel_launches += 1;
-  return 0;
+  return order_after_caller_stream(h, st);
 }
 
 int jubann_stats(jubann_t* h, uint64_t* kernel_launches, uint64_t* scan_launches, uint64_t* scan_passes,
                  double* scan_ms) {
   int rc = check_handle(h);
   if (rc) return rc;
+  GROUP_DISPATCH(group_stats(h, kernel_launches, scan_launches, scan_passes, scan_ms));
   Guard g(h);
   for (auto& ev : h->scan_events) {
     float ms = 0.0f;
@@ -1152,6 +1181,7 @@ int jubann_stats(jubann_t* h, uint64_t* kernel_launches, uint64_t* scan_launches
 int jubann_stats_reset(jubann_t* h, int time_scan_kernels) {
   int rc = check_handle(h);
   if (rc) return rc;
+  GROUP_DISPATCH(group_stats_reset(h, time_scan_kernels));
   Guard g(h);
   for (auto& ev : h->scan_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
   h->scan_events.clear();

@@ -41,6 +41,17 @@ __host__ __device__ inline uint64_t word_offset(uint32_t w32, uint64_t i, uint32
   return ((t * C + c) * 32 + lane) * (uint64_t)V + r * 4ull;
 }
 
+// Bits of 32-bit word `w` of a signature that lie below hash_num.  Words handed in by callers
+// (stored rows, MIX records, query signatures) are masked with it: storage::bit_vector keeps the
+// unused high bits of its last word zero, and a stray bit there would push a Hamming distance
+// past hash_num -- which indexes the cos table, the euclid bound table and the histogram bins.
+__host__ __device__ inline uint32_t sig_word_mask(uint32_t hash_num, uint32_t w) {
+  const uint32_t lo = w * 32u;
+  if (lo >= hash_num) return 0u;
+  const uint32_t left = hash_num - lo;
+  return left >= 32u ? 0xFFFFFFFFu : ((1u << left) - 1u);
+}
+
 struct TableView {
   void* slab;          // tile-transposed signatures
   float* norms;        // [capacity] (euclid_lsh) or nullptr
@@ -97,29 +108,33 @@ struct MergeOut {
 cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nlists, uint32_t k,
                                const MergeOut& out, cudaStream_t s);
 cudaError_t launch_merge_parts(const uint32_t* d_cand_key, const uint64_t* d_cand_index, uint32_t nq,
-                               uint32_t k, uint32_t parts, const MergeOut& out, cudaStream_t s);
+                               uint32_t k, uint32_t parts, const MergeOut& out, cudaStream_t s,
+                               size_t key_stride = 0, size_t idx_stride = 0);   // strides in elements; 0 = nq * k
 
 // ---- table mutation --------------------------------------------------------
 // rows given row-major ([n][w64] u64 words) -> slab at local slot (g / G) when g % G == rank
 cudaError_t launch_scatter_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                 uint64_t first_index, const uint64_t* d_sigs, const float* d_norms,
-                                uint32_t shard_rank, uint32_t shard_count, cudaStream_t s,
-                                const uint32_t* d_skip_if_nonzero = nullptr);
+                                uint32_t shard_rank, uint32_t shard_count, int num_sms, cudaStream_t s);
 cudaError_t launch_gather_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                uint64_t* d_sigs, float* d_norms, uint32_t shard_rank,
-                               uint32_t shard_count, cudaStream_t s);
+                               uint32_t shard_count, int num_sms, cudaStream_t s);
 cudaError_t launch_diff_pack(const TableView& t, uint64_t n, const uint64_t* d_row_index, void* d_records,
-                             uint32_t record_bytes, uint32_t shard_rank, uint32_t shard_count,
+                             uint32_t record_bytes, uint32_t shard_rank, uint32_t shard_count, int num_sms,
                              cudaStream_t s);
 cudaError_t launch_diff_apply(const TableView& t, uint64_t n, const void* d_records, uint32_t record_bytes,
-                              uint32_t shard_rank, uint32_t shard_count, cudaStream_t s);
+                              uint32_t shard_rank, uint32_t shard_count, int num_sms, cudaStream_t s);
+
+cudaError_t launch_mix_apply(const TableView& t, uint64_t m, const void* d_gathered, uint64_t slot_bytes,
+                             uint32_t record_bytes, const uint32_t* d_src_rank, const uint32_t* d_src_pos,
+                             const uint64_t* d_dst_row, int num_sms, cudaStream_t s);
 
 // ---- signatures ------------------------------------------------------------
 struct ProjCache {
   float* table;        // [slots][hash_num] gaussians narrowed to float
   uint64_t* keys;      // open-addressing keys (0 = empty, else seed | 1<<32)
   uint32_t* slot_of;   // slot per hash-table position
-  uint32_t* counters;  // [0] slots used, [1] fill-list length, [2] overflow flag
+  uint32_t* counters;  // [0] slots handed out (may run past `slots`), [1] fill-list length, [2] feature occurrences met while full (statistic)
   uint2* fill_list;    // (slot, seed) pairs awaiting generation
   uint32_t slots;      // capacity
   uint32_t table_size; // hash table positions (power of two)
@@ -131,10 +146,10 @@ cudaError_t launch_cache_fill(const ProjCache& c, uint32_t nfill, int num_sms, c
 cudaError_t launch_cache_fill_queued(const ProjCache& c, uint64_t max_entries, int num_sms, cudaStream_t s, int* launches);
 cudaError_t launch_signature_lsh(const ProjCache& c, bool euclid, uint64_t n, const uint64_t* d_indptr,
                                  const uint32_t* d_seed32, const float* d_vals, uint64_t* d_sigs,
-                                 float* d_norms, uint32_t w64, cudaStream_t s);
+                                 float* d_norms, uint32_t w64, int num_sms, bool may_miss, cudaStream_t s);
 cudaError_t launch_signature_minhash(uint32_t hash_num, uint64_t n, const uint64_t* d_indptr,
                                      const uint64_t* d_keyhash64, const float* d_vals, uint64_t* d_sigs,
-                                     float* d_norms, uint32_t w64, cudaStream_t s);
+                                     float* d_norms, uint32_t w64, int num_sms, cudaStream_t s);
 
 
 // ---- read-only view of a handle for translation units other than capi.cu ------------

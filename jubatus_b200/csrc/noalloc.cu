@@ -143,8 +143,9 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   // euclid_lsh's two-level score histogram (257 KiB per query) does not fit this fixed array: that
   // engine runs here with each CTA's own bound only
   uint32_t* hist_scratch = hi.euclid ? nullptr : reinterpret_cast<uint32_t*>(tau_scratch + nq);
+  int scan_kernels = 0;   // the scan, plus the sample pre-pass when it runs
   e = launch_scan(hi.table, hi.euclid, cfg, d_qsigs, d_qnorms, hi.coslut, nq, keff, nullptr, tau_scratch, hist_scratch,
-                  static_cast<uint64_t*>(scratch), s);
+                  static_cast<uint64_t*>(scratch), s, &scan_kernels);
   if (e != cudaSuccess) return cuda_error("scan launch (no-alloc)", e);
   MergeOut o{};
   o.kout = k; o.col0 = 0;
@@ -154,6 +155,6 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   o.out_index = d_out_index; o.out_score = d_out_score; o.out_count = d_out_count;
   e = launch_merge_local(static_cast<const uint64_t*>(scratch), nq, cfg.nchunks, keff, o, s);
   if (e != cudaSuccess) return cuda_error("merge launch (no-alloc)", e);
-  handle_add_launches(h, 3, 1, (nq + cfg.qp - 1) / cfg.qp);
+  handle_add_launches(h, (uint64_t)scan_kernels + 1, 1, (nq + cfg.qp - 1) / cfg.qp);   // + the list reduction
   return 0;
 }

@@ -866,7 +866,7 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)(q0 + q) * a.w64);
     uint32_t v;
     if (w < W32) {
-      v = (w < 2 * a.w64) ? src[w] : 0u;
+      v = (w < 2 * a.w64) ? (src[w] & sig_word_mask(a.hash_num, w)) : 0u;   // bits at or above hash_num never count
     } else if (w < W32 + 4) {
       v = tau_hi_of(a.tau_init ? a.tau_init[q0 + q] : KEY_SENTINEL);   // word W32; the pad words carry the same
     } else {   // XOR of the adder triple g of 16-word block b (hamming_t)
@@ -875,7 +875,7 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
       if (g < 5)
         for (uint32_t j = 0; j < 3; ++j) {
           const uint32_t ww = 16 * b + 3 * g + j;
-          if (ww < 2 * a.w64) v ^= src[ww];
+          if (ww < 2 * a.w64) v ^= src[ww] & sig_word_mask(a.hash_num, ww);
         }
     }
     s_q[i] = v;
@@ -1335,9 +1335,11 @@ __device__ __forceinline__ bool cand_less(uint32_t ka, uint64_t ia, uint32_t kb,
   return ka < kb || (ka == kb && ia < ib);
 }
 
+// part p's lists start at ckey + p * key_stride and cidx + p * idx_stride (elements): separate
+// [parts][nq][k] arrays, or the slots of one all-gathered buffer that packs both per rank
 __global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32_t* ckey, const uint64_t* cidx,
                                                                     uint32_t nq, uint32_t k, uint32_t parts,
-                                                                    MergeOut o) {
+                                                                    size_t key_stride, size_t idx_stride, MergeOut o) {
   const uint32_t q = blockIdx.x;
   __shared__ uint32_t s_count;
   if (threadIdx.x == 0) s_count = 0;
@@ -1345,18 +1347,19 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32
   uint32_t mine = 0;
   for (uint32_t e = threadIdx.x; e < parts * k; e += MERGE_THREADS) {
     const uint32_t p = e / k, j = e % k;
-    const size_t at = ((size_t)p * nq + q) * k + j;
-    const uint32_t key = ckey[at];
-    const uint64_t idx = cidx[at];
+    const size_t at = (size_t)q * k + j;
+    const uint32_t key = ckey[(size_t)p * key_stride + at];
+    const uint64_t idx = cidx[(size_t)p * idx_stride + at];
     if (idx == IDX_SENTINEL) continue;
     uint32_t rank = j;
     for (uint32_t p2 = 0; p2 < parts && rank < k; ++p2) {
       if (p2 == p) continue;
-      const size_t b = ((size_t)p2 * nq + q) * k;
+      const uint32_t* k2 = ckey + (size_t)p2 * key_stride + (size_t)q * k;
+      const uint64_t* i2 = cidx + (size_t)p2 * idx_stride + (size_t)q * k;
       uint32_t lo = 0, hi = k;  // first element of list p2 that is not less than (key, idx)
       while (lo < hi) {
         uint32_t mid = (lo + hi) >> 1;
-        if (cand_less(ckey[b + mid], cidx[b + mid], key, idx)) lo = mid + 1; else hi = mid;
+        if (cand_less(k2[mid], i2[mid], key, idx)) lo = mid + 1; else hi = mid;
       }
       rank += lo;
     }
@@ -1628,7 +1631,7 @@ __global__ void __launch_bounds__(TAUH_THREADS) tau_init_hamming_kernel(ScanArgs
   __shared__ uint32_t sq[32];
   if (threadIdx.x < 32) {
     const uint32_t* qw = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)q * a.w64);
-    sq[threadIdx.x] = threadIdx.x < 2 * a.w64 ? qw[threadIdx.x] : 0u;   // padding words of a row are zero
+    sq[threadIdx.x] = threadIdx.x < 2 * a.w64 ? (qw[threadIdx.x] & sig_word_mask(a.hash_num, threadIdx.x)) : 0u;   // padding words of a row are zero
   }
   __syncthreads();
   for (uint32_t i = threadIdx.x; i < S; i += TAUH_THREADS) {
@@ -1686,7 +1689,7 @@ __global__ void __launch_bounds__(TAUE_THREADS) tau_init_euclid_kernel(ScanArgs 
   const int tid = threadIdx.x, lane = tid & 31;
   if (tid < 32) {
     const uint32_t* qw = reinterpret_cast<const uint32_t*>(a.qsigs + (size_t)q * a.w64);
-    sq[tid] = (uint32_t)tid < 2 * a.w64 ? qw[tid] : 0u;
+    sq[tid] = (uint32_t)tid < 2 * a.w64 ? (qw[tid] & sig_word_mask(a.hash_num, (uint32_t)tid)) : 0u;
   }
   if (tid == 0) { s_cnt[0] = 0; s_cnt[1] = 0; s_cnt[2] = 0; s_or = 0; s_and = 0xFFFFFFFFu; }
   if (a.ghist) {   // this query's part of the shared histogram starts from zero, its bound word from "none"
@@ -1848,8 +1851,11 @@ cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nli
 }
 
 cudaError_t launch_merge_parts(const uint32_t* d_cand_key, const uint64_t* d_cand_index, uint32_t nq,
-                               uint32_t k, uint32_t parts, const MergeOut& out, cudaStream_t s) {
-  merge_parts_kernel<<<nq, MERGE_THREADS, 0, s>>>(d_cand_key, d_cand_index, nq, k, parts, out);
+                               uint32_t k, uint32_t parts, const MergeOut& out, cudaStream_t s,
+                               size_t key_stride, size_t idx_stride) {
+  if (key_stride == 0) key_stride = (size_t)nq * k;
+  if (idx_stride == 0) idx_stride = (size_t)nq * k;
+  merge_parts_kernel<<<nq, MERGE_THREADS, 0, s>>>(d_cand_key, d_cand_index, nq, k, parts, key_stride, idx_stride, out);
   return cudaGetLastError();
 }
 

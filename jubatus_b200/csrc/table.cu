@@ -12,10 +12,7 @@ namespace jbn {
 // one thread per (row, 32-bit word): row-major ABI words -> tile-transposed slab
 __global__ void scatter_rows_kernel(TableView t, uint64_t n, const uint64_t* __restrict__ row_index,
                                     uint64_t first_index, const uint64_t* __restrict__ sigs,
-                                    const float* __restrict__ norms, uint32_t rank, uint32_t G,
-                                    const uint32_t* skip_if_nonzero) {
-  // latency path: the projection cache overflowed in this very call, the signatures are not valid
-  if (skip_if_nonzero && *reinterpret_cast<const volatile uint32_t*>(skip_if_nonzero)) return;
+                                    const float* __restrict__ norms, uint32_t rank, uint32_t G) {
   const uint64_t total = n * t.w32;
   unsigned char* slab = static_cast<unsigned char*>(t.slab);
   for (uint64_t e = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; e < total;
@@ -23,10 +20,11 @@ __global__ void scatter_rows_kernel(TableView t, uint64_t n, const uint64_t* __r
     const uint64_t r = e / t.w32;
     const uint32_t w = (uint32_t)(e % t.w32);
     const uint64_t g = row_index ? row_index[r] : first_index + r;
-    if (g % G != rank) continue;
+    // IDX_SENTINEL: an entry the host struck out (a later entry of the batch writes the same row)
+    if (g == IDX_SENTINEL || g % G != rank) continue;
     const uint64_t i = g / G;
     const uint32_t* src = reinterpret_cast<const uint32_t*>(sigs + r * t.w64);
-    const uint32_t v = (w < 2 * t.w64) ? src[w] : 0u;
+    const uint32_t v = (w < 2 * t.w64) ? (src[w] & sig_word_mask(t.hash_num, w)) : 0u;
     *reinterpret_cast<uint32_t*>(slab + word_offset(t.w32, i, w)) = v;
     if (w == 0 && t.norms) t.norms[i] = norms ? norms[r] : 0.0f;
   }
@@ -89,49 +87,78 @@ __global__ void diff_apply_kernel(TableView t, uint64_t n, const unsigned char* 
     if (g == IDX_SENTINEL || g % G != rank) continue;
     const uint64_t i = g / G;
     if (i >= t.local_rows) continue;
-    const uint32_t v = (w < 2 * t.w64) ? reinterpret_cast<const uint32_t*>(in + 8)[w] : 0u;
+    const uint32_t v = (w < 2 * t.w64) ? (reinterpret_cast<const uint32_t*>(in + 8)[w] & sig_word_mask(t.hash_num, w)) : 0u;
     *reinterpret_cast<uint32_t*>(slab + word_offset(t.w32, i, w)) = v;
     if (w == 0 && t.norms) t.norms[i] = *reinterpret_cast<const float*>(in + 8 + 8ull * t.w64);
   }
 }
 
-static unsigned grid_for(uint64_t total) {
+// MIX: entry e copies record src_pos[e] of rank src_rank[e]'s slot of the all-gathered payload
+// into local row dst_row[e] (IDX_SENTINEL = struck out by the host: an older version, or a later
+// entry of this round writes the same row)
+__global__ void mix_apply_kernel(TableView t, uint64_t m, const unsigned char* __restrict__ gathered, uint64_t slot_bytes,
+                                 uint32_t rec_bytes, const uint32_t* __restrict__ src_rank,
+                                 const uint32_t* __restrict__ src_pos, const uint64_t* __restrict__ dst_row) {
+  const uint64_t total = m * t.w32;
+  unsigned char* slab = static_cast<unsigned char*>(t.slab);
+  for (uint64_t e = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; e < total;
+       e += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t r = e / t.w32;
+    const uint32_t w = (uint32_t)(e % t.w32);
+    const uint64_t i = dst_row[r];
+    if (i == IDX_SENTINEL || i >= t.local_rows) continue;
+    const unsigned char* in = gathered + (uint64_t)src_rank[r] * slot_bytes + (uint64_t)src_pos[r] * rec_bytes;
+    const uint32_t v = (w < 2 * t.w64) ? (reinterpret_cast<const uint32_t*>(in + 8)[w] & sig_word_mask(t.hash_num, w)) : 0u;
+    *reinterpret_cast<uint32_t*>(slab + word_offset(t.w32, i, w)) = v;
+    if (w == 0 && t.norms) t.norms[i] = *reinterpret_cast<const float*>(in + 8 + 8ull * t.w64);
+  }
+}
+
+static unsigned grid_for(uint64_t total, int num_sms) {
   uint64_t b = (total + 255) / 256;
-  if (b > 148ull * 32) b = 148ull * 32;
+  if (b > (uint64_t)num_sms * 32) b = (uint64_t)num_sms * 32;
   if (b < 1) b = 1;
   return (unsigned)b;
 }
 
 cudaError_t launch_scatter_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                 uint64_t first_index, const uint64_t* d_sigs, const float* d_norms,
-                                uint32_t shard_rank, uint32_t shard_count, cudaStream_t s,
-                                const uint32_t* d_skip_if_nonzero) {
+                                uint32_t shard_rank, uint32_t shard_count, int num_sms, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
-  scatter_rows_kernel<<<grid_for(n * t.w32), 256, 0, s>>>(t, n, d_row_index, first_index, d_sigs, d_norms,
-                                                          shard_rank, shard_count, d_skip_if_nonzero);
+  scatter_rows_kernel<<<grid_for(n * t.w32, num_sms), 256, 0, s>>>(t, n, d_row_index, first_index, d_sigs, d_norms,
+                                                                   shard_rank, shard_count);
   return cudaGetLastError();
 }
 cudaError_t launch_gather_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                uint64_t* d_sigs, float* d_norms, uint32_t shard_rank,
-                               uint32_t shard_count, cudaStream_t s) {
+                               uint32_t shard_count, int num_sms, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
-  gather_rows_kernel<<<grid_for(n * 2 * t.w64), 256, 0, s>>>(t, n, d_row_index, d_sigs, d_norms, shard_rank,
+  gather_rows_kernel<<<grid_for(n * 2 * t.w64, num_sms), 256, 0, s>>>(t, n, d_row_index, d_sigs, d_norms, shard_rank,
                                                              shard_count);
   return cudaGetLastError();
 }
 cudaError_t launch_diff_pack(const TableView& t, uint64_t n, const uint64_t* d_row_index, void* d_records,
-                             uint32_t record_bytes, uint32_t shard_rank, uint32_t shard_count,
+                             uint32_t record_bytes, uint32_t shard_rank, uint32_t shard_count, int num_sms,
                              cudaStream_t s) {
   if (n == 0) return cudaSuccess;
-  diff_pack_kernel<<<grid_for(n * (2 * t.w64 + 1)), 256, 0, s>>>(
+  diff_pack_kernel<<<grid_for(n * (2 * t.w64 + 1), num_sms), 256, 0, s>>>(
       t, n, d_row_index, static_cast<unsigned char*>(d_records), record_bytes, shard_rank, shard_count);
   return cudaGetLastError();
 }
 cudaError_t launch_diff_apply(const TableView& t, uint64_t n, const void* d_records, uint32_t record_bytes,
-                              uint32_t shard_rank, uint32_t shard_count, cudaStream_t s) {
+                              uint32_t shard_rank, uint32_t shard_count, int num_sms, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
-  diff_apply_kernel<<<grid_for(n * t.w32), 256, 0, s>>>(t, n, static_cast<const unsigned char*>(d_records),
+  diff_apply_kernel<<<grid_for(n * t.w32, num_sms), 256, 0, s>>>(t, n, static_cast<const unsigned char*>(d_records),
                                                         record_bytes, shard_rank, shard_count);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_mix_apply(const TableView& t, uint64_t m, const void* d_gathered, uint64_t slot_bytes,
+                             uint32_t record_bytes, const uint32_t* d_src_rank, const uint32_t* d_src_pos,
+                             const uint64_t* d_dst_row, int num_sms, cudaStream_t s) {
+  if (m == 0) return cudaSuccess;
+  mix_apply_kernel<<<grid_for(m * t.w32, num_sms), 256, 0, s>>>(t, m, static_cast<const unsigned char*>(d_gathered), slot_bytes,
+                                                               record_bytes, d_src_rank, d_src_pos, d_dst_row);
   return cudaGetLastError();
 }
 

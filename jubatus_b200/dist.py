@@ -1,5 +1,11 @@
 """Multi-GPU drivers: one process per GPU, torch.distributed (NCCL over NVLink) as plumbing.
 
+The product path for more than one GPU is inside libjubann.so (csrc/comm.cu: jubann_comm_init,
+collective jubann_query_*, jubann_mix_allgather / jubann_mix_apply, jubann_create_multi);
+:func:`comm_init_from_torch` is the only piece of this module bench.py needs for it.  The
+classes below compose the same steps from Python over torch.distributed: they carry the gloo
+tests of the host-side logic on CPU and the device-pointer entry points' tests.
+
 * :class:`ShardedEngine` -- rows sharded round-robin by global row index:
   every rank scans its shard (jubann_scan_local_dev), the shard-local top-k candidates are
   all-gathered, and jubann_merge_dev reproduces the single-table ranking bit for bit.
@@ -158,6 +164,13 @@ class ReplicaTable(object):
                     take.append((r, j, at))
         if not take:
             return 0
+        # two replicas may have shipped the same key in this round: the row is then named twice.
+        # The scatter kernel writes one thread per word with no order between records, so only the
+        # last record per destination row goes to the device (what applying them in order gives).
+        last = {}
+        for n_, (_, _, at) in enumerate(take):
+            last[at] = n_
+        take = [t for n_, t in enumerate(take) if last[t[2]] == n_]
         src = torch.tensor([r * records.shape[1] + j for r, j, _ in take], dtype=torch.int64, device=records.device)
         picked = records.reshape(-1, rb).index_select(0, src).contiguous()
         # records carry the SENDER's row index in their first 8 bytes; rewrite it to ours
@@ -194,6 +207,19 @@ class ReplicaMixer(object):
         dist.all_gather_into_tensor(gathered, mine, group=self.group)   # row payloads: device records over NCCL
         gathered = gathered.view(self.world, max_n, rb)
         return t.put_diff(metas, gathered, counts)
+
+
+def comm_init_from_torch(engine, group=None):
+    """Joins `engine`'s handle to a communicator of its own inside libjubann.so (NCCL under the
+    C-ABI): rank 0 asks the library for an id, torch.distributed only carries those 128 bytes to
+    the other ranks -- the role ZooKeeper / the RPC layer has for the Jubatus servers.  After this
+    the data path (sharded queries, MIX) runs in the library; no tensor goes through
+    torch.distributed any more."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    box = [engine.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    engine.comm_init(box[0], rank, world)
+    return rank, world
 
 
 class EngineColumns(object):

@@ -56,9 +56,20 @@ extern "C" {
 const char* jubahost_last_error() { return g_err.c_str(); }
 
 // kind: "nearest_neighbor" | "recommender" | "anomaly"; config = the server's JSON config
+void* jubahost_create_devices(const char* kind, const char* config_json, const char* lib_path, const char* my_id,
+                              const int* devices, int ndev);
 void* jubahost_create(const char* kind, const char* config_json, const char* lib_path, const char* my_id, int device) {
+  const std::vector<int> devs = devices_from_env(device);
+  return jubahost_create_devices(kind, config_json, lib_path, my_id, devs.data(), static_cast<int>(devs.size()));
+}
+// the same with the GPUs the server process may use: more than one -> the table is sharded over
+// them inside libjubann.so (jubann_create_multi)
+void* jubahost_create_devices(const char* kind, const char* config_json, const char* lib_path, const char* my_id,
+                              const int* devices, int ndev) {
   host_box* b = new host_box;
+  const std::vector<int> device(devices, devices + (ndev > 0 ? ndev : 0));
   int rc = guarded([&]() {
+    if (device.empty()) throw invalid_parameter("device list is empty");
     b->api = jubann_api::load(lib_path ? lib_path : "libjubann.so");
     const std::string k(kind);
     if (k == "nearest_neighbor") {
@@ -294,6 +305,41 @@ int jubahost_mix_pair(void* ha, void* hb) {
     weight_manager::mix(db, acc);
     a->conv_mut().weights().put_diff(acc);
     b->conv_mut().weights().put_diff(acc);
+    return 0;
+  });
+}
+// the id rank 0 ships to the other replicas / shards (JUBANN_COMM_ID_BYTES bytes)
+int jubahost_comm_unique_id(void* h, void* id) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() { b->api->check(b->api->comm_unique_id(id)); return 0; });
+}
+// joins this server's table to the communicator of the replicas it mixes with
+int jubahost_comm_init(void* h, const void* id, uint32_t rank, uint32_t world) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    b->api->check(b->api->comm_init(b->nn()->get_table()->handle(), id, rank, world));
+    return 0;
+  });
+}
+// one MIX round with every replica of the communicator (a collective: all of them call it);
+// stats: rows sent, rows gathered, rows stored, bytes of this replica's blob
+int jubahost_mix_allgather(void* h, uint64_t* stats) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    mixable_versioned_table::mix_stats st;
+    if (b->serv) {
+      st = b->serv->get_driver()->mix_allgather();
+    } else {   // recommender / anomaly / classifier: the engine's table and this box's converter
+      weight_manager::counts mine;
+      b->conv_mut().weights().get_diff(mine);
+      std::vector<std::string> extras;
+      st = b->nn()->mix_allgather(weight_manager::pack_counts(mine), &extras);
+      weight_manager::counts acc;
+      for (size_t r = 0; r < extras.size(); ++r)
+        if (!extras[r].empty()) weight_manager::mix(weight_manager::unpack_counts(extras[r]), acc);
+      b->conv_mut().weights().put_diff(acc);
+    }
+    if (stats) { stats[0] = st.rows_sent; stats[1] = st.rows_gathered; stats[2] = st.rows_stored; stats[3] = st.blob_bytes; }
     return 0;
   });
 }

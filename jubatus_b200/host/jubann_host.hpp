@@ -123,6 +123,13 @@ struct jubann_api {
   int (*query_sig)(jubann_t*, uint64_t, const uint64_t*, const float*, uint32_t, uint32_t, uint64_t*, float*, uint32_t*);
   int (*query_csr)(jubann_t*, uint64_t, const uint64_t*, const uint32_t*, const uint64_t*, const float*, uint32_t, uint32_t, uint64_t*, float*, uint32_t*);
   int (*query_rows)(jubann_t*, uint64_t, const uint64_t*, uint32_t, uint32_t, uint64_t*, float*, uint32_t*);
+  // more than one GPU
+  int (*create_multi)(const char*, uint32_t, const int*, int, jubann_t**);
+  int (*comm_unique_id)(void*);
+  int (*comm_init)(jubann_t*, const void*, uint32_t, uint32_t);
+  int (*comm_info)(jubann_t*, uint32_t*, uint32_t*);
+  int (*mix_allgather)(jubann_t*, uint64_t, const uint64_t*, const void*, uint64_t, uint64_t*, uint64_t*, const void**);
+  int (*mix_apply)(jubann_t*, uint64_t, const uint32_t*, const uint32_t*, const uint64_t*);
 
   static std::shared_ptr<jubann_api> load(const std::string& path_or_name = "libjubann.so") {
     void* dl = 0;
@@ -160,6 +167,12 @@ struct jubann_api {
     JUBANN_SYM(query_sig, "jubann_query_sig");
     JUBANN_SYM(query_csr, "jubann_query_csr");
     JUBANN_SYM(query_rows, "jubann_query_rows");
+    JUBANN_SYM(create_multi, "jubann_create_multi");
+    JUBANN_SYM(comm_unique_id, "jubann_comm_unique_id");
+    JUBANN_SYM(comm_init, "jubann_comm_init");
+    JUBANN_SYM(comm_info, "jubann_comm_info");
+    JUBANN_SYM(mix_allgather, "jubann_mix_allgather");
+    JUBANN_SYM(mix_apply, "jubann_mix_apply");
 #undef JUBANN_SYM
     return a;
   }
@@ -219,6 +232,30 @@ class weight_manager {
   static void mix(const counts& lhs, counts& acc) { acc.add(lhs); }
   void put_diff(const counts& mixed) { master_.add(mixed); diff_ = counts(); }
   uint64_t documents() const { return master_.documents + diff_.documents; }
+  // a diff on the wire (MIX)
+  static std::string pack_counts(const counts& c) {
+    std::string b;
+    put64(b, c.documents);
+    put64(b, c.frequency.size());
+    for (std::unordered_map<std::string, uint64_t>::const_iterator it = c.frequency.begin(); it != c.frequency.end(); ++it) {
+      put64(b, it->first.size()); b += it->first; put64(b, it->second);
+    }
+    return b;
+  }
+  static counts unpack_counts(const std::string& b) {
+    size_t p = 0;
+    counts c;
+    c.documents = get64(b, p);
+    const uint64_t n = get64(b, p);
+    for (uint64_t i = 0; i < n; ++i) {
+      const uint64_t len = get64(b, p);
+      if (b.size() < p + len) throw jubatus_exception("unpack: truncated weights");
+      std::string key(b, p, len);
+      p += len;
+      c.frequency[key] = get64(b, p);
+    }
+    return c;
+  }
   // save / load: master and diff folded together (a loaded model starts with an empty diff)
   std::string pack() const {
     counts all = master_;
@@ -483,6 +520,14 @@ class device_table {
       : api_(api), h_(0), hash_num_(hash_num), w64_((hash_num + 63) / 64), clock_(0) {
     api_->check(api_->create(method.c_str(), hash_num, device, 0, 1, &h_));
   }
+  // one server process, several GPUs: the rows are sharded round-robin over `devices` inside the
+  // library (jubann_create_multi); everything above this class is unchanged
+  device_table(const std::shared_ptr<jubann_api>& api, const std::string& method, uint32_t hash_num,
+               const std::vector<int>& devices)
+      : api_(api), h_(0), hash_num_(hash_num), w64_((hash_num + 63) / 64), clock_(0) {
+    if (devices.size() == 1) api_->check(api_->create(method.c_str(), hash_num, devices[0], 0, 1, &h_));
+    else api_->check(api_->create_multi(method.c_str(), hash_num, devices.data(), static_cast<int>(devices.size()), &h_));
+  }
   ~device_table() { if (h_) api_->destroy(h_); }
   device_table(const device_table&) = delete;
   device_table& operator=(const device_table&) = delete;
@@ -505,9 +550,15 @@ class device_table {
   std::vector<std::string> get_all_row_ids() const { return keys_; }
 
   // column_table::add for a batch: assigns row indices (append or in-place), stamps
-  // (owner, clock++) per row, returns the indices.
-  std::vector<uint64_t> assign(const std::vector<std::string>& keys, const std::string& owner) {
+  // (owner, clock++) per row, returns the indices.  `undo` (optional) records what was there
+  // before, so that a device call that fails afterwards leaves no row the table does not hold.
+  struct assign_journal {
+    uint64_t rows_before, clock_before;
+    std::vector<std::pair<uint64_t, version_t> > overwritten;
+  };
+  std::vector<uint64_t> assign(const std::vector<std::string>& keys, const std::string& owner, assign_journal* undo = 0) {
     std::vector<uint64_t> idx(keys.size());
+    if (undo) { undo->rows_before = keys_.size(); undo->clock_before = clock_; undo->overwritten.clear(); }
     for (size_t i = 0; i < keys.size(); ++i) {
       std::unordered_map<std::string, uint64_t>::iterator it = index_.find(keys[i]);
       if (it == index_.end()) {
@@ -517,11 +568,17 @@ class device_table {
         index_[keys[i]] = idx[i];
       } else {
         idx[i] = it->second;
+        if (undo && idx[i] < undo->rows_before) undo->overwritten.push_back(std::make_pair(idx[i], versions_[idx[i]]));
         versions_[idx[i]] = version_t(owner, clock_);
       }
       ++clock_;
     }
     return idx;
+  }
+  void rollback(const assign_journal& j) {
+    while (keys_.size() > j.rows_before) { index_.erase(keys_.back()); keys_.pop_back(); versions_.pop_back(); }
+    for (size_t i = j.overwritten.size(); i-- > 0;) versions_[j.overwritten[i].first] = j.overwritten[i].second;
+    clock_ = j.clock_before;
   }
   // column_table::delete_row: the last row moves into the hole
   bool delete_row(const std::string& key) {
@@ -582,11 +639,27 @@ class device_table {
         norms.push_back(r.norm);
       }
     }
-    // rows are appended in increasing index order and an index may repeat (later wins), which
-    // is what one ordered batch gives
+    // rows are appended in increasing index order; an index may repeat, and the library stores the
+    // last entry for it (what applying the batch in order gives)
     if (!idx.empty()) api_->check(api_->set_rows_sig(h_, idx.size(), idx.data(), sigs.data(), norms.data()));
   }
   uint64_t clock() const { return clock_; }
+  // the host half of column_table::set_row(packed) for one incoming (key, version): unknown key ->
+  // new row at the end; known key -> admitted only if the stored clock <= the incoming one.  The
+  // local clock moves past every clock seen.  *at = the row the caller has to store into.
+  bool admit(const std::string& key, const version_t& v, uint64_t* at) {
+    std::unordered_map<std::string, uint64_t>::iterator it = index_.find(key);
+    bool store = true;
+    if (it == index_.end()) {
+      *at = keys_.size();
+      keys_.push_back(key); versions_.push_back(v); index_[key] = *at;
+    } else {
+      *at = it->second;
+      if (versions_[*at].second <= v.second) versions_[*at] = v; else store = false;
+    }
+    if (clock_ <= v.second) clock_ = v.second + 1;
+    return store;
+  }
 
   // column_table::dump_json as the server's get_status uses it (nearest_neighbor_serv.cpp:72-73):
   // a short description, not the rows.
@@ -695,7 +768,77 @@ class mixable_versioned_table {
   static void mix(const std::vector<packed_row>& lhs, std::vector<packed_row>& acc) { acc.insert(acc.end(), lhs.begin(), lhs.end()); }
   bool put_diff(const std::vector<packed_row>& diff) { push(diff); return true; }
 
+  // ---- one MIX round between replicas as collectives under the C-ABI -------------------------
+  // (linear_mixer.cpp:422-544: get_diff from every server, fold in server order, put_diff on
+  // every server -- here one all-gather of every replica's diff, which every replica then applies
+  // in rank order.)  The rows' signatures never visit the host: the library packs them on the
+  // device and keeps the gathered records there; the host ships only keys and versions (`blob`)
+  // and decides which gathered records are newer than what it holds.  `extra` is appended to the
+  // blob and handed back per rank (the driver's second mixable: the converter's weight counts).
+  struct mix_stats { uint64_t rows_sent, rows_gathered, rows_stored, blob_bytes; };
+  mix_stats mix_allgather(const std::string& extra, std::vector<std::string>* extras) {
+    const jubann_api& a = table_->api();
+    uint32_t rank = 0, world = 1;
+    a.check(a.comm_info(table_->handle(), &rank, &world));
+    // get_diff: rows newer than the clocks agreed at the last round
+    std::vector<uint64_t> idx;
+    std::string blob;
+    for (uint64_t i = 0; i < table_->size(); ++i) {
+      const version_t& v = table_->get_version(i);
+      version_clock::const_iterator it = vc_.find(v.first);
+      if (it == vc_.end() || it->second < v.second) {
+        idx.push_back(i);
+        put_str(blob, table_->get_key(i)); put_str(blob, v.first); put_u64(blob, v.second);
+      }
+    }
+    const uint64_t meta_bytes = blob.size();
+    blob += extra;
+    std::vector<uint64_t> rows(world), sizes(world);
+    std::vector<const void*> blobs(world);
+    std::string head;
+    put_u64(head, meta_bytes);
+    blob.insert(0, head);
+    a.check(a.mix_allgather(table_->handle(), idx.size(), idx.data(), blob.data(), blob.size(), rows.data(), sizes.data(), blobs.data()));
+    // put_diff: every gathered record in rank order, own ones included (a row two replicas
+    // changed ends up the same everywhere: the record applied last wins among equal clocks)
+    std::vector<uint32_t> src_rank, src_pos;
+    std::vector<uint64_t> dst;
+    mix_stats st = {idx.size(), 0, 0, blob.size()};
+    if (extras) extras->assign(world, std::string());
+    for (uint32_t r = 0; r < world; ++r) {
+      if (!sizes[r]) continue;
+      const std::string b(static_cast<const char*>(blobs[r]), sizes[r]);
+      size_t p = 0;
+      const uint64_t mb = get_u64(b, p);
+      if (b.size() < 8 + mb) throw jubatus_exception("mix: truncated blob");
+      for (uint64_t j = 0; j < rows[r]; ++j) {
+        const std::string key = get_str(b, p), owner = get_str(b, p);
+        const uint64_t clock = get_u64(b, p);
+        const version_t v(owner, clock);
+        uint64_t at;
+        if (table_->admit(key, v, &at)) { src_rank.push_back(r); src_pos.push_back(static_cast<uint32_t>(j)); dst.push_back(at); }
+        update_version(v);
+        ++st.rows_gathered;
+      }
+      if (extras) (*extras)[r] = b.substr(8 + mb);
+    }
+    st.rows_stored = dst.size();
+    if (!dst.empty()) a.check(a.mix_apply(table_->handle(), dst.size(), src_rank.data(), src_pos.data(), dst.data()));
+    return st;
+  }
+
  private:
+  static void put_u64(std::string& o, uint64_t v) { o.append(reinterpret_cast<const char*>(&v), 8); }
+  static void put_str(std::string& o, const std::string& s) { put_u64(o, s.size()); o.append(s); }
+  static uint64_t get_u64(const std::string& b, size_t& p) {
+    if (b.size() < p + 8) throw jubatus_exception("mix: truncated blob");
+    uint64_t v; memcpy(&v, b.data() + p, 8); p += 8; return v;
+  }
+  static std::string get_str(const std::string& b, size_t& p) {
+    const uint64_t n = get_u64(b, p);
+    if (b.size() < p + n) throw jubatus_exception("mix: truncated blob");
+    std::string s(b.data() + p, n); p += n; return s;
+  }
   device_table* table_;
   version_clock vc_;
 };
@@ -754,6 +897,11 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
   std::shared_ptr<device_table> get_table() { return table_; }
   std::shared_ptr<const device_table> get_const_table() const { return table_; }
   mixable_versioned_table* get_mixable() { return &mixable_; }
+  // MIX round with the table's write lock held (push_mixer.cpp:458 takes the model's wlock)
+  mixable_versioned_table::mix_stats mix_allgather(const std::string& extra, std::vector<std::string>* extras) {
+    std::unique_lock<std::shared_mutex> lk(rw_);
+    return mixable_.mix_allgather(extra, extras);
+  }
   float calc_similarity(float d) const { return method_ == "euclid_lsh" ? -d : 1 - d; }
 
   void set_row(const std::string& id, const sfv_t& sfv) {
@@ -768,10 +916,16 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
     for (size_t i = 0; i < sfvs.size(); ++i) b.add(sfvs[i]);
     // like column_table's own rw-mutex: writers exclusive, the lock-free RPC readers shared
     std::unique_lock<std::shared_mutex> lk(rw_);
-    std::vector<uint64_t> idx = table_->assign(ids, my_id_);
+    device_table::assign_journal undo;
+    std::vector<uint64_t> idx = table_->assign(ids, my_id_, &undo);
     const jubann_api& a = table_->api();
-    a.check(a.set_rows_csr(table_->handle(), idx.size(), idx.data(), b.indptr.data(), b.seed32.data(),
-                           b.keyhash64.data(), b.vals.data()));
+    // a repeated id repeats its index: the library stores the last entry (column_table::add in order)
+    const int rc = a.set_rows_csr(table_->handle(), idx.size(), idx.data(), b.indptr.data(), b.seed32.data(),
+                                  b.keyhash64.data(), b.vals.data());
+    if (rc) {   // the device table is as it was: so are keys, versions and clock
+      table_->rollback(undo);
+      a.check(rc);
+    }
   }
   void neighbor_row(const sfv_t& query, neighbor_result& ids, uint64_t ret_num) const {
     std::vector<sfv_t> q(1, query);
@@ -878,14 +1032,38 @@ struct nn_parameter {
 // core::nearest_neighbor::create_nearest_neighbor(method, param, table, my_id).  The device table
 // is created here because its geometry depends on (method, hash_num); `threads` is accepted and
 // has no effect (the GPU scan is always parallel).
+// The GPUs a server process uses: the list given by the embedding code, else $JUBANN_DEVICES
+// ("0,1,2,3"), else the one device asked for.
+inline std::vector<int> devices_from_env(int device) {
+  std::vector<int> out;
+  const char* e = ::getenv("JUBANN_DEVICES");
+  if (e && *e) {
+    const std::string s(e);
+    size_t p = 0;
+    while (p < s.size()) {
+      size_t q = s.find(',', p);
+      if (q == std::string::npos) q = s.size();
+      if (q > p) out.push_back(atoi(s.substr(p, q - p).c_str()));
+      p = q + 1;
+    }
+  }
+  if (out.empty()) out.push_back(device);
+  return out;
+}
+
 inline std::shared_ptr<gpu_nearest_neighbor> create_nearest_neighbor(const std::string& method, const json::ptr& param,
                                                                      const std::shared_ptr<jubann_api>& api,
-                                                                     const std::string& my_id, int device = 0) {
+                                                                     const std::string& my_id, const std::vector<int>& devices) {
   if (method != "lsh" && method != "euclid_lsh" && method != "minhash") throw unsupported_method(method);
   nn_parameter p = nn_parameter::from_json(param);
   if (p.hash_num < 1) throw invalid_parameter("hash_num should be >= 1");
-  std::shared_ptr<device_table> table(new device_table(api, method, static_cast<uint32_t>(p.hash_num), device));
+  std::shared_ptr<device_table> table(new device_table(api, method, static_cast<uint32_t>(p.hash_num), devices));
   return std::shared_ptr<gpu_nearest_neighbor>(new gpu_nearest_neighbor(method, p.hash_num, table, my_id));
+}
+inline std::shared_ptr<gpu_nearest_neighbor> create_nearest_neighbor(const std::string& method, const json::ptr& param,
+                                                                     const std::shared_ptr<jubann_api>& api,
+                                                                     const std::string& my_id, int device = 0) {
+  return create_nearest_neighbor(method, param, api, my_id, std::vector<int>(1, device));
 }
 
 // ---------------------------------------------------------------------------------------
@@ -919,6 +1097,20 @@ class nearest_neighbor {
   void clear() { nn_->clear(); converter_->clear_weights(); }
   mixable_versioned_table* get_mixable() { return nn_->get_mixable(); }
   datum_to_fv_converter& converter_mut() { return *converter_; }
+  // One MIX round of this driver's two mixables (the versioned table, the converter's weight
+  // counts) with the other replicas of the communicator the table's handle has joined: one
+  // collective exchange under the C-ABI (see mixable_versioned_table::mix_allgather).
+  mixable_versioned_table::mix_stats mix_allgather() {
+    weight_manager::counts mine;
+    converter_->weights().get_diff(mine);
+    std::vector<std::string> extras;
+    mixable_versioned_table::mix_stats st = nn_->mix_allgather(weight_manager::pack_counts(mine), &extras);
+    weight_manager::counts acc;
+    for (size_t r = 0; r < extras.size(); ++r)
+      if (!extras[r].empty()) weight_manager::mix(weight_manager::unpack_counts(extras[r]), acc);
+    converter_->weights().put_diff(acc);
+    return st;
+  }
   // driver->pack / unpack (save_load.cpp:129,280): the table, then the converter's global weights
   std::string pack() const {
     const std::string t = nn_->pack(), w = converter_->weights().pack();
@@ -1024,7 +1216,10 @@ class query_batcher {
 class nearest_neighbor_serv {
  public:
   explicit nearest_neighbor_serv(const std::shared_ptr<jubann_api>& api, const std::string& my_id = "", int device = 0)
-      : api_(api), my_id_(my_id), device_(device), update_row_cnt_(0) {}
+      : api_(api), my_id_(my_id), devices_(1, device), update_row_cnt_(0) {}
+  // a server process that owns several GPUs: the table is sharded over them inside the library
+  nearest_neighbor_serv(const std::shared_ptr<jubann_api>& api, const std::string& my_id, const std::vector<int>& devices)
+      : api_(api), my_id_(my_id), devices_(devices), update_row_cnt_(0) {}
   void set_config(const std::string& config) {
     json::ptr root;
     try { root = json::parse(config); } catch (const json::parse_error& e) { throw config_exception(e.what()); }
@@ -1038,7 +1233,7 @@ class nearest_neighbor_serv {
     json::ptr conv = root->find("converter");
     if (!conv) throw config_exception("\"converter\" is required");
     std::shared_ptr<datum_to_fv_converter> c = datum_to_fv_converter::from_config(conv);
-    std::shared_ptr<gpu_nearest_neighbor> nn = create_nearest_neighbor(m->str, root->find("parameter"), api_, my_id_, device_);
+    std::shared_ptr<gpu_nearest_neighbor> nn = create_nearest_neighbor(m->str, root->find("parameter"), api_, my_id_, devices_);
     nearest_neighbor_.reset(new driver::nearest_neighbor(nn, c));
     config_ = config;
   }
@@ -1132,7 +1327,7 @@ class nearest_neighbor_serv {
   void check_set_config() const { if (!nearest_neighbor_) throw config_exception("config is not set"); }
   std::shared_ptr<jubann_api> api_;
   std::string my_id_;
-  int device_;
+  std::vector<int> devices_;
   std::string config_;
   uint64_t update_row_cnt_;
   std::shared_ptr<driver::nearest_neighbor> nearest_neighbor_;

@@ -43,6 +43,12 @@ def _load():
     lib.jubahost_last_error.restype = ctypes.c_char_p
     lib.jubahost_create.restype = _vp
     lib.jubahost_create.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int]
+    lib.jubahost_create_devices.restype = _vp
+    lib.jubahost_create_devices.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
+                                            ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    lib.jubahost_comm_unique_id.argtypes = [_vp, _vp]
+    lib.jubahost_comm_init.argtypes = [_vp, _vp, ctypes.c_uint32, ctypes.c_uint32]
+    lib.jubahost_mix_allgather.argtypes = [_vp, _vp]
     lib.jubahost_destroy.argtypes = [_vp]
     lib.jubahost_convert.argtypes = [ctypes.c_char_p, _vp, _vp, ctypes.c_uint64, _vp, _vp, ctypes.c_uint64, _vp,
                                      ctypes.c_uint64, _vp, ctypes.c_uint64, _vp]
@@ -213,14 +219,40 @@ def convert(converter_json, d):
 class _HostHandle(object):
     kind = None
 
-    def __init__(self, config, my_id="", device=0):
+    def __init__(self, config, my_id="", device=0, devices=None):
+        """devices: the GPUs this server process may use; more than one shards the table over
+        them inside libjubann.so (jubann_create_multi)."""
         self._lib = _load()
         capi.load_library()   # fail loudly when the CUDA library is missing
-        self._h = self._lib.jubahost_create(self.kind.encode(), config.encode(), capi.lib_path().encode(),
-                                            my_id.encode(), int(device))
+        if devices is not None:
+            devs = (ctypes.c_int * len(devices))(*[int(d) for d in devices])
+            self._h = self._lib.jubahost_create_devices(self.kind.encode(), config.encode(), capi.lib_path().encode(),
+                                                        my_id.encode(), devs, len(devices))
+        else:
+            self._h = self._lib.jubahost_create(self.kind.encode(), config.encode(), capi.lib_path().encode(),
+                                                my_id.encode(), int(device))
         if not self._h:
             _raise()
         self._config = config
+
+    # MIX between server processes as collectives under the C-ABI (jubann_mix_allgather)
+    def comm_unique_id(self):
+        buf = (ctypes.c_ubyte * capi.COMM_ID_BYTES)()
+        if self._lib.jubahost_comm_unique_id(self._h, ctypes.cast(buf, _vp)):
+            _raise()
+        return bytes(buf)
+
+    def comm_init(self, comm_id, rank, world):
+        buf = (ctypes.c_ubyte * capi.COMM_ID_BYTES).from_buffer_copy(bytes(comm_id)) if comm_id is not None else None
+        if self._lib.jubahost_comm_init(self._h, ctypes.cast(buf, _vp) if buf is not None else None, int(rank), int(world)):
+            _raise()
+
+    def mix_allgather(self):
+        """One MIX round with every replica of the communicator (all of them call it)."""
+        st = (ctypes.c_uint64 * 4)()
+        if self._lib.jubahost_mix_allgather(self._h, ctypes.cast(st, _vp)):
+            _raise()
+        return {"rows_sent": st[0], "rows_gathered": st[1], "rows_stored": st[2], "blob_bytes": st[3]}
 
     def close(self):
         if getattr(self, "_h", None):
@@ -421,8 +453,8 @@ class Recommender(_HostHandle):
 class Anomaly(_HostHandle):
     kind = "anomaly"
 
-    def __init__(self, config, my_id="", device=0):
-        super().__init__(config, my_id, device)
+    def __init__(self, config, my_id="", device=0, devices=None):
+        super().__init__(config, my_id, device, devices)
         self._next_id = 0   # global_id_generator_standalone starts at 0 (common/global_id_generator_standalone.cpp:53-57)
 
     def add(self, d):

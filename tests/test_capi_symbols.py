@@ -35,7 +35,7 @@ def test_library_exports_every_declared_symbol():
 def test_version_and_errors_without_gpu():
     from jubatus_b200 import capi
     lib = capi.load_library()
-    assert lib.jubann_abi_version() == 1
+    assert lib.jubann_abi_version() == 2
     assert b"jubann" in lib.version()
     h = ctypes.c_void_p()
     # argument validation happens before any CUDA call
