@@ -1,0 +1,274 @@
+"""The collectives under the C-ABI (csrc/comm.cu): jubann_create_multi, jubann_comm_init with collective
+queries, jubann_mix_allgather / jubann_mix_apply.
+
+One GPU is enough for the single-device forms (a group of one device, a communicator of world 1);
+the tests that need two GPUs skip on a one-GPU box and run under `gpurun --gpus 2`.  Every answer is
+compared with the oracle on the same signatures: bit-exact ids, order and score bit patterns."""
+import multiprocessing as mp
+import os
+import sys
+import traceback
+
+import numpy as np
+import pytest
+
+from gpu_util import assert_same_ranking, random_rows
+from jubatus_b200 import workload as w
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+def _table(rng, method, hash_num, n, ties=True):
+    if ties:
+        base = random_rows(rng, 40, hash_num)
+        rows = base[rng.randint(0, 40, size=n)]
+        rows[::3] = random_rows(rng, len(rows[::3]), hash_num)
+    else:
+        rows = random_rows(rng, n, hash_num)
+    norms = (rng.rand(n) * 4 + 0.1).astype(np.float32) if method == "euclid_lsh" else None
+    return rows, norms
+
+
+def _exercise_group(oracle, devices):
+    """Every host-pointer entry point of a multi-device handle against the oracle."""
+    from jubatus_b200 import Engine, SIMILAR
+    rng = np.random.RandomState(len(devices))
+    for method, hash_num, n, k in (("lsh", 128, 9001, 100), ("euclid_lsh", 256, 5000, 37), ("minhash", 64, 700, 10)):
+        rows, norms = _table(rng, method, hash_num, n)
+        nq = 7
+        q = np.concatenate([rows[:3], random_rows(rng, nq - 3, hash_num)])
+        qn = (rng.rand(nq) * 4).astype(np.float32) if norms is not None else None
+        with Engine(method, hash_num, devices=devices) as e:
+            assert e.comm_info()[1] == len(devices)
+            half = n // 2
+            e.set_rows_sig(np.arange(half), rows[:half], None if norms is None else norms[:half])
+            e.set_rows_sig(np.arange(half, n), rows[half:], None if norms is None else norms[half:])
+            assert e.size()[0] == n
+            back, bn = e.get_rows_sig(np.arange(n))
+            assert np.array_equal(back, rows)
+            if norms is not None:
+                assert np.array_equal(bn.view(np.uint32), norms.view(np.uint32))
+            got = e.query_sig(q, qn, k)
+            assert_same_ranking(got, oracle.scan_batch(method, q, qn, rows, norms, hash_num, k)[:3], nq, k)
+            got = e.query_sig(q, qn, k, SIMILAR)
+            assert_same_ranking(got, oracle.scan_batch(method, q, qn, rows, norms, hash_num, k, similar=True)[:3], nq, k)
+            # neighbor_row(id): the stored signature of rows living on different shards
+            ids = np.array([0, 1, 2, n - 1], dtype=np.uint64)
+            got = e.query_rows(ids, k)
+            want = oracle.scan_batch(method, rows[ids.astype(np.int64)], None if norms is None else norms[ids.astype(np.int64)],
+                                     rows, norms, hash_num, k)[:3]
+            assert_same_ranking(got, want, len(ids), k)
+            # delete_row = move the last row into the hole, shrink by one (both rows on different shards)
+            e.move_row(n - 1, 1)
+            e.truncate(n - 1)
+            rows2 = rows[: n - 1].copy(); rows2[1] = rows[n - 1]
+            norms2 = None
+            if norms is not None:
+                norms2 = norms[: n - 1].copy(); norms2[1] = norms[n - 1]
+            assert e.size()[0] == n - 1
+            got = e.query_sig(q, qn, k)
+            assert_same_ranking(got, oracle.scan_batch(method, q, qn, rows2, norms2, hash_num, k)[:3], nq, k)
+            # k larger than the table, k = 0, empty table
+            got = e.query_sig(q[:2], None if qn is None else qn[:2], n + 5)
+            assert (got[2] == n - 1).all()
+            e.clear()
+            assert e.size()[0] == 0
+            got = e.query_sig(q[:2], None if qn is None else qn[:2], 5)
+            assert (got[2] == 0).all()
+
+
+def _exercise_group_csr(oracle, feature_tables, devices):
+    from jubatus_b200 import Engine
+    s32, k64 = feature_tables
+    n, nq, k = 2500, 9, 20
+    ids, vals = w.synth_rows(w.MASTER_SEED, 0, n)
+    qids, qvals = w.make_queries(w.MASTER_SEED, nq, ids, vals)
+    for method, hash_num in (("lsh", 512), ("euclid_lsh", 256), ("minhash", 128)):
+        csr = w.to_csr(ids, vals, s32, k64)
+        qcsr = w.to_csr(qids, qvals, s32, k64)
+        with Engine(method, hash_num, devices=devices, cache_slots=1 << 18) as e, Engine(method, hash_num, devices[0], cache_slots=1 << 18) as one:
+            e.set_rows_csr(np.arange(n), *csr)
+            one.set_rows_csr(np.arange(n), *csr)
+            stored, norms = e.get_rows_sig(np.arange(n))
+            s1, n1 = one.get_rows_sig(np.arange(n))
+            assert np.array_equal(stored, s1) and np.array_equal(norms.view(np.uint32), n1.view(np.uint32))
+            qs, qn = e.hash_csr(*qcsr)
+            got = e.query_csr(*qcsr, k)
+            euclid = method == "euclid_lsh"
+            want = oracle.scan_batch(method, qs, qn if euclid else None, stored, norms if euclid else None, hash_num, k)[:3]
+            assert_same_ranking(got, want, nq, k)
+            assert_same_ranking(one.query_csr(*qcsr, k), want, nq, k)
+
+
+def test_group_of_one_device_answers_like_the_oracle(oracle):
+    _exercise_group(oracle, [0])
+
+
+def test_group_of_one_device_csr_entry_points(oracle, feature_tables):
+    _exercise_group_csr(oracle, feature_tables, [0])
+
+
+def test_group_of_two_devices_answers_like_the_oracle(oracle):
+    if _ngpu() < 2:
+        pytest.skip("needs two GPUs")
+    _exercise_group(oracle, [0, 1])
+
+
+def test_group_of_two_devices_csr_entry_points(oracle, feature_tables):
+    if _ngpu() < 2:
+        pytest.skip("needs two GPUs")
+    _exercise_group_csr(oracle, feature_tables, [1, 0])
+
+
+def test_group_refuses_device_pointer_entry_points_and_bad_lists():
+    from jubatus_b200 import Engine, JubannError
+    with pytest.raises(JubannError):
+        Engine("lsh", 64, devices=[0, 0])
+    with pytest.raises(JubannError):
+        Engine("lsh", 64, devices=[])
+    with Engine("lsh", 64, devices=[0]) as e:
+        with pytest.raises(JubannError):
+            e.set_rows_sig_dev(1, 0, 0, 0, 0)
+        with pytest.raises(JubannError):
+            e.set_rows_sig(np.array([5], dtype=np.uint64), np.zeros((1, 1), dtype=np.uint64))   # skips past the end
+
+
+def test_world_of_one_communicator(oracle):
+    """comm_init(world 1) needs no NCCL: the sharded query path and a MIX round run on one rank."""
+    from jubatus_b200 import Engine
+    rng = np.random.RandomState(3)
+    hash_num, n, k = 128, 3000, 50
+    rows, _ = _table(rng, "lsh", hash_num, n)
+    q = random_rows(rng, 4, hash_num)
+    with Engine("lsh", hash_num) as e:
+        e.comm_init(None, 0, 1)
+        assert e.comm_info() == (0, 1)
+        e.set_rows_sig(np.arange(n), rows)
+        assert_same_ranking(e.query_sig(q, None, k), oracle.scan_batch("lsh", q, None, rows, None, hash_num, k)[:3], 4, k)
+        # a MIX round with itself: rows 5, 6 are copied over rows 0 and n (append)
+        counts, blobs = e.mix_allgather(np.array([5, 6], dtype=np.uint64), b"keys-and-clocks")
+        assert list(counts) == [2] and blobs == [b"keys-and-clocks"]
+        e.mix_apply([0, 0], [0, 1], [0, n])
+        assert e.size()[0] == n + 1
+        back, _ = e.get_rows_sig(np.array([0, n], dtype=np.uint64))
+        assert np.array_equal(back[0], rows[5]) and np.array_equal(back[1], rows[6])
+        counts, blobs = e.mix_allgather(np.zeros(0, dtype=np.uint64), b"")       # an empty round
+        assert list(counts) == [0] and blobs == [b""]
+
+
+# ---- two processes, one GPU each: the communicator is NCCL's ------------------------------------
+def _rank_main(rank, world, id_path, out_path, what):
+    try:
+        sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+        import time
+        import oracle_lib
+        from jubatus_b200 import Engine
+        if rank == 0:
+            cid = Engine.comm_unique_id()
+            with open(id_path + ".tmp", "wb") as f:
+                f.write(cid)
+            os.rename(id_path + ".tmp", id_path)
+        else:
+            for _ in range(600):
+                if os.path.exists(id_path):
+                    break
+                time.sleep(0.05)
+            cid = open(id_path, "rb").read()
+        rng = np.random.RandomState(11)
+        if what == "sharded":
+            for method, hash_num, n, k in (("lsh", 128, 20011, 100), ("euclid_lsh", 256, 6000, 64)):
+                rows, norms = _table(rng, method, hash_num, n)
+                nq = 9
+                q = np.concatenate([rows[:2], random_rows(rng, nq - 2, hash_num)])
+                qn = (rng.rand(nq) * 4).astype(np.float32) if norms is not None else None
+                with Engine(method, hash_num, rank, rank, world) as e:
+                    if method == "lsh":
+                        e.comm_init(cid, rank, world)
+                    else:   # a second communicator from a fresh id would need another exchange: reuse the file protocol
+                        if rank == 0:
+                            cid2 = Engine.comm_unique_id()
+                            with open(id_path + ".2.tmp", "wb") as f:
+                                f.write(cid2)
+                            os.rename(id_path + ".2.tmp", id_path + ".2")
+                        else:
+                            for _ in range(600):
+                                if os.path.exists(id_path + ".2"):
+                                    break
+                                time.sleep(0.05)
+                            cid2 = open(id_path + ".2", "rb").read()
+                        e.comm_init(cid2, rank, world)
+                    e.set_rows_sig(np.arange(n), rows, norms)            # every rank is handed every row, keeps its own
+                    assert e.size() == (n, len(range(rank, n, world)))
+                    got = e.query_sig(q, qn, k)                         # collective: same call on every rank
+                    want = oracle_lib.scan_batch(method, q, qn, rows, norms, hash_num, k)[:3]
+                    assert_same_ranking(got, want, nq, k)
+                    got = e.query_sig(q[:1], None if qn is None else qn[:1], 3000)   # paginated k
+                    want = oracle_lib.scan_batch(method, q[:1], None if qn is None else qn[:1], rows, norms, hash_num, 3000)[:3]
+                    assert_same_ranking(got, want, 1, 3000)
+        else:   # MIX between two replicas
+            hash_num, n = 256, 500
+            rows, norms = _table(rng, "euclid_lsh", hash_num, 2 * n, ties=False)
+            with Engine("euclid_lsh", hash_num, rank) as e:
+                e.comm_init(cid, rank, world)
+                mine = slice(rank * n, (rank + 1) * n)                  # each replica has its own n rows ...
+                e.set_rows_sig(np.arange(n), rows[mine], norms[mine])
+                changed = np.arange(rank, n, 2, dtype=np.uint64)        # ... and ships every second one
+                counts, blobs = e.mix_allgather(changed, b"rank%d:" % rank + bytes(range(rank + 3)))
+                assert list(counts) == [len(range(0, n, 2)), len(range(1, n, 2))]
+                assert blobs == [b"rank0:" + bytes(range(3)), b"rank1:" + bytes(range(4))]
+                other = 1 - rank
+                m = int(counts[other])
+                # the other replica's records are appended after my rows, twice the last one (later entry wins)
+                src_rank = np.full(m + 1, other, dtype=np.uint32)
+                src_pos = np.concatenate([np.arange(m), [0]]).astype(np.uint32)
+                dst = np.concatenate([np.arange(n, n + m), [n + m - 1]]).astype(np.uint64)
+                e.mix_apply(src_rank, src_pos, dst)
+                assert e.size()[0] == n + m
+                back, bn = e.get_rows_sig(np.arange(n, n + m, dtype=np.uint64))
+                theirs = np.arange(other, n, 2) + other * n
+                want_rows, want_norms = rows[theirs].copy(), norms[theirs].copy()
+                want_rows[-1], want_norms[-1] = want_rows[0], want_norms[0]
+                assert np.array_equal(back, want_rows)
+                assert np.array_equal(bn.view(np.uint32), want_norms.view(np.uint32))
+                back, _ = e.get_rows_sig(np.arange(n, dtype=np.uint64))   # my own rows are untouched
+                assert np.array_equal(back, rows[mine])
+        with open(out_path % rank, "w") as f:
+            f.write("ok")
+    except Exception:
+        with open(out_path % rank, "w") as f:
+            f.write(traceback.format_exc())
+
+
+def _run_two_ranks(tmp_path, what):
+    ctx = mp.get_context("spawn")
+    id_path = str(tmp_path / "comm_id")
+    out_path = str(tmp_path / "rank%d.txt")
+    procs = [ctx.Process(target=_rank_main, args=(r, 2, id_path, out_path, what)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+    for r in range(2):
+        path = out_path % r
+        assert os.path.exists(path), "rank %d wrote no result (exit code %s)" % (r, procs[r].exitcode)
+        assert open(path).read() == "ok", open(path).read()
+
+
+def test_two_ranks_answer_a_sharded_query_collectively(tmp_path):
+    if _ngpu() < 2:
+        pytest.skip("needs two GPUs")
+    _run_two_ranks(tmp_path, "sharded")
+
+
+def test_two_replicas_mix_through_the_library(tmp_path):
+    if _ngpu() < 2:
+        pytest.skip("needs two GPUs")
+    _run_two_ranks(tmp_path, "mix")

@@ -106,39 +106,53 @@ def test_minhash_signatures(oracle, feature_tables, hash_num):
     assert agree >= 0.9999, agree
 
 
-def test_cache_full_is_reported(feature_tables):
-    from jubatus_b200 import Engine, JubannError
+@pytest.mark.parametrize("method,hash_num,slots", [("lsh", 64, 100), ("lsh", 512, 1024), ("euclid_lsh", 256, 1024),
+                                                   ("lsh", 200, 1)])
+def test_features_beyond_the_cache_are_drawn_on_the_spot(oracle, feature_tables, method, hash_num, slots):
+    # [core] lsh_function::random_projection never refuses a feature (its cache only saves the redraw):
+    # with far more distinct features than cache slots the signatures are still the oracle's
+    from jubatus_b200 import Engine
     s32, k64 = feature_tables
-    ids, vals = w.synth_rows(w.MASTER_SEED, 0, 50)
+    n = 1200                                   # ~1.1e5 distinct features of 2^20
+    ids, vals = w.synth_rows(w.MASTER_SEED, 5000, n)
     indptr, seed32, keyhash, v = w.to_csr(ids, vals, s32, k64)
-    with Engine("lsh", 64, cache_slots=100) as e:
-        with pytest.raises(JubannError) as ei:
-            e.hash_csr(indptr, seed32, None, v)
-        assert ei.value.code == -4
+    assert len(np.unique(seed32)) > 50 * slots
+    with Engine(method, hash_num, cache_slots=slots) as e:
+        got, gnorm = e.hash_csr(indptr, seed32, None, v)          # bulk path: fills the cache, the rest misses
+        got2, _ = e.hash_csr(indptr, seed32, None, v)             # again: same mix of hits and misses
+        one = [e.hash_csr(*w.to_csr(ids[r:r + 1], vals[r:r + 1], s32, k64))[0][0] for r in (0, 7, n - 1)]
+    want, wnorm, proj = oracle.signatures_csr(method, hash_num, indptr, seed32, None, v, want_aux=True)
+    _check_bits(got, want, proj, hash_num)
+    assert np.array_equal(got, got2)
+    for r, sig in zip((0, 7, n - 1), one):                        # small-request path, one datum per call
+        assert np.array_equal(sig, got[r])
+    if method == "euclid_lsh":
+        assert np.array_equal(gnorm.view(np.uint32), wnorm.view(np.uint32))
 
 
-def test_cache_full_on_the_small_request_paths_leaves_the_table_alone(feature_tables):
-    # small requests do not read the cache counters back before hashing: the scatter is guarded on
-    # the device, the error surfaces with the results
-    from jubatus_b200 import Engine, JubannError
+def test_set_row_and_query_past_the_cache_capacity(oracle, feature_tables):
+    # the small-request paths (one set_row / one query per call) with a cache of 150 slots: rows keep
+    # arriving, nothing is refused, the stored signatures and the answers stay the oracle's
+    from jubatus_b200 import Engine
+    from gpu_util import assert_same_ranking
     s32, k64 = feature_tables
-    with Engine("lsh", 64, cache_slots=150) as e:
-        ids, vals = w.synth_rows(w.MASTER_SEED, 0, 1)
-        e.set_rows_csr(np.arange(1, dtype=np.uint64), *w.to_csr(ids, vals, s32, k64))      # 100 features: fits
-        before = e.get_rows_sig(np.arange(1, dtype=np.uint64))[0].copy()
-        ids2, vals2 = w.synth_rows(w.MASTER_SEED, 7, 1)
-        csr2 = w.to_csr(ids2, vals2, s32, k64)
-        with pytest.raises(JubannError) as ei:
-            e.set_rows_csr(np.arange(1, dtype=np.uint64), *csr2)                            # 100 more: overflow
-        assert ei.value.code == -4
-        assert np.array_equal(e.get_rows_sig(np.arange(1, dtype=np.uint64))[0], before)      # row 0 not overwritten
-    with Engine("lsh", 64, cache_slots=150) as e:
-        ids, vals = w.synth_rows(w.MASTER_SEED, 0, 1)
-        e.set_rows_csr(np.arange(1, dtype=np.uint64), *w.to_csr(ids, vals, s32, k64))
-        ids2, vals2 = w.synth_rows(w.MASTER_SEED, 7, 1)
-        with pytest.raises(JubannError) as ei:
-            e.query_csr(*w.to_csr(ids2, vals2, s32, k64), 1)
-        assert ei.value.code == -4
+    n, hash_num, k = 40, 64, 5
+    ids, vals = w.synth_rows(w.MASTER_SEED, 0, n)
+    with Engine("lsh", hash_num, cache_slots=150) as e:
+        for r in range(n):
+            e.set_rows_csr(np.array([r], dtype=np.uint64), *w.to_csr(ids[r:r + 1], vals[r:r + 1], s32, k64))
+        assert e.size()[0] == n
+        stored, _ = e.get_rows_sig(np.arange(n, dtype=np.uint64))
+        qcsr = w.to_csr(ids[3:4], vals[3:4], s32, k64)
+        qs, _ = e.hash_csr(*qcsr)
+        got = e.query_csr(*qcsr, k)
+    indptr, seed32, _, v = w.to_csr(ids, vals, s32, k64)
+    want_sigs, _, proj = oracle.signatures_csr("lsh", hash_num, indptr, seed32, None, v, want_aux=True)
+    _check_bits(stored, want_sigs, proj, hash_num)
+    assert np.array_equal(qs[0], stored[3])
+    want = oracle.scan_batch("lsh", qs, None, stored, None, hash_num, k)[:3]
+    assert_same_ranking(got, want, 1, k)
+    assert got[0][0][0] == 3 and got[1][0][0] == 0.0
 
 
 def test_set_rows_csr_then_query_end_to_end(oracle, feature_tables):
