@@ -1,15 +1,27 @@
 #!/usr/bin/env python
 """Headline benchmark: neighbor queries/sec @ 100M x 512-bit LSH rows, k=100 (BASELINE.json).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+    python bench.py [--gpus N] [--steps K] [--warmup W]               # this repo's CUDA path
     python bench.py --impl reference [--gpus N] --steps K --warmup W  # CPU engine (oracle) on host cores
 
-A step = one batch of --nq neighbor queries (k=100) against the full table.  The table
-(100M rows x 512 bits = 6.4 GB; 64x the 126 MB L2, so nothing is cache-resident between
-passes) is row-sharded round-robin over the N GPUs; every rank scans its
-shard, the shard-local top-k candidates are all-gathered over NCCL and merged bit-exactly.
-`value` times the device-resident path (CUDA events on the launching stream, max over
-ranks); `e2e` times the host-buffer C-ABI call with pinned host memory, H2D and D2H inside.
+A step = one batch of --nq neighbor queries (k=100) against the full table.  The table (10^8 rows x
+512 bits = 6.4 GB; 50x the 126 MB L2, so nothing is cache-resident between passes) is built from the
+synthetic datums of SURVEY.md 8(d) -- splitmix64, seed 0x4A554241, 100 distinct ascending feature ids
+of 2^20 per row -- hashed on the device by the signature kernel, and is row-sharded round-robin over
+the N GPUs (each rank generates and hashes only the rows it keeps).  Queries come from the disjoint
+seed stream with 1 % exact and 1 % near duplicates of stored rows.
+
+`value`  device-resident path: jubann_query_sig_dev (CUDA events on the launching stream, max over
+         ranks); on N > 1 GPUs that one call is collective inside libjubann.so (shard-local scan, one
+         packed NCCL all-gather, merge).
+`e2e`    the host-buffer call an adapter makes, jubann_query_csr: pinned host CSR of the query datums
+         in, ids / scores / counts out, copies and hashing inside the timed region; collective on N > 1.
+`parity` in the same run: the table the GPU holds is brought to the host and the CPU engine (oracle)
+         ranks the same queries against it; ids, order and score bit patterns must be identical, and a
+         sample of stored signatures is re-derived from the datums by the oracle.  The run fails
+         otherwise.  That CPU scan is also the `cpu_baseline` sample.
+`configs` short runs of BASELINE.json's other configurations (c2..c5), each with its own parity check
+         and both roofline fractions (HBM and POPC issue).
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -27,7 +39,8 @@ sys.path.insert(0, ROOT)
 
 METRIC = "neighbor queries/sec @100Mx512-bit LSH rows, k=100"
 UNIT = "queries/s"
-TABLE_SEED = 0x4A554241
+NNZ = 100
+NFEAT_LOG2 = 20
 
 
 def parse_args():
@@ -46,16 +59,15 @@ def parse_args():
                     help="queries sharing one streaming pass in the headline run (2 = HBM-bound regime; 0 = library default)")
     ap.add_argument("--popc-variant", type=int, default=-1)
     ap.add_argument("--scan-variant", type=int, default=0)
-    ap.add_argument("--table", default="datums", choices=["datums", "words"],
-                    help="datums: rows are synthetic sparse datums hashed by the signature kernel (end to end); "
-                         "words: uniform random signature words (scan-only fill)")
-    ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline leg")
-    ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--configs", default="c2,c3,c4,c5", help="comma-separated subset of c2,c3,c4,c5 ('' = none)")
+    ap.add_argument("--config-scale", type=float, default=1.0, help="shrink the rows of c2..c5 (development runs)")
+    ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline / parity leg")
+    ap.add_argument("--parity-queries", type=int, default=16)
     return ap.parse_args()
 
 
-def workload_name(a):
-    return "%s hash_num=%d, %d rows, %d-query batches, k=%d" % (a.method, a.hash_num, a.rows, a.nq, a.k)
+def workload_name(method, hash_num, rows, nq, k):
+    return "%s hash_num=%d, %d rows, %d-query batches, k=%d" % (method, hash_num, rows, nq, k)
 
 
 # --------------------------------------------------------------------------------------
@@ -118,21 +130,10 @@ class ClockSampler(object):
 # --------------------------------------------------------------------------------------
 # CPU legs (oracle = the reference algorithm restated; test infrastructure, timed here only)
 # --------------------------------------------------------------------------------------
-def cpu_table(rows, w64, threads):
+def oracle():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib
-    table = np.empty((rows, w64), dtype=np.uint64)
-    oracle_lib.fill_random_words(TABLE_SEED, rows * w64, threads=threads, out=table.reshape(-1))
-    return oracle_lib, table
-
-
-def make_queries(table_rows_fn, nq, w64, seed):
-    """nq query signatures: random words; every 8th is an exact copy of a stored row."""
-    from jubatus_b200 import workload
-    q = workload.random_signatures(seed, nq, w64)
-    for j in range(0, nq, 8):
-        q[j] = table_rows_fn(j)
-    return q
+    return oracle_lib
 
 
 def cpu_rows_that_fit(rows, w64):
@@ -144,56 +145,30 @@ def cpu_rows_that_fit(rows, w64):
     return min(rows, max(1_000_000, limit))
 
 
-def run_cpu_sample(a, seconds, flavours=("v3", "O2")):
-    """Times the CPU engine on a bounded sample; returns the cpu_baseline object."""
-    threads = os.cpu_count() or 1
-    w64 = (a.hash_num + 63) // 64
-    n_cpu = cpu_rows_that_fit(a.rows, w64)
-    oracle_lib, table = cpu_table(n_cpu, w64, threads)
-    norms = None
-    qn = None
-    if a.method == "euclid_lsh":
-        norms = np.ones(n_cpu, dtype=np.float32)
-    out = {}
-    for fl in flavours:
-        q1 = make_queries(lambda j: table[(j * 7919) % n_cpu], 1, w64, 99)
-        if a.method == "euclid_lsh":
-            qn = np.ones(1, dtype=np.float32)
-        _, _, _, t1 = oracle_lib.scan_batch(a.method, q1, qn, table, norms, a.hash_num, a.k, threads=threads, flavour=fl)
-        nq = int(max(2, min(64, (seconds / len(flavours)) / max(t1, 1e-4))))
-        q = make_queries(lambda j: table[(j * 7919) % n_cpu], nq, w64, 7)
-        if a.method == "euclid_lsh":
-            qn = np.ones(nq, dtype=np.float32)
-        _, _, _, secs = oracle_lib.scan_batch(a.method, q, qn, table, norms, a.hash_num, a.k, threads=threads, flavour=fl)
-        qps = nq / secs * (n_cpu / float(a.rows))   # per-row normalised when the table had to shrink
-        out[fl] = (qps, nq, secs)
-    best = max(out, key=lambda f: out[f][0])
-    sample = "%d queries over %d rows x %d bits (k=%d), oracle engine with threads=%d row partitions" % (
-        out[best][1], n_cpu, a.hash_num, a.k, threads)
-    if n_cpu != a.rows:
-        sample += "; table shrunk to fit host RAM, value scaled by rows ratio %.3f" % (n_cpu / float(a.rows))
-    sample += "; builds: " + ", ".join("%s=%.2f q/s" % ("O3-x86-64-v3(hw popcnt)" if f == "v3" else "O2(reference flags, SWAR popcount)", out[f][0]) for f in out)
-    return {"value": out[best][0], "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
-            "scan_GBps": out[best][0] * a.rows * (a.hash_num / 8 + (4 if a.method == "euclid_lsh" else 0)) / 1e9}
-
-
 def run_reference(a):
     """--impl reference: the CPU engine (oracle port; the reference itself cannot be built here,
-    DESIGN.md) with every host thread, on the same workload; each step is a bounded sample."""
+    DESIGN.md) with every host thread, on the same workload shape; each step is a bounded sample.
+    The table is uniform random signature words (LSH bits of the synthetic datums are uniform too;
+    hashing 10^8 datums on the CPU would take longer than the run may) -- the arm that proves
+    agreement on identical data is the CUDA arm's `parity` leg."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    from jubatus_b200 import workload
+    ol = oracle()
     threads = os.cpu_count() or 1
     w64 = (a.hash_num + 63) // 64
     n_cpu = cpu_rows_that_fit(a.rows, w64)
-    oracle_lib, table = cpu_table(n_cpu, w64, threads)
-    norms = np.ones(n_cpu, dtype=np.float32) if a.method == "euclid_lsh" else None
-    fl = "v3"
+    table = np.empty((n_cpu, w64), dtype=np.uint64)
+    ol.fill_random_words(workload.MASTER_SEED, n_cpu * w64, threads=threads, out=table.reshape(-1))
+    euclid = a.method == "euclid_lsh"
+    norms = np.ones(n_cpu, dtype=np.float32) if euclid else None
 
     def step(nq, seed):
-        q = make_queries(lambda j: table[(j * 7919 + seed) % n_cpu], nq, w64, seed)
-        qn = np.ones(nq, dtype=np.float32) if a.method == "euclid_lsh" else None
-        return oracle_lib.scan_batch(a.method, q, qn, table, norms, a.hash_num, a.k, threads=threads, flavour=fl)[3]
+        q = workload.random_signatures(seed, nq, w64)
+        q[0] = table[(seed * 7919) % n_cpu]
+        qn = np.ones(nq, dtype=np.float32) if euclid else None
+        return ol.scan_batch(a.method, q, qn, table, norms, a.hash_num, a.k, threads=threads, flavour="v3")[3]
 
     t1 = step(1, 1)
     budget = 150.0
@@ -212,8 +187,9 @@ def run_reference(a):
     line = {
         "impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": total / a.steps * 1e3, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": workload_name(a), "note": "CPU engine = oracle port of jubatus_core 0.3.2 (reference not buildable here)"},
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic (uniform random signature words)",
+        "config": {"workload": workload_name(a.method, a.hash_num, a.rows, a.nq, a.k),
+                   "note": "CPU engine = oracle port of jubatus_core 0.3.2 (reference not buildable here)"},
         "cpu_baseline": {"value": qps, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -223,333 +199,557 @@ def run_reference(a):
 # --------------------------------------------------------------------------------------
 # CUDA arm
 # --------------------------------------------------------------------------------------
-def run_b200(a):
-    import torch
-    import torch.distributed as dist
-    from jubatus_b200 import Engine, workload
+class Env(object):
+    """Process-group plumbing: torch.distributed carries the barrier, the max over ranks and the
+    128-byte NCCL id of the library's own communicator; no table or query data goes through it."""
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != a.gpus and world > 1:
-        a.gpus = world
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py needs a CUDA device (no CPU fallback)")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    euclid = a.method == "euclid_lsh"
-    w64 = (a.hash_num + 63) // 64
-    G = world
-    opts = {}
-    if a.qp:
-        opts["queries_per_pass"] = a.qp
-    if a.popc_variant >= 0:
-        opts["popc_variant"] = a.popc_variant
-    if a.scan_variant:
-        opts["scan_variant"] = a.scan_variant
-    eng = Engine(a.method, a.hash_num, local_rank, rank, G, **opts)
-    eng.set_option("reserve_rows", a.rows)
-    stream = torch.cuda.current_stream().cuda_stream
+    def __init__(self, a):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world > 1:
+            a.gpus = self.world
+        if not torch.cuda.is_available():
+            raise RuntimeError("bench.py needs a CUDA device (no CPU fallback)")
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.stream = torch.cuda.current_stream().cuda_stream
+        self.peaks = {}
+        try:
+            self.peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        self.hbm_peak = float(self.peaks.get("hbm_gbs", 6650.0))
+        self.micro = {}
+        try:
+            self.micro = json.load(open(os.path.join(ROOT, "profiles", "microbench.json")))
+        except Exception:
+            pass
+        from jubatus_b200 import workload
+        s32, k64 = workload.feature_tables(NFEAT_LOG2)
+        self.s32, self.k64 = s32, k64
+        self.d_s32 = torch.from_numpy(s32.view(np.int32)).to(self.dev)
+        self.d_k64 = torch.from_numpy(k64.view(np.int64)).to(self.dev)
 
-    nnz = 100
-    nsets = 4
-    minhash = a.method == "minhash"
-    if a.table == "words":
-        # ---- table: uniform random signature words, written straight into the shard's slab ----
-        chunk = 4_000_000
-        gen = torch.Generator(device=dev)
-        for r0 in range(0, a.rows, chunk):
-            n = min(chunk, a.rows - r0)
-            gen.manual_seed(TABLE_SEED + r0)   # every rank generates the same global rows
-            sig = torch.randint(-2 ** 63, 2 ** 63 - 1, (n, w64), dtype=torch.int64, device=dev, generator=gen)
-            nrm = (torch.rand(n, device=dev, generator=gen) + 0.5) if euclid else None
-            eng.set_rows_sig_dev(n, r0, sig.data_ptr(), nrm.data_ptr() if euclid else 0, stream)
-            if r0 == 0:
-                keep_rows = sig[:4096].clone()
-            torch.cuda.synchronize()
-            del sig, nrm
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
 
-        def queries(seed):
-            q = torch.from_numpy(workload.random_signatures(seed, a.nq, w64).view(np.int64)).clone()
-            q[::8] = keep_rows[(torch.arange(0, a.nq, 8) * 13) % keep_rows.shape[0]].cpu()
-            return q
-
-        h_q = [queries(1000 + i).pin_memory() for i in range(nsets)]
-        d_q = [x.to(dev) for x in h_q]
-        h_qn = [torch.ones(a.nq, dtype=torch.float32).pin_memory() for _ in range(nsets)] if euclid else None
-        d_qn = [x.to(dev) for x in h_qn] if euclid else None
-        h_csr = None
-    else:
-        # ---- table: synthetic sparse datums (100 of 2^20 hashed features, values 1 + U[0,1)), hashed on
-        # the device by the signature kernel and stored: set_row end to end ----
-        s32, k64 = workload.feature_tables(20)
-        d_s32 = torch.from_numpy(s32.view(np.int32)).to(dev)
-        d_k64 = torch.from_numpy(k64.view(np.int64)).to(dev)
-        chunk = 1_000_000
-        gen = torch.Generator(device=dev)
-        t_build = time.time()
-        for r0 in range(0, a.rows, chunk):
-            n = min(chunk, a.rows - r0)
-            gen.manual_seed(TABLE_SEED + r0)   # every rank generates (and hashes) the same global rows
-            ids = torch.randint(0, 1 << 20, (n, nnz), device=dev, generator=gen)
-            vals = (torch.rand((n, nnz), device=dev, generator=gen) + 1.0)
-            flat = ids.reshape(-1)
-            seed = None if minhash else d_s32[flat].contiguous()
-            keyh = d_k64[flat].contiguous() if minhash else None
-            indptr = torch.arange(n + 1, device=dev, dtype=torch.int64) * nnz
-            eng.set_rows_csr_dev(n, r0, n * nnz, indptr.data_ptr(), seed.data_ptr() if seed is not None else 0,
-                                 keyh.data_ptr() if keyh is not None else 0, vals.reshape(-1).data_ptr(), stream)
-            if r0 == 0:
-                keep_ids, keep_vals = ids[:4096].clone(), vals[:4096].clone()
-            torch.cuda.synchronize()
-            del ids, vals, flat, seed, keyh, indptr
-        t_build = time.time() - t_build
-
-        # queries: datums from another stream; every 8th is an exact copy of a stored datum
-        def query_csr(seed_):
-            g2 = torch.Generator(device=dev); g2.manual_seed(seed_)
-            ids = torch.randint(0, 1 << 20, (a.nq, nnz), device=dev, generator=g2)
-            vals = torch.rand((a.nq, nnz), device=dev, generator=g2) + 1.0
-            src = (torch.arange(0, a.nq, 8, device=dev) * 13) % keep_ids.shape[0]
-            ids[::8], vals[::8] = keep_ids[src], keep_vals[src]
-            flat = ids.reshape(-1)
-            return {"indptr": (torch.arange(a.nq + 1, dtype=torch.int64) * nnz).pin_memory(),
-                    "seed": d_s32[flat].cpu().pin_memory(), "key": d_k64[flat].cpu().pin_memory(),
-                    "vals": vals.reshape(-1).cpu().pin_memory()}
-
-        h_csr = [query_csr(1000 + i) for i in range(nsets)]
-        d_csr = [{k_: v.to(dev) for k_, v in c.items()} for c in h_csr]
-        d_q = [torch.zeros((a.nq, w64), dtype=torch.int64, device=dev) for _ in range(nsets)]
-        d_qn = [torch.zeros(a.nq, dtype=torch.float32, device=dev) for _ in range(nsets)]
-        for i in range(nsets):   # query signatures resident in HBM for the device-timed region
-            c = d_csr[i]
-            eng.hash_csr_dev(a.nq, a.nq * nnz, c["indptr"].data_ptr(), 0 if minhash else c["seed"].data_ptr(),
-                             c["key"].data_ptr() if minhash else 0, c["vals"].data_ptr(), d_q[i].data_ptr(),
-                             d_qn[i].data_ptr(), stream)
-        torch.cuda.synchronize()
-        h_q = [x.cpu().pin_memory() for x in d_q]
-        h_qn = [x.cpu().pin_memory() for x in d_qn] if euclid else None
-        if not euclid:
-            d_qn = None
-    assert eng.size()[0] == a.rows
-
-    d_idx = torch.zeros((a.nq, a.k), dtype=torch.int64, device=dev)
-    d_score = torch.zeros((a.nq, a.k), dtype=torch.float32, device=dev)
-    d_count = torch.zeros(a.nq, dtype=torch.int32, device=dev)
-    if G > 1:
-        ck = torch.empty((a.nq, a.k), dtype=torch.int32, device=dev)
-        ci = torch.empty((a.nq, a.k), dtype=torch.int64, device=dev)
-        all_k = torch.empty((G, a.nq, a.k), dtype=torch.int32, device=dev)
-        all_i = torch.empty((G, a.nq, a.k), dtype=torch.int64, device=dev)
-
-    def step_device(i):
-        qn = d_qn[i % nsets].data_ptr() if euclid else 0
-        if G == 1:
-            eng.query_sig_dev(a.nq, d_q[i % nsets].data_ptr(), qn, a.k, 0, d_idx.data_ptr(), d_score.data_ptr(),
-                              d_count.data_ptr(), stream)
-        else:
-            eng.scan_local_dev(a.nq, d_q[i % nsets].data_ptr(), qn, a.k, ck.data_ptr(), ci.data_ptr(), stream)
-            dist.all_gather_into_tensor(all_k, ck)
-            dist.all_gather_into_tensor(all_i, ci)
-            eng.merge_dev(a.nq, a.k, G, all_k.data_ptr(), all_i.data_ptr(), qn, 0, d_idx.data_ptr(), d_score.data_ptr(),
-                          d_count.data_ptr(), stream)
-
-    def barrier():
-        torch.cuda.synchronize()
-        if G > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if G == 1:
+    def max_over_ranks(self, x):
+        if self.world == 1:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- device-resident timing ----
-    for i in range(a.warmup):
-        step_device(i)
-    barrier()
-    eng.stats_reset(True)
-    sampler = ClockSampler(local_rank)
+
+def issued_popc_per_pair(hash_num, popc_variant=3):
+    """POPC instructions the scan kernels issue per (row, query) pair after the carry-save adders."""
+    w32 = 2
+    while w32 * 32 < hash_num:
+        w32 *= 2
+    if popc_variant == 0 or w32 == 2:
+        return w32
+    if w32 == 4:
+        return 3
+    if w32 == 8:
+        return 4
+    per16 = {1: 11, 3: 9, 4: 7}.get(popc_variant, 5)
+    return per16 * (w32 // 16)
+
+
+def scan_kernel_name(hash_num, qp, local_rows, num_sms=148):
+    """The automatic choice of plan_scan (csrc/scan.cu): the TMA ring while a pass is memory-bound."""
+    w32 = 2
+    while w32 * 32 < hash_num:
+        w32 *= 2
+    tma = qp <= (3 if w32 >= 16 else 4) and (local_rows + 31) // 32 >= num_sms * 32
+    return "scan_tma_kernel" if tma else "scan_ldg_kernel"
+
+
+def build_table(env, eng, method, rows, seed, chunk=1_000_000):
+    """Rows g = rank, rank + G, ... of the synthetic table: generated on the device, hashed by the
+    signature kernel and stored (set_row end to end); no rank touches a row it does not keep."""
+    torch = env.torch
+    from jubatus_b200 import workload
+    G, rank = env.world, env.rank
+    minhash = method == "minhash"
+    local = (rows - rank + G - 1) // G if rows > rank else 0
+    indptr = torch.arange(chunk + 1, device=env.dev, dtype=torch.int64) * NNZ
+    t0 = time.time()
+    for j0 in range(0, local, chunk):
+        n = min(chunk, local - j0)
+        g = (torch.arange(j0, j0 + n, device=env.dev, dtype=torch.int64) * G + rank)
+        ids, vals = workload.synth_rows_torch(seed, g, NNZ, NFEAT_LOG2)
+        flat = ids.reshape(-1)
+        seed32 = None if minhash else env.d_s32[flat].contiguous()
+        keyh = env.d_k64[flat].contiguous() if minhash else None
+        v = vals.reshape(-1).contiguous()
+        eng.set_rows_csr_strided_dev(n, rank + G * j0, G, n * NNZ, indptr.data_ptr(),
+                                     seed32.data_ptr() if seed32 is not None else 0,
+                                     keyh.data_ptr() if keyh is not None else 0, v.data_ptr(), env.stream)
+        torch.cuda.synchronize()
+        del g, ids, vals, flat, seed32, keyh, v
+    torch.cuda.synchronize()
+    return time.time() - t0
+
+
+class QuerySets(object):
+    """`nsets` batches of `nq` query datums (disjoint seed stream, 1 % exact + 1 % near
+    duplicates of stored rows): pinned host CSR (what the adapter hands to jubann_query_csr), a device
+    copy, and their signatures resident in HBM for the device-timed region."""
+
+    def __init__(self, env, eng, method, hash_num, rows, nq, nsets, seed):
+        torch = env.torch
+        from jubatus_b200 import workload
+        self.nq, self.nsets = nq, nsets
+        self.minhash = method == "minhash"
+        self.euclid = method == "euclid_lsh"
+        w64 = (hash_num + 63) // 64
+        self.h, self.d_q, self.d_qn, self.exact_of = [], [], [], []
+        for i in range(nsets):
+            ids, vals, exact_of, _ = workload.make_queries_lazy(seed, nq, rows, NNZ, NFEAT_LOG2, query_row0=i * nq)
+            indptr, seed32, keyhash, v = workload.to_csr(ids, vals, env.s32, env.k64)
+            c = {"indptr": torch.from_numpy(indptr.view(np.int64)).pin_memory(),
+                 "seed": torch.from_numpy(seed32.view(np.int32)).pin_memory(),
+                 "key": torch.from_numpy(keyhash.view(np.int64)).pin_memory(),
+                 "vals": torch.from_numpy(v).pin_memory()}
+            self.h.append(c)
+            dc = {k_: x.to(env.dev) for k_, x in c.items()}
+            q = torch.zeros((nq, w64), dtype=torch.int64, device=env.dev)
+            qn = torch.zeros(nq, dtype=torch.float32, device=env.dev)
+            eng.hash_csr_dev(nq, nq * NNZ, dc["indptr"].data_ptr(), 0 if self.minhash else dc["seed"].data_ptr(),
+                             dc["key"].data_ptr() if self.minhash else 0, dc["vals"].data_ptr(), q.data_ptr(), qn.data_ptr(),
+                             env.stream)
+            self.d_q.append(q); self.d_qn.append(qn); self.exact_of.append(exact_of)
+        torch.cuda.synchronize()
+        self.h2d_bytes = nq * NNZ * (4 + (8 if self.minhash else 4)) + (nq + 1) * 8
+
+
+def fetch_table(env, eng, method, rows, w64):
+    """The table the GPUs hold, on rank 0's host: [rows][w64] words (+ norms).  Shards of other ranks
+    travel through /dev/shm files (host-side test plumbing, after the timed regions)."""
+    G, rank = env.world, env.rank
+    euclid = method == "euclid_lsh"
+    local = (rows - rank + G - 1) // G if rows > rank else 0
+    sig = np.empty((local, w64), dtype=np.uint64)
+    nrm = np.empty(local, dtype=np.float32) if euclid else None
+    step = 4_000_000
+    for j0 in range(0, local, step):
+        n = min(step, local - j0)
+        idx = (np.arange(j0, j0 + n, dtype=np.uint64) * np.uint64(G) + np.uint64(rank))
+        s, m = eng.get_rows_sig(idx)
+        sig[j0:j0 + n] = s
+        if euclid:
+            nrm[j0:j0 + n] = m
+    if G == 1:
+        return sig, nrm
+    tag = "/dev/shm/jubann_bench_%d_" % os.getppid()
+    np.save(tag + "sig_%d.npy" % rank, sig)
+    if euclid:
+        np.save(tag + "nrm_%d.npy" % rank, nrm)
+    del sig, nrm
+    env.barrier()
+    table = norms = None
     if rank == 0:
+        table = np.empty((rows, w64), dtype=np.uint64)
+        norms = np.empty(rows, dtype=np.float32) if euclid else None
+        for r in range(G):
+            table[r::G] = np.load(tag + "sig_%d.npy" % r, mmap_mode="r")
+            if euclid:
+                norms[r::G] = np.load(tag + "nrm_%d.npy" % r, mmap_mode="r")
+    env.barrier()
+    for suffix in ("sig_%d.npy" % rank, "nrm_%d.npy" % rank):
+        try:
+            os.remove(tag + suffix)
+        except OSError:
+            pass
+    return table, norms
+
+
+def check_parity(env, eng, method, hash_num, rows, k, flags, qs, got, nparity, seed, threads):
+    """Rank 0: the oracle ranks the first `nparity` queries of set 0 against the GPU's own table and a
+    sample of stored signatures is re-derived from the datums.  Returns (parity dict, oracle seconds)."""
+    from jubatus_b200 import workload
+    w64 = (hash_num + 63) // 64
+    euclid = method == "euclid_lsh"
+    table, norms = fetch_table(env, eng, method, rows, w64)
+    if env.rank != 0:
+        return None, None, 0
+    ol = oracle()
+    # a few of each kind: exact duplicates, near duplicates, plain queries
+    ndup = max(1, qs.nq // 100)
+    sel = sorted(set([0, 1, ndup, ndup + 1] + list(range(2 * ndup, 2 * ndup + nparity))))
+    sel = np.array([i for i in sel if i < qs.nq][:nparity], dtype=np.int64)
+    nparity = len(sel)
+    q = qs.d_q[0].cpu().numpy().view(np.uint64)[sel]
+    qn = qs.d_qn[0].cpu().numpy()[sel] if euclid else None
+    widx, wscore, wcount, secs = ol.scan_batch(method, q, qn, table, norms, hash_num, k, threads=threads,
+                                               similar=bool(flags & 1), flavour="v3")
+    gidx, gscore, gcount = got[0][sel], got[1][sel], got[2][sel]
+    exact_of = qs.exact_of[0][sel]
+    exact = True
+    for i in range(nparity):
+        c = int(wcount[i])
+        exact = exact and int(gcount[i]) == c and np.array_equal(gidx[i, :c], widx[i, :c]) and \
+            np.array_equal(gscore[i, :c].view(np.uint32), wscore[i, :c].view(np.uint32))
+    # planted exact duplicates come back first at distance 0 (score 1 / -0 for similarity flags)
+    planted = [int(r) for r in exact_of if r >= 0]
+    found = all(int(r) in gidx[i, :max(1, int(gcount[i]))] for i, r in enumerate(exact_of) if r >= 0)
+    # signatures: the oracle re-derives a sample of stored rows from their datums
+    sample = np.unique(np.concatenate([np.arange(0, min(rows, 256)), (np.arange(256) * 2654435761) % rows]).astype(np.int64))
+    ids = np.zeros((len(sample), NNZ), dtype=np.uint32)
+    vals = np.zeros((len(sample), NNZ), dtype=np.float32)
+    for j, r in enumerate(sample):
+        i1, v1 = workload.synth_rows(seed, int(r), 1, NNZ, NFEAT_LOG2)
+        ids[j], vals[j] = i1[0], v1[0]
+    indptr, seed32, keyhash, v = workload.to_csr(ids, vals, env.s32, env.k64)
+    want, wnorm = ol.signatures_csr(method, hash_num, indptr, None if method == "minhash" else seed32,
+                                    keyhash if method == "minhash" else None, v, threads=threads)
+    diff = np.unpackbits((want ^ table[sample]).view(np.uint8)).sum()
+    agreement = 1.0 - float(diff) / (len(sample) * hash_num)
+    norms_equal = bool(np.array_equal(wnorm.view(np.uint32), norms[sample].view(np.uint32))) if euclid else None
+    parity = {"queries": int(nparity), "rows": int(rows), "k": int(k), "exact": bool(exact and found),
+              "compared": "ids, order and score bit patterns against the CPU engine (oracle) on the table the GPUs hold",
+              "planted_duplicates_found": len(planted) if found else 0,
+              "signature_bit_agreement": agreement, "signature_rows_checked": int(len(sample))}
+    if euclid:
+        parity["norms_bit_exact"] = norms_equal
+    if not parity["exact"] or agreement < 0.9999 or norms_equal is False:
+        raise RuntimeError("PARITY FAILURE: %s" % json.dumps(parity))
+    del table, norms
+    return parity, secs, nparity
+
+
+def time_device_steps(env, eng, qs, k, flags, steps, warmup, outs, sampler=None):
+    torch = env.torch
+    d_idx, d_score, d_count = outs
+
+    def step(i):
+        s = i % qs.nsets
+        eng.query_sig_dev(qs.nq, qs.d_q[s].data_ptr(), qs.d_qn[s].data_ptr() if qs.euclid else 0, k, flags,
+                          d_idx.data_ptr(), d_score.data_ptr(), d_count.data_ptr(), env.stream)
+
+    for i in range(warmup):
+        step(i)
+    env.barrier()
+    eng.stats_reset(True)
+    if sampler is not None:
         sampler.start()
         time.sleep(0.25)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    t_wall0 = time.time()
+    env.barrier()
+    t0 = time.time()
     ev0.record()
-    for i in range(a.steps):
-        step_device(a.warmup + i)
+    for i in range(steps):
+        step(warmup + i)
     ev1.record()
-    barrier()
-    t_wall1 = time.time()
-    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
-    clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
-    st = eng.stats()
-    value = a.steps * a.nq / (ms_total * 1e-3)
+    env.barrier()
+    t1 = time.time()
+    ms = env.max_over_ranks(ev0.elapsed_time(ev1))
+    clocks = sampler.stop(t0, t1) if sampler is not None else None
+    return ms, eng.stats(), clocks
 
-    # sanity: the planted exact copies come back first with distance 0
-    torch.cuda.synchronize()
-    last = (a.warmup + a.steps - 1) % nsets
-    got_idx = d_idx.cpu().numpy()
-    got_score = d_score.cpu().numpy()
-    assert int(d_count.min().item()) == min(a.k, a.rows)
-    if not euclid:
-        planted = ((np.arange(0, a.nq, 8) * 13) % 4096)
-        assert (got_score[::8, 0] == 0).all() and (got_idx[::8, 0] == planted).all(), "planted rows not found"
-        assert (np.diff(got_score, axis=1) >= 0).all()
 
-    # ---- roofline of the dominant kernel (scan), from live CUDA-event timings per launch ----
+def regime(env, method, hash_num, local_rows, nq, steps, ms, st, popc_variant=3):
+    """Both roofline fractions of a timed region from the library's per-launch CUDA events."""
+    euclid = method == "euclid_lsh"
+    w64 = (hash_num + 63) // 64
+    row_bytes = w64 * 8 + (4 if euclid else 0)
+    passes = max(1, st["scan_passes"])
+    qp_eff = nq * steps / float(passes)
+    pass_ms = st["scan_ms"] / passes
+    gbps = local_rows * row_bytes / (pass_ms * 1e-3) / 1e9
+    pairs = local_rows * qp_eff / (pass_ms * 1e-3)
+    out = {"queries_per_pass": qp_eff, "value": steps * nq / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
+           "pass_ms": pass_ms, "hbm_GBps": gbps, "hbm_frac": gbps / env.hbm_peak,
+           "scan_share_of_step": st["scan_ms"] / ms,
+           "int_popc32_per_s": pairs * (hash_num / 32.0)}
+    peak = env.micro.get("popc_only_per_s")
+    if peak:
+        out["popc_issue_frac"] = pairs * issued_popc_per_pair(hash_num, popc_variant) / peak
+        out["int_frac_of_measured_popc_peak"] = out["int_popc32_per_s"] / peak
+        out["binding"] = "hbm" if out["hbm_frac"] >= out["popc_issue_frac"] else "popc issue (XU pipe)"
+    return out
+
+
+def bench_scan(env, a, name, method, hash_num, rows, nq, k, qp, flags, steps, warmup, main, second_qp=None, second_nq=None):
+    """One configuration: table build, device-timed steps, (main: throughput regime, e2e), parity."""
+    torch = env.torch
+    from jubatus_b200 import Engine, dist as jd, workload
+    G, rank = env.world, env.rank
+    euclid, minhash = method == "euclid_lsh", method == "minhash"
+    w64 = (hash_num + 63) // 64
+    row_bytes = w64 * 8 + (4 if euclid else 0)
+    opts = {}
+    if qp:
+        opts["queries_per_pass"] = qp
+    if main and a.popc_variant >= 0:
+        opts["popc_variant"] = a.popc_variant
+    if main and a.scan_variant:
+        opts["scan_variant"] = a.scan_variant
+    eng = Engine(method, hash_num, env.local_rank, rank, G, **opts)
+    if G > 1:
+        jd.comm_init_from_torch(eng)          # the library's own NCCL communicator; queries are collective from here on
+    eng.set_option("reserve_rows", rows)
+    seed = workload.MASTER_SEED
+    t_build = build_table(env, eng, method, rows, seed)
+    assert eng.size()[0] == rows
     local_rows = eng.size()[1]
-    row_bytes = a.hash_num // 8 + (4 if euclid else 0) if a.hash_num % 64 == 0 else w64 * 8 + (4 if euclid else 0)
-    bytes_per_launch = local_rows * row_bytes
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
+    nsets = 4 if nq <= 256 else 2
+    qs = QuerySets(env, eng, method, hash_num, rows, nq, nsets, seed)
+    outs = (torch.zeros((nq, k), dtype=torch.int64, device=env.dev), torch.zeros((nq, k), dtype=torch.float32, device=env.dev),
+            torch.zeros(nq, dtype=torch.int32, device=env.dev))
+
+    sampler = ClockSampler(env.local_rank) if (main and rank == 0) else None
+    ms, st, clocks = time_device_steps(env, eng, qs, k, flags, steps, warmup, outs, sampler)
+    first = regime(env, method, hash_num, local_rows, nq, steps, ms, st)
+    res = {"workload": workload_name(method, hash_num, rows, nq, k) + (", similar_row" if flags & 1 else ""),
+           "value": first["value"], "unit": UNIT, "ms_per_step": ms / steps, "steps": steps,
+           "table_build_s": round(t_build, 2), "rows_per_gpu": local_rows,
+           "regimes": [first], "gpu_launches": st["kernel_launches"]}
+
+    # the answers to set 0, for the parity leg
+    eng.query_sig_dev(nq, qs.d_q[0].data_ptr(), qs.d_qn[0].data_ptr() if euclid else 0, k, flags, outs[0].data_ptr(),
+                      outs[1].data_ptr(), outs[2].data_ptr(), env.stream)
+    torch.cuda.synchronize()
+    got = (outs[0].cpu().numpy().view(np.uint64), outs[1].cpu().numpy(), outs[2].cpu().numpy().view(np.uint32))
+    assert int(got[2].min()) == min(k, rows)
+
+    # ---- second regime on the same table (popcount-bound when the first one is HBM-bound) ----
+    if second_qp is not None:
+        eng.set_option("queries_per_pass", second_qp)
+        if main and a.scan_variant:
+            eng.set_option("scan_variant", 0)
+        qs2, outs2 = qs, outs
+        if second_nq and second_nq != nq:
+            qs2 = QuerySets(env, eng, method, hash_num, rows, second_nq, 2, seed ^ 0x77)
+            outs2 = (torch.zeros((second_nq, k), dtype=torch.int64, device=env.dev),
+                     torch.zeros((second_nq, k), dtype=torch.float32, device=env.dev),
+                     torch.zeros(second_nq, dtype=torch.int32, device=env.dev))
+        t_steps = max(2, steps // 2)
+        ms2, st2, _ = time_device_steps(env, eng, qs2, k, flags, t_steps, 2, outs2)
+        res["regimes"].append(regime(env, method, hash_num, local_rows, qs2.nq, t_steps, ms2, st2))
+        if qs2 is qs:   # same queries: the two regimes must give the same answers
+            eng.query_sig_dev(nq, qs.d_q[0].data_ptr(), qs.d_qn[0].data_ptr() if euclid else 0, k, flags, outs[0].data_ptr(),
+                              outs[1].data_ptr(), outs[2].data_ptr(), env.stream)
+            torch.cuda.synchronize()
+            assert np.array_equal(outs[0].cpu().numpy().view(np.uint64), got[0]), "regimes disagree"
+        eng.set_option("queries_per_pass", qp)
+        if main and a.scan_variant:
+            eng.set_option("scan_variant", a.scan_variant)
+
+    # ---- end to end: the host-buffer call (pinned CSR in, ids / scores out; hashing, copies and, on
+    # N > 1, the collective inside) ----
+    e2e = None
+    if main or minhash:
+        h_idx = torch.zeros((nq, k), dtype=torch.int64).pin_memory()
+        h_score = torch.zeros((nq, k), dtype=torch.float32).pin_memory()
+        h_count = torch.zeros(nq, dtype=torch.int32).pin_memory()
+
+        def step_e2e(i):
+            c = qs.h[i % qs.nsets]
+            eng.query_csr_ptr(nq, c["indptr"].data_ptr(), 0 if minhash else c["seed"].data_ptr(),
+                              c["key"].data_ptr() if minhash else 0, c["vals"].data_ptr(), k, flags, h_idx.data_ptr(),
+                              h_score.data_ptr(), h_count.data_ptr())
+
+        e2e_steps = max(2, steps // 2)
+        for i in range(2):
+            step_e2e(i)
+        env.barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            step_e2e(i)
+        env.barrier()
+        e2e_s = env.max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": e2e_steps * nq / e2e_s, "unit": UNIT, "h2d_bytes_per_step": qs.h2d_bytes,
+               "d2h_bytes_per_step": nq * k * 12 + nq * 4, "steps": e2e_steps,
+               "api": "jubann_query_csr (host CSR of the query datums -> ids/scores)" +
+                      ("; collective on the %d shard handles: scan, one packed ncclAllGather, merge inside libjubann.so" % G if G > 1 else "")}
+        step_e2e(0)
+        assert np.array_equal(h_idx.numpy().view(np.uint64), got[0]), "host-buffer path and device path disagree"
+        assert np.array_equal(h_score.numpy().view(np.uint32), got[1].view(np.uint32))
+        res["e2e"] = e2e
+
+    # ---- parity in the same run, and the CPU baseline from the same scan ----
+    parity = cpu = None
+    if not a.skip_cpu:
+        threads = os.cpu_count() or 1
+        nparity = a.parity_queries if main else min(8, a.parity_queries)
+        parity, secs, nparity = check_parity(env, eng, method, hash_num, rows, k, flags, qs, got, nparity, seed, threads)
+        if rank == 0:
+            res["parity"] = parity
+            cpu = {"value": nparity / secs, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": "%d of the batch's queries over the GPUs' own table of %d rows x %d bits (k=%d), oracle engine with "
+                             "threads=%d row partitions, build -O3 -march=x86-64-v3 (hw popcnt)" % (nparity, rows, hash_num, k, threads),
+                   "scan_GBps": nparity / secs * rows * row_bytes / 1e9}
+            res["cpu_baseline"] = cpu
+    eng.close()
+    del qs, outs
+    torch.cuda.empty_cache()
+    return res, clocks, st
+
+
+def bench_c5(env, a, rows, adds, scores, interval=512):
+    """Config 5: jubaanomaly light_lof over lsh hash_num=256 through the C++ host stack.  Every rank is a
+    replica holding the whole table (bulk-loaded to `rows`); then `adds` streaming add() calls per replica
+    (each: set_row, two reverse-neighbour collections, a batched re-scoring, calc_score) with a MIX round
+    (jubann_mix_allgather under the host's mixable) every `interval` adds when N > 1, then calc_score calls."""
+    from jubatus_b200 import nn, workload
+    G, rank = env.world, env.rank
+    conv = {"string_filter_types": {}, "string_filter_rules": [], "num_filter_types": {}, "num_filter_rules": [],
+            "string_types": {}, "string_rules": [], "num_types": {}, "num_rules": [{"key": "*", "type": "num"}]}
+    cfg = json.dumps({"method": "light_lof", "converter": conv,
+                      "parameter": {"nearest_neighbor_num": 10, "reverse_nearest_neighbor_num": 30, "method": "lsh",
+                                    "parameter": {"hash_num": 256}}})
+    an = nn.Anomaly(cfg, my_id="replica%d" % rank, device=env.local_rank)
+    if G > 1:
+        box = [an.comm_unique_id() if rank == 0 else None]
+        env.dist.broadcast_object_list(box, src=0)
+        an.comm_init(box[0], rank, G)
+    t0 = time.time()
+    chunk = 100_000
+    for r0 in range(0, rows, chunk):
+        n = min(chunk, rows - r0)
+        ids, vals = workload.synth_rows(workload.MASTER_SEED, r0, n, NNZ, NFEAT_LOG2)
+        an.add_bulk_numeric(ids, vals, prefix="b")
+    t_load = time.time() - t0
+    if G > 1:
+        an.mix_allgather()            # the bulk load is known to every replica already: settle the clocks
+    # the streamed datums: a disjoint stream, every replica its own rows
+    ids, vals = workload.synth_rows(workload.QUERY_SEED, 10_000_000 + rank * (adds + scores), adds + scores, NNZ, NFEAT_LOG2)
+    for i in range(3):
+        an.calc_score_numeric(ids[adds + i % max(1, scores)], vals[adds + i % max(1, scores)])
+    env.barrier()
+    t0 = time.perf_counter()
+    mix_rounds, mix_bytes, finite = 0, 0, []
+    for i in range(adds):
+        finite.append(an.add_numeric(ids[i], vals[i], prefix="r%d_" % rank)[1])
+        if G > 1 and (i + 1) % interval == 0:
+            stt = an.mix_allgather()
+            mix_rounds += 1
+            mix_bytes += stt["blob_bytes"] + stt["rows_sent"] * (8 + 32 + 8)
+    if G > 1 and adds % interval:
+        stt = an.mix_allgather(); mix_rounds += 1
+        mix_bytes += stt["blob_bytes"] + stt["rows_sent"] * (8 + 32 + 8)
+    env.barrier()
+    t_add = env.max_over_ranks(time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    for i in range(scores):
+        finite.append(an.calc_score_numeric(ids[adds + i], vals[adds + i]))
+    env.barrier()
+    t_score = env.max_over_ranks(time.perf_counter() - t0)
+    size = an.size()
+    digest = an.table_digest()
+    same = True
+    if G > 1:
+        all_d = [None] * G
+        env.dist.all_gather_object(all_d, (size, digest))
+        same = all(d == all_d[0] for d in all_d)
+        if not same:
+            raise RuntimeError("config 5: replicas differ after MIX: %r" % (all_d,))
+    ok = [s for s in finite if s == s and abs(s) != float("inf")]
+    res = {"workload": "light_lof over lsh hash_num=256 (nn=10, rnn=30), %d-row table per replica, streaming add/calc_score, "
+                       "MIX every %d adds across %d replica(s)" % (rows, interval, G),
+           "value": G * adds / t_add, "unit": "add/s (all replicas, MIX included)", "adds_per_replica": adds,
+           "ms_per_add": t_add / max(1, adds) * 1e3, "calc_score_per_s": G * scores / t_score if scores else None,
+           "bulk_load_s": round(t_load, 2), "rows_after": size, "mix_rounds": mix_rounds,
+           "mix_bytes_sent_per_round": mix_bytes / mix_rounds if mix_rounds else 0,
+           "replicas_identical_after_mix": bool(same), "mean_score": float(np.mean(ok)) if ok else None,
+           "api": "jubatus_b200 host stack (C++ light_lof / mixable_versioned_table) over the C-ABI; MIX = jubann_mix_allgather + jubann_mix_apply"}
+    expect = rows + G * adds
+    if size != expect:
+        raise RuntimeError("config 5: %d rows after the run, expected %d" % (size, expect))
+    an.close()
+    return res
+
+
+def run_b200(a):
+    env = Env(a)
+    torch = env.torch
+    G, rank = env.world, env.rank
+    hres, clocks, st = bench_scan(env, a, "headline", a.method, a.hash_num, a.rows, a.nq, a.k, a.qp, 0, a.steps, a.warmup,
+                                  main=True, second_qp=0 if a.qp else None)
+    head = hres["regimes"][0]
+    w64 = (a.hash_num + 63) // 64
+    euclid = a.method == "euclid_lsh"
+    row_bytes = w64 * 8 + (4 if euclid else 0)
+    local_rows = hres["rows_per_gpu"]
     passes_per_launch = st["scan_passes"] / float(max(1, st["scan_launches"]))
-    bytes_per_launch = bytes_per_launch * passes_per_launch   # a launch streams the shard once per pass
+    bytes_per_launch = local_rows * row_bytes * passes_per_launch
     avg_ms = st["scan_ms"] / max(1, st["scan_launches"])
     achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9
-    traffic = None
-    micro = {}
+    traffic, traffic_source = None, None
     try:
         prof = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json")))
         if prof.get("algorithmic_bytes_per_pass") == local_rows * row_bytes:   # captured on this very workload
-            traffic = prof["dram_bytes_per_pass"] * (st["scan_passes"] / float(max(1, st["scan_launches"])))
+            traffic = prof["dram_bytes_per_pass"] * passes_per_launch
+            traffic_source = "profiles/scan_traffic.json: dram__bytes_read+write of one ncu --set full capture of this kernel on this " \
+                             "workload (per pass, times the passes per launch); not measured in this run"
     except Exception:
         pass
-    try:
-        micro = json.load(open(os.path.join(ROOT, "profiles", "microbench.json")))
-    except Exception:
-        pass
-    qp_eff = (a.nq * a.steps) / float(max(1, st["scan_passes"]))
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                "kernel": "scan_*_kernel", "bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_ms,
-                "launches": st["scan_launches"], "passes_per_launch": passes_per_launch, "queries_per_pass": qp_eff,
-                "scan_share_of_step": st["scan_ms"] / ms_total}
-    popc32 = local_rows * qp_eff * passes_per_launch * (a.hash_num / 32.0) / (avg_ms * 1e-3)
-    roofline["int_popc32_per_s"] = popc32
-    if micro.get("popc_only_per_s"):
-        roofline["int_frac_of_measured_popc_peak"] = popc32 / micro["popc_only_per_s"]
-
-    # ---- second regime, same table: the library's default of 32 queries per pass, where the scan
-    # is bound by the popcount pipes instead of HBM (SURVEY 8d asks for both fractions) ----
-    throughput_mode = None
-    if a.qp:
-        eng.set_option("queries_per_pass", 0)
-        eng.set_option("scan_variant", 0)
-        for i in range(2):
-            step_device(i)
-        barrier()
-        eng.stats_reset(True)
-        t_steps = max(2, a.steps // 2)
-        ev0.record()
-        for i in range(t_steps):
-            step_device(i)
-        ev1.record()
-        barrier()
-        t_ms = max_over_ranks(ev0.elapsed_time(ev1))
-        st2 = eng.stats()
-        qp2 = (a.nq * t_steps) / float(max(1, st2["scan_passes"]))
-        pass_ms = st2["scan_ms"] / max(1, st2["scan_passes"])
-        popc2 = local_rows * qp2 * (a.hash_num / 32.0) / (pass_ms * 1e-3)
-        throughput_mode = {"queries_per_pass": qp2, "value": t_steps * a.nq / (t_ms * 1e-3), "unit": UNIT,
-                           "ms_per_step": t_ms / t_steps, "hbm_GBps": local_rows * row_bytes / (pass_ms * 1e-3) / 1e9,
-                           "hbm_frac": local_rows * row_bytes / (pass_ms * 1e-3) / 1e9 / peak,
-                           "int_popc32_per_s": popc2,
-                           "int_frac_of_measured_popc_peak": popc2 / micro["popc_only_per_s"] if micro.get("popc_only_per_s") else None,
-                           "note": "algorithmic popcounts (16 per 512-bit pair); the kernel issues 9 after carry-save adders"}
-        eng.set_option("queries_per_pass", a.qp)
-        if a.scan_variant:
-            eng.set_option("scan_variant", a.scan_variant)
-
-    # ---- end to end: host buffers through the C-ABI (pinned; H2D + D2H inside the call) ----
-    h_idx = torch.zeros((a.nq, a.k), dtype=torch.int64).pin_memory()
-    h_score = torch.zeros((a.nq, a.k), dtype=torch.float32).pin_memory()
-    h_count = torch.zeros(a.nq, dtype=torch.int32).pin_memory()
-    h2d = a.nq * w64 * 8 + (a.nq * 4 if euclid else 0)
-    d2h = a.nq * a.k * 12 + a.nq * 4
-
-    if h_csr is not None:
-        h2d = a.nq * nnz * (4 + (8 if minhash else 4)) + (a.nq + 1) * 8
-
-    def step_e2e(i):
-        qn_h = h_qn[i % nsets].data_ptr() if euclid else 0
-        if G == 1 and h_csr is not None:
-            # neighbor_row_from_datum as the adapter calls it: host CSR of the query datums in, ids/scores out
-            c = h_csr[i % nsets]
-            eng.query_csr_ptr(a.nq, c["indptr"].data_ptr(), 0 if minhash else c["seed"].data_ptr(),
-                              c["key"].data_ptr() if minhash else 0, c["vals"].data_ptr(), a.k, 0, h_idx.data_ptr(),
-                              h_score.data_ptr(), h_count.data_ptr())
-        elif G == 1:
-            eng.query_sig_ptr(a.nq, h_q[i % nsets].data_ptr(), qn_h, a.k, 0, h_idx.data_ptr(), h_score.data_ptr(),
-                              h_count.data_ptr())
-        else:
-            if h_csr is not None:
-                c, dc = h_csr[i % nsets], d_csr[i % nsets]
-                for k_ in ("indptr", "vals", "key" if minhash else "seed"):
-                    dc[k_].copy_(c[k_], non_blocking=True)
-                eng.hash_csr_dev(a.nq, a.nq * nnz, dc["indptr"].data_ptr(), 0 if minhash else dc["seed"].data_ptr(),
-                                 dc["key"].data_ptr() if minhash else 0, dc["vals"].data_ptr(), d_q[i % nsets].data_ptr(),
-                                 (d_qn[i % nsets] if euclid else scratch_norm).data_ptr(), stream)
-            else:
-                d_q[i % nsets].copy_(h_q[i % nsets], non_blocking=True)
-                if euclid:
-                    d_qn[i % nsets].copy_(h_qn[i % nsets], non_blocking=True)
-            step_device(i)
-            h_idx.copy_(d_idx, non_blocking=True)
-            h_score.copy_(d_score, non_blocking=True)
-            h_count.copy_(d_count, non_blocking=True)
-            torch.cuda.synchronize()
-
-    scratch_norm = torch.zeros(a.nq, dtype=torch.float32, device=dev)
-    e2e_steps = max(2, a.steps // 2)
-    for i in range(2):
-        step_e2e(i)
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        step_e2e(i)
-    barrier()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    e2e = {"value": e2e_steps * a.nq / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-           "steps": e2e_steps, "api": ("jubann_query_csr (host CSR of the query datums -> ids/scores)" if h_csr is not None else "jubann_query_sig (host buffers)") if G == 1 else
-           "H2D + (jubann_hash_csr_dev) + jubann_scan_local_dev + NCCL all_gather + jubann_merge_dev + D2H"}
-    step_device(e2e_steps - 1)          # same query set as the last end-to-end step
-    torch.cuda.synchronize()
-    assert np.array_equal(h_idx.numpy(), d_idx.cpu().numpy()), "host-buffer path and device path disagree"
-    assert np.array_equal(h_score.numpy(), d_score.cpu().numpy())
-
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": env.hbm_peak, "unit": "GB/s", "frac": achieved / env.hbm_peak,
+                "traffic": traffic, "traffic_source": traffic_source,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if env.peaks else "fallback 6650 (of fallback)",
+                "kernel": scan_kernel_name(a.hash_num, head["queries_per_pass"], local_rows),
+                "bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_ms, "launches": st["scan_launches"],
+                "passes_per_launch": passes_per_launch, "queries_per_pass": head["queries_per_pass"],
+                "scan_share_of_step": head["scan_share_of_step"], "int_popc32_per_s": head["int_popc32_per_s"],
+                "popc_issue_frac": head.get("popc_issue_frac"),
+                "int_frac_of_measured_popc_peak": head.get("int_frac_of_measured_popc_peak")}
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": G, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "u32", "data": ("synthetic sparse datums (100 of 2^20 hashed features) hashed by the signature kernel; queries are datums, "
-                                 "every 8th an exact copy of a stored one" if a.table == "datums" else
-                                 "synthetic (uniform random signature words, scan-only fill; queries random + planted exact copies)"),
-        "config": {"workload": workload_name(a), "parallelism": "rows sharded round-robin over %d GPU(s)" % G,
+        "metric": METRIC, "value": hres["value"], "unit": UNIT, "n_gpus": G, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": hres["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u32",
+        "data": "synthetic sparse datums of SURVEY 8(d) (splitmix64 seed 0x4A554241, 100 distinct ascending ids of 2^20, values 1+U[0,1)) "
+                "hashed by the signature kernel; queries from the disjoint stream with 1% exact + 1% near duplicates",
+        "config": {"workload": hres["workload"], "parallelism": "rows sharded round-robin over %d GPU(s)" % G,
                    "cache": "table %.1f GB per GPU >> 126 MB L2, streamed once per pass (inputs larger than L2)" % (local_rows * row_bytes / 1e9),
-                   "queries_per_pass": qp_eff},
-        "roofline": roofline, "e2e": e2e, "gpu_launches": st["kernel_launches"], "clocks": clocks,
-        "throughput_mode": throughput_mode,
+                   "queries_per_pass": head["queries_per_pass"], "table_build_s": hres["table_build_s"]},
+        "roofline": roofline, "e2e": hres.get("e2e"), "gpu_launches": hres["gpu_launches"], "clocks": clocks,
+        "throughput_mode": hres["regimes"][1] if len(hres["regimes"]) > 1 else None,
+        "parity": hres.get("parity"),
     }
-    if G == 1 and rank == 0 and not a.skip_cpu:
-        eng.close()
-        del d_q
-        torch.cuda.empty_cache()
-        line["cpu_baseline"] = run_cpu_sample(a, a.cpu_seconds)
+    if G == 1 and "cpu_baseline" in hres:
+        line["cpu_baseline"] = hres["cpu_baseline"]
+
+    # ---- BASELINE.json's other configurations, short runs ----
+    want = [c for c in a.configs.split(",") if c]
+    configs = {}
+    sc = a.config_scale
+    short = max(2, min(4, a.steps))
+    if "c2" in want:   # lsh 512 bits, 10^7 rows, 4096-query batches, k=10 (popcount regime)
+        r, _, _ = bench_scan(env, a, "c2", "lsh", 512, int(10_000_000 * sc), 4096, 10, 0, 0, short, 3, main=False)
+        configs["c2"] = r
+    if "c3" in want:   # euclid_lsh 256 bits + norm, 10^8 rows, k=100: HBM regime at 2 per pass, then 4096-query batches
+        r, _, _ = bench_scan(env, a, "c3", "euclid_lsh", 256, int(100_000_000 * sc), 64, 100, 2, 0, max(short, 4), 3, main=False,
+                             second_qp=0, second_nq=4096 if sc >= 0.1 else 256)
+        configs["c3"] = r
+    if "c4" in want:   # nearest_neighbor_recommender / minhash 128 bits, 2*10^7 rows, similar_row_from_datum k=50
+        r, _, _ = bench_scan(env, a, "c4", "minhash", 128, int(20_000_000 * sc), 4096, 50, 0, 1, short, 3, main=False)
+        configs["c4"] = r
+    if "c5" in want:
+        configs["c5"] = bench_c5(env, a, int(1_000_000 * sc), 1024, 512)
+    for name, r in configs.items():
+        if "regimes" in r:
+            best = max(r["regimes"], key=lambda g: max(g.get("hbm_frac", 0), g.get("popc_issue_frac", 0) or 0))
+            r["roofline"] = {"kernel": scan_kernel_name(int(r["workload"].split("hash_num=")[1].split(",")[0]), r["regimes"][0]["queries_per_pass"], r["rows_per_gpu"]),
+                             "hbm_frac": r["regimes"][0]["hbm_frac"], "popc_issue_frac": r["regimes"][0].get("popc_issue_frac"),
+                             "binding": r["regimes"][0].get("binding"), "best_fraction_any_regime": max(best.get("hbm_frac", 0), best.get("popc_issue_frac", 0) or 0)}
+    if configs:
+        line["configs"] = configs
     if rank == 0:
         emit(line)
     if G > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        env.dist.barrier()
+        env.dist.destroy_process_group()
 
 
 _REAL_STDOUT = None

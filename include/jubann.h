@@ -178,6 +178,15 @@ int jubann_hash_csr_dev(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d
 int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, uint64_t nnz, const uint64_t* d_indptr,
                             const uint32_t* d_seed32, const uint64_t* d_keyhash64, const float* d_vals, void* stream);
 
+/* jubann_set_rows_csr_dev for rows first_row_index + i * row_stride: a shard of a table spread over
+ * G ranks is bulk-loaded with its own rows only (row_stride = shard_count, first_row_index a row of
+ * this shard), so that no rank hashes a row it does not keep.  Same reference functions
+ * ({lsh,minhash,euclid_lsh}::set_row -> column_table::add, nearest_neighbor_serv.cpp:134) behind the
+ * reference's placement of a row on its owner (#@cht(1), nearest_neighbor.idl:10). */
+int jubann_set_rows_csr_strided_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, uint64_t row_stride, uint64_t nnz,
+                                    const uint64_t* d_indptr, const uint32_t* d_seed32, const uint64_t* d_keyhash64,
+                                    const float* d_vals, void* stream);
+
 /* No counterpart in the reference.  Same inputs, outputs and results as
  * jubann_query_sig_dev, for callers that may not allocate device memory once they are
  * running: a server whose GPU memory is parcelled out at start-up by its own pool, RPC

@@ -20,7 +20,7 @@ EXPORTS = [
     "jubann_diff_record_bytes", "jubann_diff_pack_dev", "jubann_diff_apply_dev", "jubann_stats",
     "jubann_stats_reset", "jubann_query_sig_noalloc_dev", "jubann_hash_csr_dev", "jubann_set_rows_csr_dev",
     "jubann_create_multi", "jubann_comm_unique_id", "jubann_comm_init", "jubann_comm_info",
-    "jubann_mix_allgather", "jubann_mix_apply",
+    "jubann_mix_allgather", "jubann_mix_apply", "jubann_set_rows_csr_strided_dev",
 ]
 COMM_ID_BYTES = 128
 
@@ -81,6 +81,8 @@ def load_library():
         "jubann_set_rows_sig_dev": [H, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp],
         "jubann_hash_csr_dev": [H, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
         "jubann_set_rows_csr_dev": [H, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp, _vp, _vp],
+        "jubann_set_rows_csr_strided_dev": [H, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp, _vp,
+                                            _vp],
         "jubann_scan_local_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, _vp, _vp, _vp],
         "jubann_merge_dev": [H, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp, ctypes.c_uint32,
                              _vp, _vp, _vp, _vp],
@@ -289,6 +291,12 @@ class Engine(object):
                                                  _vp(d_seed32) if d_seed32 else None,
                                                  _vp(d_keyhash64) if d_keyhash64 else None, _vp(d_vals),
                                                  _vp(stream) if stream else None))
+
+    def set_rows_csr_strided_dev(self, n, first_row_index, row_stride, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, stream=0):
+        _check(self._lib.jubann_set_rows_csr_strided_dev(self._h, int(n), int(first_row_index), int(row_stride), int(nnz),
+                                                         _vp(d_indptr), _vp(d_seed32) if d_seed32 else None,
+                                                         _vp(d_keyhash64) if d_keyhash64 else None, _vp(d_vals),
+                                                         _vp(stream) if stream else None))
 
     def scan_local_dev(self, nq, d_qsigs, d_qnorms, k, d_cand_key, d_cand_index, stream=0):
         _check(self._lib.jubann_scan_local_dev(self._h, int(nq), _vp(d_qsigs), _vp(d_qnorms) if d_qnorms else None,

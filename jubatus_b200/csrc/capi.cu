@@ -1064,8 +1064,10 @@ int jubann_hash_csr_dev(jubann_t* h, uint64_t n, uint64_t nnz, const uint64_t* d
                      static_cast<cudaStream_t>(stream), false);
 }
 
-int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, uint64_t nnz, const uint64_t* d_indptr,
-                            const uint32_t* d_seed32, const uint64_t* d_keyhash64, const float* d_vals, void* stream) {
+// rows first_row_index + i * row_stride (stride 1: a contiguous run; stride = shard_count: the rows of one shard only)
+static int set_rows_csr_dev_impl(jubann_t* h, uint64_t n, uint64_t first_row_index, uint64_t row_stride, uint64_t nnz,
+                                 const uint64_t* d_indptr, const uint32_t* d_seed32, const uint64_t* d_keyhash64,
+                                 const float* d_vals, void* stream) {
   int rc = check_handle(h);
   if (rc) return rc;
   if (n == 0) return 0;
@@ -1073,8 +1075,14 @@ int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, u
   if (h->method == MINHASH ? (nnz && !d_keyhash64) : (nnz && !d_seed32)) return fail(JUBANN_E_INVALID, "missing feature hashes for this method");
   NOT_FOR_GROUPS();
   Guard g(h);
-  if (first_row_index > h->global_rows) return fail(JUBANN_E_RANGE, "row index skips past the table end");
-  const uint64_t new_global = std::max(h->global_rows, first_row_index + n);
+  if (row_stride != 1) {
+    if (row_stride != h->shard_count || first_row_index % h->shard_count != h->shard_rank)
+      return fail(JUBANN_E_INVALID, "a strided batch must step by the shard count and start on a row of this shard");
+    if (first_row_index / h->shard_count > h->local_rows) return fail(JUBANN_E_RANGE, "row index skips past the end of this shard");
+  } else if (first_row_index > h->global_rows) {
+    return fail(JUBANN_E_RANGE, "row index skips past the table end");
+  }
+  const uint64_t new_global = std::max(h->global_rows, first_row_index + (n - 1) * row_stride + 1);
   rc = reserve_global(h, new_global);
   if (rc) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -1083,10 +1091,23 @@ int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, u
   rc = hash_device(h, n, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, h->b_sigs.as<uint64_t>(), h->b_norms.as<float>(), st, false);
   if (rc) return rc;
   CK(launch_scatter_rows(view_grown(h, new_global), n, nullptr, first_row_index, h->b_sigs.as<uint64_t>(),
-                         h->method == EUCLID_LSH ? h->b_norms.as<float>() : nullptr, h->shard_rank, h->shard_count, h->num_sms, st));
+                         h->method == EUCLID_LSH ? h->b_norms.as<float>() : nullptr, h->shard_rank, h->shard_count, h->num_sms, st,
+                         row_stride));
   h->kernel_launches += 1;
   commit_global(h, new_global);
   return order_after_caller_stream(h, st);
+}
+
+int jubann_set_rows_csr_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, uint64_t nnz, const uint64_t* d_indptr,
+                            const uint32_t* d_seed32, const uint64_t* d_keyhash64, const float* d_vals, void* stream) {
+  return set_rows_csr_dev_impl(h, n, first_row_index, 1, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, stream);
+}
+
+int jubann_set_rows_csr_strided_dev(jubann_t* h, uint64_t n, uint64_t first_row_index, uint64_t row_stride, uint64_t nnz,
+                                    const uint64_t* d_indptr, const uint32_t* d_seed32, const uint64_t* d_keyhash64,
+                                    const float* d_vals, void* stream) {
+  if (row_stride == 0) return fail(JUBANN_E_INVALID, "row_stride is zero");
+  return set_rows_csr_dev_impl(h, n, first_row_index, row_stride, nnz, d_indptr, d_seed32, d_keyhash64, d_vals, stream);
 }
 
 int jubann_scan_local_dev(jubann_t* h, uint64_t nq, const uint64_t* d_qsigs, const float* d_qnorms, uint32_t k,

@@ -115,7 +115,8 @@ cudaError_t launch_merge_parts(const uint32_t* d_cand_key, const uint64_t* d_can
 // rows given row-major ([n][w64] u64 words) -> slab at local slot (g / G) when g % G == rank
 cudaError_t launch_scatter_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                 uint64_t first_index, const uint64_t* d_sigs, const float* d_norms,
-                                uint32_t shard_rank, uint32_t shard_count, int num_sms, cudaStream_t s);
+                                uint32_t shard_rank, uint32_t shard_count, int num_sms, cudaStream_t s,
+                                uint64_t index_stride = 1);   // without d_row_index: row r goes to first_index + r * index_stride
 cudaError_t launch_gather_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                uint64_t* d_sigs, float* d_norms, uint32_t shard_rank,
                                uint32_t shard_count, int num_sms, cudaStream_t s);

@@ -11,7 +11,7 @@ namespace jbn {
 
 // one thread per (row, 32-bit word): row-major ABI words -> tile-transposed slab
 __global__ void scatter_rows_kernel(TableView t, uint64_t n, const uint64_t* __restrict__ row_index,
-                                    uint64_t first_index, const uint64_t* __restrict__ sigs,
+                                    uint64_t first_index, uint64_t stride, const uint64_t* __restrict__ sigs,
                                     const float* __restrict__ norms, uint32_t rank, uint32_t G) {
   const uint64_t total = n * t.w32;
   unsigned char* slab = static_cast<unsigned char*>(t.slab);
@@ -19,7 +19,7 @@ __global__ void scatter_rows_kernel(TableView t, uint64_t n, const uint64_t* __r
        e += (uint64_t)gridDim.x * blockDim.x) {
     const uint64_t r = e / t.w32;
     const uint32_t w = (uint32_t)(e % t.w32);
-    const uint64_t g = row_index ? row_index[r] : first_index + r;
+    const uint64_t g = row_index ? row_index[r] : first_index + r * stride;
     // IDX_SENTINEL: an entry the host struck out (a later entry of the batch writes the same row)
     if (g == IDX_SENTINEL || g % G != rank) continue;
     const uint64_t i = g / G;
@@ -123,10 +123,11 @@ static unsigned grid_for(uint64_t total, int num_sms) {
 
 cudaError_t launch_scatter_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,
                                 uint64_t first_index, const uint64_t* d_sigs, const float* d_norms,
-                                uint32_t shard_rank, uint32_t shard_count, int num_sms, cudaStream_t s) {
+                                uint32_t shard_rank, uint32_t shard_count, int num_sms, cudaStream_t s,
+                                uint64_t index_stride) {
   if (n == 0) return cudaSuccess;
-  scatter_rows_kernel<<<grid_for(n * t.w32, num_sms), 256, 0, s>>>(t, n, d_row_index, first_index, d_sigs, d_norms,
-                                                                   shard_rank, shard_count);
+  scatter_rows_kernel<<<grid_for(n * t.w32, num_sms), 256, 0, s>>>(t, n, d_row_index, first_index, index_stride, d_sigs,
+                                                                   d_norms, shard_rank, shard_count);
   return cudaGetLastError();
 }
 cudaError_t launch_gather_rows(const TableView& t, uint64_t n, const uint64_t* d_row_index,

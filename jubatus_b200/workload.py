@@ -126,3 +126,89 @@ def random_signatures(seed, n, w64):
     i = np.arange(n * w64, dtype=np.uint64)
     with np.errstate(over="ignore"):
         return splitmix64(np.uint64(seed) + i).reshape(n, w64)
+
+
+# --------------------------------------------------------------------------------------
+# The same generator on a torch device (bench.py builds 10^8-row tables with it; the numpy
+# form above would take minutes).  int64 tensors stand for the uint64 values: add / multiply /
+# xor wrap the same way, right shifts are made logical by masking.  Bit-identical to
+# synth_rows (tests/test_workload.py).
+# --------------------------------------------------------------------------------------
+def _s64(c):
+    c &= 0xFFFFFFFFFFFFFFFF
+    return c - (1 << 64) if c >= (1 << 63) else c
+
+
+def _lsr(x, s):
+    return (x >> s) & ((1 << (64 - s)) - 1)
+
+
+def splitmix64_torch(x):
+    x = x + _s64(0x9E3779B97F4A7C15)
+    x = (x ^ _lsr(x, 30)) * _s64(0xBF58476D1CE4E5B9)
+    x = (x ^ _lsr(x, 27)) * _s64(0x94D049BB133111EB)
+    return x ^ _lsr(x, 31)
+
+
+def synth_draw_torch(seed, row, t):
+    return splitmix64_torch(splitmix64_torch(splitmix64_torch(row) ^ _s64(seed)) + t)
+
+
+def synth_rows_torch(seed, rows, nnz=100, nfeat_log2=20):
+    """rows: int64 tensor of global row numbers (any order, any device).
+    Returns ids int64 [n][nnz] ascending and vals float32 [n][nnz], equal to synth_rows row by row."""
+    import torch
+    dev = rows.device
+    n = rows.shape[0]
+    mask = (1 << nfeat_log2) - 1
+    draws = nnz + 32
+    t = torch.arange(draws, dtype=torch.int64, device=dev)
+    d = synth_draw_torch(seed, rows[:, None], t[None, :]) & mask
+    sd, order = torch.sort(d, dim=1, stable=True)
+    first = torch.ones_like(sd, dtype=torch.bool)
+    first[:, 1:] = sd[:, 1:] != sd[:, :-1]
+    is_first = torch.zeros_like(first)
+    is_first.scatter_(1, order, first)
+    del sd, order, first
+    rank = torch.cumsum(is_first, dim=1)
+    ok = rank[:, -1] >= nnz
+    sel = is_first & (rank <= nnz)
+    del rank, is_first
+    if bool(ok.all()):
+        ids = d[sel].reshape(n, nnz)
+    else:   # a row with more than 32 repeated draws (never seen; kept exact all the same)
+        ids = torch.zeros((n, nnz), dtype=torch.int64, device=dev)
+        ids[ok] = d[ok][sel[ok]].reshape(-1, nnz)
+        bad = (~ok).nonzero().reshape(-1)
+        for b in bad.tolist():
+            one, _ = synth_rows(seed, int(rows[b].item()), 1, nnz, nfeat_log2)
+            ids[b] = torch.from_numpy(one[0].astype(np.int64)).to(dev)
+    del d, sel
+    ids, _ = torch.sort(ids, dim=1)
+    dv = synth_draw_torch(seed, rows[:, None], ids + (1 << 32))
+    vals = _lsr(dv, 40).to(torch.float32) * (1.0 / 16777216.0) + 1.0
+    return ids, vals
+
+
+def make_queries_lazy(seed, nq, nrows, nnz=100, nfeat_log2=20, query_row0=0):
+    """make_queries without the stored rows in hand: the duplicated rows are regenerated on demand
+    (row r of the table is a function of (seed, r) alone).  Returns ids, vals, and for each query
+    the stored row it was copied from (-1: none; the near duplicates share 90 of 100 features)."""
+    ids, vals = synth_rows(seed ^ 0x51, query_row0, nq, nnz, nfeat_log2)
+    exact_of = np.full(nq, -1, dtype=np.int64)
+    near_of = np.full(nq, -1, dtype=np.int64)
+    if nrows:
+        ndup = max(1, nq // 100)
+        for j in range(min(ndup, nq)):
+            src = int(splitmix64(np.uint64(seed + 7 * (query_row0 + j))) % np.uint64(nrows))
+            sid, sval = synth_rows(seed, src, 1, nnz, nfeat_log2)
+            ids[j], vals[j] = sid[0], sval[0]
+            exact_of[j] = src
+        for j in range(ndup, min(2 * ndup, nq)):
+            src = int(splitmix64(np.uint64(seed + 7 * (query_row0 + j) + 3)) % np.uint64(nrows))
+            sid, _ = synth_rows(seed, src, 1, nnz, nfeat_log2)
+            mixed = np.unique(np.concatenate([sid[0][: nnz - nnz // 10], ids[j]]))[:nnz]
+            if len(mixed) == nnz:
+                ids[j] = mixed
+                near_of[j] = src
+    return ids, vals, exact_of, near_of
