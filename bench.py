@@ -501,8 +501,8 @@ def bench_scan(env, a, name, method, hash_num, rows, nq, k, qp, flags, steps, wa
     eng.set_option("reserve_rows", rows)
     seed = workload.MASTER_SEED
     t_build = build_table(env, eng, method, rows, seed)
-    assert eng.size()[0] == rows
     local_rows = eng.size()[1]
+    assert local_rows == ((rows - rank + G - 1) // G if rows > rank else 0)   # (a shard knows the table up to its own last row)
     nsets = 4 if nq <= 256 else 2
     qs = QuerySets(env, eng, method, hash_num, rows, nq, nsets, seed)
     outs = (torch.zeros((nq, k), dtype=torch.int64, device=env.dev), torch.zeros((nq, k), dtype=torch.float32, device=env.dev),
@@ -615,11 +615,13 @@ def bench_c5(env, a, rows, adds, scores, interval=512):
         env.dist.broadcast_object_list(box, src=0)
         an.comm_init(box[0], rank, G)
     t0 = time.time()
-    chunk = 100_000
+    chunk = 250_000
     for r0 in range(0, rows, chunk):
         n = min(chunk, rows - r0)
-        ids, vals = workload.synth_rows(workload.MASTER_SEED, r0, n, NNZ, NFEAT_LOG2)
-        an.add_bulk_numeric(ids, vals, prefix="b")
+        g = env.torch.arange(r0, r0 + n, device=env.dev, dtype=env.torch.int64)
+        ids, vals = workload.synth_rows_torch(workload.MASTER_SEED, g, NNZ, NFEAT_LOG2)   # the same rows on every replica
+        an.add_bulk_numeric(ids.cpu().numpy().astype(np.uint32), vals.cpu().numpy(), prefix="b")
+        del g, ids, vals
     t_load = time.time() - t0
     if G > 1:
         an.mix_allgather()            # the bulk load is known to every replica already: settle the clocks
@@ -771,10 +773,18 @@ def main():
     sys.stdout.flush()
     _REAL_STDOUT = os.dup(1)
     os.dup2(2, 1)
-    if a.impl == "reference":
-        run_reference(a)
-    else:
-        run_b200(a)
+    try:
+        if a.impl == "reference":
+            run_reference(a)
+        else:
+            run_b200(a)
+    except BaseException:
+        # a rank that fails must not linger in a destructor that waits for its peers (they would wait
+        # for it in the next collective): report and leave at once, so that the launcher ends the job
+        import traceback
+        traceback.print_exc()
+        sys.stderr.flush()
+        os._exit(1)
 
 
 if __name__ == "__main__":

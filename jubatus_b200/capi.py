@@ -44,6 +44,25 @@ _f32p = ctypes.POINTER(ctypes.c_float)
 _vp = ctypes.c_void_p
 
 
+def _point_at_torch_nccl():
+    """libjubann.so opens NCCL by SONAME on first use.  In a Python process torch brings its own build of
+    libnccl.so.2 (the nvidia-nccl wheel); whichever copy is loaded first serves both, and torch does not
+    import against an older system copy.  So name torch's copy to the library up front (no torch import
+    needed); a C++ host has no such second copy and uses the system one."""
+    if os.environ.get("JUBANN_NCCL_LIBRARY"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (list(spec.submodule_search_locations) if spec and spec.submodule_search_locations else []):
+            cand = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["JUBANN_NCCL_LIBRARY"] = cand
+                return
+    except Exception:
+        pass
+
+
 def load_library():
     """dlopen the CUDA library.  No fallback: a missing library is an error."""
     global _lib
@@ -54,6 +73,7 @@ def load_library():
         raise ImportError(
             "%s not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(jubatus_b200 has no CPU fallback)" % path)
+    _point_at_torch_nccl()
     lib = ctypes.CDLL(path)
     lib.version.restype = ctypes.c_char_p
     lib.jubann_last_error.restype = ctypes.c_char_p

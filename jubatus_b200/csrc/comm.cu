@@ -123,8 +123,10 @@ void comm_destroy(jubann_t* h) {
   h->shards.clear();
   CommState* c = h->comm;
   if (!c) return;
-  const NcclApi* api = nccl_api();
-  if (c->comm && api) api->CommDestroy(c->comm);
+  if (c->comm) {   // (NCCL is looked up only by a handle that has a communicator: no need to load it to tear down a world of one)
+    const NcclApi* api = nccl_api();
+    if (api) api->CommDestroy(c->comm);
+  }
   DevBuf* bufs[] = {&c->send, &c->recv, &c->qbuf, &c->mix_send, &c->mix_recv, &c->mix_counts, &c->mix_sel};
   for (DevBuf* b : bufs) b->release();
   c->mix_host.release();

@@ -332,12 +332,25 @@ int jubahost_mix_allgather(void* h, uint64_t* stats) {
     } else {   // recommender / anomaly / classifier: the engine's table and this box's converter
       weight_manager::counts mine;
       b->conv_mut().weights().get_diff(mine);
+      // extra = [u64 length | converter weight counts | light_lof (kdist, lrd) diff]
+      const std::string counts = weight_manager::pack_counts(mine);
+      std::string extra;
+      const uint64_t clen = counts.size();
+      extra.append(reinterpret_cast<const char*>(&clen), 8);
+      extra += counts;
+      if (b->lof) extra += b->lof->pack_param_diff();
       std::vector<std::string> extras;
-      st = b->nn()->mix_allgather(weight_manager::pack_counts(mine), &extras);
+      st = b->nn()->mix_allgather(extra, &extras);
       weight_manager::counts acc;
-      for (size_t r = 0; r < extras.size(); ++r)
-        if (!extras[r].empty()) weight_manager::mix(weight_manager::unpack_counts(extras[r]), acc);
+      for (size_t r = 0; r < extras.size(); ++r) {
+        if (extras[r].size() < 8) continue;
+        uint64_t len; memcpy(&len, extras[r].data(), 8);
+        if (extras[r].size() < 8 + len) throw jubatus_exception("mix: truncated blob");
+        if (len) weight_manager::mix(weight_manager::unpack_counts(extras[r].substr(8, len)), acc);
+        if (b->lof) b->lof->apply_param_diff(extras[r], 8 + len);   // rank order: the same result on every replica
+      }
       b->conv_mut().weights().put_diff(acc);
+      if (b->lof) b->lof->clear_param_dirty();
     }
     if (stats) { stats[0] = st.rows_sent; stats[1] = st.rows_gathered; stats[2] = st.rows_stored; stats[3] = st.blob_bytes; }
     return 0;
@@ -599,6 +612,90 @@ int jubahost_calc_score_id(void* h, const char* id, float* score) {
 int jubahost_lof_params(void* h, const char* id, float* kdist, float* lrd) {
   host_box* b = static_cast<host_box*>(h);
   return guarded([&]() { return b->lof && b->lof->get_row_parameter(id, kdist, lrd) ? 0 : 1; });
+}
+
+// ---- number-only datums whose keys are decimal feature ids (the synthetic workload of SURVEY 8d):
+// the datum is built here, in C++, and takes the same road as any other (converter -> sfv -> engine);
+// what is saved is the Python-side marshalling of 100 key strings per datum. ----
+static datum numeric_datum(uint32_t nnz, const uint32_t* fids, const float* vals) {
+  datum d;
+  d.num_values.reserve(nnz);
+  char key[16];
+  for (uint32_t j = 0; j < nnz; ++j) {
+    char* e = key + sizeof key;   // decimal digits, written backwards
+    char* p = e;
+    uint32_t f = fids[j];
+    do { *--p = static_cast<char>('0' + f % 10); f /= 10; } while (f);
+    d.num_values.push_back(std::make_pair(std::string(p, e - p), static_cast<double>(vals[j])));
+  }
+  return d;
+}
+// rows "<prefix><first_id + i>": batched set_rows (nearest_neighbor) or light_lof::set_rows_bulk (anomaly)
+int jubahost_set_rows_numeric(void* h, uint64_t n, const char* prefix, uint64_t first_id, uint32_t nnz, const uint32_t* fids,
+                              const float* vals) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->serv && !b->lof) throw jubatus_exception("set_rows: nearest_neighbor and anomaly servers only");
+    std::vector<std::string> vid(n);
+    for (uint64_t i = 0; i < n; ++i) vid[i] = std::string(prefix ? prefix : "") + std::to_string(first_id + i);
+    std::vector<sfv_t> v;
+    const unsigned threads = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    b->conv_mut().convert_and_update_weight_batch(
+        n, [&](size_t i) { return numeric_datum(nnz, fids + i * nnz, vals + i * nnz); }, v, threads);
+    if (b->lof) b->lof->set_rows_bulk(vid, v); else b->nn()->set_rows(vid, v);
+    return 0;
+  });
+}
+// anomaly add(datum) with a given id: set_row, then the new row's score (anomaly_serv.cpp:157-176)
+int jubahost_add_numeric(void* h, const char* id, uint32_t nnz, const uint32_t* fids, const float* vals, float* score) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->lof) throw jubatus_exception("add: anomaly server only");
+    sfv_t v;
+    b->conv_mut().convert_and_update_weight(numeric_datum(nnz, fids, vals), v);
+    b->lof->set_row(id, v);
+    *score = b->lof->calc_anomaly_score(std::string(id));
+    return 0;
+  });
+}
+int jubahost_calc_score_numeric(void* h, uint32_t nnz, const uint32_t* fids, const float* vals, float* score) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    if (!b->lof) throw jubatus_exception("calc_score: anomaly server only");
+    sfv_t v;
+    b->conv().convert(numeric_datum(nnz, fids, vals), v);
+    *score = b->lof->calc_anomaly_score(v);
+    return 0;
+  });
+}
+// out[0]: order-independent digest of (key, signature, norm) over the whole table; out[1]: of the
+// light_lof (kdist, lrd) table (0 for other servers).  Replicas that hold the same rows agree.
+int jubahost_table_digest(void* h, uint64_t* out) {
+  host_box* b = static_cast<host_box*>(h);
+  return guarded([&]() {
+    const std::shared_ptr<device_table> t = b->nn()->get_table();
+    const uint64_t n = t->size();
+    uint64_t acc = 0;
+    const uint64_t step = 1u << 18;
+    std::vector<uint64_t> idx;
+    std::vector<packed_row> rows;
+    for (uint64_t r0 = 0; r0 < n; r0 += step) {
+      const uint64_t r1 = std::min(n, r0 + step);
+      idx.resize(r1 - r0);
+      for (uint64_t i = r0; i < r1; ++i) idx[i - r0] = i;
+      t->get_rows(idx, rows);
+      for (size_t i = 0; i < rows.size(); ++i) {
+        uint64_t x = calc_string_hash(rows[i].key);
+        for (size_t w = 0; w < rows[i].sig.size(); ++w) { x ^= rows[i].sig[w]; x *= 0x9E3779B97F4A7C15ULL; x ^= x >> 29; }
+        uint32_t nb; memcpy(&nb, &rows[i].norm, 4);
+        x ^= nb; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33;
+        acc += x;
+      }
+    }
+    out[0] = acc;
+    out[1] = b->lof ? b->lof->param_digest() : 0;
+    return 0;
+  });
 }
 
 }  // extern "C"

@@ -45,6 +45,7 @@
 #include <stdexcept>
 #include <string>
 #include <unordered_map>
+#include <thread>
 #include <unordered_set>
 #include <utility>
 #include <vector>
@@ -227,6 +228,7 @@ class weight_manager {
     fv.resize(w);
   }
   void clear() { master_ = counts(); diff_ = counts(); }
+  void add_documents(uint64_t n) { diff_.documents += n; }   // n stored rows without any idf feature
   // MIX: every replica's diff is summed and the sum lands in every master
   void get_diff(counts& out) const { out = diff_; }
   static void mix(const counts& lhs, counts& acc) { acc.add(lhs); }
@@ -398,6 +400,32 @@ class datum_to_fv_converter {
     weights_.get_weight(out);
     finish(out);
   }
+  // A batch of stored rows, same result as convert_and_update_weight row by row.  Without an idf
+  // rule a row's weights do not depend on the rows before it (only the document count moves), so
+  // the conversion itself is spread over `threads` host threads; with one, rows go in order.
+  bool has_idf() const {
+    for (size_t r = 0; r < string_rules_.size(); ++r) if (string_rules_[r].global_weight == "idf") return true;
+    return false;
+  }
+  template <typename MakeDatum>
+  void convert_and_update_weight_batch(size_t n, MakeDatum make, std::vector<sfv_t>& out, unsigned threads) {
+    out.resize(n);
+    if (has_idf() || threads < 2 || n < 1024) {
+      for (size_t i = 0; i < n; ++i) convert_and_update_weight(make(i), out[i]);
+      return;
+    }
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < threads; ++t)
+      th.push_back(std::thread([&, t]() {
+        for (size_t i = n * t / threads; i < n * (t + 1) / threads; ++i) {
+          convert_unweighted(make(i), out[i]);
+          weights_.get_weight(out[i]);
+          finish(out[i]);
+        }
+      }));
+    for (size_t t = 0; t < th.size(); ++t) th[t].join();
+    weights_.add_documents(n);
+  }
   weight_manager& weights() { return weights_; }
   const weight_manager& weights() const { return weights_; }
   void clear_weights() { weights_.clear(); }
@@ -538,8 +566,16 @@ class device_table {
   uint32_t words() const { return w64_; }
   void clear() {
     api_->check(api_->clear(h_));
-    keys_.clear(); versions_.clear(); index_.clear(); clock_ = 0;
+    keys_.clear(); versions_.clear(); index_.clear(); clock_ = 0; dirty_.clear();
   }
+  // rows stamped locally since the last MIX round (what get_diff has to look at: a row whose
+  // version is newer than the agreed clocks got that version here, through assign or unpack)
+  std::vector<uint64_t> dirty_rows() const {
+    std::vector<uint64_t> d(dirty_.begin(), dirty_.end());
+    std::sort(d.begin(), d.end());
+    return d;
+  }
+  void clear_dirty() { dirty_.clear(); }
   std::pair<bool, uint64_t> exact_match(const std::string& key) const {
     std::unordered_map<std::string, uint64_t>::const_iterator it = index_.find(key);
     if (it == index_.end()) return std::make_pair(false, 0);
@@ -571,12 +607,13 @@ class device_table {
         if (undo && idx[i] < undo->rows_before) undo->overwritten.push_back(std::make_pair(idx[i], versions_[idx[i]]));
         versions_[idx[i]] = version_t(owner, clock_);
       }
+      dirty_.insert(idx[i]);
       ++clock_;
     }
     return idx;
   }
   void rollback(const assign_journal& j) {
-    while (keys_.size() > j.rows_before) { index_.erase(keys_.back()); keys_.pop_back(); versions_.pop_back(); }
+    while (keys_.size() > j.rows_before) { index_.erase(keys_.back()); keys_.pop_back(); versions_.pop_back(); dirty_.erase(keys_.size()); }
     for (size_t i = j.overwritten.size(); i-- > 0;) versions_[j.overwritten[i].first] = j.overwritten[i].second;
     clock_ = j.clock_before;
   }
@@ -590,7 +627,11 @@ class device_table {
       keys_[idx] = keys_[last];
       versions_[idx] = versions_[last];
       index_[keys_[idx]] = idx;
+      if (dirty_.count(last)) dirty_.insert(idx); else dirty_.erase(idx);
+    } else {
+      dirty_.erase(idx);
     }
+    dirty_.erase(last);
     api_->check(api_->truncate(h_, last));
     index_.erase(key);
     keys_.pop_back(); versions_.pop_back();
@@ -710,7 +751,7 @@ class device_table {
       api_->check(api_->set_rows_sig(h_, n, idx.data(), sigs.data(), norms.data()));
     }
     keys_.swap(keys); versions_.swap(versions); clock_ = clock;
-    for (uint64_t i = 0; i < n; ++i) index_[keys_[i]] = i;
+    for (uint64_t i = 0; i < n; ++i) { index_[keys_[i]] = i; dirty_.insert(i); }
   }
 
  private:
@@ -732,6 +773,7 @@ class device_table {
   std::vector<std::string> keys_;
   std::vector<version_t> versions_;
   std::unordered_map<std::string, uint64_t> index_;
+  std::unordered_set<uint64_t> dirty_;
 };
 
 // ---------------------------------------------------------------------------------------
@@ -783,7 +825,9 @@ class mixable_versioned_table {
     // get_diff: rows newer than the clocks agreed at the last round
     std::vector<uint64_t> idx;
     std::string blob;
-    for (uint64_t i = 0; i < table_->size(); ++i) {
+    const std::vector<uint64_t> touched = table_->dirty_rows();   // not the whole table: a round costs what changed
+    for (size_t t = 0; t < touched.size(); ++t) {
+      const uint64_t i = touched[t];
       const version_t& v = table_->get_version(i);
       version_clock::const_iterator it = vc_.find(v.first);
       if (it == vc_.end() || it->second < v.second) {
@@ -824,6 +868,7 @@ class mixable_versioned_table {
     }
     st.rows_stored = dst.size();
     if (!dst.empty()) a.check(a.mix_apply(table_->handle(), dst.size(), src_rank.data(), src_pos.data(), dst.data()));
+    table_->clear_dirty();   // every row sent is now covered by the agreed clocks
     return st;
   }
 
@@ -1604,11 +1649,60 @@ class light_lof {
     // the victim leaves the engine's table and the (kdist, lrd) table; rows that had it as a
     // neighbour keep their parameters until they are next re-scored
     if (unlearner_) unlearner_->set_callback([this](const std::string& victim) {
-      nn_->delete_row(victim); kdist_.erase(victim); lrd_.erase(victim);
+      nn_->delete_row(victim); kdist_.erase(victim); lrd_.erase(victim); param_dirty_.erase(victim);
     });
   }
-  void clear() { nn_->clear(); kdist_.clear(); lrd_.clear(); if (unlearner_) unlearner_->clear(); }
+  void clear() { nn_->clear(); kdist_.clear(); lrd_.clear(); param_dirty_.clear(); if (unlearner_) unlearner_->clear(); }
   const unlearner_base* get_unlearner() const { return unlearner_.get(); }
+
+  // light_lof's second mixable ([core] anomaly/light_lof: a versioned table of (kdist, lrd) beside
+  // the engine's; anomaly_serv.cpp:134-138 registers both with the mixer).  The diff is every row
+  // whose parameters were (re)computed here since the last round; every replica applies the
+  // gathered diffs in rank order, so a row two replicas re-scored ends up the same everywhere.
+  std::string pack_param_diff() const {
+    std::string out;
+    const uint64_t n = param_dirty_.size();
+    out.append(reinterpret_cast<const char*>(&n), 8);
+    std::vector<std::string> keys(param_dirty_.begin(), param_dirty_.end());
+    std::sort(keys.begin(), keys.end());
+    for (size_t i = 0; i < keys.size(); ++i) {
+      const uint64_t len = keys[i].size();
+      const float kd = kdist_.find(keys[i])->second, lr = lrd_.find(keys[i])->second;
+      out.append(reinterpret_cast<const char*>(&len), 8);
+      out.append(keys[i]);
+      out.append(reinterpret_cast<const char*>(&kd), 4);
+      out.append(reinterpret_cast<const char*>(&lr), 4);
+    }
+    return out;
+  }
+  // returns the bytes consumed; rows this replica does not hold (unlearned meanwhile) are skipped
+  size_t apply_param_diff(const std::string& b, size_t p = 0) {
+    if (b.size() < p + 8) throw jubatus_exception("mix: truncated light_lof diff");
+    uint64_t n; memcpy(&n, b.data() + p, 8); p += 8;
+    for (uint64_t i = 0; i < n; ++i) {
+      if (b.size() < p + 8) throw jubatus_exception("mix: truncated light_lof diff");
+      uint64_t len; memcpy(&len, b.data() + p, 8); p += 8;
+      if (b.size() < p + len + 8) throw jubatus_exception("mix: truncated light_lof diff");
+      const std::string key(b.data() + p, len); p += len;
+      float kd, lr; memcpy(&kd, b.data() + p, 4); memcpy(&lr, b.data() + p + 4, 4); p += 8;
+      if (nn_->get_table()->exact_match(key).first) { kdist_[key] = kd; lrd_[key] = lr; }
+    }
+    return p;
+  }
+  void clear_param_dirty() { param_dirty_.clear(); }
+  // order-independent digest of the (kdist, lrd) table (tests, bench: replicas agree after MIX)
+  uint64_t param_digest() const {
+    uint64_t acc = 0;
+    for (std::unordered_map<std::string, float>::const_iterator it = kdist_.begin(); it != kdist_.end(); ++it) {
+      uint32_t a, b;
+      const float lr = lrd_.find(it->first)->second;
+      memcpy(&a, &it->second, 4); memcpy(&b, &lr, 4);
+      uint64_t h = calc_string_hash(it->first) ^ (static_cast<uint64_t>(a) << 32 | b);
+      h ^= h >> 33; h *= 0xff51afd7ed558ccdULL; h ^= h >> 33;
+      acc += h;
+    }
+    return acc;
+  }
   static float calculate_lof(float lrd, const std::vector<float>& neighbor_lrds) {
     if (neighbor_lrds.empty()) return lrd == 0 ? 1.0f : std::numeric_limits<float>::infinity();
     float sum = 0.0f;
@@ -1653,6 +1747,7 @@ class light_lof {
         sum_reach += std::max(nn[i][j].second, it == kdist_.end() ? 0.0f : it->second);
       }
       lrd_[ids[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
+      param_dirty_.insert(ids[i]);
     }
   }
   // Bulk load for a table that is built in one go (benchmarks, restoring from raw data): rows go
@@ -1678,6 +1773,7 @@ class light_lof {
         float sum_reach = 0.0f;
         for (size_t j = 0; j < length; ++j) sum_reach += std::max(nn[i][j].second, kdist_[nn[i][j].first]);
         lrd_[part[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
+        param_dirty_.insert(part[i]);
       }
     }
   }
@@ -1716,6 +1812,7 @@ class light_lof {
   int nn_num_, rnn_num_;
   std::shared_ptr<unlearner_base> unlearner_;
   std::unordered_map<std::string, float> kdist_, lrd_;
+  std::unordered_set<std::string> param_dirty_;
 };
 
 }  // namespace jubatus_b200

@@ -58,6 +58,10 @@ def _load():
     lib.jubahost_set_row.argtypes = [_vp, ctypes.c_char_p, _vp, _vp, ctypes.c_uint64, _vp, _vp, ctypes.c_uint64]
     lib.jubahost_set_rows.argtypes = [_vp, ctypes.c_uint64, _vp, _vp, _vp, _vp]
     lib.jubahost_delete_row.argtypes = [_vp, ctypes.c_char_p]
+    lib.jubahost_set_rows_numeric.argtypes = [_vp, ctypes.c_uint64, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_uint32, _vp, _vp]
+    lib.jubahost_add_numeric.argtypes = [_vp, ctypes.c_char_p, ctypes.c_uint32, _vp, _vp, _vp]
+    lib.jubahost_calc_score_numeric.argtypes = [_vp, ctypes.c_uint32, _vp, _vp, _vp]
+    lib.jubahost_table_digest.argtypes = [_vp, _vp]
     lib.jubahost_query_datum.argtypes = [_vp, _vp, _vp, ctypes.c_uint64, _vp, _vp, ctypes.c_uint64, ctypes.c_uint64,
                                          ctypes.c_int, _vp, ctypes.c_uint64, _vp, ctypes.c_uint64, _vp]
     lib.jubahost_query_id.argtypes = [_vp, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int, _vp, ctypes.c_uint64, _vp,
@@ -253,6 +257,14 @@ class _HostHandle(object):
         if self._lib.jubahost_mix_allgather(self._h, ctypes.cast(st, _vp)):
             _raise()
         return {"rows_sent": st[0], "rows_gathered": st[1], "rows_stored": st[2], "blob_bytes": st[3]}
+
+    def table_digest(self):
+        """(digest of the rows, digest of light_lof's (kdist, lrd) table): order-independent, equal on
+        replicas that hold the same content."""
+        out = (ctypes.c_uint64 * 2)()
+        if self._lib.jubahost_table_digest(self._h, ctypes.cast(out, _vp)):
+            _raise()
+        return int(out[0]), int(out[1])
 
     def close(self):
         if getattr(self, "_h", None):
@@ -483,6 +495,39 @@ class Anomaly(_HostHandle):
                                        vals.ctypes.data_as(_vp)):
             _raise()
         return ids
+
+    # number-only datums keyed by decimal feature ids (SURVEY 8d's synthetic workload): the datum is
+    # built in the C++ host layer instead of being marshalled key by key from Python
+    def add_bulk_numeric(self, ids, vals, prefix=""):
+        ids = np.ascontiguousarray(ids, dtype=np.uint32)
+        vals = np.ascontiguousarray(vals, dtype=np.float32)
+        n, nnz = ids.shape
+        if self._lib.jubahost_set_rows_numeric(self._h, n, prefix.encode(), self._next_id, nnz, ids.ctypes.data_as(_vp),
+                                               vals.ctypes.data_as(_vp)):
+            _raise()
+        first = self._next_id
+        self._next_id += n
+        return first
+
+    def add_numeric(self, ids, vals, prefix=""):
+        ids = np.ascontiguousarray(ids, dtype=np.uint32)
+        vals = np.ascontiguousarray(vals, dtype=np.float32)
+        row_id = prefix + str(self._next_id)
+        self._next_id += 1
+        s = ctypes.c_float()
+        if self._lib.jubahost_add_numeric(self._h, row_id.encode(), len(ids), ids.ctypes.data_as(_vp), vals.ctypes.data_as(_vp),
+                                          ctypes.byref(s)):
+            _raise()
+        return row_id, s.value
+
+    def calc_score_numeric(self, ids, vals):
+        ids = np.ascontiguousarray(ids, dtype=np.uint32)
+        vals = np.ascontiguousarray(vals, dtype=np.float32)
+        s = ctypes.c_float()
+        if self._lib.jubahost_calc_score_numeric(self._h, len(ids), ids.ctypes.data_as(_vp), vals.ctypes.data_as(_vp),
+                                                 ctypes.byref(s)):
+            _raise()
+        return s.value
 
     def calc_score(self, d):
         _, _, _, nk, nv, nn = _datum_args(d)

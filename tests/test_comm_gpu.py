@@ -210,7 +210,7 @@ def _rank_main(rank, world, id_path, out_path, what):
                     got = e.query_sig(q[:1], None if qn is None else qn[:1], 3000)   # paginated k
                     want = oracle_lib.scan_batch(method, q[:1], None if qn is None else qn[:1], rows, norms, hash_num, 3000)[:3]
                     assert_same_ranking(got, want, 1, 3000)
-        else:   # MIX between two replicas
+        elif what == "mix":   # MIX between two replicas
             hash_num, n = 256, 500
             rows, norms = _table(rng, "euclid_lsh", hash_num, 2 * n, ties=False)
             with Engine("euclid_lsh", hash_num, rank) as e:
@@ -237,6 +237,8 @@ def _rank_main(rank, world, id_path, out_path, what):
                 assert np.array_equal(bn.view(np.uint32), want_norms.view(np.uint32))
                 back, _ = e.get_rows_sig(np.arange(n, dtype=np.uint64))   # my own rows are untouched
                 assert np.array_equal(back, rows[mine])
+        if what == "lof":
+            _lof_replicas(rank, world, cid)
         with open(out_path % rank, "w") as f:
             f.write("ok")
     except Exception:
@@ -244,7 +246,58 @@ def _rank_main(rank, world, id_path, out_path, what):
             f.write(traceback.format_exc())
 
 
+def _lof_replicas(rank, world, cid):
+    """jubaanomaly replicas (light_lof through the C++ host stack): rows stream into each replica, a MIX
+    round carries the row diffs (device records) and the (kdist, lrd) diffs; afterwards both replicas hold
+    the same rows and the same parameters and score alike."""
+    import json
+    from jubatus_b200 import nn
+    conv = {"string_filter_types": {}, "string_filter_rules": [], "num_filter_types": {}, "num_filter_rules": [],
+            "string_types": {}, "string_rules": [], "num_types": {}, "num_rules": [{"key": "*", "type": "num"}]}
+    cfg = json.dumps({"method": "light_lof", "converter": conv,
+                      "parameter": {"nearest_neighbor_num": 4, "reverse_nearest_neighbor_num": 8, "method": "lsh",
+                                    "parameter": {"hash_num": 256}}})
+    an = nn.Anomaly(cfg, my_id="replica%d" % rank, device=rank)
+    an.comm_init(cid, rank, world)
+    ids, vals = w.synth_rows(w.MASTER_SEED, 0, 400, nnz=12, nfeat_log2=8)
+    an.add_bulk_numeric(ids[:200], vals[:200], prefix="b")        # the same 200 rows on both
+    st = an.mix_allgather()
+    assert st["rows_sent"] == 200 and st["rows_gathered"] == 400
+    assert an.size() == 200
+    for rnd in range(3):
+        lo = 200 + rnd * 60 + rank * 30
+        for r in range(lo, lo + 30):                               # 30 rows of its own per round
+            an.add_numeric(ids[r], vals[r], prefix="r%d_" % rank)
+        st = an.mix_allgather()
+        assert st["rows_sent"] == 30 and st["rows_gathered"] == 60 and st["rows_stored"] >= 30
+        assert an.size() == 200 + (rnd + 1) * 60
+    st = an.mix_allgather()                                        # nothing changed: an empty round
+    assert st["rows_sent"] == 0 and st["rows_gathered"] == 0
+    digest = an.table_digest()
+    scores = [an.calc_score_numeric(ids[r], vals[r]) for r in range(380, 400)]
+    import pickle
+    path = os.environ["JUBANN_TEST_TMP"]
+    with open(os.path.join(path, "lof_%d.pkl.tmp" % rank), "wb") as f:
+        pickle.dump((digest, scores, sorted(an.get_all_rows())), f)
+    os.rename(os.path.join(path, "lof_%d.pkl.tmp" % rank), os.path.join(path, "lof_%d.pkl" % rank))
+    import time
+    other = os.path.join(path, "lof_%d.pkl" % (1 - rank))
+    for _ in range(1200):
+        if os.path.exists(other):
+            break
+        time.sleep(0.05)
+    d2, s2, keys2 = pickle.load(open(other, "rb"))
+    assert sorted(an.get_all_rows()) == keys2
+    assert digest == d2, (digest, d2)
+    # (replicas store the rows in different orders, so a tie at the k-th neighbour may resolve differently:
+    # scores are compared loosely, content exactly)
+    close = sum(1 for a, b in zip(scores, s2) if a == b or (a != a and b != b) or abs(a - b) <= 0.05 * abs(a))
+    assert close >= len(scores) - 2, (scores, s2)
+    an.close()
+
+
 def _run_two_ranks(tmp_path, what):
+    os.environ["JUBANN_TEST_TMP"] = str(tmp_path)
     ctx = mp.get_context("spawn")
     id_path = str(tmp_path / "comm_id")
     out_path = str(tmp_path / "rank%d.txt")
@@ -272,3 +325,9 @@ def test_two_replicas_mix_through_the_library(tmp_path):
     if _ngpu() < 2:
         pytest.skip("needs two GPUs")
     _run_two_ranks(tmp_path, "mix")
+
+
+def test_two_light_lof_replicas_mix_rows_and_parameters(tmp_path):
+    if _ngpu() < 2:
+        pytest.skip("needs two GPUs")
+    _run_two_ranks(tmp_path, "lof")

@@ -168,6 +168,30 @@ def test_anomaly_light_lof(oracle):
         nn.Anomaly(json.dumps({"method": "lof", "converter": CONVERTER, "parameter": {"method": "lsh", "parameter": {}}}))
 
 
+def test_anomaly_numeric_entry_points_equal_the_datum_ones():
+    # add_numeric / calc_score_numeric / add_bulk_numeric build the datum in C++ from feature ids: same
+    # rows, scores and parameters as datums marshalled key by key
+    cfg = json.dumps({"method": "light_lof", "converter": CONVERTER,
+                      "parameter": {"nearest_neighbor_num": 3, "reverse_nearest_neighbor_num": 6, "method": "lsh",
+                                    "parameter": {"hash_num": 128}}})
+    a, b = nn.Anomaly(cfg), nn.Anomaly(cfg)
+    ids, vals = w.synth_rows(w.MASTER_SEED, 11, 60, nnz=8, nfeat_log2=6)
+    a.add_bulk([datum_of(ids[r], vals[r]) for r in range(30)])
+    assert b.add_bulk_numeric(ids[:30], vals[:30]) == 0
+    for r in range(30, 50):
+        ra, sa = a.add(datum_of(ids[r], vals[r]))
+        rb, sb = b.add_numeric(ids[r], vals[r])
+        assert ra == rb and (sa == sb or (np.isnan(sa) and np.isnan(sb))), (r, sa, sb)
+    for r in range(50, 60):
+        sa, sb = a.calc_score(datum_of(ids[r], vals[r])), b.calc_score_numeric(ids[r], vals[r])
+        assert sa == sb or (np.isnan(sa) and np.isnan(sb))
+    assert a.table_digest() == b.table_digest()
+    for r in (0, 29, 31, 49):
+        assert a.lof_params(str(r)) == b.lof_params(str(r))
+    b.add_numeric(ids[0], vals[0])
+    assert a.table_digest() != b.table_digest()
+
+
 def test_concurrent_queries_are_coalesced_by_the_batcher(oracle):
     # the server answers queries from several RPC worker threads without the model lock
     # (nearest_neighbor_impl.cpp:75-102); the batcher turns them into batched launches
