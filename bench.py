@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--scan-variant", type=int, default=0)
     ap.add_argument("--configs", default="c2,c3,c4,c5", help="comma-separated subset of c2,c3,c4,c5 ('' = none)")
     ap.add_argument("--config-scale", type=float, default=1.0, help="shrink the rows of c2..c5 (development runs)")
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value for the headline engine (tuning runs)")
     ap.add_argument("--skip-cpu", action="store_true", help="omit the cpu_baseline / parity leg")
     ap.add_argument("--parity-queries", type=int, default=16)
     return ap.parse_args()
@@ -495,6 +496,9 @@ def bench_scan(env, a, name, method, hash_num, rows, nq, k, qp, flags, steps, wa
         opts["popc_variant"] = a.popc_variant
     if main and a.scan_variant:
         opts["scan_variant"] = a.scan_variant
+    if main:
+        for kv in a.opt:
+            opts[kv.split("=")[0]] = int(kv.split("=")[1])
     eng = Engine(method, hash_num, env.local_rank, rank, G, **opts)
     if G > 1:
         jd.comm_init_from_torch(eng)          # the library's own NCCL communicator; queries are collective from here on

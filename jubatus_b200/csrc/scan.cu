@@ -18,9 +18,12 @@
 // The CTA's k best are written to scratch; merge_local_kernel reduces the per-CTA lists.
 #include "internal.h"
 
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
+#include <vector>
 
 namespace jbn {
 
@@ -46,6 +49,8 @@ struct ScanArgs {
   uint32_t nq, k, cap, qp, w64, hash_num, tiles_per_chunk, nchunks;
   uint32_t w32;
   uint32_t interleave;  // 1: CTAs take turns tile-group by tile-group (one sweep front); 0: one contiguous range per CTA
+  unsigned long long* trace;   // tuning experiments ($JUBANN_SCAN_TRACE): per (CTA < 4, group) timestamps of warp 0
+  uint32_t debug;       // tuning experiments ($JUBANN_SCAN_DEBUG): 1 no early refresh, 2 no shared histogram, 4 no polling, 8 no refresh after a flush
 };
 
 // ---------------------------------------------------------------------------
@@ -303,11 +308,9 @@ __host__ __device__ __forceinline__ uint32_t tau_hi_of(unsigned long long tau) {
 //   every operation rounds towards +inf, and the result is moved one more float up.
 // A non-finite c or T disables the filter for that entry (+inf); a discriminant that is negative
 // even after rounding up means no norm is admissible at that distance (-inf).
-__device__ __forceinline__ float euclid_bound(double c, uint32_t tau_hi) {
+__device__ __forceinline__ float euclid_bound_core(float c_add, float c_mag, uint32_t tau_hi) {
   const float Tf = key_float(tau_hi);
-  if (!(fabsf(Tf) < INFINITY) || !(fabs(c) < (double)INFINITY)) return INFINITY;
-  const float c_add = __double2float_ru(c);
-  const float c_mag = c >= 0.0 ? c_add : __double2float_rd(c);          // |c_mag| >= |c|
+  if (!(fabsf(Tf) < INFINITY) || !(fabsf(c_mag) < INFINITY)) return INFINITY;
   float Tu = Tf + 0.0f;                                                   // -0 -> +0
   Tu = __uint_as_float(Tu >= 0.0f ? __float_as_uint(Tu) + 2u : (__float_as_uint(Tu) >= 0x80000002u ? __float_as_uint(Tu) - 2u : 1u));
   Tu = __fadd_ru(Tu, __fmaf_ru(1.5e-14f, __fmul_ru(c_mag, c_mag), 1e-37f));
@@ -317,6 +320,19 @@ __device__ __forceinline__ float euclid_bound(double c, uint32_t tau_hi) {
   const float hi = __fmul_ru(0.5f, __fadd_ru(c_add, __fsqrt_ru(disc)));
   if (!(fabsf(hi) < INFINITY)) return INFINITY;
   return __uint_as_float(hi >= 0.0f ? __float_as_uint(hi + 0.0f) + 1u : __float_as_uint(hi) - 1u);   // one more float up
+}
+__device__ __forceinline__ float euclid_bound(double c, uint32_t tau_hi) {
+  if (!(fabs(c) < (double)INFINITY)) return INFINITY;
+  const float c_add = __double2float_ru(c);
+  const float c_mag = c >= 0.0 ? c_add : __double2float_rd(c);          // |c_mag| >= |c|
+  return euclid_bound_core(c_add, c_mag, tau_hi);
+}
+// the same from c rounded up to float alone (the per-query table the TMA kernel keeps in shared memory,
+// so that re-deriving a query's bounds touches neither global memory nor the double pipe): where c is
+// squared, a negative c is taken one float further from zero, which covers the rounding of c_add
+__device__ __forceinline__ float euclid_bound_f(float c_add, uint32_t tau_hi) {
+  const float c_mag = c_add >= 0.0f ? c_add : __uint_as_float(__float_as_uint(c_add) + 1u);
+  return euclid_bound_core(c_add, c_mag, tau_hi);
 }
 
 // ---------------------------------------------------------------------------
@@ -340,8 +356,11 @@ struct ListCtl {
   uint32_t has_floor;
   uint32_t nq, q0, hist_stride;
   uint32_t* ghist;     // global: [nq] bound words | [nq][hist_stride] counts; nullptr when unused
+  uint32_t no_flush_refresh;
   // euclid only
   uint32_t bnd_off;    // float [qp][hash_num + 1]: norm above which a row at that distance cannot be admitted
+  uint32_t ctab_off;   // float [qp][hash_num + 1]: 2 * norm_q * cos(pi d / hash_num) rounded up, or NO_CTAB
+  uint32_t cos_off, qn_off;   // with a ctab: double [hash_num + 1] cos table and float [qp] query norms in shared memory
   uint32_t hash_num;
   const double* coslut;   // global: cos(pi * d / hash_num)
   const float* qnorms;    // global: query norms
@@ -349,6 +368,7 @@ struct ListCtl {
 #ifndef JBN_REFRESH_MOD
 #define JBN_REFRESH_MOD 4   // every JBN_REFRESH_MOD-th warp re-derives the shared bound after a flush
 #endif
+static const uint32_t NO_CTAB = 0xFFFFFFFFu;
 __shared__ ListCtl s_L;   // written once by the prologue, read by the rare-path functions
 
 __device__ __forceinline__ unsigned long long* sm_u64(uint32_t off) { return reinterpret_cast<unsigned long long*>(g_smem + off); }
@@ -359,9 +379,14 @@ __device__ __forceinline__ uint32_t* sm_u32(uint32_t off) { return reinterpret_c
 // admits every admissible norm.
 __device__ __noinline__ void euclid_bounds_update(uint32_t q, int lane) {
   const uint32_t th = *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride);
-  const double two_nq = (double)(2.0f * s_L.qnorms[s_L.q0 + q]);
   float* b = reinterpret_cast<float*>(g_smem + s_L.bnd_off) + (size_t)q * (s_L.hash_num + 1);
-  for (uint32_t d = lane; d <= s_L.hash_num; d += 32) b[d] = euclid_bound(__dmul_rn(two_nq, s_L.coslut[d]), th);
+  if (s_L.ctab_off != NO_CTAB) {
+    const float* c = reinterpret_cast<const float*>(g_smem + s_L.ctab_off) + (size_t)q * (s_L.hash_num + 1);
+    for (uint32_t d = lane; d <= s_L.hash_num; d += 32) b[d] = euclid_bound_f(c[d], th);
+  } else {
+    const double two_nq = (double)(2.0f * s_L.qnorms[s_L.q0 + q]);
+    for (uint32_t d = lane; d <= s_L.hash_num; d += 32) b[d] = euclid_bound(__dmul_rn(two_nq, s_L.coslut[d]), th);
+  }
   __syncwarp();
 }
 
@@ -471,40 +496,6 @@ __device__ __forceinline__ void hist_count(uint32_t gq, uint32_t key_hi) {
   }
 }
 
-// First bin b in [first, last] at which `run` + (counts of first..b) reaches k, or 0xFFFFFFFF;
-// `run` is advanced to the count of the bins before the returned one (or past `last`).  Eight
-// 32-bin blocks per round with their loads all in flight together (one L2 round trip per 256
-// bins).  `first` is a multiple of 32.
-__device__ __forceinline__ uint32_t hist_find(const volatile uint32_t* h, uint32_t first, uint32_t last, uint32_t& run,
-                                              uint32_t k, int lane) {
-  for (uint32_t base0 = first; base0 <= last; base0 += 256) {
-    uint32_t v[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const uint32_t d = base0 + 32u * j + lane;
-      v[j] = (d <= last) ? h[d] : 0u;
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const uint32_t tot = __reduce_add_sync(FULL_MASK, v[j]);
-      if (run + tot >= k) {   // the crossing is inside this block: locate it with one prefix scan
-        uint32_t x = v[j];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t n = __shfl_up_sync(FULL_MASK, x, o);
-          if (lane >= o) x += n;
-        }
-        const unsigned hit = __ballot_sync(FULL_MASK, run + x >= k);
-        const int l = __ffs(hit) - 1;
-        run += __shfl_sync(FULL_MASK, x - v[j], l);
-        return base0 + 32u * j + l;
-      }
-      run += tot;
-    }
-  }
-  return 0xFFFFFFFFu;
-}
-
 template <bool EUCLID>
 __device__ __noinline__ void hist_refresh(uint32_t q, int lane);
 
@@ -551,17 +542,54 @@ __device__ __noinline__ void hist_refresh<false>(uint32_t q, int lane) {
   __syncwarp();
 }
 
-// euclid_lsh: coarse bins locate the 256 fine bins in which the count reaches k
+// one 256-bin block [base0, base0 + 256) clipped at `last`: all eight loads of a lane in flight together
+__device__ __forceinline__ void hist_load8(const volatile uint32_t* h, uint32_t base0, uint32_t last, int lane, uint32_t (&v)[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t d = base0 + 32u * j + lane;
+    v[j] = (d <= last) ? h[d] : 0u;
+  }
+}
+// first bin of the loaded block at which run + (counts up to it) reaches k, or 0xFFFFFFFF; `run` is
+// advanced to the count of the bins before the returned one (or past the block)
+__device__ __forceinline__ uint32_t hist_scan8(const uint32_t (&v)[8], uint32_t base0, uint32_t& run, uint32_t k, int lane) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t tot = __reduce_add_sync(FULL_MASK, v[j]);
+    if (run + tot >= k) {
+      uint32_t x = v[j];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(FULL_MASK, x, o);
+        if (lane >= o) x += n;
+      }
+      const unsigned hit = __ballot_sync(FULL_MASK, run + x >= k);
+      const int l = __ffs(hit) - 1;
+      run += __shfl_sync(FULL_MASK, x - v[j], l);
+      return base0 + 32u * j + l;
+    }
+    run += tot;
+  }
+  return 0xFFFFFFFFu;
+}
+
+// euclid_lsh: coarse bins locate the 256 fine bins in which the count reaches k.  The bound rarely
+// leaves its coarse bin between two refreshes, so the fine bins under the current bound's coarse bin
+// are fetched together with the coarse ones: one L2 round trip instead of two in the common case.
 template <>
 __device__ __noinline__ void hist_refresh<true>(uint32_t q, int lane) {
   const uint32_t gq = s_L.q0 + q;
   const volatile uint32_t* h = s_L.ghist + s_L.nq + (size_t)gq * s_L.hist_stride;
   const uint32_t cur = *reinterpret_cast<volatile uint32_t*>(sm_u32(s_L.tauhi_off) + (size_t)q * s_L.tau_stride);
-  const uint32_t last16 = cur >> 16;
+  const uint32_t last16 = cur >> 16, Cg = last16 >> 8;
+  uint32_t vc[8], vf[8];
+  hist_load8(h, 0, Cg, lane, vc);
+  hist_load8(h + EUCLID_COARSE_BINS, Cg << 8, last16, lane, vf);
   uint32_t run = 0;
-  const uint32_t C = hist_find(h, 0, last16 >> 8, run, s_L.k, lane);
+  const uint32_t C = hist_scan8(vc, 0, run, s_L.k, lane);
   if (C == 0xFFFFFFFFu) return;
-  const uint32_t word = hist_find(h + EUCLID_COARSE_BINS, C << 8, min((C << 8) | 0xFFu, last16), run, s_L.k, lane);
+  if (C != Cg) hist_load8(h + EUCLID_COARSE_BINS, C << 8, (C << 8) | 0xFFu, lane, vf);   // (C < Cg: the whole coarse bin lies below the bound)
+  const uint32_t word = hist_scan8(vf, C << 8, run, s_L.k, lane);
   if (word == 0xFFFFFFFFu) return;
   const uint32_t bound = (word << 16) | 0xFFFFu;   // every key of that fine bin stays admissible
   if (bound < cur) {
@@ -577,7 +605,7 @@ __device__ __noinline__ void hist_refresh<true>(uint32_t q, int lane) {
 
 // Insert everything this warp has stashed (grouped by query, one list_offer per distinct query).
 template <bool EUCLID>
-__device__ __noinline__ void stash_flush(int warp, int lane) {
+__device__ __noinline__ void stash_flush(int warp, int lane, bool refresh = true) {
   unsigned char* base = g_smem + s_L.stash_off + (size_t)warp * (32 * 8 + 32 * 4 + 16);
   unsigned long long* skey = reinterpret_cast<unsigned long long*>(base);
   uint32_t* sq = reinterpret_cast<uint32_t*>(base + 32 * 8);
@@ -589,13 +617,12 @@ __device__ __noinline__ void stash_flush(int warp, int lane) {
   const uint32_t q = have ? sq[lane] : 0xFFFFFFFFu;
   __syncwarp();
   if (lane == 0) *scnt = 0;
-  if (s_L.ghist && have) hist_count<EUCLID>(s_L.q0 + q, (uint32_t)(key >> 32));
   unsigned todo = __ballot_sync(FULL_MASK, have);
   while (todo) {
     const uint32_t qcur = __shfl_sync(FULL_MASK, q, __ffs(todo) - 1);
     const bool sel = have && q == qcur;
     list_offer<EUCLID>(qcur, (uint32_t)(key >> 32), (uint32_t)key, sel, lane);
-    if (s_L.ghist && (warp % JBN_REFRESH_MOD) == 0) hist_refresh<EUCLID>(qcur, lane);
+    if (refresh && s_L.ghist && (warp % JBN_REFRESH_MOD) == 0 && !s_L.no_flush_refresh) hist_refresh<EUCLID>(qcur, lane);
     todo &= ~__ballot_sync(FULL_MASK, sel);
   }
 }
@@ -646,6 +673,10 @@ __device__ __noinline__ void stash_push(uint32_t q, uint32_t key_hi, uint32_t ro
   if (s_L.has_floor) pass = pass && key > sm_u64(s_L.floor_off)[q];
   const unsigned m = __ballot_sync(FULL_MASK, pass);
   if (!m) return;
+  // counted in the GPU-wide histogram right away, not when the stash is flushed: at the start of a pass
+  // every CTA holds a few candidates per warp, and the bound all of them together imply is what ends
+  // that phase (each (row, query) pair comes by here once, so no row is counted twice)
+  if (s_L.ghist && pass) hist_count<EUCLID>(s_L.q0 + q, key_hi);
   unsigned char* base = g_smem + s_L.stash_off + (size_t)warp * (32 * 8 + 32 * 4 + 16);
   volatile uint32_t* scnt = reinterpret_cast<uint32_t*>(base + 32 * 8 + 32 * 4);
   uint32_t n = *scnt;
@@ -671,8 +702,16 @@ __device__ __noinline__ void euclid_offer(uint32_t q, uint32_t d, float nif, uin
   uint32_t key = 0;
   if (cand) {
     const double ni = (double)nif;
-    const float two_nq = 2.0f * s_L.qnorms[s_L.q0 + q];
-    const double l2 = __dmul_rn((double)two_nq, s_L.coslut[d]);
+    float two_nq;
+    double cosd;
+    if (s_L.ctab_off != NO_CTAB) {   // TMA kernel: both operands sit in shared memory
+      two_nq = 2.0f * reinterpret_cast<const float*>(g_smem + s_L.qn_off)[q];
+      cosd = reinterpret_cast<const double*>(g_smem + s_L.cos_off)[d];
+    } else {
+      two_nq = 2.0f * s_L.qnorms[s_L.q0 + q];
+      cosd = s_L.coslut[d];
+    }
+    const double l2 = __dmul_rn((double)two_nq, cosd);
     key = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l2))));
   }
   stash_push<true>(q, key, row, cand, warp, lane);
@@ -685,6 +724,7 @@ __device__ __forceinline__ uint32_t stash_count(const ListCtl& L, int warp) {
 // Insertions are batched: one lock acquisition moves up to 32 candidates, which matters while a
 // CTA's threshold is still loose and every tile yields some.
 static const uint32_t STASH_FLUSH_AT = 16;
+static const uint32_t EARLY_REFRESH_STAGES = 4;
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 // a query's shared-memory block: W32 signature words, then the fast-reject threshold word
@@ -700,14 +740,17 @@ static const uint32_t STASH_BYTES = STASH * 8 + STASH * 4 + 16;
 static const uint32_t STASH_WARPS = 33;
 
 struct SmemPlan {
-  size_t q_off, lut_off, list_off, tau_off, floor_off, cnt_off, lock_off, tauhi_off, stash_off, total;
+  size_t q_off, lut_off, ctab_off, cos_off, qn_off, list_off, tau_off, floor_off, cnt_off, lock_off, tauhi_off, stash_off, total;
 };
 __host__ __device__ inline SmemPlan plan_smem(uint32_t qp, uint32_t w32, uint32_t cap, bool euclid,
-                                              uint32_t hash_num, size_t base) {
+                                              uint32_t hash_num, size_t base, bool ctab = false) {
   SmemPlan p;
   size_t o = base;
   p.q_off = o; o = align16(o + (size_t)qp * q_stride(w32) * 4);
   p.lut_off = o; if (euclid) o = align16(o + (size_t)qp * (hash_num + 1) * 4);
+  p.ctab_off = o; if (euclid && ctab) o = align16(o + (size_t)qp * (hash_num + 1) * 4);
+  p.cos_off = o; if (euclid && ctab) o = align16(o + (size_t)(hash_num + 1) * 8);   // cos(pi d / hash_num), once per CTA
+  p.qn_off = o; if (euclid && ctab) o = align16(o + (size_t)qp * 4);                // the group's query norms
   p.list_off = o; o = align16(o + (size_t)qp * cap * 8);
   p.tau_off = o; o = align16(o + (size_t)qp * 8);
   p.floor_off = o; o = align16(o + (size_t)qp * 8);
@@ -842,7 +885,7 @@ __device__ __forceinline__ void rank_reg(const uint32_t (&rows)[NR][W32], const 
 }
 
 // shared prologue: query blocks, euclid norm intervals, list control
-template <int W32, bool EUCLID>
+template <int W32, bool EUCLID, bool CTAB = false>
 __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* smem, const SmemPlan& sp, ListCtl& L,
                                               uint32_t*& s_q, float*& s_bnd, uint32_t q0, uint32_t nqp, int tid,
                                               int nthreads) {
@@ -857,7 +900,11 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
   L.local_rows = (uint32_t)a.local_rows;
   L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr) ? 1u : 0u;
   L.nq = a.nq; L.q0 = q0; L.hist_stride = a.hist_stride; L.ghist = a.ghist;
+  L.no_flush_refresh = (a.debug & 8u) ? 1u : 0u;
   L.bnd_off = (uint32_t)sp.lut_off; L.hash_num = a.hash_num;
+  L.ctab_off = (EUCLID && CTAB) ? (uint32_t)sp.ctab_off : NO_CTAB;
+  L.cos_off = (uint32_t)sp.cos_off; L.qn_off = (uint32_t)sp.qn_off;
+  if (EUCLID && CTAB && (uint32_t)tid < nqp) reinterpret_cast<float*>(smem + sp.qn_off)[tid] = a.qnorms[q0 + tid];
   L.coslut = EUCLID ? a.coslut : nullptr; L.qnorms = EUCLID ? a.qnorms : nullptr;
   if (tid == 0) s_L = L;
   if ((uint32_t)tid < STASH_WARPS) *reinterpret_cast<uint32_t*>(smem + sp.stash_off + (size_t)tid * STASH_BYTES + STASH * 12) = 0u;
@@ -885,8 +932,15 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
     for (uint32_t i = tid; i < nqp * hn; i += nthreads) {
       uint32_t q = i / hn, h = i % hn;
       float two_nq = 2.0f * a.qnorms[q0 + q];
-      s_bnd[i] = euclid_bound(__dmul_rn((double)two_nq, a.coslut[h]),
-                               tau_hi_of(a.tau_init ? a.tau_init[q0 + q] : KEY_SENTINEL));
+      const double c = __dmul_rn((double)two_nq, a.coslut[h]);
+      const uint32_t th = tau_hi_of(a.tau_init ? a.tau_init[q0 + q] : KEY_SENTINEL);
+      if (CTAB) {
+        const float c_add = (fabs(c) < (double)INFINITY) ? __double2float_ru(c) : INFINITY;
+        reinterpret_cast<float*>(smem + sp.ctab_off)[i] = c_add;
+        s_bnd[i] = euclid_bound_f(c_add, th);
+      } else {
+        s_bnd[i] = euclid_bound(c, th);
+      }
     }
   }
   if ((uint32_t)tid < nqp) {
@@ -991,7 +1045,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, W32 >= 16 ? 1 : 2) scan_ldg_kern
     ncur = nnxt;
   }
   }
-  if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane);
+  if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane, false);
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += SCAN_WARPS) {
     uint32_t n = list_compact<EUCLID>(q, sm_u32(L.cnt_off)[q], lane, true);
@@ -1054,7 +1108,7 @@ __host__ __device__ inline TmaPlan plan_tma(uint32_t qp, uint32_t w32, uint32_t 
   TmaPlan t;
   t.stages = stages; t.tiles_per_warp = tiles_per_warp;
   const size_t stage_tiles = (size_t)TMA_CONSUMER_WARPS * tiles_per_warp;
-  size_t o = (plan_smem(qp, w32, cap, euclid, hash_num, 0).total + 127) & ~(size_t)127;
+  size_t o = (plan_smem(qp, w32, cap, euclid, hash_num, 0, true).total + 127) & ~(size_t)127;
   t.ring_off = o; o += stages * stage_tiles * w32 * 128;
   t.norm_off = o; if (euclid) o += stages * stage_tiles * 128;
   t.bar_off = o; o += (size_t)stages * 16;
@@ -1078,10 +1132,64 @@ __device__ __forceinline__ void load_row_smem(const unsigned char* stage, uint32
   }
 }
 
+// named barrier of the consumer warps only (the producer warp never joins: it keeps the ring full
+// while the consumers change over from one query group to the next)
+__device__ __forceinline__ void consumer_barrier() {
+  asm volatile("bar.sync 1, %0;" ::"r"(TMA_CONSUMER_WARPS * 32) : "memory");
+}
+
+// The CTA's candidate lists of one query group -> scratch, k per (query, CTA).  A list of up to 512
+// entries is cut to its k smallest by counting: entry i's rank is the number of smaller entries (keys
+// are distinct), the k smallest go to out[rank] -- no search for the k-th key, no packing, and the
+// list leaves sorted.  The queries of the group are shared out over teams of warps.  Longer lists (k
+// above 256) keep the one-warp selection of list_compact.
+template <bool EUCLID>
+__device__ __forceinline__ void write_lists(const ScanArgs& a, const ListCtl& L, uint32_t q0, uint32_t nqp, int warp, int lane,
+                                            int nwarps) {
+  if (a.cap <= 512) {
+    const uint32_t nteams = min(nqp, (uint32_t)nwarps), wpt = (uint32_t)nwarps / nteams;
+    const uint32_t team = (uint32_t)warp / wpt;
+    if (team >= nteams) return;
+    const uint32_t tid = ((uint32_t)warp % wpt) * 32 + lane, tsize = wpt * 32;
+    for (uint32_t q = team; q < nqp; q += nteams) {
+      const uint32_t cnt = sm_u32(L.cnt_off)[q];
+      const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
+      unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) + ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
+      if (cnt <= a.k) {
+        for (uint32_t j = tid; j < a.k; j += tsize) out[j] = (j < cnt) ? src[j] : KEY_SENTINEL;
+        continue;
+      }
+      for (uint32_t i = tid; i < cnt; i += tsize) {
+        const unsigned long long v = src[i];
+        uint32_t rank = 0;
+        uint32_t j = 0;
+        for (; j + 4 <= cnt; j += 4)
+          rank += (src[j] < v ? 1u : 0u) + (src[j + 1] < v ? 1u : 0u) + (src[j + 2] < v ? 1u : 0u) + (src[j + 3] < v ? 1u : 0u);
+        for (; j < cnt; ++j) rank += src[j] < v ? 1u : 0u;
+        if (rank < a.k) out[rank] = v;
+      }
+    }
+    return;
+  }
+  for (uint32_t q = warp; q < nqp; q += nwarps) {
+    uint32_t n = list_compact<EUCLID>(q, sm_u32(L.cnt_off)[q], lane, true);
+    const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
+    unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) + ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
+    for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n) ? src[j] : KEY_SENTINEL;
+  }
+}
+
+// Persistent over the query groups of the launch: grid = one CTA per SM; a CTA walks its share of the
+// table once per group of qp queries.  The producer's ring does not stop at a group boundary -- while
+// the consumers write out the lists of group g and set up the queries, thresholds and (euclid) norm
+// bounds of group g + 1, the stages of g + 1 are already landing -- so a launch pays one ring fill and
+// one drain, not one per group, which is what a 12.5 M-row shard (0.1 ms per pass) spent a third of
+// its time on.  The share of a CTA rotates with the group, so that the CTAs that get the odd extra
+// stage are not the same every time.
 template <int W32, bool EUCLID, int PV, int NQ>
 __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, uint32_t stages, uint32_t tiles_per_warp) {
   unsigned char* smem = g_smem;
-  const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0);
+  const SmemPlan sp = plan_smem(a.qp, W32, a.cap, EUCLID, a.hash_num, 0, true);
   const TmaPlan tp = plan_tma(a.qp, W32, a.cap, EUCLID, a.hash_num, stages, tiles_per_warp);
   unsigned char* ring = smem + tp.ring_off;
   float* nring = reinterpret_cast<float*>(smem + tp.norm_off);
@@ -1089,15 +1197,10 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
   uint64_t* empty_bar = full_bar + stages;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t q0 = blockIdx.y * a.qp;
-  const uint32_t nqp = min(a.qp, a.nq - q0);
+  const uint32_t ngroups = (a.nq + a.qp - 1) / a.qp;
   const uint32_t stage_tiles = TMA_CONSUMER_WARPS * tiles_per_warp;
   const size_t tile_bytes = (size_t)W32 * 128;
   const size_t stage_bytes = stage_tiles * tile_bytes;
-  ListCtl L;
-  uint32_t* s_q;
-  float* s_bnd;
-  scan_prologue<W32, EUCLID>(a, smem, sp, L, s_q, s_bnd, q0, nqp, tid, TMA_THREADS);
   if (tid == 0) {
     for (uint32_t s = 0; s < stages; ++s) {
       mbar_init(full_bar + s, 1);
@@ -1108,45 +1211,73 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
   }
   __syncthreads();
 
-  // stage `it` of this CTA starts at tile stage_t0(it)
-  uint64_t t_first, t_stride, t_end;
-  uint32_t iters;
-  if (a.interleave) {
-    const uint64_t nstage = (a.ntiles + stage_tiles - 1) / stage_tiles;
-    t_first = (uint64_t)blockIdx.x * stage_tiles;
-    t_stride = (uint64_t)gridDim.x * stage_tiles;
-    t_end = a.ntiles;
-    iters = nstage > blockIdx.x ? (uint32_t)((nstage - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0u;
-  } else {
-    t_first = (uint64_t)blockIdx.x * a.tiles_per_chunk;
-    t_stride = stage_tiles;
-    t_end = min(a.ntiles, t_first + (uint64_t)a.tiles_per_chunk);
-    const uint64_t my_tiles = t_end > t_first ? t_end - t_first : 0;
-    iters = (uint32_t)((my_tiles + stage_tiles - 1) / stage_tiles);
-  }
+  // the CTA's share of the table for group g: stage `it` starts at tile t_first + it * t_stride
+  const uint64_t nstage = (a.ntiles + stage_tiles - 1) / stage_tiles;
+  auto share = [&](uint32_t g, uint64_t& t_first, uint64_t& t_stride, uint64_t& t_end, uint32_t& iters) {
+    const uint32_t c = (blockIdx.x + g) % gridDim.x;
+    if (a.interleave) {
+      t_first = (uint64_t)c * stage_tiles;
+      t_stride = (uint64_t)gridDim.x * stage_tiles;
+      t_end = a.ntiles;
+      iters = nstage > c ? (uint32_t)((nstage - c + gridDim.x - 1) / gridDim.x) : 0u;
+    } else {
+      t_first = (uint64_t)c * a.tiles_per_chunk;
+      t_stride = stage_tiles;
+      t_end = min(a.ntiles, t_first + (uint64_t)a.tiles_per_chunk);
+      const uint64_t my_tiles = t_end > t_first ? t_end - t_first : 0;
+      iters = (uint32_t)((my_tiles + stage_tiles - 1) / stage_tiles);
+    }
+  };
 
   if (warp == TMA_CONSUMER_WARPS) {
-    // ---- producer: one elected thread feeds the ring ----
+    // ---- producer: one elected thread feeds the ring, group after group without a pause ----
     if (lane == 0) {
-      uint32_t s = 0, ph = 0;
-      uint64_t t0 = t_first;
-      for (uint32_t it = 0; it < iters; ++it, t0 += t_stride) {
-        if (it >= stages) mbar_wait(empty_bar + s, ph ^ 1u);
-        const uint32_t ntile = (uint32_t)min((uint64_t)stage_tiles, t_end - t0);
-        const uint32_t bytes = ntile * (uint32_t)tile_bytes;
-        mbar_expect_tx(full_bar + s, bytes + (EUCLID ? ntile * 128u : 0u));
-        bulk_g2s(ring + s * stage_bytes, a.slab + t0 * tile_bytes, bytes, full_bar + s);
-        if (EUCLID) bulk_g2s(nring + (size_t)s * stage_tiles * 32, a.norms + t0 * 32, ntile * 128u, full_bar + s);
-        if (++s == stages) { s = 0; ph ^= 1u; }
+      uint32_t s = 0, ph = 0, issued = 0;
+      for (uint32_t g = 0; g < ngroups; ++g) {
+        uint64_t t0, t_stride, t_end;
+        uint32_t iters;
+        share(g, t0, t_stride, t_end, iters);
+        for (uint32_t it = 0; it < iters; ++it, t0 += t_stride, ++issued) {
+          if (issued >= stages) mbar_wait(empty_bar + s, ph ^ 1u);
+          const uint32_t ntile = (uint32_t)min((uint64_t)stage_tiles, t_end - t0);
+          const uint32_t bytes = ntile * (uint32_t)tile_bytes;
+          mbar_expect_tx(full_bar + s, bytes + (EUCLID ? ntile * 128u : 0u));
+          bulk_g2s(ring + s * stage_bytes, a.slab + t0 * tile_bytes, bytes, full_bar + s);
+          if (EUCLID) bulk_g2s(nring + (size_t)s * stage_tiles * 32, a.norms + t0 * 32, ntile * 128u, full_bar + s);
+          if (++s == stages) { s = 0; ph ^= 1u; }
+        }
       }
     }
     __syncwarp();
-  } else {
-    // ---- consumers: warp w owns tiles 2w, 2w+1 (+ 2*16 per further pair) of every stage ----
-    uint32_t s = 0, ph = 0;
-    uint64_t t0 = t_first;
-    constexpr int NQR = NQ > 0 ? NQ : 1;
-    constexpr uint32_t QS = q_stride(W32);
+    return;
+  }
+
+  // ---- consumers: warp w owns tiles 2w, 2w+1 (+ 2*15 per further pair) of every stage ----
+  constexpr int CT = TMA_CONSUMER_WARPS * 32;
+  constexpr int NQR = NQ > 0 ? NQ : 1;
+  constexpr uint32_t QS = q_stride(W32);
+  uint32_t s = 0, ph = 0;
+  ListCtl L;
+  uint32_t* s_q;
+  float* s_bnd;
+  if (EUCLID)   // the cos table serves every group (visible after the first group's prologue barrier)
+    for (uint32_t d = tid; d <= a.hash_num; d += CT) reinterpret_cast<double*>(smem + sp.cos_off)[d] = a.coslut[d];
+  for (uint32_t g = 0; g < ngroups; ++g) {
+    const uint32_t q0 = g * a.qp;
+    const uint32_t nqp = min(a.qp, a.nq - q0);
+#define JBN_TRACE(slot)                                                                                     \
+  if (a.trace && blockIdx.x < 4 && tid == 0) {                                                              \
+    unsigned long long t_;                                                                                  \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                  \
+    a.trace[((size_t)blockIdx.x * ngroups + g) * 8 + (slot)] = t_;                                          \
+  }
+    JBN_TRACE(0)
+    scan_prologue<W32, EUCLID, true>(a, smem, sp, L, s_q, s_bnd, q0, nqp, tid, CT);
+    consumer_barrier();
+    JBN_TRACE(1)
+    uint64_t t0, t_stride, t_end;
+    uint32_t iters;
+    share(g, t0, t_stride, t_end, iters);
     uint32_t qreg[NQR][W32];
     if (NQ > 0) {
 #pragma unroll
@@ -1155,7 +1286,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
     for (uint32_t it = 0; it < iters; ++it, t0 += t_stride) {
       mbar_wait(full_bar + s, ph);
       const unsigned char* stage = ring + s * stage_bytes;
-      const float* nstage = nring + (size_t)s * stage_tiles * 32;
+      const float* nstage_p = nring + (size_t)s * stage_tiles * 32;
       if (NQ > 0) {
         uint32_t tau[NQR];
 #pragma unroll
@@ -1171,7 +1302,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
             load_row_smem<W32>(stage, tis + 1, lane, rows[1]);
             const uint32_t rowid[2] = {rowa, rowa + 32};
             float ni[2] = {0.0f, 0.0f};
-            if (EUCLID) { ni[0] = nstage[tis * 32 + lane]; ni[1] = nstage[(tis + 1) * 32 + lane]; }
+            if (EUCLID) { ni[0] = nstage_p[tis * 32 + lane]; ni[1] = nstage_p[(tis + 1) * 32 + lane]; }
             rank_reg<W32, EUCLID, PV, NQR, 2>(rows, rowid, ni, qreg, tau, s_bnd, a.hash_num, warp, lane);
           } else {
             const uint32_t ntile = (t + 1 < t_end) ? 2u : 1u;
@@ -1180,7 +1311,7 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
               load_row_smem<W32>(stage, tis + u, lane, rows[0]);
               const uint32_t rowid[1] = {rowa + 32 * u};
               float ni[1] = {0.0f};
-              if (EUCLID) ni[0] = nstage[(tis + u) * 32 + lane];
+              if (EUCLID) ni[0] = nstage_p[(tis + u) * 32 + lane];
               rank_reg<W32, EUCLID, PV, NQR, 1>(rows, rowid, ni, qreg, tau, s_bnd, a.hash_num, warp, lane);
             }
           }
@@ -1193,13 +1324,13 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
         uint32_t ra[W32];
         load_row_smem<W32>(stage, tis, lane, ra);
         float nia = 0.0f;
-        if (EUCLID) nia = nstage[tis * 32 + lane];
+        if (EUCLID) nia = nstage_p[tis * 32 + lane];
         const uint32_t rowa = (uint32_t)(t * 32 + lane);
         if (t + 1 < t_end) {
           uint32_t rb[W32];
           load_row_smem<W32>(stage, tis + 1, lane, rb);
           float nib = 0.0f;
-          if (EUCLID) nib = nstage[(tis + 1) * 32 + lane];
+          if (EUCLID) nib = nstage_p[(tis + 1) * 32 + lane];
           rank_tile2<W32, EUCLID, PV>(ra, rb, rowa, rowa + 32, nia, nib, nqp, s_q, s_bnd, a.hash_num, L, lane);
         } else {
           rank_tile<W32, EUCLID, PV>(ra, rowa, nia, nqp, s_q, s_bnd, a.hash_num, L, lane);
@@ -1210,19 +1341,27 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
       if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush<EUCLID>(warp, lane);   // ... then do the slow insertions
       // euclid: a tighter bound means recomputing that query's norm bounds, so poll less often
       // and take turns (a warp that lags holds up the whole ring)
-      if (EUCLID ? ((it & 7u) == 7u && (uint32_t)warp == (it >> 3) % TMA_CONSUMER_WARPS) : (warp == 0))
+      if (a.debug & 4u) {
+      } else if (L.ghist && it < EARLY_REFRESH_STAGES && !(a.debug & 1u)) {
+        // start of a pass: the thresholds come from a small sample and are loose; after one stage per
+        // CTA the histogram already holds far more than k candidates, so one warp per stage (in turn)
+        // derives the bound from it directly instead of waiting for somebody's flush to publish one
+        // (query q by warp (stage + q) mod 15: no warp is held up by more than one refresh)
+        const uint32_t slot = ((uint32_t)warp + TMA_CONSUMER_WARPS - it % TMA_CONSUMER_WARPS) % TMA_CONSUMER_WARPS;
+        for (uint32_t q = slot; q < nqp; q += TMA_CONSUMER_WARPS) hist_refresh<EUCLID>(q, lane);
+      } else if (EUCLID ? ((it & 7u) == 7u && (uint32_t)warp == (it >> 3) % TMA_CONSUMER_WARPS) : (warp == 0)) {
         poll_shared_bounds<EUCLID>(L, nqp, lane);
+      }
       if (++s == stages) { s = 0; ph ^= 1u; }
+      if (it == 0) { JBN_TRACE(2) } else if (it == 3) { JBN_TRACE(3) } else if (it == 11) { JBN_TRACE(4) }
     }
-    if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane);
-  }
-  __syncthreads();
-  for (uint32_t q = warp; q < nqp; q += TMA_CONSUMER_WARPS + 1) {
-    uint32_t n = list_compact<EUCLID>(q, sm_u32(L.cnt_off)[q], lane, true);
-    const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
-    unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
-                              ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
-    for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n) ? src[j] : KEY_SENTINEL;
+    JBN_TRACE(5)
+    if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane, false);   // the pass is over: a tighter bound serves nobody
+    consumer_barrier();
+    JBN_TRACE(6)
+    write_lists<EUCLID>(a, L, q0, nqp, warp, lane, TMA_CONSUMER_WARPS);
+    consumer_barrier();   // the lists are out: the next group's prologue may overwrite them
+    JBN_TRACE(7)
   }
 }
 
@@ -1574,6 +1713,7 @@ static cudaError_t launch_tma_t(const ScanArgs& a, const ScanConfig& cfg, dim3 g
   auto kern = scan_tma_kernel<W32, EUCLID, PV, NQ>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem_bytes);
   if (e != cudaSuccess) return e;
+  grid.y = 1;   // persistent over the query groups
   kern<<<grid, TMA_THREADS, cfg.smem_bytes, s>>>(a, cfg.stages, cfg.tiles_per_warp);
   return cudaGetLastError();
 }
@@ -1680,7 +1820,8 @@ __global__ void __launch_bounds__(TAUH_THREADS) tau_init_hamming_kernel(ScanArgs
 
 // euclid_lsh: the sample's k-th smallest score key by an MSB-first bit search over keys held in
 // registers (one barrier per varying bit) instead of a bitonic sort of the whole sample.
-static const int TAUE_THREADS = 1024, TAUE_KPT = 8;   // up to 8192 sample rows
+static const int TAUE_THREADS = 1024;   // up to 1024 * TAUE_KPT sample rows
+template <int TAUE_KPT>
 __global__ void __launch_bounds__(TAUE_THREADS) tau_init_euclid_kernel(ScanArgs a, uint32_t S, unsigned long long* tau_out) {
   __shared__ uint32_t sq[32];
   __shared__ uint32_t s_cnt[3];
@@ -1787,7 +1928,18 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   a.tiles_per_chunk = cfg.tiles_per_chunk; a.nchunks = cfg.nchunks;
   a.w32 = t.w32;
   a.interleave = cfg.interleave;
-  const bool use_hist = d_hist_scratch && t.local_rows >= (1u << 16);
+  static const uint32_t dbg = getenv("JUBANN_SCAN_DEBUG") ? (uint32_t)atoi(getenv("JUBANN_SCAN_DEBUG")) : 0u;
+  a.debug = dbg;
+  a.trace = nullptr;
+  static const char* trace_path = getenv("JUBANN_SCAN_TRACE");
+  static unsigned long long* d_trace = nullptr;
+  const uint32_t trace_groups = (nq + cfg.qp - 1) / cfg.qp;
+  if (trace_path && cfg.variant == 2 && trace_groups <= 64) {
+    if (!d_trace) cudaMalloc(&d_trace, 4 * 64 * 8 * 8);
+    cudaMemsetAsync(d_trace, 0, 4 * 64 * 8 * 8, s);
+    a.trace = d_trace;
+  }
+  const bool use_hist = d_hist_scratch && t.local_rows >= (1u << 16) && !(dbg & 2u);
   if (use_hist) a.ghist = d_hist_scratch;
   bool hist_cleared = false;
   // sample pre-pass (not with a pagination floor: the bound would not hold for keys above it),
@@ -1797,12 +1949,17 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
     if (S > 8192) S = 8192;
     // ranking a sample is cheap (counting / bit search): take the largest one the table allows
     if (t.local_rows >= 16 * 8192) S = 8192;
+    // a launch of many passes pays for a loose bound at the start of every one of them (the first stage
+    // of a pass ran at a quarter of the speed of the others on a 12.5 M-row shard): a larger sample then
+    const uint32_t groups = (nq + cfg.qp - 1) / cfg.qp;
+    if (groups >= 8 && t.local_rows >= (1u << 22)) S = euclid ? 16384 : 32768;
     // small tables: a quarter of the rows at most (without any bound a CTA's first rows all go
     // through the list, which is what a query on a 10^4-row table spent its time in)
     while (S > 256 && t.local_rows < 4 * S) S >>= 1;
     if (t.local_rows >= 4 * S && k <= S) {
       if (euclid) {
-        tau_init_euclid_kernel<<<nq, TAUE_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+        if (S > 8192) tau_init_euclid_kernel<16><<<nq, TAUE_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
+        else tau_init_euclid_kernel<8><<<nq, TAUE_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
         hist_cleared = use_hist;
       } else {
         tau_init_hamming_kernel<<<nq, TAUH_THREADS, 0, s>>>(a, (uint32_t)S, reinterpret_cast<unsigned long long*>(d_tau_scratch));
@@ -1821,7 +1978,22 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   }
   dim3 grid(cfg.nchunks, (nq + cfg.qp - 1) / cfg.qp, 1);
   if (kernels_launched) ++*kernels_launched;
-  return euclid ? launch_scan_w<true>(t.w32, a, cfg, grid, s) : launch_scan_w<false>(t.w32, a, cfg, grid, s);
+  const cudaError_t launched = euclid ? launch_scan_w<true>(t.w32, a, cfg, grid, s) : launch_scan_w<false>(t.w32, a, cfg, grid, s);
+  if (a.trace && launched == cudaSuccess) {   // tuning aid: the last launch's timestamps, one line per (CTA, group)
+    std::vector<unsigned long long> hbuf(4 * 64 * 8);
+    cudaStreamSynchronize(s);
+    cudaMemcpy(hbuf.data(), d_trace, hbuf.size() * 8, cudaMemcpyDeviceToHost);
+    if (FILE* f = fopen(trace_path, "w")) {
+      for (uint32_t c = 0; c < 4; ++c)
+        for (uint32_t g = 0; g < trace_groups; ++g) {
+          fprintf(f, "%u %u", c, g);
+          for (int j = 0; j < 8; ++j) fprintf(f, " %llu", hbuf[((size_t)c * trace_groups + g) * 8 + j]);
+          fprintf(f, "\n");
+        }
+      fclose(f);
+    }
+  }
+  return launched;
 }
 
 cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nlists, uint32_t k,
