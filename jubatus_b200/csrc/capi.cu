@@ -333,8 +333,9 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
         o.out_score = d_out_score + (size_t)q0 * k;
         o.out_count = d_out_count + q0;
       }
-      CK(launch_merge_local(h->b_cand.as<uint64_t>(), nql, cfg.nchunks, kthis, o, s));
-      h->kernel_launches += scan_kernels + 1;   // + the list reduction
+      int merge_kernels = 0;   // (the thresholds of the scan are spent: their scratch carries the reduction's flags)
+      CK(launch_merge_local(h->b_cand.as<uint64_t>(), nql, cfg.nchunks, kthis, o, s, h->b_tau.as<uint32_t>(), &merge_kernels));
+      h->kernel_launches += scan_kernels + merge_kernels;
       h->scan_launches += 1;
       h->scan_passes += (nql + cfg.qp - 1) / cfg.qp;
     }

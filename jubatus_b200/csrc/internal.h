@@ -105,8 +105,11 @@ struct MergeOut {
   const float* qnorms;
   int count_accumulate;  // add to out_count instead of overwriting (pagination)
 };
+// d_dense (nullable): nq words of scratch; with it the reduction first collects the few keys the scan
+// left below its final thresholds and only falls back to selection for queries with thousands of them
 cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nlists, uint32_t k,
-                               const MergeOut& out, cudaStream_t s);
+                               const MergeOut& out, cudaStream_t s, uint32_t* d_dense = nullptr,
+                               int* kernels_launched = nullptr);
 cudaError_t launch_merge_parts(const uint32_t* d_cand_key, const uint64_t* d_cand_index, uint32_t nq,
                                uint32_t k, uint32_t parts, const MergeOut& out, cudaStream_t s,
                                size_t key_stride = 0, size_t idx_stride = 0);   // strides in elements; 0 = nq * k

@@ -1052,7 +1052,8 @@ __global__ void __launch_bounds__(SCAN_THREADS, W32 >= 16 ? 1 : 2) scan_ldg_kern
     const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
                               ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
-    for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n) ? src[j] : KEY_SENTINEL;
+    const unsigned long long tau = sm_u64(L.tau_off)[q];   // (what lies above the final threshold leaves as padding)
+    for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n && src[j] <= tau) ? src[j] : KEY_SENTINEL;
   }
 }
 
@@ -1155,8 +1156,12 @@ __device__ __forceinline__ void write_lists(const ScanArgs& a, const ListCtl& L,
       const uint32_t cnt = sm_u32(L.cnt_off)[q];
       const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
       unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) + ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
+      // What is above the CTA's final threshold (its own k-th best or the bound the whole GPU agreed on)
+      // cannot be in the answer: it leaves as padding, and the list reduction only ever looks at the
+      // few hundred keys per query that are left (merge_sparse_kernel).
+      const unsigned long long tau = sm_u64(L.tau_off)[q];
       if (cnt <= a.k) {
-        for (uint32_t j = tid; j < a.k; j += tsize) out[j] = (j < cnt) ? src[j] : KEY_SENTINEL;
+        for (uint32_t j = tid; j < a.k; j += tsize) out[j] = (j < cnt && src[j] <= tau) ? src[j] : KEY_SENTINEL;
         continue;
       }
       for (uint32_t i = tid; i < cnt; i += tsize) {
@@ -1166,7 +1171,7 @@ __device__ __forceinline__ void write_lists(const ScanArgs& a, const ListCtl& L,
         for (; j + 4 <= cnt; j += 4)
           rank += (src[j] < v ? 1u : 0u) + (src[j + 1] < v ? 1u : 0u) + (src[j + 2] < v ? 1u : 0u) + (src[j + 3] < v ? 1u : 0u);
         for (; j < cnt; ++j) rank += src[j] < v ? 1u : 0u;
-        if (rank < a.k) out[rank] = v;
+        if (rank < a.k) out[rank] = (v <= tau) ? v : KEY_SENTINEL;   // cnt > k: every rank below k is written by somebody
       }
     }
     return;
@@ -1175,7 +1180,8 @@ __device__ __forceinline__ void write_lists(const ScanArgs& a, const ListCtl& L,
     uint32_t n = list_compact<EUCLID>(q, sm_u32(L.cnt_off)[q], lane, true);
     const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) + ((size_t)(q0 + q) * a.nchunks + blockIdx.x) * a.k;
-    for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n) ? src[j] : KEY_SENTINEL;
+    const unsigned long long tau = sm_u64(L.tau_off)[q];
+    for (uint32_t j = lane; j < a.k; j += 32) out[j] = (j < n && src[j] <= tau) ? src[j] : KEY_SENTINEL;
   }
 }
 
@@ -1342,10 +1348,16 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
       // euclid: a tighter bound means recomputing that query's norm bounds, so poll less often
       // and take turns (a warp that lags holds up the whole ring)
       if (a.debug & 4u) {
-      } else if (L.ghist && it < EARLY_REFRESH_STAGES && !(a.debug & 1u)) {
+      } else if (L.ghist && !(a.debug & 1u) &&
+                 (it < EARLY_REFRESH_STAGES || (!EUCLID && (it & (it - 1u)) == 0u) || it + 3u == iters)) {
         // start of a pass: the thresholds come from a small sample and are loose; after one stage per
         // CTA the histogram already holds far more than k candidates, so one warp per stage (in turn)
-        // derives the bound from it directly instead of waiting for somebody's flush to publish one
+        // derives the bound from it directly instead of waiting for somebody's flush to publish one.
+        // Later candidates are so rare that nobody flushes any more: the bound is re-derived at stages
+        // 4, 8, 16, ... (hamming engines: one short read; a euclid_lsh refresh costs a warp two
+        // microseconds, which a pass that is exactly as fast as HBM has no room for) and once more three
+        // stages before the end, so that what the lists hold above
+        // the final bound (blanked in write_lists) is a few keys, not thousands.
         // (query q by warp (stage + q) mod 15: no warp is held up by more than one refresh)
         const uint32_t slot = ((uint32_t)warp + TMA_CONSUMER_WARPS - it % TMA_CONSUMER_WARPS) % TMA_CONSUMER_WARPS;
         for (uint32_t q = slot; q < nqp; q += TMA_CONSUMER_WARPS) hist_refresh<EUCLID>(q, lane);
@@ -1400,8 +1412,9 @@ __device__ __forceinline__ float final_score(uint32_t key_hi, const MergeOut& o,
 // half: elements kept between sorts (>= k, >= MERGE_THREADS*2, power of two); smem holds 2*half keys
 __global__ void __launch_bounds__(MERGE_THREADS) merge_local_kernel(const unsigned long long* cand,
                                                                     uint32_t nlists, uint32_t k,
-                                                                    uint32_t half, MergeOut o) {
+                                                                    uint32_t half, MergeOut o, const uint32_t* only_dense) {
   extern __shared__ __align__(16) unsigned char smem[];
+  if (only_dense && !only_dense[blockIdx.x]) return;   // merge_sparse_kernel has answered this query
   unsigned long long* buf = reinterpret_cast<unsigned long long*>(smem);
   __shared__ uint32_t s_n;
   const int tid = threadIdx.x;
@@ -1521,9 +1534,63 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_parts_kernel(const uint32
 // or, for large k, by a bitonic sort.  The streaming variant above sorts 2 * half keys per 256
 // candidates read, which is what a single small query spent most of its time in.
 static const uint32_t MSEL_MAX_KEYS = 24576;
+
+// List reduction for the common case: the scan CTAs have already blanked everything above their final
+// thresholds, so of the nlists * k slots of a query only a few hundred hold keys.  They are collected
+// in shared memory and ordered by counting (keys are distinct: the number of smaller keys is the
+// position).  A query with more than MSP_CAP live keys (long runs of equal distances) is flagged in
+// `dense` and left to the selection kernels below, which skip the queries that are not flagged.
+static const uint32_t MSP_CAP = 2048, MSP_THREADS = 512;
+__global__ void __launch_bounds__(MSP_THREADS) merge_sparse_kernel(const unsigned long long* cand, uint32_t nlists, uint32_t k,
+                                                                   MergeOut o, uint32_t* dense) {
+  __shared__ unsigned long long buf[MSP_CAP];
+  __shared__ uint32_t s_n;
+  const uint32_t q = blockIdx.x, tid = threadIdx.x;
+  const size_t M = (size_t)nlists * k;
+  const unsigned long long* src = cand + (size_t)q * M;
+  if (tid == 0) s_n = 0;
+  __syncthreads();
+  for (size_t i = tid; i < M; i += MSP_THREADS) {
+    const unsigned long long v = src[i];
+    if (v != KEY_SENTINEL) {
+      const uint32_t pos = atomicAdd(&s_n, 1u);
+      if (pos < MSP_CAP) buf[pos] = v;
+    }
+  }
+  __syncthreads();
+  const uint32_t n = s_n;
+  if (n > MSP_CAP) { if (tid == 0) dense[q] = 1u; return; }
+  if (tid == 0) dense[q] = 0u;
+  const uint32_t want = min(k, n);
+  for (uint32_t i = tid; i < n; i += MSP_THREADS) {
+    const unsigned long long key = buf[i];
+    uint32_t rank = 0, j = 0;
+    for (; j + 4 <= n; j += 4)
+      rank += (buf[j] < key ? 1u : 0u) + (buf[j + 1] < key ? 1u : 0u) + (buf[j + 2] < key ? 1u : 0u) + (buf[j + 3] < key ? 1u : 0u);
+    for (; j < n; ++j) rank += buf[j] < key ? 1u : 0u;
+    if (rank >= want) continue;
+    const uint32_t key_hi = (uint32_t)(key >> 32);
+    const uint64_t gidx = (uint64_t)(uint32_t)key * o.shard_count + o.shard_rank;
+    if (o.cand_key) {  // unused slots were pre-filled with sentinels by the host
+      o.cand_key[(size_t)q * o.kout + o.col0 + rank] = key_hi;
+      o.cand_index[(size_t)q * o.kout + o.col0 + rank] = gidx;
+    }
+    if (o.out_index) {
+      o.out_index[(size_t)q * o.kout + o.col0 + rank] = gidx;
+      o.out_score[(size_t)q * o.kout + o.col0 + rank] = final_score(key_hi, o, q);
+    }
+    if (rank == want - 1 && o.last_key) o.last_key[q] = key;
+  }
+  if (tid == 0) {
+    if (o.out_count) o.out_count[q] = (o.count_accumulate ? o.out_count[q] : 0u) + want;
+    if (o.last_key && want == 0) o.last_key[q] = KEY_SENTINEL;
+  }
+}
+
 template <int KPT, int THREADS>
 __global__ void __launch_bounds__(THREADS) merge_small_kernel(const unsigned long long* cand, uint32_t nlists,
-                                                              uint32_t k, uint32_t kp, MergeOut o) {
+                                                              uint32_t k, uint32_t kp, MergeOut o, const uint32_t* only_dense) {
+  if (only_dense && !only_dense[blockIdx.x]) return;   // merge_sparse_kernel has answered this query
   extern __shared__ __align__(16) unsigned char smem[];
   unsigned long long* top = reinterpret_cast<unsigned long long*>(smem);   // [kp], kp = pow2 >= k
   __shared__ uint32_t s_cnt[3];
@@ -1997,19 +2064,30 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
 }
 
 cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nlists, uint32_t k,
-                               const MergeOut& out, cudaStream_t s) {
+                               const MergeOut& out, cudaStream_t s, uint32_t* d_dense, int* kernels_launched) {
   const uint64_t M = (uint64_t)nlists * k;
+  const unsigned long long* c = reinterpret_cast<const unsigned long long*>(d_cand);
+  // the sparse reduction first (when the caller has nq words of scratch for the flags and there is
+  // something to skip: a single short list is as quick to select from directly)
+  const uint32_t* only = nullptr;
+  if (d_dense && M > 2048) {
+    merge_sparse_kernel<<<nq, MSP_THREADS, 0, s>>>(c, nlists, k, out, d_dense);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    if (kernels_launched) ++*kernels_launched;
+    only = d_dense;
+  }
+  if (kernels_launched) ++*kernels_launched;
   if (M <= MSEL_MAX_KEYS) {
     uint32_t kp = 32;
     while (kp < k) kp <<= 1;
     const size_t sm = (size_t)kp * 8 * (kp <= 512 ? 2 : 1);
-    const unsigned long long* c = reinterpret_cast<const unsigned long long*>(d_cand);
-    if (M <= 128u * 4u) merge_small_kernel<4, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out);
-    else if (M <= 128u * 16u) merge_small_kernel<16, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out);
-    else if (M <= 128u * 32u) merge_small_kernel<32, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out);
-    else if (M <= 1024u * 8u) merge_small_kernel<8, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out);
-    else if (M <= 1024u * 16u) merge_small_kernel<16, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out);
-    else merge_small_kernel<24, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out);
+    if (M <= 128u * 4u) merge_small_kernel<4, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out, only);
+    else if (M <= 128u * 16u) merge_small_kernel<16, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out, only);
+    else if (M <= 128u * 32u) merge_small_kernel<32, 128><<<nq, 128, sm, s>>>(c, nlists, k, kp, out, only);
+    else if (M <= 1024u * 8u) merge_small_kernel<8, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out, only);
+    else if (M <= 1024u * 16u) merge_small_kernel<16, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out, only);
+    else merge_small_kernel<24, 1024><<<nq, 1024, sm, s>>>(c, nlists, k, kp, out, only);
     return cudaGetLastError();
   }
   uint32_t half = 2 * MERGE_THREADS;
@@ -2017,8 +2095,7 @@ cudaError_t launch_merge_local(const uint64_t* d_cand, uint32_t nq, uint32_t nli
   const size_t smem = (size_t)2 * half * 8;
   cudaError_t e = cudaFuncSetAttribute(merge_local_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  merge_local_kernel<<<nq, MERGE_THREADS, smem, s>>>(reinterpret_cast<const unsigned long long*>(d_cand),
-                                                     nlists, k, half, out);
+  merge_local_kernel<<<nq, MERGE_THREADS, smem, s>>>(c, nlists, k, half, out, only);
   return cudaGetLastError();
 }
 
