@@ -1313,7 +1313,11 @@ class nearest_neighbor_serv {
   // (build_local_path, server_base.cpp:41-50; defaults of server_util.cpp: /tmp, port 9199)
   void set_storage(const std::string& datadir, const std::string& eth, int port) { datadir_ = datadir; eth_ = eth; port_ = port; }
   static const char* type() { return "nearest_neighbor"; }
-  uint64_t user_data_version() const { return 1; }   // nearest_neighbor_serv.cpp:77-79
+  // nearest_neighbor_serv.cpp:77-79 returns 1 for a payload in jubatus_core's msgpack form.  The payload
+  // written here is this build's own table blob, so it carries a version of its own ("JBN", 1): a stock
+  // server refuses such a file at the version check ("user data version mismatched"), and this one refuses
+  // a stock file the same way, instead of either of them failing somewhere inside unpack.
+  uint64_t user_data_version() const { return 0x4A424E01ull; }
   std::string local_path(const std::string& id) const {
     std::ostringstream p; p << datadir_ << '/' << eth_ << '_' << port_ << '_' << type() << '_' << id << ".jubatus";
     return p.str();

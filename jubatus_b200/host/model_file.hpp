@@ -34,6 +34,7 @@
 #include <ostream>
 #include <sstream>
 #include <stdexcept>
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -197,6 +198,18 @@ inline bool same_config(const std::string& a, const std::string& b) {   // compa
   return json::dump(json::parse(a)) == json::dump(json::parse(b));
 }
 
+inline void read_exact(std::istream& is, uint64_t n, std::string& out) {
+  const uint64_t STEP = 16ull << 20;
+  out.clear();
+  while (out.size() < n) {
+    const uint64_t want = std::min<uint64_t>(STEP, n - out.size());
+    const size_t at = out.size();
+    out.resize(at + want);
+    is.read(&out[at], static_cast<std::streamsize>(want));
+    if (static_cast<uint64_t>(is.gcount()) != want) throw std::ios_base::failure("cannot read input file");
+  }
+}
+
 // load_server (save_load.cpp:168-283).  Returns the driver pack; `sys` receives the system data.
 // expected_config is ignored when overwrite_config (load_file, server_base.cpp:207-209).
 inline std::string load(std::istream& is, const std::string& expected_type, const std::string& expected_config,
@@ -220,11 +233,11 @@ inline std::string load(std::istream& is, const std::string& expected_type, cons
   const uint32_t crc_expected = read_be32(header + 28);
   const uint64_t sys_size = read_be64(header + 32), user_size = read_be64(header + 40);
   if (sys_size > (1ull << 32) || user_size > (1ull << 40)) throw format_error("invalid file format");
-  std::string sys(sys_size, '\0'), user(user_size, '\0');
-  if (sys_size) is.read(&sys[0], static_cast<std::streamsize>(sys_size));
-  if (static_cast<uint64_t>(is.gcount()) != sys_size && sys_size) throw std::ios_base::failure("cannot read input file");
-  if (user_size) is.read(&user[0], static_cast<std::streamsize>(user_size));
-  if (static_cast<uint64_t>(is.gcount()) != user_size && user_size) throw std::ios_base::failure("cannot read input file");
+  // the sizes come from the file: memory is taken as the bytes actually arrive (16 MiB at a time), so a
+  // header that claims a terabyte costs nothing before the stream runs dry
+  std::string sys, user;
+  read_exact(is, sys_size, sys);
+  read_exact(is, user_size, user);
   const uint32_t crc_actual = container_crc32(header, sys, user);
   if (crc_actual != crc_expected) {
     std::ostringstream m; m << "invalid crc32 checksum: " << std::hex << crc_actual << ", expected " << crc_expected;

@@ -135,3 +135,23 @@ def test_broken_system_and_user_data_are_reported_as_such():
         nn.model_read(container(good_sys, msgpack.packb([1, b"a", b"b"])), "nearest_neighbor", "{}")
     with pytest.raises(nn.JubatusError, match="user data is broken"):
         nn.model_read(container(good_sys, msgpack.packb([1, 17])), "nearest_neighbor", "{}")
+
+
+def test_a_header_that_claims_huge_sections_costs_nothing():
+    # sizes come from the file: a crafted header (1 TiB of user data) must fail on the short stream,
+    # not by allocating what it claims
+    import resource
+    import struct
+    header = bytearray(48)
+    header[0:8] = b"jubatus\x00"
+    struct.pack_into(">Q", header, 8, 1)
+    struct.pack_into(">III", header, 16, 0, 9, 2)
+    struct.pack_into(">Q", header, 32, 1 << 31)       # system data: 2 GiB claimed
+    struct.pack_into(">Q", header, 40, 1 << 40)       # user data: 1 TiB claimed
+    blob = bytes(header) + b"x" * 1000
+    before = resource.getrusage(resource.RUSAGE_SELF).ru_maxrss
+    with pytest.raises(nn.JubatusError) as ei:
+        nn.model_read(blob, "nearest_neighbor", "{}", False, 1)
+    assert "cannot read input file" in str(ei.value)
+    after = resource.getrusage(resource.RUSAGE_SELF).ru_maxrss
+    assert after - before < 200 * 1024                # KiB: far below the claimed sizes

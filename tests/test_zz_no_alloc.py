@@ -41,7 +41,7 @@ def _same(a, b):
 
 
 @pytest.mark.parametrize("method,hash_num", [("lsh", 512), ("euclid_lsh", 256)])
-def test_two_calls_in_a_row_match_the_allocating_entry_point(method, hash_num):
+def test_two_calls_in_a_row_match_the_allocating_entry_point(oracle, method, hash_num):
     from jubatus_b200 import Engine, SIMILAR
     rng = np.random.RandomState(hash_num)
     n, k = 60000, 100
@@ -60,8 +60,11 @@ def test_two_calls_in_a_row_match_the_allocating_entry_point(method, hash_num):
         q2[3] = rows[n - 1]
         qn2 = (rng.rand(4) * 4).astype(np.float32) if norms is not None else None
         _same(_run(e, "noalloc", q2, qn2, 37, SIMILAR), _run(e, "alloc", q2, qn2, 37, SIMILAR))
-        # and the first batch again: same answer as before
-        _same(_run(e, "noalloc", q1, qn1, k), _run(e, "alloc", q1, qn1, k))
+        # and the first batch again: same answer as before -- and the CPU engine's, checked directly
+        again = _run(e, "noalloc", q1, qn1, k)
+        _same(again, _run(e, "alloc", q1, qn1, k))
+        widx, wscore, wcount, _ = oracle.scan_batch(method, q1, qn1, rows, norms, hash_num, k)
+        _same((again[0].view(np.uint64), again[1], again[2]), (widx, wscore, wcount))
 
 
 def test_small_tables_and_k_edges():
