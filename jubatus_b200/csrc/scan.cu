@@ -73,6 +73,18 @@ __device__ __forceinline__ float ld_stream_f32(const float* p) {
   return r;
 }
 
+// the same addresses as a hint: bring the tile into L2 while the current one is being ranked
+template <int W32>
+__device__ __forceinline__ void prefetch_row_l2(const unsigned char* slab, uint64_t tile, int lane) {
+  if (W32 == 2) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(slab + (tile * 32 + lane) * 8ull));
+  } else {
+    constexpr int C = W32 / 4;
+#pragma unroll
+    for (int c = 0; c < C; ++c) asm volatile("prefetch.global.L2 [%0];" ::"l"(slab + ((tile * C + c) * 32 + lane) * 16ull));
+  }
+}
+
 template <int W32>
 __device__ __forceinline__ void load_row(const unsigned char* slab, uint64_t tile, int lane,
                                          uint32_t (&r)[W32]) {
@@ -271,6 +283,55 @@ __device__ __forceinline__ uint32_t hamming_t(const uint32_t (&r)[W32], const ui
     d += ones + 2 * twos;
   }
   return d;
+}
+
+// The same with two more adder levels (9 adders, 7 POPC per 512-bit pair instead of 9) for the
+// popcount regime, where the XU pipe (POPC, a quarter of the ALU rate) and the ALU pipe (LOP3, adds,
+// compares) are both near their limits: the weighted sum of the seven popcounts is accumulated with
+// integer multiply-adds, which issue on the FMA pipe, so it costs neither of the two.  To keep the
+// compiler from turning them back into adds and shifts the sum is kept scaled by HT4_SCALE (weights
+// 7 / 14 / 28); the caller compares against the threshold scaled alike and divides on the rare path.
+static const uint32_t HT4_SCALE = 7;
+__device__ __forceinline__ uint32_t mad_u32(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+template <int W32>
+__device__ __forceinline__ uint32_t hamming_t4(const uint32_t (&r)[W32], const uint32_t (&rt)[(W32 / 16) * 5],
+                                               const uint32_t* sq) {
+  uint32_t q[W32];
+  load_query<W32>(sq, q);
+  uint32_t acc = 0;
+#pragma unroll
+  for (int b = 0; b < W32 / 16; ++b) {
+    const uint4 qa = *reinterpret_cast<const uint4*>(sq + W32 + 4 + 8 * b);
+    const uint32_t q4 = sq[W32 + 4 + 8 * b + 4];
+    const uint32_t qt[5] = {qa.x, qa.y, qa.z, qa.w, q4};
+    uint32_t o[7], t[9], f[2];
+#pragma unroll
+    for (int g = 0; g < 5; ++g) {
+      const uint32_t sum = rt[5 * b + g] ^ qt[g];
+      const uint32_t x0 = r[16 * b + 3 * g] ^ q[16 * b + 3 * g];
+      const uint32_t x1 = r[16 * b + 3 * g + 1] ^ q[16 * b + 3 * g + 1];
+      uint32_t carry;
+      asm("lop3.b32 %0, %1, %2, %3, 0xD4;" : "=r"(carry) : "r"(x0), "r"(x1), "r"(sum));
+      o[g] = sum; t[g] = carry;
+    }
+    const uint32_t x15 = r[16 * b + 15] ^ q[16 * b + 15];
+    CSA(t[5], o[5], o[0], o[1], o[2]);
+    CSA(t[6], o[6], o[3], o[4], x15);
+    CSA(f[0], t[7], t[0], t[1], t[2]);
+    CSA(f[1], t[8], t[3], t[4], t[5]);
+    acc = mad_u32(__popc(o[5]), HT4_SCALE, acc);
+    acc = mad_u32(__popc(o[6]), HT4_SCALE, acc);
+    acc = mad_u32(__popc(t[6]), 2 * HT4_SCALE, acc);
+    acc = mad_u32(__popc(t[7]), 2 * HT4_SCALE, acc);
+    acc = mad_u32(__popc(t[8]), 2 * HT4_SCALE, acc);
+    acc = mad_u32(__popc(f[0]), 4 * HT4_SCALE, acc);
+    acc = mad_u32(__popc(f[1]), 4 * HT4_SCALE, acc);
+  }
+  return acc;
 }
 
 // order-preserving image of a float (no NaN expected); -0 is folded into +0 first so that
@@ -770,7 +831,8 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
                                           const uint32_t* s_q, const float* s_bnd, uint32_t hash_num,
                                           const ListCtl& L, int lane) {
   constexpr uint32_t QS = q_stride(W32);
-  constexpr bool TRIPLES = JBN_TRIPLES && W32 >= 16 && PV == 3;
+  constexpr bool TRIPLES = JBN_TRIPLES && W32 >= 16 && (PV == 3 || PV == 4);
+  constexpr bool SCALED = TRIPLES && PV == 4 && !EUCLID;   // distances carried as HT4_SCALE * d (hamming_t4)
   constexpr int NT = W32 >= 16 ? (W32 / 16) * 5 : 1;
   const int warp = threadIdx.x >> 5;
   uint32_t rt[NT];
@@ -780,7 +842,10 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
     const uint32_t* b0 = s_q + q * QS;
     const uint32_t* b1 = b0 + QS;
     uint32_t d0, d1;
-    if constexpr (TRIPLES) {
+    if constexpr (SCALED) {
+      d0 = hamming_t4<W32>(cur, rt, b0);
+      d1 = hamming_t4<W32>(cur, rt, b1);
+    } else if constexpr (TRIPLES) {
       d0 = hamming_t<W32>(cur, rt, b0);
       d1 = hamming_t<W32>(cur, rt, b1);
     } else {
@@ -795,11 +860,14 @@ __device__ __forceinline__ void rank_tile(const uint32_t (&cur)[W32], uint32_t r
         euclid_offer(q + 1, d1, ni, row, c1, warp, lane);
       }
     } else {
-      const bool c0 = d0 <= *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
-      const bool c1 = d1 <= *reinterpret_cast<const volatile uint32_t*>(b1 + W32);
+      const uint32_t t0 = *reinterpret_cast<const volatile uint32_t*>(b0 + W32);
+      const uint32_t t1 = *reinterpret_cast<const volatile uint32_t*>(b1 + W32);
+      // (a threshold of 0xFFFFFFFF, "none yet", must not wrap when scaled)
+      const bool c0 = SCALED ? (d0 <= mad_u32(min(t0, 0x10000u), HT4_SCALE, 0u)) : (d0 <= t0);
+      const bool c1 = SCALED ? (d1 <= mad_u32(min(t1, 0x10000u), HT4_SCALE, 0u)) : (d1 <= t1);
       if (__any_sync(FULL_MASK, c0 || c1)) {
-        stash_push<false>(q, d0, row, c0, warp, lane);
-        stash_push<false>(q + 1, d1, row, c1, warp, lane);
+        stash_push<false>(q, SCALED ? d0 / HT4_SCALE : d0, row, c0, warp, lane);
+        stash_push<false>(q + 1, SCALED ? d1 / HT4_SCALE : d1, row, c1, warp, lane);
       }
     }
   }
@@ -990,39 +1058,47 @@ __global__ void __launch_bounds__(SCAN_THREADS, W32 >= 16 ? 1 : 2) scan_ldg_kern
     t_step = SCAN_WARPS * TPS;
   }
   uint32_t poll_tick = 0;
+  // Rows of 512 bits and more (one CTA per SM, 128 registers): the next tile is loaded into registers
+  // while the current one is ranked.  Shorter rows run two CTAs per SM at 64 registers, where a row
+  // held across the calls of the insertion path was kept on the stack -- the store sat right behind
+  // its load and waited for it (6 % of all samples in the ncu capture of the 128-bit kernel).  There
+  // the next tile is only pulled into L2 and loaded when its turn comes: 32 resident warps per SM
+  // hide an L2 hit.
+  constexpr bool REG_PREFETCH = W32 >= 16;
   if constexpr (PAIR) {
-    uint32_t ca[W32], cb[W32], na[W32], nb[W32];
-    float fa = 0.0f, fb = 0.0f, ga = 0.0f, gb = 0.0f;
-#pragma unroll
-    for (int w = 0; w < W32; ++w) { cb[w] = 0u; nb[w] = 0u; }
-    if (t < t_end) {
+    uint32_t ca[W32], cb[W32];
+    float fa = 0.0f, fb = 0.0f;
+    for (; t < t_end; t += t_step) {
+      const bool two = t + 1 < t_end;
       load_row<W32>(a.slab, t, lane, ca);
       if (EUCLID) fa = ld_stream_f32(a.norms + t * 32 + lane);
-      if (t + 1 < t_end) {
+      if (two) {
         load_row<W32>(a.slab, t + 1, lane, cb);
         if (EUCLID) fb = ld_stream_f32(a.norms + (t + 1) * 32 + lane);
       }
-    }
-    for (; t < t_end; t += t_step) {
       const uint64_t tn = t + t_step;
       if (tn < t_end) {
-        load_row<W32>(a.slab, tn, lane, na);
-        if (EUCLID) ga = ld_stream_f32(a.norms + tn * 32 + lane);
-        if (tn + 1 < t_end) {
-          load_row<W32>(a.slab, tn + 1, lane, nb);
-          if (EUCLID) gb = ld_stream_f32(a.norms + (tn + 1) * 32 + lane);
-        }
+        prefetch_row_l2<W32>(a.slab, tn, lane);
+        if (tn + 1 < t_end) prefetch_row_l2<W32>(a.slab, tn + 1, lane);
       }
-      if (t + 1 < t_end)
+      if (two)
         rank_tile2<W32, EUCLID, PV>(ca, cb, (uint32_t)(t * 32 + lane), (uint32_t)(t * 32 + 32 + lane), fa, fb, nqp, s_q, s_bnd,
                                     a.hash_num, L, lane);
       else
         rank_tile<W32, EUCLID, PV>(ca, (uint32_t)(t * 32 + lane), fa, nqp, s_q, s_bnd, a.hash_num, L, lane);
       if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush<EUCLID>(warp, lane);
       if (warp == 0 && ((++poll_tick) & 7u) == 0u) poll_shared_bounds<EUCLID>(L, nqp, lane);
-#pragma unroll
-      for (int w = 0; w < W32; ++w) { ca[w] = na[w]; cb[w] = nb[w]; }
-      fa = ga; fb = gb;
+    }
+  } else if constexpr (!REG_PREFETCH) {
+    uint32_t cur[W32];
+    float ncur = 0.0f;
+    for (; t < t_end; t += t_step) {
+      load_row<W32>(a.slab, t, lane, cur);
+      if (EUCLID) ncur = ld_stream_f32(a.norms + t * 32 + lane);
+      if (t + t_step < t_end) prefetch_row_l2<W32>(a.slab, t + t_step, lane);
+      rank_tile<W32, EUCLID, PV>(cur, (uint32_t)(t * 32 + lane), ncur, nqp, s_q, s_bnd, a.hash_num, L, lane);
+      if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush<EUCLID>(warp, lane);
+      if (warp == 0 && ((++poll_tick) & 7u) == 0u) poll_shared_bounds<EUCLID>(L, nqp, lane);
     }
   } else {
   uint32_t cur[W32], nxt[W32];

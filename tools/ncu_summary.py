@@ -16,6 +16,9 @@ WANT = [
     "sm__cycles_elapsed.avg.per_second", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
     "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smsp__warps_eligible.avg.per_cycle_active",
     "lts__t_sector_hit_rate.pct", "lts__t_bytes.sum",
+    "smsp__inst_executed_op_local_ld.sum", "smsp__inst_executed_op_local_st.sum",
+    "smsp__inst_executed_op_global_ld.sum", "smsp__inst_executed_op_shared_ld.sum",
+    "l1tex__t_bytes_pipe_lsu_mem_global_op_ld.sum", "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
 ]
 
 
