@@ -156,6 +156,17 @@ int jubann_query_csr(jubann_t* h, uint64_t nq, const uint64_t* indptr, const uin
 int jubann_query_rows(jubann_t* h, uint64_t nq, const uint64_t* row_index, uint32_t k,
                       uint32_t flags, uint64_t* out_index, float* out_score, uint32_t* out_count);
 
+/* set_row immediately followed by neighbor_row(id) / similar_row(id) of the row just stored: what
+ * anomaly add does (anomaly_serv.cpp:157-176 -> [core] light_lof::set_row, which stores the row and at
+ * once collects its neighbours) and what set_row + neighbor_row_from_id give when issued back to back
+ * (nearest_neighbor_serv.cpp:134,144).  The sparse vector is hashed once, stored at row_index (append or
+ * overwrite, as jubann_set_rows_csr) and ranked against the table that now contains it: one host round
+ * trip instead of two.  Single-shard handles; rows whose CSR does not fit the 1 MiB staging buffer take
+ * the two separate calls. */
+int jubann_set_row_query_csr(jubann_t* h, uint64_t row_index, uint64_t nnz, const uint32_t* seed32, const uint64_t* keyhash64,
+                             const float* vals, uint32_t k, uint32_t flags, uint64_t* out_index, float* out_score,
+                             uint32_t* out_count);
+
 /* ---- device-pointer entry points (bench, torch.distributed / NCCL plumbing) ---- */
 
 /* jubann_query_sig with device-resident queries and outputs; the library owns and grows the

@@ -20,7 +20,7 @@ EXPORTS = [
     "jubann_diff_record_bytes", "jubann_diff_pack_dev", "jubann_diff_apply_dev", "jubann_stats",
     "jubann_stats_reset", "jubann_query_sig_noalloc_dev", "jubann_hash_csr_dev", "jubann_set_rows_csr_dev",
     "jubann_create_multi", "jubann_comm_unique_id", "jubann_comm_init", "jubann_comm_info",
-    "jubann_mix_allgather", "jubann_mix_apply", "jubann_set_rows_csr_strided_dev",
+    "jubann_mix_allgather", "jubann_mix_apply", "jubann_set_rows_csr_strided_dev", "jubann_set_row_query_csr",
 ]
 COMM_ID_BYTES = 128
 
@@ -95,6 +95,8 @@ def load_library():
         "jubann_query_sig": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp],
         "jubann_query_csr": [H, ctypes.c_uint64, _vp, _vp, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp],
         "jubann_query_rows": [H, ctypes.c_uint64, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp],
+        "jubann_set_row_query_csr": [H, ctypes.c_uint64, ctypes.c_uint64, _vp, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp,
+                                     _vp],
         "jubann_query_sig_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp, _vp],
         "jubann_query_sig_noalloc_dev": [H, ctypes.c_uint64, _vp, _vp, ctypes.c_uint32, ctypes.c_uint32, _vp, _vp, _vp,
                                          _vp],
@@ -260,6 +262,16 @@ class Engine(object):
         idx, score, count = self._outs(nq, k)
         _check(self._lib.jubann_query_csr(self._h, nq, _ptr(indptr), _ptr(seed32), _ptr(keyhash64), _ptr(vals),
                                           int(k), int(flags), _ptr(idx), _ptr(score), _ptr(count)))
+        return idx, score, count
+
+    def set_row_query_csr(self, row_index, seed32, keyhash64, vals, k, flags=0):
+        """set_row of one sparse vector, then neighbor_row(id) of it, in one call."""
+        vals = _arr(vals, np.float32)
+        seed32 = None if seed32 is None else _arr(seed32, np.uint32)
+        keyhash64 = None if keyhash64 is None else _arr(keyhash64, np.uint64)
+        idx, score, count = self._outs(1, k)
+        _check(self._lib.jubann_set_row_query_csr(self._h, int(row_index), len(vals), _ptr(seed32), _ptr(keyhash64), _ptr(vals),
+                                                  int(k), int(flags), _ptr(idx), _ptr(score), _ptr(count)))
         return idx, score, count
 
     def query_rows(self, row_index, k, flags=0):

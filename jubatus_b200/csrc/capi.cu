@@ -936,6 +936,64 @@ static int set_rows_csr_small(jubann_t* h, uint64_t n, const uint64_t* row_index
   return 0;
 }
 
+// set_row followed at once by neighbor_row(id) of that row: one copy in, one hash, one copy out.
+int jubann_set_row_query_csr(jubann_t* h, uint64_t row_index, uint64_t nnz, const uint32_t* seed32, const uint64_t* keyhash64,
+                             const float* vals, uint32_t k, uint32_t flags, uint64_t* out_index, float* out_score,
+                             uint32_t* out_count) {
+  int rc = check_handle(h);
+  if (rc) return rc;
+  if (!out_count || (k && (!out_index || !out_score)) || (nnz && !vals)) return fail(JUBANN_E_INVALID, "null argument");
+  if (!h->shards.empty() || h->shard_count != 1)
+    return fail(JUBANN_E_INVALID, "set_row_query needs a single-shard handle (sharded hosts call set_rows_csr, then query_rows)");
+  Guard g(h);
+  const bool mh = h->method == MINHASH;
+  if (mh ? (nnz && !keyhash64) : (nnz && !seed32)) return fail(JUBANN_E_INVALID, "missing feature hashes for this method");
+  uint64_t new_global;
+  rc = check_row_indices(h, 1, &row_index, &new_global);
+  if (rc) return rc;
+  rc = reserve_global(h, new_global);
+  if (rc) return rc;
+  const size_t ip_b = up256(16), val_b = up256(nnz * 4), key_b = up256(nnz * (mh ? 8 : 4)), ri_b = up256(8);
+  const SmallPlan p = small_plan(h, 1, k, ip_b + val_b + key_b + ri_b, true);
+  if (p.total > SMALL_STAGE_BYTES) return fail(JUBANN_E_INVALID, "set_row_query: the row or k is too large for the one-copy path");
+  uint64_t* ip = reinterpret_cast<uint64_t*>(h->h_stage);
+  ip[0] = 0; ip[1] = nnz;
+  if (nnz) {
+    memcpy(h->h_stage + ip_b, vals, nnz * 4);
+    if (mh) memcpy(h->h_stage + ip_b + val_b, keyhash64, nnz * 8);
+    else memcpy(h->h_stage + ip_b + val_b, seed32, nnz * 4);
+  }
+  memcpy(h->h_stage + ip_b + val_b + key_b, &row_index, 8);
+  unsigned char* d = h->b_stage.as<unsigned char>();
+  CK(cudaMemcpyAsync(d, h->h_stage, p.in_bytes, cudaMemcpyHostToDevice, h->stream));
+  const uint64_t* d_ip = reinterpret_cast<const uint64_t*>(d);
+  const float* d_vals = reinterpret_cast<const float*>(d + ip_b);
+  const uint64_t* d_ri = reinterpret_cast<const uint64_t*>(d + ip_b + val_b + key_b);
+  uint64_t* d_sigs = reinterpret_cast<uint64_t*>(d + p.sig_off);
+  float* d_norms = reinterpret_cast<float*>(d + p.norm_off);
+  int launches = 0;
+  if (mh) {
+    CK(launch_signature_minhash(h->hash_num, 1, d_ip, reinterpret_cast<const uint64_t*>(d + ip_b + val_b), d_vals, d_sigs,
+                                d_norms, h->w64, h->num_sms, h->stream));
+    ++launches;
+  } else {
+    rc = ensure_cache(h);
+    if (rc) return rc;
+    const uint32_t* d_seed = reinterpret_cast<const uint32_t*>(d + ip_b + val_b);
+    CK(launch_cache_resolve(h->cache, d_seed, nnz, h->num_sms, h->stream, &launches));
+    CK(launch_cache_fill_queued(h->cache, nnz, h->num_sms, h->stream, &launches));
+    if (nnz) CK(cudaMemsetAsync(h->cache.counters + 1, 0, 4, h->stream));
+    h->cache_used_ub += nnz;
+    CK(launch_signature_lsh(h->cache, h->method == EUCLID_LSH, 1, d_ip, d_seed, d_vals, d_sigs, d_norms, h->w64, h->num_sms,
+                            h->cache_used_ub >= h->cache.slots, h->stream));
+    ++launches;
+  }
+  CK(launch_scatter_rows(view_grown(h, new_global), 1, d_ri, 0, d_sigs, d_norms, 0, 1, h->num_sms, h->stream));
+  h->kernel_launches += launches + 1;
+  commit_global(h, new_global);   // the scan that follows on the same stream ranks the table with the row in it
+  return small_finish(h, p, 1, d_sigs, d_norms, k, flags, out_index, out_score, out_count);
+}
+
 int jubann_query_sig(jubann_t* h, uint64_t nq, const uint64_t* qsigs, const float* qnorms, uint32_t k,
                      uint32_t flags, uint64_t* out_index, float* out_score, uint32_t* out_count) {
   int rc = check_handle(h);

@@ -1025,6 +1025,9 @@ template <int W32, bool EUCLID, int PV>
 #ifndef JBN_V1_PAIR
 #define JBN_V1_PAIR 1
 #endif
+#ifndef JBN_V1_PAIR_MAX_W32
+#define JBN_V1_PAIR_MAX_W32 4
+#endif
 // rows of 512 bits and more: one CTA per SM with 128 registers per thread (the row, its
 // prefetched successor, the adder triples and two queries fit without spilling: +16 % at 32
 // queries per pass, +17..42 % on 1024-bit rows); shorter rows: two CTAs per SM at 64 registers
@@ -1043,8 +1046,8 @@ __global__ void __launch_bounds__(SCAN_THREADS, W32 >= 16 ? 1 : 2) scan_ldg_kern
 
   // rows of <= 128 bits: a warp takes two adjacent tiles per step, so that every query word
   // fetched from shared memory serves two rows (+6..11 % measured; at 256 bits the second row
-  // costs more in spilled registers than it saves)
-  constexpr bool PAIR = JBN_V1_PAIR && W32 <= 4;
+  // costs more in spilled registers than it saves: 6.0 k against 6.4 k queries/s at 24 per pass)
+  constexpr bool PAIR = JBN_V1_PAIR && W32 <= JBN_V1_PAIR_MAX_W32;
   constexpr uint64_t TPS = PAIR ? 2 : 1;   // tiles per warp and step
   uint64_t t, t_end, t_step;
   if (a.interleave) {
@@ -1124,6 +1127,9 @@ __global__ void __launch_bounds__(SCAN_THREADS, W32 >= 16 ? 1 : 2) scan_ldg_kern
   if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane, false);
   __syncthreads();
   for (uint32_t q = warp; q < nqp; q += SCAN_WARPS) {
+    // one last look at what the whole GPU has counted: the CTA's own k-th best is a loose bound when
+    // hundreds of CTAs each keep k, and everything above the common bound leaves as padding below
+    if (L.ghist) hist_refresh<EUCLID>(q, lane);
     uint32_t n = list_compact<EUCLID>(q, sm_u32(L.cnt_off)[q], lane, true);
     const unsigned long long* src = sm_u64(L.list_off) + (size_t)q * a.cap;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(a.cand) +
@@ -1616,7 +1622,7 @@ static const uint32_t MSEL_MAX_KEYS = 24576;
 // in shared memory and ordered by counting (keys are distinct: the number of smaller keys is the
 // position).  A query with more than MSP_CAP live keys (long runs of equal distances) is flagged in
 // `dense` and left to the selection kernels below, which skip the queries that are not flagged.
-static const uint32_t MSP_CAP = 2048, MSP_THREADS = 512;
+static const uint32_t MSP_CAP = 1024, MSP_THREADS = 512;   // (ordering by counting is quadratic: 1024 keys = 2 x 1024 compares per thread)
 __global__ void __launch_bounds__(MSP_THREADS) merge_sparse_kernel(const unsigned long long* cand, uint32_t nlists, uint32_t k,
                                                                    MergeOut o, uint32_t* dense) {
   __shared__ unsigned long long buf[MSP_CAP];

@@ -653,8 +653,7 @@ int jubahost_add_numeric(void* h, const char* id, uint32_t nnz, const uint32_t* 
     if (!b->lof) throw jubatus_exception("add: anomaly server only");
     sfv_t v;
     b->conv_mut().convert_and_update_weight(numeric_datum(nnz, fids, vals), v);
-    b->lof->set_row(id, v);
-    *score = b->lof->calc_anomaly_score(std::string(id));
+    *score = b->lof->set_row_and_score(id, v);
     return 0;
   });
 }

@@ -131,6 +131,9 @@ struct jubann_api {
   int (*comm_info)(jubann_t*, uint32_t*, uint32_t*);
   int (*mix_allgather)(jubann_t*, uint64_t, const uint64_t*, const void*, uint64_t, uint64_t*, uint64_t*, const void**);
   int (*mix_apply)(jubann_t*, uint64_t, const uint32_t*, const uint32_t*, const uint64_t*);
+  // optional (0 when the library predates it): set_row + neighbor_row(id) in one call
+  int (*set_row_query_csr)(jubann_t*, uint64_t, uint64_t, const uint32_t*, const uint64_t*, const float*, uint32_t, uint32_t,
+                           uint64_t*, float*, uint32_t*);
 
   static std::shared_ptr<jubann_api> load(const std::string& path_or_name = "libjubann.so") {
     void* dl = 0;
@@ -175,6 +178,7 @@ struct jubann_api {
     JUBANN_SYM(mix_allgather, "jubann_mix_allgather");
     JUBANN_SYM(mix_apply, "jubann_mix_apply");
 #undef JUBANN_SYM
+    *reinterpret_cast<void**>(&a->set_row_query_csr) = ::dlsym(dl, "jubann_set_row_query_csr");
     return a;
   }
   void check(int rc) const {
@@ -545,14 +549,14 @@ struct packed_row {                                        // what column_table:
 class device_table {
  public:
   device_table(const std::shared_ptr<jubann_api>& api, const std::string& method, uint32_t hash_num, int device)
-      : api_(api), h_(0), hash_num_(hash_num), w64_((hash_num + 63) / 64), clock_(0) {
+      : api_(api), h_(0), hash_num_(hash_num), w64_((hash_num + 63) / 64), clock_(0), multi_(false) {
     api_->check(api_->create(method.c_str(), hash_num, device, 0, 1, &h_));
   }
   // one server process, several GPUs: the rows are sharded round-robin over `devices` inside the
   // library (jubann_create_multi); everything above this class is unchanged
   device_table(const std::shared_ptr<jubann_api>& api, const std::string& method, uint32_t hash_num,
                const std::vector<int>& devices)
-      : api_(api), h_(0), hash_num_(hash_num), w64_((hash_num + 63) / 64), clock_(0) {
+      : api_(api), h_(0), hash_num_(hash_num), w64_((hash_num + 63) / 64), clock_(0), multi_(devices.size() > 1) {
     if (devices.size() == 1) api_->check(api_->create(method.c_str(), hash_num, devices[0], 0, 1, &h_));
     else api_->check(api_->create_multi(method.c_str(), hash_num, devices.data(), static_cast<int>(devices.size()), &h_));
   }
@@ -561,6 +565,7 @@ class device_table {
   device_table& operator=(const device_table&) = delete;
 
   jubann_t* handle() const { return h_; }
+  bool multi_device() const { return multi_; }
   const jubann_api& api() const { return *api_; }
   uint64_t size() const { return keys_.size(); }
   uint32_t words() const { return w64_; }
@@ -774,6 +779,7 @@ class device_table {
   std::vector<version_t> versions_;
   std::unordered_map<std::string, uint64_t> index_;
   std::unordered_set<uint64_t> dirty_;
+  bool multi_;
 };
 
 // ---------------------------------------------------------------------------------------
@@ -971,6 +977,36 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
       table_->rollback(undo);
       a.check(rc);
     }
+  }
+  // set_row(id, sfv) followed by neighbor_row(id, ret_num) -- what light_lof::set_row does back to
+  // back -- as one device call when the table lives on one GPU (jubann_set_row_query_csr); the same
+  // answers as the two calls, which it falls back to otherwise.
+  void set_row_and_neighbors(const std::string& id, const sfv_t& sfv, neighbor_result& out, uint64_t ret_num) {
+    const jubann_api& a = table_->api();
+    if (!a.set_row_query_csr || table_->multi_device()) {
+      set_row(id, sfv);
+      neighbor_row(id, out, ret_num);
+      return;
+    }
+    csr_batch b;
+    b.add(sfv);
+    std::unique_lock<std::shared_mutex> lk(rw_);
+    device_table::assign_journal undo;
+    std::vector<std::string> ids(1, id);
+    const std::vector<uint64_t> idx = table_->assign(ids, my_id_, &undo);
+    const uint32_t k = clamp_k(ret_num);
+    std::vector<uint64_t> oi(std::max<uint32_t>(k, 1));
+    std::vector<float> os(oi.size());
+    std::vector<uint32_t> oc(1);
+    const int rc = a.set_row_query_csr(table_->handle(), idx[0], b.vals.size(), b.seed32.data(), b.keyhash64.data(), b.vals.data(), k, 0,
+                                       oi.data(), os.data(), oc.data());
+    if (rc) {
+      table_->rollback(undo);
+      a.check(rc);
+    }
+    std::vector<neighbor_result> res;
+    emit(1, k, oi, os, oc, std::vector<bool>(), res);
+    out.swap(res[0]);
   }
   void neighbor_row(const sfv_t& query, neighbor_result& ids, uint64_t ret_num) const {
     std::vector<sfv_t> q(1, query);
@@ -1724,21 +1760,20 @@ class light_lof {
     nn_->neighbor_row(id, nb, nn_num_);
     return score_from_neighbors(nb);
   }
-  bool set_row(const std::string& id, const sfv_t& sfv) {
-    if (unlearner_ && !unlearner_->touch(id)) throw jubatus_exception("no more space available to add new ID: " + id);
-    std::vector<std::string> order;
-    std::unordered_set<std::string> seen;
-    if (nn_->get_table()->exact_match(id).first) collect_neighbors(id, order, seen);
-    nn_->set_row(id, sfv);
-    collect_neighbors(id, order, seen);
-    kdist_[id] = -1.0f; lrd_[id] = -1.0f;
-    if (seen.insert(id).second) order.push_back(id);
-    update_entries(order);
-    return true;
+  bool set_row(const std::string& id, const sfv_t& sfv) { return set_row_impl(id, sfv, 0); }
+  // anomaly add: set_row, then the new row's score (anomaly_serv.cpp:157-176).  The row's neighbour
+  // list is already at hand from the re-scoring of set_row and the table has not changed since, so
+  // the score costs no further device call; the value is calc_anomaly_score(id)'s.
+  float set_row_and_score(const std::string& id, const sfv_t& sfv) {
+    neighbor_result own;
+    set_row_impl(id, sfv, &own);
+    return score_from_neighbors(own);
   }
-  void update_entries(const std::vector<std::string>& ids) {
+  void update_entries(const std::vector<std::string>& ids, const std::string* want_id = 0, neighbor_result* want = 0) {
     std::vector<neighbor_result> nn;
     nn_->neighbor_rows_from_ids(ids, nn, nn_num_, false);   // one device call for every id
+    if (want_id && want)
+      for (size_t i = 0; i < ids.size(); ++i) if (ids[i] == *want_id) *want = nn[i];
     for (size_t i = 0; i < ids.size(); ++i) {
       if (kdist_.find(ids[i]) == kdist_.end()) throw jubatus_exception("row not found in lof table: " + ids[i]);
       kdist_[ids[i]] = nn[i].empty() ? 0.0f : nn[i].back().second;
@@ -1789,6 +1824,31 @@ class light_lof {
   }
   gpu_nearest_neighbor* engine() { return nn_.get(); }
  private:
+  bool set_row_impl(const std::string& id, const sfv_t& sfv, neighbor_result* own) {
+    if (unlearner_ && !unlearner_->touch(id)) throw jubatus_exception("no more space available to add new ID: " + id);
+    std::vector<std::string> order;
+    std::unordered_set<std::string> seen;
+    if (nn_->get_table()->exact_match(id).first) collect_neighbors(id, order, seen);
+    // set_row, then the row's reverse-neighbour candidates: one device call
+    neighbor_result nb;
+    static const bool trace = ::getenv("JUBANN_HOST_TRACE") != 0;
+    static double t_set = 0, t_upd = 0; static uint64_t n_calls = 0;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    nn_->set_row_and_neighbors(id, sfv, nb, rnn_num_);
+    std::chrono::steady_clock::time_point t1 = std::chrono::steady_clock::now();
+    for (size_t i = 0; i < nb.size(); ++i) if (seen.insert(nb[i].first).second) order.push_back(nb[i].first);
+    kdist_[id] = -1.0f; lrd_[id] = -1.0f;
+    if (seen.insert(id).second) order.push_back(id);
+    update_entries(order, own ? &id : 0, own);
+    if (trace) {
+      std::chrono::steady_clock::time_point t2 = std::chrono::steady_clock::now();
+      t_set += std::chrono::duration<double>(t1 - t0).count(); t_upd += std::chrono::duration<double>(t2 - t1).count();
+      if (++n_calls % 256 == 0)
+        fprintf(stderr, "[light_lof] %llu set_row: set_row+neighbours %.1f us, re-scoring of %zu rows %.1f us (means)\n",
+                (unsigned long long)n_calls, t_set / n_calls * 1e6, order.size(), t_upd / n_calls * 1e6);
+    }
+    return true;
+  }
   void collect_neighbors(const std::string& id, std::vector<std::string>& order, std::unordered_set<std::string>& seen) const {
     neighbor_result nb;
     nn_->neighbor_row(id, nb, rnn_num_);

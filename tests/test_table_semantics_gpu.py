@@ -109,3 +109,39 @@ def test_device_pointer_writes_are_ordered_before_the_handle_stream(oracle):
             assert_same_ranking(got, want, 4, k)
         back, _ = e.get_rows_sig(np.arange(total, dtype=np.uint64))
         assert np.array_equal(back, np.concatenate(chunks))
+
+
+@pytest.mark.parametrize("method,hash_num", [("lsh", 256), ("euclid_lsh", 256), ("minhash", 128)])
+def test_set_row_query_is_set_row_then_neighbor_row_from_id(oracle, feature_tables, method, hash_num):
+    # jubann_set_row_query_csr: one call stores a row and ranks the table with the row in it -- the answers of
+    # set_rows_csr followed by query_rows, for appended rows and for rows overwritten in place
+    from jubatus_b200 import Engine, SIMILAR, workload as w
+    s32, k64 = feature_tables
+    n, k = 300, 12
+    ids, vals = w.synth_rows(w.MASTER_SEED, 0, n + 20, nnz=30, nfeat_log2=10)
+    euclid = method == "euclid_lsh"
+    with Engine(method, hash_num) as fused, Engine(method, hash_num) as plain:
+        csr = w.to_csr(ids[:n], vals[:n], s32, k64)
+        fused.set_rows_csr(np.arange(n), *csr)
+        plain.set_rows_csr(np.arange(n), *csr)
+        for step, (src, at) in enumerate([(n, n), (n + 1, n + 1), (n + 2, 5), (n + 3, n + 2), (n + 4, 0)]):
+            indptr, seed32, keyhash, v = w.to_csr(ids[src:src + 1], vals[src:src + 1], s32, k64)
+            flags = SIMILAR if step % 2 else 0
+            got = fused.set_row_query_csr(at, seed32, keyhash, v, k, flags)
+            plain.set_rows_csr(np.array([at], dtype=np.uint64), indptr, seed32, keyhash, v)
+            want = plain.query_rows(np.array([at], dtype=np.uint64), k, flags)
+            assert_same_ranking(got, want, 1, k)
+            assert got[0][0][0] == at or got[1][0][0] == want[1][0][0]      # the row itself leads (ties by row index aside)
+            assert fused.size() == plain.size()
+        total = fused.size()[0]
+        a, an = fused.get_rows_sig(np.arange(total, dtype=np.uint64))
+        b, bn = plain.get_rows_sig(np.arange(total, dtype=np.uint64))
+        assert np.array_equal(a, b) and np.array_equal(an.view(np.uint32), bn.view(np.uint32))
+        # and against the CPU engine on the stored table
+        q = a[:3]
+        got = fused.query_sig(q, an[:3] if euclid else None, k)
+        want = oracle.scan_batch(method, q, an[:3] if euclid else None, a, an if euclid else None, hash_num, k)[:3]
+        assert_same_ranking(got, want, 3, k)
+        with pytest.raises(Exception):
+            fused.set_row_query_csr(total + 3, seed32, keyhash, v, k)          # skips past the end: refused, nothing stored
+        assert fused.size()[0] == total

@@ -65,3 +65,12 @@ for k in (1, 10, 100):
 ridx = np.array([5], dtype=np.uint64)
 print("set_rows_csr host 1 row: %.1f us" % t(lambda: e.set_rows_csr(ridx, *csr)))
 print("query_rows host 1 row, k=10: %.1f us" % t(lambda: e.query_rows(ridx, 10)))
+
+# batches of stored rows as queries (light_lof re-scores up to 61 rows per add with one such call)
+for nq, k in ((1, 30), (8, 10), (31, 10), (61, 10)):
+    rows = (np.arange(nq, dtype=np.uint64) * 7919) % n
+    e.stats_reset(True)
+    us = t(lambda: e.query_rows(rows, k), reps=200)
+    st = e.stats()
+    print("query_rows %2d rows, k=%d: %.1f us per call; scan+sample kernels %.1f us, %d kernels per call" % (
+        nq, k, us, st["scan_ms"] / 220 * 1e3, st["kernel_launches"] // 220))
