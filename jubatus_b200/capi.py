@@ -122,6 +122,8 @@ def load_library():
         "jubann_mix_apply": [H, ctypes.c_uint64, _vp, _vp, _vp],
     }
     for name, argtypes in sig.items():
+        if os.environ.get("JUBANN_LIBRARY") and not hasattr(lib, name):
+            continue   # (an older build named for an A/B run: it simply lacks the newer entry points)
         fn = getattr(lib, name)
         fn.argtypes = argtypes
         fn.restype = ctypes.c_int

@@ -1353,12 +1353,16 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
   for (uint32_t g = 0; g < ngroups; ++g) {
     const uint32_t q0 = g * a.qp;
     const uint32_t nqp = min(a.qp, a.nq - q0);
+#ifdef JBN_SCAN_TRACE   // tuning builds only (tools/scan_trace.py): the stage loop pays for every test in it
 #define JBN_TRACE(slot)                                                                                     \
   if (a.trace && blockIdx.x < 4 && tid == 0) {                                                              \
     unsigned long long t_;                                                                                  \
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                  \
     a.trace[((size_t)blockIdx.x * ngroups + g) * 8 + (slot)] = t_;                                          \
   }
+#else
+#define JBN_TRACE(slot)
+#endif
     JBN_TRACE(0)
     scan_prologue<W32, EUCLID, true>(a, smem, sp, L, s_q, s_bnd, q0, nqp, tid, CT);
     consumer_barrier();
@@ -1371,6 +1375,9 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
 #pragma unroll
       for (int q = 0; q < NQR; ++q) load_query<W32>(s_q + q * QS, qreg[q]);
     }
+    uint32_t next_refresh = (L.ghist && !(a.debug & 1u)) ? 0u : 0xFFFFFFFFu;
+    const uint32_t poll_mask = (L.ghist && !(a.debug & 4u)) ? (EUCLID ? 7u : 3u) : 0xFFFFFFFFu;   // (all ones: never equal below)
+    uint32_t poll_warp = 0;
     for (uint32_t it = 0; it < iters; ++it, t0 += t_stride) {
       mbar_wait(full_bar + s, ph);
       const unsigned char* stage = ring + s * stage_bytes;
@@ -1429,25 +1436,36 @@ __global__ void __launch_bounds__(TMA_THREADS, 1) scan_tma_kernel(ScanArgs a, ui
       if (stash_count(L, warp) >= STASH_FLUSH_AT) stash_flush<EUCLID>(warp, lane);   // ... then do the slow insertions
       // euclid: a tighter bound means recomputing that query's norm bounds, so poll less often
       // and take turns (a warp that lags holds up the whole ring)
-      if (a.debug & 4u) {
-      } else if (L.ghist && !(a.debug & 1u) &&
-                 (it < EARLY_REFRESH_STAGES || (!EUCLID && (it & (it - 1u)) == 0u) || it + 3u == iters)) {
+      // bounds maintenance, kept to one compare per stage on the common path (46 more instructions per
+      // warp and stage here cost the 10^8-row headline 7 %)
+      if (it == next_refresh) {
         // start of a pass: the thresholds come from a small sample and are loose; after one stage per
         // CTA the histogram already holds far more than k candidates, so one warp per stage (in turn)
         // derives the bound from it directly instead of waiting for somebody's flush to publish one.
         // Later candidates are so rare that nobody flushes any more: the bound is re-derived at stages
         // 4, 8, 16, ... (hamming engines: one short read; a euclid_lsh refresh costs a warp two
         // microseconds, which a pass that is exactly as fast as HBM has no room for) and once more three
-        // stages before the end, so that what the lists hold above
-        // the final bound (blanked in write_lists) is a few keys, not thousands.
+        // stages before the end, so that what the lists hold above the final bound (blanked in
+        // write_lists) is a few keys, not thousands.
         // (query q by warp (stage + q) mod 15: no warp is held up by more than one refresh)
         const uint32_t slot = ((uint32_t)warp + TMA_CONSUMER_WARPS - it % TMA_CONSUMER_WARPS) % TMA_CONSUMER_WARPS;
         for (uint32_t q = slot; q < nqp; q += TMA_CONSUMER_WARPS) hist_refresh<EUCLID>(q, lane);
-      } else if (EUCLID ? ((it & 7u) == 7u && (uint32_t)warp == (it >> 3) % TMA_CONSUMER_WARPS) : (warp == 0)) {
-        poll_shared_bounds<EUCLID>(L, nqp, lane);
+        uint32_t nx = 0xFFFFFFFFu;
+        if (it + 1 < EARLY_REFRESH_STAGES) nx = it + 1;
+        else if (!EUCLID) nx = 1u << (32 - __clz(it));   // the next power of two above it
+        if (iters >= 3 && iters - 3 > it && iters - 3 < nx) nx = iters - 3;
+        next_refresh = nx;
+      } else if ((it & poll_mask) == poll_mask) {
+        // published bounds (one word per query from L2): every 4th stage for the hamming engines; for
+        // euclid_lsh, where a tighter bound means recomputing that query's norm bounds, every 8th, the
+        // warps taking turns (a warp that lags holds up the whole ring)
+        if ((uint32_t)warp == poll_warp) poll_shared_bounds<EUCLID>(L, nqp, lane);
+        if (EUCLID) poll_warp = poll_warp + 1 == TMA_CONSUMER_WARPS ? 0u : poll_warp + 1;   // (every warp keeps the same count)
       }
       if (++s == stages) { s = 0; ph ^= 1u; }
+#ifdef JBN_SCAN_TRACE
       if (it == 0) { JBN_TRACE(2) } else if (it == 3) { JBN_TRACE(3) } else if (it == 11) { JBN_TRACE(4) }
+#endif
     }
     JBN_TRACE(5)
     if (stash_count(L, warp)) stash_flush<EUCLID>(warp, lane, false);   // the pass is over: a tighter bound serves nobody
