@@ -23,6 +23,10 @@ NVCC_FLAGS = [
 ]
 
 
+# extra nvcc flags for tuning builds, e.g. JUBANN_NVCC_EXTRA=-DJBN_SCAN_TRACE (tools/scan_trace.py)
+NVCC_FLAGS += [f for f in os.environ.get("JUBANN_NVCC_EXTRA", "").split() if f]
+
+
 def _nvcc():
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and os.path.exists(cand):

@@ -1,4 +1,7 @@
 """Tuning aid: per-group timeline of the persistent TMA scan kernel (JUBANN_SCAN_TRACE).
+Needs a library built with the trace points compiled in:
+    JUBANN_NVCC_EXTRA=-DJBN_SCAN_TRACE python -c "from jubatus_b200 import build; build.build_cuda()"
+(touch csrc/scan.cu first; the default build leaves them out, they cost the stage loop instructions).
     python tools/scan_trace.py [method hash_num rows]
 Prints, per query group, microseconds between the trace points of CTA 0 (warp 0):
 prologue | stage 0 | stages 1-3 | stages 4-11 | remaining stages | final flush + barrier | write lists."""
