@@ -93,7 +93,11 @@ int jubann_destroy(jubann_t* h);
  * POPC per word, 1..4 = carry-save adder trees of growing depth, default 3), "scan_order" (1 = CTAs take turns over
  * consecutive tile groups so the whole GPU sweeps one front, 0 = one contiguous range per CTA),
  * "reserve_rows" (allocate the slab for this
- * many global rows up front; may be set at any time). */
+ * many global rows up front; may be set at any time).  Two switches select alternates of choices
+ * that jubatus_core's source would settle (0 = the frozen choice the parity tests
+ * run under): "gaussian_form" (1: the Box-Muller variate is taken with sin instead of cos; before
+ * the first row or query) and "euclid_score" (1: cosf and the whole score expression in float
+ * instead of double). */
 int jubann_set_option(jubann_t* h, const char* name, int64_t value);
 
 /* nearest_neighbor_base::clear() -> column_table::clear()  (nearest_neighbor_serv.cpp:125) */

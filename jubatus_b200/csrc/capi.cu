@@ -266,6 +266,19 @@ void record_scan_end(jubann_t* h, cudaStream_t s, cudaEvent_t a, cudaEvent_t b) 
   h->scan_events.push_back(std::make_pair(a, b));
 }
 
+// cos(theta_d), theta_d = (float)(d * M_PI / (float)hash_num), evaluated by the host libm so that the
+// table holds the very values the CPU engine computes per row: in double (score_mode 0, the frozen
+// choice) or with cosf (score_mode 1, the SURVEY A.9 alternate; stored widened, which is exact)
+cudaError_t upload_coslut(jubann_t* h) {
+  std::vector<double> lut(h->hash_num + 1);
+  const float denom = static_cast<float>(h->hash_num);
+  for (uint32_t i = 0; i <= h->hash_num; ++i) {
+    const float theta = static_cast<float>(static_cast<uint64_t>(i) * M_PI / denom);
+    lut[i] = h->score_mode ? static_cast<double>(cosf(theta)) : cos(static_cast<double>(theta));
+  }
+  return cudaMemcpy(h->d_coslut, lut.data(), lut.size() * 8, cudaMemcpyHostToDevice);
+}
+
 // The query path.  All pointers are device pointers; work is enqueued on `s`.
 // Exactly one of (final outputs) / (raw candidate outputs) is given.
 int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const float* d_qnorms, uint32_t k,
@@ -293,6 +306,7 @@ int query_device(jubann_t* h, uint64_t nq64, const uint64_t* d_qsigs, const floa
   ScanConfig cfg;
   if (!plan_scan(t, euclid, nq, kpage, h->variant_opt, h->popc_variant_opt, h->qp_opt, h->interleave_opt, h->num_sms, &cfg))
     return fail(JUBANN_E_INVALID, "cannot plan a scan for k=%u", kpage);
+  cfg.score_mode = (uint32_t)h->score_mode;
   // queries per launch bounded by candidate + shared-histogram scratch (<= 256 MiB)
   const size_t per_query = (size_t)cfg.nchunks * kpage * 8;
   const size_t hist_per_query = hist_scratch_bytes(1, h->hash_num, euclid);
@@ -377,6 +391,7 @@ int handle_info(jubann* h, HandleInfo* out) {
   out->shard_rank = h->shard_rank; out->shard_count = h->shard_count;
   out->variant = h->variant_opt; out->popc_variant = h->popc_variant_opt; out->interleave = h->interleave_opt;
   out->qp = h->qp_opt; out->num_sms = h->num_sms; out->coslut = h->d_coslut; out->mu = &h->mu;
+  out->score_mode = h->score_mode;
   return 0;
 }
 void handle_add_launches(jubann* h, uint64_t kernels, uint64_t scans, uint64_t passes) {
@@ -427,16 +442,8 @@ int jubann_create(const char* method, uint32_t hash_num, int device, uint32_t sh
   ok = ok && cudaMallocHost(reinterpret_cast<void**>(&h->h_stage), SMALL_STAGE_BYTES) == cudaSuccess;
   ok = ok && h->b_stage.ensure(SMALL_STAGE_BYTES) == cudaSuccess;
   if (ok && m == EUCLID_LSH) {
-    // cos(theta_h), theta_h = (float)(h * M_PI / (float)hash_num), evaluated in double by the host
-    // libm so that the table holds the very values the CPU engine computes per row
-    std::vector<double> lut(hash_num + 1);
-    const float denom = static_cast<float>(hash_num);
-    for (uint32_t i = 0; i <= hash_num; ++i) {
-      const float theta = static_cast<float>(static_cast<uint64_t>(i) * M_PI / denom);
-      lut[i] = cos(static_cast<double>(theta));
-    }
-    ok = ok && cudaMalloc(reinterpret_cast<void**>(&h->d_coslut), lut.size() * 8) == cudaSuccess;
-    ok = ok && cudaMemcpy(h->d_coslut, lut.data(), lut.size() * 8, cudaMemcpyHostToDevice) == cudaSuccess;
+    ok = ok && cudaMalloc(reinterpret_cast<void**>(&h->d_coslut), ((size_t)hash_num + 1) * 8) == cudaSuccess;
+    ok = ok && upload_coslut(h) == cudaSuccess;
   }
   if (!ok) {
     cudaError_t le = cudaGetLastError();
@@ -509,6 +516,17 @@ int jubann_set_option(jubann_t* h, const char* name, int64_t value) {
       if (h->slab) cudaFree(h->slab);
       if (h->norms) cudaFree(h->norms);
       h->slab = nslab; h->norms = nnorms; h->cap_rows = want;
+    }
+  } else if (!strcmp(name, "gaussian_form")) {   // SURVEY A.9 alternate: 0 = cos (frozen choice), 1 = sin
+    if (value < 0 || value > 1) return fail(JUBANN_E_INVALID, "gaussian_form out of range (0..1)");
+    if (h->cache_used_ub || h->global_rows) return fail(JUBANN_E_INVALID, "gaussian_form must be set before the first row or query");
+    h->cache.gauss_form = (uint32_t)value;
+  } else if (!strcmp(name, "euclid_score")) {    // SURVEY A.9 alternate: 0 = double (frozen choice), 1 = cosf and float
+    if (value < 0 || value > 1) return fail(JUBANN_E_INVALID, "euclid_score out of range (0..1)");
+    h->score_mode = (int)value;
+    if (h->method == EUCLID_LSH) {
+      CK(cudaStreamSynchronize(h->stream));   // (no scan of this handle is reading the table while it changes)
+      CK(upload_coslut(h));
     }
   } else if (!strcmp(name, "queries_per_pass")) {
     if (value < 0 || value > 64) return fail(JUBANN_E_INVALID, "queries_per_pass out of range (0..64)");

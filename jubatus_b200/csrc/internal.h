@@ -71,6 +71,7 @@ struct ScanConfig {
   uint32_t cap;       // candidate list capacity per (CTA, query), power of two
   uint32_t stages, tiles_per_warp;  // TMA ring geometry (variant 2)
   uint32_t interleave;
+  uint32_t score_mode;   // euclid_lsh: 0 = cos and score in double (frozen choice), 1 = cosf and score in float
   size_t smem_bytes;
 };
 
@@ -143,6 +144,7 @@ struct ProjCache {
   uint32_t slots;      // capacity
   uint32_t table_size; // hash table positions (power of two)
   uint32_t hash_num;
+  uint32_t gauss_form; // 0: sqrt(-2 log(1-a)) cos(2 pi b) (frozen choice); 1: ... sin(2 pi b)
 };
 cudaError_t launch_cache_resolve(const ProjCache& c, const uint32_t* d_seed32, uint64_t nnz, int num_sms,
                                  cudaStream_t s, int* launches);
@@ -166,6 +168,7 @@ struct HandleInfo {
   uint32_t qp;
   int num_sms;
   const double* coslut;
+  int score_mode;
   std::mutex* mu;
 };
 }  // namespace jbn

@@ -121,6 +121,7 @@ extern "C" int jubann_query_sig_noalloc_dev(jubann_t* h, uint64_t nq64, const ui
   if (keff) {
     if (!plan_scan(hi.table, hi.euclid, nq, keff, hi.variant, hi.popc_variant, hi.qp, hi.interleave, hi.num_sms, &cfg))
       return set_error(JUBANN_E_INVALID, "no-alloc query: cannot plan a scan for this k");
+    cfg.score_mode = (uint32_t)hi.score_mode;
     const uint64_t need = (uint64_t)nq * cfg.nchunks * keff * 8ull + (uint64_t)nq * 8ull +   // lists + one threshold per query
                           (hi.euclid ? 0 : hist_scratch_bytes(nq, hi.table.hash_num, false));  // + shared distance histogram (hamming engines)
     if (need > (uint64_t)JUBANN_NOALLOC_SCRATCH_BYTES) {

@@ -50,6 +50,7 @@ struct ScanArgs {
   uint32_t w32;
   uint32_t interleave;  // 1: CTAs take turns tile-group by tile-group (one sweep front); 0: one contiguous range per CTA
   unsigned long long* trace;   // tuning experiments ($JUBANN_SCAN_TRACE): per (CTA < 4, group) timestamps of warp 0
+  uint32_t score_mode;  // euclid_lsh: 0 = score in double (cos table of doubles), 1 = all in float (table holds cosf values)
   uint32_t debug;       // tuning experiments ($JUBANN_SCAN_DEBUG): 1 no early refresh, 2 no shared histogram, 4 no polling, 8 no refresh after a flush
 };
 
@@ -369,12 +370,8 @@ __host__ __device__ __forceinline__ uint32_t tau_hi_of(unsigned long long tau) {
 //   every operation rounds towards +inf, and the result is moved one more float up.
 // A non-finite c or T disables the filter for that entry (+inf); a discriminant that is negative
 // even after rounding up means no norm is admissible at that distance (-inf).
-__device__ __forceinline__ float euclid_bound_core(float c_add, float c_mag, uint32_t tau_hi) {
-  const float Tf = key_float(tau_hi);
-  if (!(fabsf(Tf) < INFINITY) || !(fabsf(c_mag) < INFINITY)) return INFINITY;
-  float Tu = Tf + 0.0f;                                                   // -0 -> +0
-  Tu = __uint_as_float(Tu >= 0.0f ? __float_as_uint(Tu) + 2u : (__float_as_uint(Tu) >= 0x80000002u ? __float_as_uint(Tu) - 2u : 1u));
-  Tu = __fadd_ru(Tu, __fmaf_ru(1.5e-14f, __fmul_ru(c_mag, c_mag), 1e-37f));
+// upper root of n^2 - c n - Tu = 0, every operation rounded up (+inf: no filtering; -inf: nothing admissible)
+__device__ __forceinline__ float euclid_upper_root(float c_add, float c_mag, float Tu) {
   const float disc = __fmaf_ru(c_mag, c_mag, __fmul_ru(4.0f, Tu));
   if (!(disc < INFINITY)) return INFINITY;                                // overflow or NaN: no filtering
   if (disc < 0.0f) return -INFINITY;
@@ -382,18 +379,35 @@ __device__ __forceinline__ float euclid_bound_core(float c_add, float c_mag, uin
   if (!(fabsf(hi) < INFINITY)) return INFINITY;
   return __uint_as_float(hi >= 0.0f ? __float_as_uint(hi + 0.0f) + 1u : __float_as_uint(hi) - 1u);   // one more float up
 }
-__device__ __forceinline__ float euclid_bound(double c, uint32_t tau_hi) {
+// fmode: the score is computed in float (score_mode 1).  Its three roundings can move it by up to
+// 2^-24 * n * (2 n + 3 |c|) (+ second-order terms) away from the exact value, n being the row norm; n is
+// what the bound limits, so the slack is taken at a norm 1 % above a first estimate of the bound and the
+// result is used only if it stays below that norm (else: no filtering at that distance).
+__device__ __forceinline__ float euclid_bound_core(float c_add, float c_mag, uint32_t tau_hi, bool fmode = false) {
+  const float Tf = key_float(tau_hi);
+  if (!(fabsf(Tf) < INFINITY) || !(fabsf(c_mag) < INFINITY)) return INFINITY;
+  float Tu = Tf + 0.0f;                                                   // -0 -> +0
+  Tu = __uint_as_float(Tu >= 0.0f ? __float_as_uint(Tu) + 2u : (__float_as_uint(Tu) >= 0x80000002u ? __float_as_uint(Tu) - 2u : 1u));
+  Tu = __fadd_ru(Tu, __fmaf_ru(1.5e-14f, __fmul_ru(c_mag, c_mag), 1e-37f));
+  const float hi = euclid_upper_root(c_add, c_mag, Tu);
+  if (!fmode || !(fabsf(hi) < INFINITY)) return hi;
+  const float n1 = __fadd_ru(__fmul_ru(fabsf(hi), 1.01f), 1e-30f);
+  const float slack = __fmul_ru(2.4e-7f, __fmul_ru(n1, __fadd_ru(__fmul_ru(2.0f, n1), __fmul_ru(3.0f, fabsf(c_mag)))));   // 4 * 2^-24: twice the first-order bound
+  const float hi2 = euclid_upper_root(c_add, c_mag, __fadd_ru(Tu, slack));
+  return (hi2 <= n1) ? hi2 : INFINITY;
+}
+__device__ __forceinline__ float euclid_bound(double c, uint32_t tau_hi, bool fmode = false) {
   if (!(fabs(c) < (double)INFINITY)) return INFINITY;
   const float c_add = __double2float_ru(c);
   const float c_mag = c >= 0.0 ? c_add : __double2float_rd(c);          // |c_mag| >= |c|
-  return euclid_bound_core(c_add, c_mag, tau_hi);
+  return euclid_bound_core(c_add, c_mag, tau_hi, fmode);
 }
 // the same from c rounded up to float alone (the per-query table the TMA kernel keeps in shared memory,
 // so that re-deriving a query's bounds touches neither global memory nor the double pipe): where c is
 // squared, a negative c is taken one float further from zero, which covers the rounding of c_add
-__device__ __forceinline__ float euclid_bound_f(float c_add, uint32_t tau_hi) {
+__device__ __forceinline__ float euclid_bound_f(float c_add, uint32_t tau_hi, bool fmode = false) {
   const float c_mag = c_add >= 0.0f ? c_add : __uint_as_float(__float_as_uint(c_add) + 1u);
-  return euclid_bound_core(c_add, c_mag, tau_hi);
+  return euclid_bound_core(c_add, c_mag, tau_hi, fmode);
 }
 
 // ---------------------------------------------------------------------------
@@ -418,6 +432,7 @@ struct ListCtl {
   uint32_t nq, q0, hist_stride;
   uint32_t* ghist;     // global: [nq] bound words | [nq][hist_stride] counts; nullptr when unused
   uint32_t no_flush_refresh;
+  uint32_t score_mode;
   // euclid only
   uint32_t bnd_off;    // float [qp][hash_num + 1]: norm above which a row at that distance cannot be admitted
   uint32_t ctab_off;   // float [qp][hash_num + 1]: 2 * norm_q * cos(pi d / hash_num) rounded up, or NO_CTAB
@@ -443,10 +458,10 @@ __device__ __noinline__ void euclid_bounds_update(uint32_t q, int lane) {
   float* b = reinterpret_cast<float*>(g_smem + s_L.bnd_off) + (size_t)q * (s_L.hash_num + 1);
   if (s_L.ctab_off != NO_CTAB) {
     const float* c = reinterpret_cast<const float*>(g_smem + s_L.ctab_off) + (size_t)q * (s_L.hash_num + 1);
-    for (uint32_t d = lane; d <= s_L.hash_num; d += 32) b[d] = euclid_bound_f(c[d], th);
+    for (uint32_t d = lane; d <= s_L.hash_num; d += 32) b[d] = euclid_bound_f(c[d], th, s_L.score_mode != 0);
   } else {
     const double two_nq = (double)(2.0f * s_L.qnorms[s_L.q0 + q]);
-    for (uint32_t d = lane; d <= s_L.hash_num; d += 32) b[d] = euclid_bound(__dmul_rn(two_nq, s_L.coslut[d]), th);
+    for (uint32_t d = lane; d <= s_L.hash_num; d += 32) b[d] = euclid_bound(__dmul_rn(two_nq, s_L.coslut[d]), th, s_L.score_mode != 0);
   }
   __syncwarp();
 }
@@ -755,6 +770,15 @@ __device__ __noinline__ void stash_push(uint32_t q, uint32_t key_hi, uint32_t ro
   __syncwarp();
 }
 
+// the engine's score of a row: n_i * (n_i - 2 n_q cos(theta_d)).  mode 0 (frozen choice): the expression in
+// double, one rounding per operation, narrowed to float; mode 1 (SURVEY A.9 alternate: std::cos on a float
+// picks cosf, the expression stays float): the table holds cosf values and every operation is a float one
+__device__ __forceinline__ float euclid_exact_score(float nif, float two_nq, double cosd, uint32_t mode) {
+  if (mode) return __fmul_rn(nif, __fsub_rn(nif, __fmul_rn(two_nq, (float)cosd)));
+  const double ni = (double)nif;
+  return __double2float_rn(__dmul_rn(ni, __dsub_rn(ni, __dmul_rn((double)two_nq, cosd))));
+}
+
 // euclid slow path, warp-uniform: lanes with cand compute the exact score of (row, query q) --
 // double arithmetic with one rounding per operation, narrowed to float: the same values as the
 // CPU engine -- and offer it.
@@ -762,7 +786,6 @@ __device__ __noinline__ void euclid_offer(uint32_t q, uint32_t d, float nif, uin
   if (!__any_sync(FULL_MASK, cand)) return;
   uint32_t key = 0;
   if (cand) {
-    const double ni = (double)nif;
     float two_nq;
     double cosd;
     if (s_L.ctab_off != NO_CTAB) {   // TMA kernel: both operands sit in shared memory
@@ -772,8 +795,7 @@ __device__ __noinline__ void euclid_offer(uint32_t q, uint32_t d, float nif, uin
       two_nq = 2.0f * s_L.qnorms[s_L.q0 + q];
       cosd = s_L.coslut[d];
     }
-    const double l2 = __dmul_rn((double)two_nq, cosd);
-    key = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l2))));
+    key = float_key(euclid_exact_score(nif, two_nq, cosd, s_L.score_mode));
   }
   stash_push<true>(q, key, row, cand, warp, lane);
 }
@@ -969,6 +991,7 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
   L.cap = a.cap; L.k = a.k; L.has_floor = (a.floor_keys != nullptr) ? 1u : 0u;
   L.nq = a.nq; L.q0 = q0; L.hist_stride = a.hist_stride; L.ghist = a.ghist;
   L.no_flush_refresh = (a.debug & 8u) ? 1u : 0u;
+  L.score_mode = a.score_mode;
   L.bnd_off = (uint32_t)sp.lut_off; L.hash_num = a.hash_num;
   L.ctab_off = (EUCLID && CTAB) ? (uint32_t)sp.ctab_off : NO_CTAB;
   L.cos_off = (uint32_t)sp.cos_off; L.qn_off = (uint32_t)sp.qn_off;
@@ -1005,9 +1028,9 @@ __device__ __forceinline__ void scan_prologue(const ScanArgs& a, unsigned char* 
       if (CTAB) {
         const float c_add = (fabs(c) < (double)INFINITY) ? __double2float_ru(c) : INFINITY;
         reinterpret_cast<float*>(smem + sp.ctab_off)[i] = c_add;
-        s_bnd[i] = euclid_bound_f(c_add, th);
+        s_bnd[i] = euclid_bound_f(c_add, th, a.score_mode != 0);
       } else {
-        s_bnd[i] = euclid_bound(c, th);
+        s_bnd[i] = euclid_bound(c, th, a.score_mode != 0);
       }
     }
   }
@@ -1832,7 +1855,7 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
   // (a table that cannot give every SM a stage or two is not worth the ring's set-up either)
   const uint32_t tma_max_qp = t.w32 >= 16 ? 3 : 4;   // 512-bit rows: the LDG kernel is ahead from 4 queries per pass on
   cfg->variant = variant <= 0 ? ((qp <= tma_max_qp && ntiles >= (uint64_t)num_sms * 32) ? 2 : 1) : variant;
-  cfg->stages = 0; cfg->tiles_per_warp = 0;
+  cfg->stages = 0; cfg->tiles_per_warp = 0; cfg->score_mode = 0;
   cfg->interleave = interleave ? 1u : 0u;
   uint64_t max_chunks;
   if (cfg->variant == 2) {
@@ -2006,7 +2029,7 @@ __global__ void __launch_bounds__(TAUE_THREADS) tau_init_euclid_kernel(ScanArgs 
     for (uint32_t i = tid; i < a.hist_stride; i += TAUE_THREADS) g[i] = 0;
   }
   __syncthreads();
-  const double two_nq = (double)(2.0f * a.qnorms[q]);
+  const float two_nq_f = 2.0f * a.qnorms[q];
   uint32_t r[TAUE_KPT];
   uint32_t vor = 0, vand = 0xFFFFFFFFu;
 #pragma unroll
@@ -2031,9 +2054,7 @@ __global__ void __launch_bounds__(TAUE_THREADS) tau_init_euclid_kernel(ScanArgs 
             d += __popc(v[c].x ^ sq[4 * c]) + __popc(v[c].y ^ sq[4 * c + 1]) + __popc(v[c].z ^ sq[4 * c + 2]) +
                  __popc(v[c].w ^ sq[4 * c + 3]);
       }
-      const double ni = (double)a.norms[i];
-      const double l2 = __dmul_rn(two_nq, a.coslut[d]);
-      key = float_key(__double2float_rn(__dmul_rn(ni, __dsub_rn(ni, l2))));
+      key = float_key(euclid_exact_score(a.norms[i], two_nq_f, a.coslut[d], a.score_mode));
       vor |= key; vand &= key;
     }
     r[j] = key;
@@ -2095,6 +2116,7 @@ cudaError_t launch_scan(const TableView& t, bool euclid, const ScanConfig& cfg, 
   a.tiles_per_chunk = cfg.tiles_per_chunk; a.nchunks = cfg.nchunks;
   a.w32 = t.w32;
   a.interleave = cfg.interleave;
+  a.score_mode = cfg.score_mode;
   static const uint32_t dbg = getenv("JUBANN_SCAN_DEBUG") ? (uint32_t)atoi(getenv("JUBANN_SCAN_DEBUG")) : 0u;
   a.debug = dbg;
   a.trace = nullptr;

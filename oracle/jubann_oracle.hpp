@@ -59,6 +59,25 @@ inline uint64_t calc_string_hash(const std::string& s) {
 // next_gaussian = Box-Muller, no cached second variate (4 draws each).
 // Frozen form: sqrt(-2*log(1-a)) * cos(2*pi*b), a drawn first.
 // ---------------------------------------------------------------------------
+// ---------------------------------------------------------------------------
+// Alternates for the recalled choices most likely to differ from jubatus_core, behind
+// one switch each so that adopting the real behaviour is a flag, not a rewrite.  Defaults = the
+// frozen choices.  The CUDA path has the same two switches (jubann_set_option "gaussian_form",
+// "euclid_score"); tests/golden/nn_golden_variants.json freezes the oracle's answers under each.
+//   gaussian_form  0: sqrt(-2 log(1-a)) * cos(2 pi b)   1: ... * sin(2 pi b)
+//   euclid_score   0: cos in double, score expression in double, narrowed to float
+//                  1: cosf(theta) and the whole score in float (std::cos on a float argument picks
+//                     the float overload in C++)
+// ---------------------------------------------------------------------------
+struct variants {
+  int gaussian_form;
+  int euclid_score;
+};
+inline variants& variant_switches() {
+  static variants v = {0, 0};
+  return v;
+}
+
 class mtrand {
  public:
   explicit mtrand(uint32_t seed) { init(seed); }
@@ -85,6 +104,7 @@ class mtrand {
   double next_gaussian() {
     double a = next_double();
     double b = next_double();
+    if (variant_switches().gaussian_form == 1) return sqrt(-2.0 * log(1.0 - a)) * sin(2.0 * M_PI * b);
     return sqrt(-2.0 * log(1.0 - a)) * cos(2.0 * M_PI * b);
   }
 
@@ -348,6 +368,13 @@ inline void ranking_hamming_bit_vectors(const uint64_t* q, const uint64_t* rows,
 inline float euclid_score(float norm_i, float norm_q, uint32_t hamm, uint32_t hash_num) {
   const float denom = static_cast<float>(hash_num);
   const float theta = static_cast<float>(hamm * M_PI / denom);
+  if (variant_switches().euclid_score == 1) {   // every operation in float, one rounding each
+    volatile float cf = cosf(theta);
+    volatile float tf = (2 * norm_q) * cf;
+    volatile float uf = norm_i - tf;
+    volatile float sf = norm_i * uf;
+    return sf;
+  }
   volatile double c = cos(static_cast<double>(theta));
   volatile double t = static_cast<double>(2 * norm_q) * c;
   volatile double u = static_cast<double>(norm_i) - t;

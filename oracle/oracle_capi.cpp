@@ -38,6 +38,11 @@ int emit(const std::vector<std::pair<std::string, float> >& r, char* ids_buf, ui
 extern "C" {
 
 const char* oracle_last_error() { return g_err.c_str(); }
+// the alternates of SURVEY A.9 (see `variants` in jubann_oracle.hpp); -1 leaves a switch as it is
+void oracle_set_variants(int gaussian_form, int euclid_score) {
+  if (gaussian_form >= 0) variant_switches().gaussian_form = gaussian_form;
+  if (euclid_score >= 0) variant_switches().euclid_score = euclid_score;
+}
 
 uint64_t oracle_fnv1_64(const char* s, uint64_t n) { return calc_string_hash(s, n); }
 

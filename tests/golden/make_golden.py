@@ -47,7 +47,27 @@ def build(method, hash_num):
     return out
 
 
+VARIANTS = [   # (name, oracle switches, engine options of the CUDA path, engines)
+    ("gaussian_form=1", {"gaussian_form": 1}, {"gaussian_form": 1}, [("lsh", 64), ("lsh", 512), ("euclid_lsh", 256)]),
+    ("euclid_score=1", {"euclid_score": 1}, {"euclid_score": 1}, [("euclid_lsh", 64), ("euclid_lsh", 256)]),
+]
+
+
+def main_variants():
+    """The SURVEY A.9 alternates: the oracle's answers under each switch, frozen like the main file."""
+    out = {"generator": "tests/golden/make_golden.py", "variants": []}
+    for name, sw, opts, engines in VARIANTS:
+        oracle_lib.set_variants(**sw)
+        out["variants"].append({"name": name, "oracle": sw, "options": opts, "engines": [build(m, h) for m, h in engines]})
+        oracle_lib.set_variants(gaussian_form=0, euclid_score=0)
+    with open(os.path.join(HERE, "nn_golden_variants.json"), "w") as f:
+        json.dump(out, f, separators=(",", ":"))
+        f.write("\n")
+    print("wrote", os.path.join(HERE, "nn_golden_variants.json"))
+
+
 def main():
+    main_variants()
     data = {"generator": "tests/golden/make_golden.py", "workload": "workload.synth_rows(MASTER_SEED, 77000, 300, nnz=10, nfeat_log2=6)",
             "engines": [build(m, h) for m, h in ENGINES]}
     with open(os.path.join(HERE, "nn_golden.json"), "w") as f:

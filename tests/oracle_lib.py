@@ -84,6 +84,14 @@ def load(flavour="O2"):
 
 
 # ---- array-level helpers -------------------------------------------------------
+def set_variants(gaussian_form=-1, euclid_score=-1):
+    """SURVEY A.9 alternates (0 = the frozen choice); applies to both oracle builds."""
+    for fl in ("O2", "v3"):
+        lib = load(fl)
+        lib.oracle_set_variants.argtypes = [ctypes.c_int, ctypes.c_int]
+        lib.oracle_set_variants(int(gaussian_form), int(euclid_score))
+
+
 def fnv1_64(s):
     if isinstance(s, str):
         s = s.encode("utf-8")

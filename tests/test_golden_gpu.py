@@ -34,3 +34,30 @@ def test_cuda_path_reproduces_the_golden_fixtures(feature_tables):
                         assert np.allclose(got, ref, rtol=1e-5, atol=1e-6)      # the norm enters: tolerance of north_star
                     else:
                         assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+
+
+def test_cuda_path_reproduces_the_variant_fixtures(feature_tables):
+    # the same switches on the CUDA path (jubann_set_option "gaussian_form" / "euclid_score")
+    from jubatus_b200 import Engine
+    from test_golden_cpu import load_variants
+    (indptr, seed32, keyhash, v), (qip, qs32, qk64, qv) = table_and_queries(feature_tables)
+    for var in load_variants()["variants"]:
+        for e in var["engines"]:
+            method, h = e["method"], e["hash_num"]
+            with Engine(method, h, **var["options"]) as eng:
+                eng.set_rows_csr(np.arange(300, dtype=np.uint64), indptr, seed32, keyhash, v)
+                sigs, norms = eng.get_rows_sig(np.arange(8, dtype=np.uint64))
+                want = np.array(e["datum_signatures"], dtype=np.uint64)
+                diff = sum(bin(int(a) ^ int(b)).count("1") for a, b in zip(sigs.reshape(-1), want.reshape(-1)))
+                assert diff <= 8 * h * 1e-4, (var["name"], method, h, diff)
+                if diff:
+                    continue
+                idx, score, count = eng.query_csr(qip, qs32, qk64, qv, 10, 0)
+                for q in range(3):
+                    c = int(count[q])
+                    assert [int(x) for x in idx[q, :c]] == e["neighbor"]["ids"][q], (var["name"], method, h, q)
+                    ref = np.array(e["neighbor"]["score_bits"][q], dtype=np.uint32).view(np.float32)
+                    if method == "euclid_lsh":
+                        assert np.allclose(score[q, :c], ref, rtol=1e-5, atol=1e-6)
+                    else:
+                        assert np.array_equal(score[q, :c].view(np.uint32), ref.view(np.uint32))

@@ -279,3 +279,42 @@ def test_euclid_norm_bound_filter_adversarial(oracle, hash_num, n, k, qp, scan_v
     assert_same_ranking(got, want, nq, k)
     want_sim = oracle.scan_batch("euclid_lsh", q, qn, rows, norms, hash_num, k, similar=True, threads=4)[:3]
     assert_same_ranking(got_sim, want_sim, nq, k)
+
+
+@pytest.mark.parametrize("hash_num,n,k,qp,scan_variant", [(256, 120000, 100, 2, 0), (256, 70000, 10, 0, 1), (64, 30000, 50, 3, 0)])
+def test_euclid_score_in_float_variant(oracle, hash_num, n, k, qp, scan_variant):
+    """SURVEY A.9 alternate: cosf(theta) and the whole score in float (option "euclid_score" 1) against the
+    oracle under the same switch -- bit-exact, on the adversarial table of the norm-bound test (the float
+    bound has to allow for the float score's own rounding)."""
+    import oracle_lib
+    rng = np.random.RandomState(hash_num + k)
+    nq = 12
+    rows = random_rows(rng, n, hash_num)
+    q = random_rows(rng, nq, hash_num)
+    norms = np.exp(rng.uniform(np.log(1e-3), np.log(1e3), n)).astype(np.float32)
+    norms[rng.randint(0, n, n // 50)] = 0.0
+    norms[1000:3000] = np.float32(0.75)
+    qn = np.exp(rng.uniform(np.log(1e-2), np.log(1e2), nq)).astype(np.float32)
+    qn[3] = 0.0
+    for j in range(nq // 2):
+        for c in range(40):
+            r = rng.randint(0, n)
+            rows[r] = q[j]
+            for b in rng.randint(0, hash_num, rng.randint(0, 6)):
+                rows[r, b // 64] ^= np.uint64(1) << np.uint64(b % 64)
+            norms[r] = np.float32(qn[j] * rng.uniform(0.3, 2.5))
+    opts = {"queries_per_pass": qp} if qp else {}
+    with _engine("euclid_lsh", hash_num, scan_variant=scan_variant, euclid_score=1, **opts) as e:
+        e.set_rows_sig(np.arange(n), rows, norms)
+        got = e.query_sig(q, qn, k)
+        e.set_option("euclid_score", 0)
+        got0 = e.query_sig(q, qn, k)
+    try:
+        oracle_lib.set_variants(euclid_score=1)
+        want = oracle.scan_batch("euclid_lsh", q, qn, rows, norms, hash_num, k, threads=4)[:3]
+    finally:
+        oracle_lib.set_variants(euclid_score=0)
+    assert_same_ranking(got, want, nq, k)
+    want0 = oracle.scan_batch("euclid_lsh", q, qn, rows, norms, hash_num, k, threads=4)[:3]
+    assert_same_ranking(got0, want0, nq, k)        # and back: the frozen choice again
+    assert not np.array_equal(got[1].view(np.uint32), got0[1].view(np.uint32))
