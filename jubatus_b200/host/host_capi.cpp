@@ -229,6 +229,7 @@ int jubahost_delete_row(void* h, const char* id) {
   host_box* b = static_cast<host_box*>(h);
   return guarded([&]() {
     if (b->recommender) { b->recommender->clear_row(id); return 0; }
+    if (b->lof) return b->lof->delete_row(id) ? 0 : 1;   // both of its tables
     return b->nn()->delete_row(id) ? 0 : 1;
   });
 }

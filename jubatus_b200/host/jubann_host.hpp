@@ -1057,6 +1057,58 @@ class gpu_nearest_neighbor : public nearest_neighbor_base {
     }
     emit(query_ids.size(), k, oi, os, oc, known, out);
   }
+  // ---- the same queries with row indices instead of ids in and out (no strings built): what an
+  // embedder that keeps its own per-row columns needs (light_lof's kdist / lrd) ----
+  struct raw_neighbors {
+    uint32_t k;                       // row stride of idx / dist
+    std::vector<uint64_t> idx;        // [n][k] row indices
+    std::vector<float> dist;          // [n][k]
+    std::vector<uint32_t> count;      // [n]
+    void reset(size_t n, uint32_t kk) { k = std::max<uint32_t>(kk, 1); idx.assign(n * k, 0); dist.assign(n * k, 0.0f); count.assign(n, 0); }
+  };
+  void neighbor_rows_raw(const std::vector<uint64_t>& rows, uint64_t ret_num, raw_neighbors& out) const {
+    std::shared_lock<std::shared_mutex> lk(rw_);
+    const uint32_t k = clamp_k(ret_num);
+    out.reset(rows.size(), k);
+    if (rows.empty()) return;
+    const jubann_api& a = table_->api();
+    a.check(a.query_rows(table_->handle(), rows.size(), rows.data(), k, 0, out.idx.data(), out.dist.data(), out.count.data()));
+  }
+  void neighbor_row_raw(const sfv_t& query, uint64_t ret_num, raw_neighbors& out) const {
+    csr_batch b;
+    b.add(query);
+    std::shared_lock<std::shared_mutex> lk(rw_);
+    const uint32_t k = clamp_k(ret_num);
+    out.reset(1, k);
+    const jubann_api& a = table_->api();
+    a.check(a.query_csr(table_->handle(), 1, b.indptr.data(), b.seed32.data(), b.keyhash64.data(), b.vals.data(), k, 0,
+                        out.idx.data(), out.dist.data(), out.count.data()));
+  }
+  // set_row(id, sfv) then neighbor_row(id): *row = the row's index (see set_row_and_neighbors)
+  void set_row_and_neighbors_raw(const std::string& id, const sfv_t& sfv, uint64_t ret_num, uint64_t* row, raw_neighbors& out) {
+    const jubann_api& a = table_->api();
+    if (!a.set_row_query_csr || table_->multi_device()) {
+      set_row(id, sfv);
+      *row = table_->exact_match(id).second;
+      neighbor_rows_raw(std::vector<uint64_t>(1, *row), ret_num, out);
+      return;
+    }
+    csr_batch b;
+    b.add(sfv);
+    std::unique_lock<std::shared_mutex> lk(rw_);
+    device_table::assign_journal undo;
+    std::vector<std::string> ids(1, id);
+    const std::vector<uint64_t> idx = table_->assign(ids, my_id_, &undo);
+    *row = idx[0];
+    const uint32_t k = clamp_k(ret_num);
+    out.reset(1, k);
+    const int rc = a.set_row_query_csr(table_->handle(), idx[0], b.vals.size(), b.seed32.data(), b.keyhash64.data(), b.vals.data(), k, 0,
+                                       out.idx.data(), out.dist.data(), out.count.data());
+    if (rc) {
+      table_->rollback(undo);
+      a.check(rc);
+    }
+  }
   void get_all_row_ids(std::vector<std::string>& ids) const { std::shared_lock<std::shared_mutex> lk(rw_); ids = table_->get_all_row_ids(); }
   // nearest_neighbor_base::pack / unpack delegate to the table
   std::string pack() const { std::shared_lock<std::shared_mutex> lk(rw_); return table_->pack(); }
@@ -1681,6 +1733,7 @@ class nearest_neighbor_classifier {
 // ---------------------------------------------------------------------------------------
 class light_lof {
  public:
+  typedef gpu_nearest_neighbor::raw_neighbors raw_neighbors;
   light_lof(const std::shared_ptr<gpu_nearest_neighbor>& nn, int nearest_neighbor_num, int reverse_nearest_neighbor_num,
             const std::shared_ptr<unlearner_base>& unlearner = std::shared_ptr<unlearner_base>())
       : nn_(nn), nn_num_(nearest_neighbor_num), rnn_num_(reverse_nearest_neighbor_num), unlearner_(unlearner) {
@@ -1688,12 +1741,25 @@ class light_lof {
     if (rnn_num_ < nn_num_) throw invalid_parameter("reverse_nearest_neighbor_num should be >= nearest_neighbor_num");
     // the victim leaves the engine's table and the (kdist, lrd) table; rows that had it as a
     // neighbour keep their parameters until they are next re-scored
-    if (unlearner_) unlearner_->set_callback([this](const std::string& victim) {
-      nn_->delete_row(victim); kdist_.erase(victim); lrd_.erase(victim); param_dirty_.erase(victim);
-    });
+    if (unlearner_) unlearner_->set_callback([this](const std::string& victim) { delete_row(victim); });
   }
   void clear() { nn_->clear(); kdist_.clear(); lrd_.clear(); param_dirty_.clear(); if (unlearner_) unlearner_->clear(); }
   const unlearner_base* get_unlearner() const { return unlearner_.get(); }
+  // column_table::delete_row on both tables: the engine's last row moves into the hole, so does its
+  // (kdist, lrd) entry
+  bool delete_row(const std::string& id) {
+    const std::pair<bool, uint64_t> hit = nn_->get_table()->exact_match(id);
+    if (!hit.first) return false;
+    const uint64_t at = hit.second, last = nn_->get_table()->size() - 1;
+    sync_rows();
+    nn_->delete_row(id);
+    kdist_[at] = kdist_[last]; lrd_[at] = lrd_[last];
+    kdist_.pop_back(); lrd_.pop_back();
+    const bool last_dirty = param_dirty_.erase(last) != 0;
+    param_dirty_.erase(at);
+    if (last_dirty && at != last) param_dirty_.insert(at);
+    return true;
+  }
 
   // light_lof's second mixable ([core] anomaly/light_lof: a versioned table of (kdist, lrd) beside
   // the engine's; anomaly_serv.cpp:134-138 registers both with the mixer).  The diff is every row
@@ -1703,13 +1769,15 @@ class light_lof {
     std::string out;
     const uint64_t n = param_dirty_.size();
     out.append(reinterpret_cast<const char*>(&n), 8);
-    std::vector<std::string> keys(param_dirty_.begin(), param_dirty_.end());
+    std::vector<std::pair<std::string, uint64_t> > keys;
+    for (std::unordered_set<uint64_t>::const_iterator it = param_dirty_.begin(); it != param_dirty_.end(); ++it)
+      keys.push_back(std::make_pair(nn_->get_table()->get_key(*it), *it));
     std::sort(keys.begin(), keys.end());
     for (size_t i = 0; i < keys.size(); ++i) {
-      const uint64_t len = keys[i].size();
-      const float kd = kdist_.find(keys[i])->second, lr = lrd_.find(keys[i])->second;
+      const uint64_t len = keys[i].first.size();
+      const float kd = kdist_[keys[i].second], lr = lrd_[keys[i].second];
       out.append(reinterpret_cast<const char*>(&len), 8);
-      out.append(keys[i]);
+      out.append(keys[i].first);
       out.append(reinterpret_cast<const char*>(&kd), 4);
       out.append(reinterpret_cast<const char*>(&lr), 4);
     }
@@ -1719,13 +1787,15 @@ class light_lof {
   size_t apply_param_diff(const std::string& b, size_t p = 0) {
     if (b.size() < p + 8) throw jubatus_exception("mix: truncated light_lof diff");
     uint64_t n; memcpy(&n, b.data() + p, 8); p += 8;
+    sync_rows();
     for (uint64_t i = 0; i < n; ++i) {
       if (b.size() < p + 8) throw jubatus_exception("mix: truncated light_lof diff");
       uint64_t len; memcpy(&len, b.data() + p, 8); p += 8;
       if (b.size() < p + len + 8) throw jubatus_exception("mix: truncated light_lof diff");
       const std::string key(b.data() + p, len); p += len;
       float kd, lr; memcpy(&kd, b.data() + p, 4); memcpy(&lr, b.data() + p + 4, 4); p += 8;
-      if (nn_->get_table()->exact_match(key).first) { kdist_[key] = kd; lrd_[key] = lr; }
+      const std::pair<bool, uint64_t> hit = nn_->get_table()->exact_match(key);
+      if (hit.first) { kdist_[hit.second] = kd; lrd_[hit.second] = lr; }
     }
     return p;
   }
@@ -1733,11 +1803,11 @@ class light_lof {
   // order-independent digest of the (kdist, lrd) table (tests, bench: replicas agree after MIX)
   uint64_t param_digest() const {
     uint64_t acc = 0;
-    for (std::unordered_map<std::string, float>::const_iterator it = kdist_.begin(); it != kdist_.end(); ++it) {
+    const size_t n = std::min<size_t>(kdist_.size(), nn_->get_table()->size());
+    for (size_t i = 0; i < n; ++i) {
       uint32_t a, b;
-      const float lr = lrd_.find(it->first)->second;
-      memcpy(&a, &it->second, 4); memcpy(&b, &lr, 4);
-      uint64_t h = calc_string_hash(it->first) ^ (static_cast<uint64_t>(a) << 32 | b);
+      memcpy(&a, &kdist_[i], 4); memcpy(&b, &lrd_[i], 4);
+      uint64_t h = calc_string_hash(nn_->get_table()->get_key(i)) ^ (static_cast<uint64_t>(a) << 32 | b);
       h ^= h >> 33; h *= 0xff51afd7ed558ccdULL; h ^= h >> 33;
       acc += h;
     }
@@ -1751,42 +1821,45 @@ class light_lof {
     return sum / (neighbor_lrds.size() * lrd);
   }
   float calc_anomaly_score(const sfv_t& query) const {
-    neighbor_result nb;
-    nn_->neighbor_row(query, nb, nn_num_);
-    return score_from_neighbors(nb);
+    raw_neighbors nb;
+    nn_->neighbor_row_raw(query, nn_num_, nb);
+    return score_from_neighbors(nb, 0);
   }
   float calc_anomaly_score(const std::string& id) const {
-    neighbor_result nb;
-    nn_->neighbor_row(id, nb, nn_num_);
-    return score_from_neighbors(nb);
+    const std::pair<bool, uint64_t> hit = nn_->get_table()->exact_match(id);
+    raw_neighbors nb;
+    if (hit.first) nn_->neighbor_rows_raw(std::vector<uint64_t>(1, hit.second), nn_num_, nb);
+    else nb.reset(1, 1);       // unknown id: no neighbours (neighbor_row(id) gives an empty list)
+    return score_from_neighbors(nb, 0);
   }
   bool set_row(const std::string& id, const sfv_t& sfv) { return set_row_impl(id, sfv, 0); }
   // anomaly add: set_row, then the new row's score (anomaly_serv.cpp:157-176).  The row's neighbour
   // list is already at hand from the re-scoring of set_row and the table has not changed since, so
   // the score costs no further device call; the value is calc_anomaly_score(id)'s.
   float set_row_and_score(const std::string& id, const sfv_t& sfv) {
-    neighbor_result own;
+    raw_neighbors own;
+    own.reset(1, 1);
     set_row_impl(id, sfv, &own);
-    return score_from_neighbors(own);
+    return score_from_neighbors(own, 0);
   }
-  void update_entries(const std::vector<std::string>& ids, const std::string* want_id = 0, neighbor_result* want = 0) {
-    std::vector<neighbor_result> nn;
-    nn_->neighbor_rows_from_ids(ids, nn, nn_num_, false);   // one device call for every id
-    if (want_id && want)
-      for (size_t i = 0; i < ids.size(); ++i) if (ids[i] == *want_id) *want = nn[i];
-    for (size_t i = 0; i < ids.size(); ++i) {
-      if (kdist_.find(ids[i]) == kdist_.end()) throw jubatus_exception("row not found in lof table: " + ids[i]);
-      kdist_[ids[i]] = nn[i].empty() ? 0.0f : nn[i].back().second;
-    }
-    for (size_t i = 0; i < ids.size(); ++i) {
-      const size_t length = std::min<size_t>(nn[i].size(), nn_num_);
+  // kdist, then lrd of the listed rows from one batched device call (every row's nn_num_ nearest);
+  // want_row's own neighbour list is handed back when asked for
+  void update_entries(const std::vector<uint64_t>& rows, const uint64_t* want_row = 0, raw_neighbors* want = 0) {
+    raw_neighbors nn;
+    nn_->neighbor_rows_raw(rows, nn_num_, nn);
+    sync_rows();
+    for (size_t i = 0; i < rows.size(); ++i) kdist_[rows[i]] = nn.count[i] ? nn.dist[i * nn.k + nn.count[i] - 1] : 0.0f;
+    for (size_t i = 0; i < rows.size(); ++i) {
+      const size_t length = std::min<size_t>(nn.count[i], nn_num_);
       float sum_reach = 0.0f;
-      for (size_t j = 0; j < length; ++j) {
-        std::unordered_map<std::string, float>::const_iterator it = kdist_.find(nn[i][j].first);
-        sum_reach += std::max(nn[i][j].second, it == kdist_.end() ? 0.0f : it->second);
+      for (size_t j = 0; j < length; ++j) sum_reach += std::max(nn.dist[i * nn.k + j], kdist_of(nn.idx[i * nn.k + j]));
+      lrd_[rows[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
+      param_dirty_.insert(rows[i]);
+      if (want_row && want && rows[i] == *want_row) {
+        want->reset(1, nn.k);
+        want->count[0] = nn.count[i];
+        for (uint32_t j = 0; j < nn.count[i]; ++j) { want->idx[j] = nn.idx[i * nn.k + j]; want->dist[j] = nn.dist[i * nn.k + j]; }
       }
-      lrd_[ids[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
-      param_dirty_.insert(ids[i]);
     }
   }
   // Bulk load for a table that is built in one go (benchmarks, restoring from raw data): rows go
@@ -1795,51 +1868,68 @@ class light_lof {
   void set_rows_bulk(const std::vector<std::string>& ids, const std::vector<sfv_t>& sfvs, size_t batch = 4096) {
     if (unlearner_) throw jubatus_exception("bulk load is not available with an unlearner (rows must arrive one by one)");
     nn_->set_rows(ids, sfvs);
-    for (size_t i = 0; i < ids.size(); ++i) { kdist_[ids[i]] = -1.0f; lrd_[ids[i]] = -1.0f; }
-    std::vector<std::string> all;
-    nn_->get_all_row_ids(all);
-    std::vector<neighbor_result> nn;
-    for (size_t b = 0; b < all.size(); b += batch) {
-      std::vector<std::string> part(all.begin() + b, all.begin() + std::min(all.size(), b + batch));
-      nn_->neighbor_rows_from_ids(part, nn, nn_num_, false);
-      for (size_t i = 0; i < part.size(); ++i) kdist_[part[i]] = nn[i].empty() ? 0.0f : nn[i].back().second;
-    }
-    for (size_t b = 0; b < all.size(); b += batch) {
-      std::vector<std::string> part(all.begin() + b, all.begin() + std::min(all.size(), b + batch));
-      nn_->neighbor_rows_from_ids(part, nn, nn_num_, false);
-      for (size_t i = 0; i < part.size(); ++i) {
-        const size_t length = std::min<size_t>(nn[i].size(), nn_num_);
-        float sum_reach = 0.0f;
-        for (size_t j = 0; j < length; ++j) sum_reach += std::max(nn[i][j].second, kdist_[nn[i][j].first]);
-        lrd_[part[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
-        param_dirty_.insert(part[i]);
+    sync_rows();
+    const uint64_t n = nn_->get_table()->size();
+    raw_neighbors nn;
+    std::vector<uint64_t> part;
+    for (int phase = 0; phase < 2; ++phase) {
+      for (uint64_t b = 0; b < n; b += batch) {
+        part.resize(std::min<uint64_t>(n, b + batch) - b);
+        for (size_t i = 0; i < part.size(); ++i) part[i] = b + i;
+        nn_->neighbor_rows_raw(part, nn_num_, nn);
+        for (size_t i = 0; i < part.size(); ++i) {
+          if (phase == 0) {
+            kdist_[part[i]] = nn.count[i] ? nn.dist[i * nn.k + nn.count[i] - 1] : 0.0f;
+          } else {
+            const size_t length = std::min<size_t>(nn.count[i], nn_num_);
+            float sum_reach = 0.0f;
+            for (size_t j = 0; j < length; ++j) sum_reach += std::max(nn.dist[i * nn.k + j], kdist_[nn.idx[i * nn.k + j]]);
+            lrd_[part[i]] = sum_reach == 0 ? std::numeric_limits<float>::infinity() : length / sum_reach;
+            param_dirty_.insert(part[i]);
+          }
+        }
       }
     }
   }
   bool get_row_parameter(const std::string& id, float* kdist, float* lrd) const {
-    std::unordered_map<std::string, float>::const_iterator a = kdist_.find(id), b = lrd_.find(id);
-    if (a == kdist_.end() || b == lrd_.end()) return false;
-    *kdist = a->second; *lrd = b->second;
+    const std::pair<bool, uint64_t> hit = nn_->get_table()->exact_match(id);
+    if (!hit.first || hit.second >= kdist_.size()) return false;
+    *kdist = kdist_[hit.second]; *lrd = lrd_[hit.second];
     return true;
   }
   gpu_nearest_neighbor* engine() { return nn_.get(); }
  private:
-  bool set_row_impl(const std::string& id, const sfv_t& sfv, neighbor_result* own) {
+  // The (kdist, lrd) columns are kept by row index of the engine's table (two flat arrays, like the
+  // float columns of the reference's second column_table) -- an add touches some 350 entries, which
+  // in string-keyed hash maps of 10^6 entries was a quarter of its time.  Rows the table has gained
+  // since (MIX appends) start without parameters (-1) until their owner's diff arrives.
+  void sync_rows() {
+    const size_t n = nn_->get_table()->size();
+    if (kdist_.size() < n) { kdist_.resize(n, -1.0f); lrd_.resize(n, -1.0f); }
+  }
+  float kdist_of(uint64_t row) const { return row < kdist_.size() ? kdist_[row] : 0.0f; }
+  bool set_row_impl(const std::string& id, const sfv_t& sfv, raw_neighbors* own) {
     if (unlearner_ && !unlearner_->touch(id)) throw jubatus_exception("no more space available to add new ID: " + id);
-    std::vector<std::string> order;
-    std::unordered_set<std::string> seen;
-    if (nn_->get_table()->exact_match(id).first) collect_neighbors(id, order, seen);
+    std::vector<uint64_t> order;
+    std::unordered_set<uint64_t> seen;
+    const std::pair<bool, uint64_t> before = nn_->get_table()->exact_match(id);
+    raw_neighbors nb;
+    if (before.first) {   // an update: the neighbours of the row as it was are re-scored too
+      nn_->neighbor_rows_raw(std::vector<uint64_t>(1, before.second), rnn_num_, nb);
+      for (uint32_t j = 0; j < nb.count[0]; ++j) if (seen.insert(nb.idx[j]).second) order.push_back(nb.idx[j]);
+    }
     // set_row, then the row's reverse-neighbour candidates: one device call
-    neighbor_result nb;
     static const bool trace = ::getenv("JUBANN_HOST_TRACE") != 0;
     static double t_set = 0, t_upd = 0; static uint64_t n_calls = 0;
     std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
-    nn_->set_row_and_neighbors(id, sfv, nb, rnn_num_);
+    uint64_t row = 0;
+    nn_->set_row_and_neighbors_raw(id, sfv, rnn_num_, &row, nb);
     std::chrono::steady_clock::time_point t1 = std::chrono::steady_clock::now();
-    for (size_t i = 0; i < nb.size(); ++i) if (seen.insert(nb[i].first).second) order.push_back(nb[i].first);
-    kdist_[id] = -1.0f; lrd_[id] = -1.0f;
-    if (seen.insert(id).second) order.push_back(id);
-    update_entries(order, own ? &id : 0, own);
+    for (uint32_t j = 0; j < nb.count[0]; ++j) if (seen.insert(nb.idx[j]).second) order.push_back(nb.idx[j]);
+    sync_rows();
+    kdist_[row] = -1.0f; lrd_[row] = -1.0f;
+    if (seen.insert(row).second) order.push_back(row);
+    update_entries(order, own ? &row : 0, own);
     if (trace) {
       std::chrono::steady_clock::time_point t2 = std::chrono::steady_clock::now();
       t_set += std::chrono::duration<double>(t1 - t0).count(); t_upd += std::chrono::duration<double>(t2 - t1).count();
@@ -1849,34 +1939,31 @@ class light_lof {
     }
     return true;
   }
-  void collect_neighbors(const std::string& id, std::vector<std::string>& order, std::unordered_set<std::string>& seen) const {
-    neighbor_result nb;
-    nn_->neighbor_row(id, nb, rnn_num_);
-    for (size_t i = 0; i < nb.size(); ++i) if (seen.insert(nb[i].first).second) order.push_back(nb[i].first);
-  }
-  float score_from_neighbors(const neighbor_result& nb) const {
+  // LOF of a point from its neighbour list `i` of nb: lrd of the point over the mean lrd of the neighbours
+  float score_from_neighbors(const raw_neighbors& nb, size_t i) const {
+    const uint32_t cnt = nb.count.empty() ? 0 : nb.count[i];
     std::vector<float> lrds;
     float lrd;
-    if (nb.empty()) {
+    if (cnt == 0) {
       lrd = std::numeric_limits<float>::infinity();
     } else {
-      lrds.resize(nb.size());
+      lrds.resize(cnt);
       float sum_reach = 0.0f;
-      for (size_t i = 0; i < nb.size(); ++i) {
-        std::unordered_map<std::string, float>::const_iterator a = kdist_.find(nb[i].first), b = lrd_.find(nb[i].first);
-        if (a == kdist_.end() || b == lrd_.end()) throw jubatus_exception("row not found in lof table: " + nb[i].first);
-        lrds[i] = b->second;
-        sum_reach += std::max(nb[i].second, a->second);
+      for (uint32_t j = 0; j < cnt; ++j) {
+        const uint64_t r = nb.idx[i * nb.k + j];
+        if (r >= kdist_.size()) throw jubatus_exception("row not found in lof table: " + nn_->get_table()->get_key(r));
+        lrds[j] = lrd_[r];
+        sum_reach += std::max(nb.dist[i * nb.k + j], kdist_[r]);
       }
-      lrd = sum_reach == 0 ? std::numeric_limits<float>::infinity() : nb.size() / sum_reach;
+      lrd = sum_reach == 0 ? std::numeric_limits<float>::infinity() : cnt / sum_reach;
     }
     return calculate_lof(lrd, lrds);
   }
   std::shared_ptr<gpu_nearest_neighbor> nn_;
   int nn_num_, rnn_num_;
   std::shared_ptr<unlearner_base> unlearner_;
-  std::unordered_map<std::string, float> kdist_, lrd_;
-  std::unordered_set<std::string> param_dirty_;
+  std::vector<float> kdist_, lrd_;               // by row index of the engine's table
+  std::unordered_set<uint64_t> param_dirty_;     // rows whose parameters changed here since the last MIX round
 };
 
 }  // namespace jubatus_b200

@@ -16,6 +16,8 @@ method = sys.argv[4] if len(sys.argv) > 4 else "lsh"
 euclid = method == "euclid_lsh"
 print("table: %d rows x %d bits (%s), k=10" % (n, h, method))
 opts = {"scan_variant": int(sys.argv[3])} if len(sys.argv) > 3 else {}
+if os.environ.get("PROBE_QP"):
+    opts["queries_per_pass"] = int(os.environ["PROBE_QP"])
 e = Engine(method, h, **opts)
 sig = w.random_signatures(1, n, h // 64)
 norms = (np.random.RandomState(1).rand(n) * 3 + 0.5).astype(np.float32) if euclid else None
