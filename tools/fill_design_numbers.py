@@ -17,7 +17,7 @@ def cfg(d, c):
 rows = [
  ("headline, device-resident", "%s queries/s, %.2f of HBM" % (k(d1["value"]), d1["roofline"]["frac"]), "%s queries/s, %.2f of HBM on the 12.5 M-row shards" % (k(d8["value"]), d8["roofline"]["frac"])),
  ("headline, end to end", k(d1["e2e"]["value"]), k(d8["e2e"]["value"])),
- ("32 per pass (`throughput_mode`)", k(d1["throughput_mode"]["value"]), k(d8["throughput_mode"]["value"])),
+ ("`throughput_mode` (library default: %d / %d queries per pass)" % (round(d1["throughput_mode"]["queries_per_pass"]), round(d8["throughput_mode"]["queries_per_pass"])), k(d1["throughput_mode"]["value"]), k(d8["throughput_mode"]["value"])),
  ("c2", cfg(d1, "c2"), cfg(d8, "c2")),
  ("c3 at 2 per pass / 24 per pass", cfg(d1, "c3"), cfg(d8, "c3")),
  ("c4 (device-resident / end to end)", cfg(d1, "c4"), cfg(d8, "c4")),
