@@ -1851,7 +1851,9 @@ bool plan_scan(const TableView& t, bool euclid, uint32_t nq, uint32_t k, int var
   // one CTA per SM with twice the shared memory, and 64 queries per pass beat 32 at every table size
   // (4467 against 4362 queries/s on 10^8 rows, 277 k against 255 k on a 1.25 M-row shard: a pass's fixed
   // costs are shared by twice the queries)
-  uint32_t qp = qp_opt ? qp_opt : (euclid ? 24 : (t.w32 >= 16 ? 64 : 32));
+  // (rows of up to 128 bits likewise, where the lists fit: minhash 128 bits, k=50: 63.2 k -> 66.0 k queries/s on
+  // 2*10^7 rows, 272 k -> 318 k on a 2.5 M-row shard; 256-bit rows stay at 32, euclid_lsh at 24)
+  uint32_t qp = qp_opt ? qp_opt : (euclid ? 24 : ((t.w32 >= 16 || t.w32 <= 4) ? 64 : 32));
   if (qp > nq) qp = nq;
   if (qp < 1) qp = 1;
   // automatic variant: the TMA ring wins while the pass is memory-bound, the LDG kernel's
