@@ -448,10 +448,11 @@ def test_recommender_and_light_lof_with_unlearner():
         nn.Anomaly(acfg.replace('{"max_size": 20}', '{"max_size": 0}'))
 
 
-def test_classifier_nn_method():
+def test_classifier_nn_method(oracle):
     """jubaclassifier method "NN" (config/classifier/nn.json): votes exp(-local_sensitivity * distance)
     of the nearest_neighbor_num nearest training rows, checked against the same engine queried
-    directly."""
+    directly and against the CPU oracle's engine holding the same rows (an independent path from
+    datum to neighbours: its own signatures, its own ranking)."""
     import math
     k, alpha, hash_num = 8, 1.0, 128
     cfg = json.dumps({"method": "NN", "converter": CONVERTER,
@@ -459,6 +460,7 @@ def test_classifier_nn_method():
                                     "nearest_neighbor_num": k, "local_sensitivity": alpha}})
     clf = nn.Classifier(cfg)
     eng = nn.NearestNeighbor(config("euclid_lsh", hash_num))
+    ora = oracle.OracleNN("euclid_lsh", hash_num)
     ids, vals = w.synth_rows(w.MASTER_SEED, 800, 90, nnz=10, nfeat_log2=7)
     labels = ["spam", "ham", "eggs"]
     assert clf.set_label("unused") is True and clf.set_label("unused") is False
@@ -467,18 +469,26 @@ def test_classifier_nn_method():
         lab = labels[r % 3]
         assert clf.train([(lab, datum_of(ids[r], vals[r]))]) == 1
         eng.set_row("%s_%d" % (lab, serial), datum_of(ids[r], vals[r]))
+        ora.set_row("%s_%d" % (lab, serial), sfv_of(ids[r], vals[r]))
         serial += 1
     assert clf.get_labels() == {"spam": 27, "ham": 27, "eggs": 26, "unused": 0}
-    queries = [datum_of(ids[r], vals[r]) for r in range(80, 90)] + [datum_of(ids[4], vals[4])]
+    qrows = list(range(80, 90)) + [4]
+    queries = [datum_of(ids[r], vals[r]) for r in qrows]
     got = clf.classify(queries)
     assert len(got) == len(queries)
-    for d, res in zip(queries, got):
+    for r, d, res in zip(qrows, queries, got):
         want = {"spam": 0.0, "ham": 0.0, "eggs": 0.0, "unused": 0.0}
         for rid, dist in eng.neighbor_row_from_datum(d, k):
             want[rid.rsplit("_", 1)[0]] += math.exp(-alpha * dist)
         assert [lab for lab, _ in res] == sorted(want)              # every known label, label order
         for lab, score in res:
             assert abs(score - want[lab]) <= 1e-5 * max(1.0, want[lab]), (lab, score, want[lab])
+        # the oracle's engine: same neighbours, distances within the tolerance of north_star (1e-5 relative)
+        want_o = {"spam": 0.0, "ham": 0.0, "eggs": 0.0, "unused": 0.0}
+        for rid, dist in ora.neighbor_row_from_datum(sfv_of(ids[r], vals[r]), k):
+            want_o[rid.rsplit("_", 1)[0]] += math.exp(-alpha * dist)
+        for lab, score in res:
+            assert abs(score - want_o[lab]) <= 1e-4 * max(1.0, want_o[lab]), (lab, score, want_o[lab])
     # a stored datum votes for its own label with weight exp(0) = 1 at least
     own = dict(got[-1])
     assert own[labels[4 % 3]] >= 1.0 - 1e-6
