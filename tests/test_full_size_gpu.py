@@ -102,10 +102,10 @@ def test_c2_lsh_512_bits_10m_rows_k10():
 
 
 def test_c3_euclid_256_bits_k100_property_checks():
-    """config 3 (one GPU's worth): euclid_lsh hash_num=256, 20M rows, k=100."""
+    """config 3 at its full size on one GPU: euclid_lsh hash_num=256, 10^8 rows, k=100."""
     import torch
     from jubatus_b200 import Engine
-    n, h, w64, k, nq = 20_000_000, 256, 4, 100, 32
+    n, h, w64, k, nq = 100_000_000, 256, 4, 100, 32
     with Engine("euclid_lsh", h) as e:
         table, norms, stream = _fill(e, n, w64, True, 12)
         e.set_rows_sig_dev(n, 0, table.data_ptr(), norms.data_ptr(), stream)
@@ -158,24 +158,24 @@ def test_c4_minhash_128_bits_20m_rows_similar_k50():
             assert np.array_equal(want, os_[qi].cpu().numpy())
 
 
-def test_headline_shape_64m_rows_k100_both_regimes():
-    """headline shape (lsh 512 bits, k=100) at 64M rows, in the HBM-bound (2 queries per pass) and
-    the popcount-bound (16 per pass) regime: both must give the same exact answer."""
+def test_headline_shape_100m_rows_k100_both_regimes():
+    """the headline configuration at its full size (lsh 512 bits, 10^8 rows, k=100), in the HBM-bound (2 queries
+    per pass) and the popcount-bound (library default) regime: both must give the same exact answer."""
     import torch
     from jubatus_b200 import Engine
-    n, h, w64, k, nq = 64_000_000, 512, 8, 100, 32
+    n, h, w64, k, nq = 100_000_000, 512, 8, 100, 32
     with Engine("lsh", h) as e:
         table, _, stream = _fill(e, n, w64, False, 14)
         e.set_rows_sig_dev(n, 0, table.data_ptr(), 0, stream)
         gen = torch.Generator(device=table.device); gen.manual_seed(8)
         q = torch.randint(-2 ** 63, 2 ** 63 - 1, (nq, w64), dtype=torch.int64, device=table.device, generator=gen)
-        q[4] = table[63_999_999]
+        q[4] = table[n - 1]
         e.set_option("queries_per_pass", 2)
         a = _query(e, q, None, k)
-        e.set_option("queries_per_pass", 16)
+        e.set_option("queries_per_pass", 0)
         b = _query(e, q, None, k)
         assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2])
-        assert int(a[0][4, 0]) == 63_999_999
+        assert int(a[0][4, 0]) == n - 1
         for qi in (4, 9):
             d = _torch_hamming(table, q[qi])
             key = d * n + torch.arange(n, device=d.device)
