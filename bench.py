@@ -352,7 +352,23 @@ def fetch_table(env, eng, method, rows, w64):
             nrm[j0:j0 + n] = m
     if G == 1:
         return sig, nrm
-    tag = "/dev/shm/jubann_bench_%d_" % os.getppid()
+    # where the shards meet: /dev/shm if it has the room, else the temp directory; rank 0 decides for all
+    choice = [None]
+    if rank == 0:
+        import shutil
+        import tempfile
+        need = int(rows * (w64 * 8 + 4) * 1.2)
+        for d in ("/dev/shm", tempfile.gettempdir()):
+            try:
+                if shutil.disk_usage(d).free >= need:
+                    choice[0] = d
+                    break
+            except OSError:
+                pass
+    env.dist.broadcast_object_list(choice, src=0)
+    if choice[0] is None:
+        return None, "no directory with %d bytes free to bring the shards together" % int(rows * (w64 * 8 + 4) * 1.2)
+    tag = os.path.join(choice[0], "jubann_bench_%d_" % os.getppid())
     np.save(tag + "sig_%d.npy" % rank, sig)
     if euclid:
         np.save(tag + "nrm_%d.npy" % rank, nrm)
@@ -382,6 +398,8 @@ def check_parity(env, eng, method, hash_num, rows, k, flags, qs, got, nparity, s
     w64 = (hash_num + 63) // 64
     euclid = method == "euclid_lsh"
     table, norms = fetch_table(env, eng, method, rows, w64)
+    if table is None and isinstance(norms, str):   # (N > 1 only) the host could not hold the exchange files: say so, do not guess
+        return ({"exact": None, "skipped": norms} if env.rank == 0 else None), None, 0
     if env.rank != 0:
         return None, None, 0
     ol = oracle()
@@ -588,7 +606,9 @@ def bench_scan(env, a, name, method, hash_num, rows, nq, k, qp, flags, steps, wa
         threads = os.cpu_count() or 1
         nparity = a.parity_queries if main else min(8, a.parity_queries)
         parity, secs, nparity = check_parity(env, eng, method, hash_num, rows, k, flags, qs, got, nparity, seed, threads)
-        if rank == 0:
+        if rank == 0 and secs is None:
+            res["parity"] = parity
+        elif rank == 0:
             res["parity"] = parity
             cpu = {"value": nparity / secs, "unit": UNIT, "cores": threads, "kind": "port",
                    "sample": "%d of the batch's queries over the GPUs' own table of %d rows x %d bits (k=%d), oracle engine with "
